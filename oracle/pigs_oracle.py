@@ -1,0 +1,246 @@
+"""TEST INFRASTRUCTURE ONLY — ctypes front-end of the CPU oracle (oracle/pigs_oracle.c).
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module; the product (pigs_b200/) never does.  numpy in, numpy out.
+Each function names the reference entry point it restates (paths relative to
+/root/reference/diff-gaussian-sampling).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+FN_VALUE, FN_DERIV, FN_HESS, FN_THIRD = 0, 1, 2, 3
+
+
+def build():
+    """Compile oracle/pigs_oracle.c -> oracle/libpigs_oracle.so (gcc, OpenMP)."""
+    subprocess.run(["make", "-s", "-C", _HERE, "libpigs_oracle.so"], check=True)
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        so = os.path.join(_HERE, "libpigs_oracle.so")
+        if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(os.path.join(_HERE, "pigs_oracle.c")):
+            build()
+        _LIB = ctypes.CDLL(so)
+        _LIB.pigs_oracle_tile_grid.restype = ctypes.c_int
+        _LIB.pigs_oracle_bin_gaussians.restype = ctypes.c_int64
+        _LIB.pigs_oracle_neighbor_counts.restype = ctypes.c_int64
+    return _LIB
+
+
+def _f32(a):
+    return np.ascontiguousarray(np.asarray(a, dtype=np.float32))
+
+
+def _p(a):
+    return a.ctypes.data_as(ctypes.c_void_p)
+
+
+_i64 = ctypes.c_int64
+_int = ctypes.c_int
+
+
+def out_shape(fn, N, D, C):
+    return (N,) + (D,) * fn + (C,)
+
+
+def preprocess(means, covariances, samples, recip_mode=1, bounds=None):
+    """PreprocessCUDA (sample_points.cu:37-98) + Sampler::preprocess (sampler_impl.cu:216-330).
+
+    Returns a dict with min_b, max_b, grid, blocks, radii, touched, num_rendered, point_list,
+    ranges [(blocks+1),2] u32, sample_list, sample_tiles, sample_ranges.  `bounds=(min_b,max_b)`
+    overrides the per-call sample bounding box (multi-GPU: global bounds)."""
+    L = lib()
+    means = _f32(means)
+    P = means.shape[0]
+    D = means.shape[-1] if means.ndim > 1 else 1
+    means = means.reshape(P, D)
+    cov = _f32(covariances).reshape(P, D * (D + 1) // 2)
+    samples = _f32(samples).reshape(-1, D)
+    N = samples.shape[0]
+    min_b = np.zeros(D, np.float32)
+    max_b = np.zeros(D, np.float32)
+    if bounds is None:
+        L.pigs_oracle_bounds(_p(samples), _i64(N), _int(D), _p(min_b), _p(max_b))
+    else:
+        min_b[:] = bounds[0]
+        max_b[:] = bounds[1]
+    grid = np.zeros(D, np.int32)
+    blocks = L.pigs_oracle_tile_grid(_p(min_b), _p(max_b), _int(D), _int(recip_mode), _p(grid))
+    radii = np.zeros(P, np.float32)
+    touched = np.zeros(P, np.uint32)
+    L.pigs_oracle_radii(_i64(P), _int(D), _p(means), _p(cov), _p(min_b), _p(grid), _p(radii), _p(touched))
+    R = int(touched.astype(np.int64).sum())
+    point_list = np.zeros(max(R, 1), np.uint32)
+    ranges = np.zeros((blocks + 1, 2), np.uint32)
+    R2 = L.pigs_oracle_bin_gaussians(_i64(P), _int(D), _p(means), _p(radii), _p(min_b), _p(grid), _int(blocks),
+                                     _p(point_list), _p(ranges))
+    if R2 < 0:
+        raise ValueError("input hits the reference's out-of-range tile alias (sampler_impl.cu:108-110)")
+    assert R2 == R, (R2, R)
+    sample_list = np.zeros(max(N, 1), np.uint32)
+    sample_tiles = np.zeros(max(N, 1), np.uint32)
+    sample_ranges = np.zeros((blocks + 1, 2), np.uint32)
+    L.pigs_oracle_bin_samples(_i64(N), _int(D), _p(samples), _p(min_b), _p(grid), _int(blocks), _p(sample_list),
+                              _p(sample_tiles), _p(sample_ranges))
+    return dict(P=P, D=D, N=N, min_b=min_b, max_b=max_b, grid=grid, blocks=blocks, radii=radii, touched=touched,
+                num_rendered=R, point_list=point_list[:R], ranges=ranges, sample_list=sample_list[:N],
+                sample_tiles=sample_tiles[:N], sample_ranges=sample_ranges)
+
+
+def pair_count(st):
+    """Size of the reference pair set: sum over tiles of n_samples(tile) * n_gaussians(tile)."""
+    b = st["blocks"]
+    g = st["ranges"][:b].astype(np.int64)
+    s = st["sample_ranges"][:b].astype(np.int64)
+    return int(((g[:, 1] - g[:, 0]) * (s[:, 1] - s[:, 0])).sum())
+
+
+def forward(fn, st, means, values, conics, samples, acc64=False):
+    """SampleGaussians{,Derivative,Laplacian,Third}CUDA (sample_points.cu:198-297) -> renderCUDA<F>
+    (cuda_sampler/forward.cu:88-275).  Output [N, D^fn.., C] fp32."""
+    L = lib()
+    P, D, N = st["P"], st["D"], st["N"]
+    means = _f32(means).reshape(P, D)
+    values = _f32(values).reshape(P, -1)
+    C = values.shape[1]
+    conics = _f32(conics).reshape(P, D * (D + 1) // 2)
+    samples = _f32(samples).reshape(N, D)
+    out = np.zeros(out_shape(fn, N, D, C), np.float32)
+    if P and N:
+        L.pigs_oracle_forward(_int(fn), _int(D), _int(C), _int(st["blocks"]), _p(st["ranges"]),
+                              _p(st["sample_ranges"]), _p(np.ascontiguousarray(st["point_list"])),
+                              _p(np.ascontiguousarray(st["sample_list"])), _p(means), _p(values), _p(conics),
+                              _p(samples), _p(out), _int(1 if acc64 else 0))
+    return out
+
+
+def backward(fn, st, means, values, conics, samples, dL_dout):
+    """SampleGaussians*BackwardCUDA (sample_points.cu:146-196,299-372) -> backward renderCUDA<F>
+    (cuda_sampler/backward.cu:27-416).  Returns dL_dmeans [P,D], dL_dvalues [P,C], dL_dconics [P,D(D+1)/2]."""
+    L = lib()
+    P, D, N = st["P"], st["D"], st["N"]
+    means = _f32(means).reshape(P, D)
+    values = _f32(values).reshape(P, -1)
+    C = values.shape[1]
+    K = D * (D + 1) // 2
+    conics = _f32(conics).reshape(P, K)
+    samples = _f32(samples).reshape(N, D)
+    g = _f32(dL_dout).reshape(out_shape(fn, N, D, C))
+    dm = np.zeros((P, D), np.float32)
+    dv = np.zeros((P, C), np.float32)
+    dc = np.zeros((P, K), np.float32)
+    if P and N:
+        L.pigs_oracle_backward(_int(fn), _int(P), _int(D), _int(C), _int(st["blocks"]), _p(st["ranges"]),
+                               _p(st["sample_ranges"]), _p(np.ascontiguousarray(st["point_list"])),
+                               _p(np.ascontiguousarray(st["sample_list"])), _p(means), _p(values), _p(conics),
+                               _p(samples), _p(g), _p(dm), _p(dv), _p(dc))
+    return dm, dv, dc
+
+
+def dense(which, means, conics_full, values, samples):
+    """/root/reference/gaussians.py:48-58, 89-101, 103-116 (dense, no cutoff, no torus, full conics).
+    which: bit0 value, bit1 derivative, bit2 second derivative. Returns (u, du, ddu)."""
+    L = lib()
+    means = _f32(means)
+    n, d = means.shape
+    conics_full = _f32(conics_full).reshape(n, d, d)
+    values = _f32(values).reshape(n, -1)
+    C = values.shape[1]
+    samples = _f32(samples).reshape(-1, d)
+    N = samples.shape[0]
+    u = np.zeros((N, C), np.float32)
+    du = np.zeros((N, d, C), np.float32)
+    ddu = np.zeros((N, d, d, C), np.float32)
+    L.pigs_oracle_dense(_int(which), _i64(n), _int(d), _int(C), _i64(N), _p(means), _p(conics_full), _p(values),
+                        _p(samples), _p(u), _p(du), _p(ddu))
+    return u, du, ddu
+
+
+def neighbors(means, conics, radii):
+    """AggregateNeighborsPreprocessCUDA (aggregate_neighbors.cu:323-367): findCollisions + cumsum + preprocess.
+    Returns indices i64[M], ranges i64[P] (inclusive cumsum), dists f32[M,D], densities f32[M], inv_total f32[P]."""
+    L = lib()
+    means = _f32(means)
+    P, D = means.shape
+    conics = _f32(conics).reshape(P, D * (D + 1) // 2)
+    radii = _f32(radii).reshape(P)
+    counts = np.zeros(P, np.int64)
+    M = L.pigs_oracle_neighbor_counts(_i64(P), _int(D), _p(means), _p(radii), _p(counts))
+    ranges = np.cumsum(counts).astype(np.int64)
+    indices = np.full(M, -1, np.int64)
+    dists = np.zeros((M, D), np.float32)
+    densities = np.zeros(M, np.float32)
+    inv_total = np.zeros(P, np.float32)
+    L.pigs_oracle_neighbor_fill(_i64(P), _int(D), _p(means), _p(conics), _p(radii), _p(ranges), _p(indices),
+                                _p(dists), _p(densities), _p(inv_total))
+    return indices, ranges, dists, densities, inv_total
+
+
+def aggregate_forward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                      densities, inv_total):
+    """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415) -> aggregateNeighbors (:129-207).
+    Returns weights, embeddings, factors [M], neighbor_features [P,L]."""
+    L_ = lib()
+    features = _f32(features)
+    P, L = features.shape
+    transform = _f32(transform)
+    queries = _f32(queries)
+    keys = _f32(keys)
+    K = queries.shape[-1]
+    frequencies = _f32(frequencies)
+    dt = _f32(distance_transform)
+    E = dt.shape[-1] // 2
+    dists = _f32(dists)
+    D = dists.shape[-1]
+    M = densities.shape[0]
+    indices = np.ascontiguousarray(indices, np.int64)
+    ranges = np.ascontiguousarray(ranges, np.int64)
+    densities = _f32(densities)
+    inv_total = _f32(inv_total)
+    w = np.zeros(M, np.float32)
+    e = np.zeros(M, np.float32)
+    f = np.zeros(M, np.float32)
+    out = np.zeros((P, L), np.float32)
+    L_.pigs_oracle_aggregate_forward(_i64(P), _int(D), _int(L), _int(K), _int(E), _p(features), _p(transform),
+                                     _p(queries), _p(keys), _p(frequencies), _p(dt), _p(indices), _p(ranges),
+                                     _p(dists), _p(densities), _p(inv_total), _p(w), _p(e), _p(f), _p(out))
+    return w, e, f, out
+
+
+def aggregate_backward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                       densities, weights, embeddings, factors, inv_total, dL_dout):
+    """AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475) -> aggregateNeighborsBackward (:210-321)."""
+    L_ = lib()
+    features = _f32(features)
+    P, L = features.shape
+    transform = _f32(transform)
+    queries = _f32(queries)
+    keys = _f32(keys)
+    K = queries.shape[-1]
+    frequencies = _f32(frequencies)
+    dt = _f32(distance_transform)
+    E = dt.shape[-1] // 2
+    dists = _f32(dists)
+    D = dists.shape[-1]
+    indices = np.ascontiguousarray(indices, np.int64)
+    ranges = np.ascontiguousarray(ranges, np.int64)
+    gf = np.zeros_like(features)
+    gt = np.zeros_like(transform)
+    gq = np.zeros_like(queries)
+    gk = np.zeros_like(keys)
+    gfr = np.zeros_like(frequencies)
+    gdt = np.zeros_like(dt)
+    L_.pigs_oracle_aggregate_backward(_i64(P), _int(D), _int(L), _int(K), _int(E), _p(features), _p(transform),
+                                      _p(queries), _p(keys), _p(frequencies), _p(dt), _p(indices), _p(ranges),
+                                      _p(dists), _p(_f32(densities)), _p(_f32(weights)), _p(_f32(embeddings)),
+                                      _p(_f32(factors)), _p(_f32(inv_total)), _p(_f32(dL_dout)), _p(gf), _p(gt),
+                                      _p(gq), _p(gk), _p(gfr), _p(gdt))
+    return gf, gt, gq, gk, gfr, gdt
