@@ -1,0 +1,149 @@
+/*
+ * pigs_b200.h — C ABI of libpigs_b200.so: the B200-native (sm_100a) implementation of the
+ * differentiable Gaussian-mixture sampling path of kr4b/pigs (`diff-gaussian-sampling`).
+ *
+ * This is the drop-in boundary.  Every entry point takes plain device pointers, sizes and a
+ * cudaStream_t (as void*), returns an int status (0 = ok, >0 = cudaError_t, <0 = argument
+ * error; pigs_last_error() gives the text), never allocates, never frees, never retains a
+ * pointer past the call, and never synchronises the host unless documented.  The caller
+ * (torch, through pigs_b200/_C.py) owns every allocation.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference/diff-gaussian-sampling):
+ *   ext.cpp:20-31                  the 12 pybind entry points
+ *   sample_points.h:20-131         PreprocessCUDA / SampleGaussians*CUDA / *BackwardCUDA
+ *   aggregate_neighbors.h:11-47    AggregateNeighbors{Preprocess,,Backward}CUDA
+ *   cuda_sampler/sampler.h:26-80   CudaSampler::Sampler::{preprocess,forward,backward}
+ *
+ * All float data is fp32, ids are u32, tile ranges are uint2 (start,end) pairs, the aggregate
+ * CSR is int64 — the same dtypes the reference exposes.
+ */
+#ifndef PIGS_B200_H
+#define PIGS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PIGS_TILE_WIDTH 0.51f /* cuda_sampler/config.h:18 BLOCK_SIZE */
+
+/* function bits (cuda_sampler/sampler.h:22 enum Function {gaussian, derivative, laplacian, third}) */
+#define PIGS_FN_VALUE 1u /* u        -> [N, C]          */
+#define PIGS_FN_DERIV 2u /* grad u   -> [N, D, C]       */
+#define PIGS_FN_HESS 4u  /* Hessian  -> [N, D, D, C]    */
+#define PIGS_FN_THIRD 8u /* 3rd der. -> [N, D, D, D, C] */
+
+/* Device-resident header written by pigs_preprocess_count at the start of `geom_ws` and copied to
+ * the start of `binning_buffer` by pigs_preprocess_bin.  The host reads it back ONCE per preprocess
+ * (one pinned-memory copy) to size the binning buffers — the reference needs two host syncs there
+ * (sample_points.cu:74 `.item()`, sampler_impl.cu:257 cudaMemcpy) and one more in every
+ * forward/backward call (sample_points.cu:124,174), which this ABI does not need at all. */
+typedef struct pigs_header {
+    uint32_t magic;        /* 'PIGS' */
+    int32_t D;             /* 1 or 2 */
+    int32_t grid[2];       /* tiles per dimension (sample_points.cu:73) */
+    int32_t blocks;        /* prod(grid) */
+    int32_t nslots;        /* tile-id slots incl. alias slots: blocks + grid[0] + 2 */
+    float min_b[2];        /* grid offset = per-dimension min over samples (sample_points.cu:70) */
+    float max_b[2];
+    int64_t P, N;
+    int64_t num_rendered;  /* Gaussian/tile instances (sampler_impl.cu:256-257) */
+    uint32_t reserved[48]; /* pad to 256 bytes */
+} pigs_header;
+
+int pigs_version(void);
+const char *pigs_last_error(void);
+
+/* Library-level option.  recip=1 (default): tile grid = ceil((max-min+1e-6f) * fl(1/0.51f)), the
+ * arithmetic of ATen's CUDA division-by-scalar which the reference calls at sample_points.cu:73;
+ * recip=0: IEEE division. */
+void pigs_set_grid_recip_mode(int recip);
+
+/* ---- S1: sample bounds (replaces samples.min(0)/max(0), sample_points.cu:70-71) ------------------
+ * d_minmax: device float[2*D] = {min[0..D), max[0..D)}.  Multi-GPU callers all-reduce it
+ * (MIN on the first D, MAX on the last D) before pigs_preprocess_count. */
+int pigs_sample_bounds(const float *samples, int64_t N, int D, float *d_minmax, void *stream);
+
+/* ---- preprocess stage A: grid, radii, tiles_touched, offsets (forward.cu:24-83, sampler_impl.cu:253) */
+size_t pigs_geom_workspace_bytes(int64_t P);
+int pigs_preprocess_count(int64_t P, int D, int64_t N, const float *means, const float *covariances,
+                          const float *d_minmax, float *radii /* [P] out */, void *geom_ws,
+                          void *stream);
+/* after this call the first sizeof(pigs_header) bytes of geom_ws hold the header (device memory) */
+
+/* ---- preprocess stage B: key emission, stable sort by tile, ranges; sample binning ---------------
+ * (sampler_impl.cu:54-189, 259-327).  Sizes are functions of the header values read back by the host. */
+size_t pigs_binning_bytes(int64_t num_rendered, int blocks);
+size_t pigs_sample_binning_bytes(int64_t N, int blocks, int D);
+size_t pigs_sort_workspace_bytes(int64_t num_rendered, int64_t N);
+int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_rendered, const float *means,
+                        const float *samples, const float *radii, const void *geom_ws,
+                        void *binning_buffer, void *sample_binning_buffer,
+                        void *ranges /* uint2[blocks+1] out */, void *sample_ranges /* uint2[blocks+1] out */,
+                        void *sort_ws, void *stream);
+
+/* views into the opaque buffers (device pointers; for parity tests and debugging) */
+const uint32_t *pigs_point_list(const void *binning_buffer);           /* [num_rendered] (tile asc, id asc) */
+const uint32_t *pigs_point_tiles(const void *binning_buffer, int64_t num_rendered);
+const uint32_t *pigs_sample_list(const void *sample_binning_buffer);   /* [N] (tile asc, id asc) */
+
+/* ---- evaluation (forward.cu:88-343, backward.cu:27-499) -----------------------------------------
+ * fn_mask: any non-empty subset of PIGS_FN_*; outputs whose bit is clear may be NULL.
+ * Outputs MUST be zero-initialised by the caller (as sample_points.cu:215,240,265,290 / :165-167 do);
+ * results are accumulated with atomic adds.  No host synchronisation. */
+size_t pigs_eval_workspace_bytes(int64_t num_rendered, int64_t N, int blocks, int D, int C, unsigned fn_mask);
+int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, int blocks, int64_t num_rendered,
+                        const float *means, const float *values, const float *conics, const float *samples,
+                        const void *binning_buffer, const void *sample_binning_buffer, const void *ranges,
+                        const void *sample_ranges, float *out_u, float *out_du, float *out_ddu,
+                        float *out_dddu, void *workspace, size_t workspace_bytes, void *stream);
+int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, int blocks, int64_t num_rendered,
+                         const float *means, const float *values, const float *conics, const float *samples,
+                         const void *binning_buffer, const void *sample_binning_buffer, const void *ranges,
+                         const void *sample_ranges, const float *dL_du, const float *dL_ddu,
+                         const float *dL_dddu, const float *dL_ddddu, float *dL_dmeans, float *dL_dvalues,
+                         float *dL_dconics, void *workspace, size_t workspace_bytes, void *stream);
+
+/* number of kernels launched by this library since load (bench.py's gpu_launches) and the pair count
+ * of the last forward/backward work list (device scalar, int64) */
+int64_t pigs_launch_count(void);
+
+/* ---- neighbour lists + aggregation (aggregate_neighbors.cu:18-475) ------------------------------ */
+size_t pigs_neighbor_workspace_bytes(int64_t P, int D);
+/* stage A: per-Gaussian neighbour counts (findCollisions semantics) -> counts int64[P] */
+int pigs_neighbors_count(int64_t P, int D, const float *means, const float *radii, int64_t *counts,
+                         void *workspace, void *stream);
+/* stage B: caller computes ranges = inclusive cumsum(counts) (int64[P]) and allocates the CSR arrays
+ * (indices pre-filled with -1, dists/densities with 0); this fills them (preprocess, :57-127). */
+int pigs_neighbors_fill(int64_t P, int D, const float *means, const float *conics, const float *radii,
+                        const int64_t *ranges, int64_t *indices, float *dists, float *densities,
+                        float *inv_total_densities, void *workspace, void *stream);
+int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float *features,
+                           const float *transform, const float *queries, const float *keys,
+                           const float *frequencies, const float *distance_transform,
+                           const int64_t *indices, const int64_t *ranges, const float *dists,
+                           const float *densities, const float *inv_total_densities, float *weights,
+                           float *embeddings, float *factors, float *neighbor_features, void *stream);
+size_t pigs_aggregate_backward_workspace_bytes(int64_t P, int L, int K, int E);
+int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, const float *features,
+                            const float *transform, const float *queries, const float *keys,
+                            const float *frequencies, const float *distance_transform,
+                            const int64_t *indices, const int64_t *ranges, const float *dists,
+                            const float *densities, const float *weights, const float *embeddings,
+                            const float *factors, const float *inv_total_densities,
+                            const float *dL_dneighbor_features, float *dL_dfeatures, float *dL_dtransform,
+                            float *dL_dqueries, float *dL_dkeys, float *dL_dfrequencies,
+                            float *dL_ddistance_transform, void *workspace, void *stream);
+
+/* ---- roofline microbenchmarks (bench.py): register-resident FFMA / MUFU.EX2 loops ---------------
+ * Each launches `ctas` CTAs x 256 threads running `iters` iterations of 64 independent ops per thread
+ * and returns the number of lane-ops executed. Timing is done by the caller with CUDA events. */
+int64_t pigs_microbench_ffma(int ctas, int iters, float *sink, void *stream);
+int64_t pigs_microbench_ex2(int ctas, int iters, float *sink, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PIGS_B200_H */

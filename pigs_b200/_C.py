@@ -1,0 +1,309 @@
+"""The reference's 12 native entry points (diff-gaussian-sampling/ext.cpp:20-31), same names, same
+argument order, same return values — implemented as thin tensor -> pointer glue over the C ABI of
+libpigs_b200.so (include/pigs_b200.h).  torch owns every allocation; the library only launches
+kernels on torch's current CUDA stream.
+
+Differences a caller can observe (all documented in DESIGN.md):
+  * the byte buffers (`binning_buffer`, `sample_binning_buffer`) have our own internal layout — they
+    are opaque in the reference too (sample_points.cu:48-55);
+  * preprocess costs ONE device->host readback (reference: two), forward/backward cost none
+    (reference: one `.item()` each, sample_points.cu:124,174).
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import HEADER_BYTES, PigsHeader, check
+
+FN_VALUE, FN_DERIV, FN_HESS, FN_THIRD = 1, 2, 4, 8
+
+_pinned = {}
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _f32c(t, name):
+    """fp32 + CUDA asserted; non-contiguous inputs are copied like the reference's `.contiguous()`."""
+    if not isinstance(t, torch.Tensor):
+        raise TypeError(f"{name} must be a torch.Tensor")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name}: expected scalar type Float but found {t.dtype}")  # reference: .data<float>() throws
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (pigs_b200 has no CPU path)")
+    return t.contiguous()
+
+
+def _bytes(n, device):
+    return torch.empty(int(n), dtype=torch.uint8, device=device)
+
+
+def _dims(means, values, samples):
+    P = means.size(0)
+    D = means.size(-1)
+    N = samples.size(0)
+    C = values.size(-1)
+    return P, D, N, C
+
+
+def sample_bounds(samples, D):
+    """float32[2*D] on the device: per-dimension min then max of the samples (sample_points.cu:70-71)."""
+    L = _lib.lib()
+    samples = _f32c(samples, "samples")
+    mm = torch.empty(2 * D, dtype=torch.float32, device=samples.device)
+    check(L.pigs_sample_bounds(_ptr(samples), samples.numel() // D, D, _ptr(mm), _stream()), "pigs_sample_bounds")
+    return mm
+
+
+def read_header(buf):
+    """One pinned-memory readback of the 256-byte device header at the start of `buf`."""
+    dev = buf.device
+    key = (dev.index, torch.cuda.current_stream().cuda_stream)
+    host = _pinned.get(key)
+    if host is None:
+        host = torch.empty(HEADER_BYTES, dtype=torch.uint8).pin_memory()
+        _pinned[key] = host
+    host.copy_(buf[:HEADER_BYTES], non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return PigsHeader.from_buffer_copy(host.numpy().tobytes())
+
+
+def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None):
+    """PreprocessCUDA (sample_points.cu:37-98).  Returns
+    (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii).
+    `bounds` (device float32[2*D], optional, extension) overrides the sample bounding box — used by
+    the multi-GPU sampler so every rank bins on the global tile grid."""
+    L = _lib.lib()
+    means = _f32c(means, "means")
+    P, D, N, C = _dims(means, values, samples)
+    dev = means.device
+    radii = torch.zeros(P, dtype=torch.float32, device=dev)
+    empty = torch.empty(0, dtype=torch.uint8, device=dev)
+    if P == 0 or N == 0:
+        return 0, empty, empty.clone(), empty.clone(), empty.clone(), radii
+    if D not in (1, 2):
+        raise RuntimeError(f"pigs_b200 supports 1-D and 2-D mixtures (got D={D}), like the reference kernels")
+    cov = _f32c(covariances, "covariances")
+    samples = _f32c(samples, "samples")
+    _f32c(values, "values"), _f32c(conics, "conics")
+    if cov.numel() != P * D * (D + 1) // 2:
+        raise RuntimeError("covariances must hold P*D*(D+1)/2 elements")
+    st = _stream()
+    mm = sample_bounds(samples, D) if bounds is None else _f32c(bounds, "bounds")
+    geom = _bytes(L.pigs_geom_workspace_bytes(P), dev)
+    check(L.pigs_preprocess_count(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom), st),
+          "pigs_preprocess_count")
+    h = read_header(geom)
+    blocks, R = int(h.blocks), int(h.num_rendered)
+    binning = _bytes(L.pigs_binning_bytes(R, blocks), dev)
+    sbinning = _bytes(L.pigs_sample_binning_bytes(N, blocks, D), dev)
+    ranges = torch.zeros(blocks * 8 + 8, dtype=torch.uint8, device=dev)
+    sample_ranges = torch.zeros(blocks * 8 + 8, dtype=torch.uint8, device=dev)
+    sort_ws = _bytes(L.pigs_sort_workspace_bytes(R, N), dev)
+    check(L.pigs_preprocess_bin(P, D, N, blocks, R, _ptr(means), _ptr(samples), _ptr(radii), _ptr(geom), _ptr(binning),
+                                _ptr(sbinning), _ptr(ranges), _ptr(sample_ranges), _ptr(sort_ws), st),
+          "pigs_preprocess_bin")
+    if debug:
+        torch.cuda.synchronize()
+    return R, binning, sbinning, ranges, sample_ranges, radii
+
+
+def _blocks_of(ranges):
+    return ranges.numel() // 8 - 1
+
+
+def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
+                   sample_ranges, debug):
+    """Fused forward for any subset of {value, derivative, Hessian, third}.  Returns a 4-tuple with
+    None for the functions not requested."""
+    L = _lib.lib()
+    means = _f32c(means, "means")
+    values = _f32c(values, "values")
+    conics = _f32c(conics, "conics")
+    samples = _f32c(samples, "samples")
+    P, D, N, C = _dims(means, values, samples)
+    dev = means.device
+    shp = lambda k: (N,) + (D,) * k + (C,)
+    outs = [torch.zeros(shp(k), dtype=torch.float32, device=dev) if fn_mask & (1 << k) else None for k in range(4)]
+    if P != 0 and N != 0:
+        blocks = _blocks_of(ranges)
+        ws_bytes = L.pigs_eval_workspace_bytes(num_rendered, N, blocks, D, C, fn_mask)
+        ws = _bytes(ws_bytes, dev)
+        check(L.pigs_sample_forward(fn_mask, P, D, N, C, blocks, num_rendered, _ptr(means), _ptr(values), _ptr(conics),
+                                    _ptr(samples), _ptr(binning_buffer), _ptr(sample_binning_buffer), _ptr(ranges),
+                                    _ptr(sample_ranges), _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(outs[3]),
+                                    _ptr(ws), ws_bytes, _stream()), "pigs_sample_forward")
+        if debug:
+            torch.cuda.synchronize()
+    return tuple(outs)
+
+
+def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads, binning_buffer, sample_binning_buffer,
+                    ranges, sample_ranges, debug):
+    """Fused backward; `grads` is a 4-tuple of upstream gradients (None = zero).  Returns
+    (dL_dmeans [P,D], dL_dvalues [P,C], dL_dconics [P,D(D+1)/2])."""
+    L = _lib.lib()
+    means = _f32c(means, "means")
+    values = _f32c(values, "values")
+    conics = _f32c(conics, "conics")
+    samples = _f32c(samples, "samples")
+    P, D, N, C = _dims(means, values, samples)
+    dev = means.device
+    dm = torch.zeros((P, D), dtype=torch.float32, device=dev)
+    dv = torch.zeros((P, C), dtype=torch.float32, device=dev)
+    dc = torch.zeros((P, D * (D + 1) // 2), dtype=torch.float32, device=dev)
+    g = [None if x is None else _f32c(x, "dL_dout") for x in grads]
+    if P != 0 and N != 0:
+        blocks = _blocks_of(ranges)
+        ws_bytes = L.pigs_eval_workspace_bytes(num_rendered, N, blocks, D, C, fn_mask)
+        ws = _bytes(ws_bytes, dev)
+        check(L.pigs_sample_backward(fn_mask, P, D, N, C, blocks, num_rendered, _ptr(means), _ptr(values), _ptr(conics),
+                                     _ptr(samples), _ptr(binning_buffer), _ptr(sample_binning_buffer), _ptr(ranges),
+                                     _ptr(sample_ranges), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]), _ptr(g[3]), _ptr(dm),
+                                     _ptr(dv), _ptr(dc), _ptr(ws), ws_bytes, _stream()), "pigs_sample_backward")
+        if debug:
+            torch.cuda.synchronize()
+    return dm, dv, dc
+
+
+def _single(bit):
+    k = bit.bit_length() - 1
+
+    def fwd(means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges,
+            debug):
+        return sample_forward(bit, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer,
+                              ranges, sample_ranges, debug)[k]
+
+    def bwd(means, values, conics, samples, num_rendered, dL_dout, binning_buffer, sample_binning_buffer, ranges,
+            sample_ranges, debug):
+        grads = [None] * 4
+        grads[k] = dL_dout
+        return sample_backward(bit, means, values, conics, samples, num_rendered, grads, binning_buffer,
+                               sample_binning_buffer, ranges, sample_ranges, debug)
+
+    return fwd, bwd
+
+
+# ext.cpp:21-28
+sample_gaussians, sample_gaussians_backward = _single(FN_VALUE)
+sample_gaussians_derivative, sample_gaussians_derivative_backward = _single(FN_DERIV)
+sample_gaussians_laplacian, sample_gaussians_laplacian_backward = _single(FN_HESS)
+sample_gaussians_third_derivative, sample_gaussians_third_derivative_backward = _single(FN_THIRD)
+
+
+def point_lists(num_rendered, binning_buffer, sample_binning_buffer, N):
+    """(point_list u32[R], point_tiles u32[R], sample_point_list u32[N]) as int32 tensor views of the
+    opaque buffers — for parity tests / debugging (the reference's BinningState::point_list)."""
+    L = _lib.lib()
+
+    def view(buf, addr, n):
+        off = addr - buf.data_ptr()
+        return buf[off:off + 4 * n].view(torch.int32)
+
+    pl = view(binning_buffer, L.pigs_point_list(_ptr(binning_buffer)), num_rendered)
+    pt = view(binning_buffer, L.pigs_point_tiles(_ptr(binning_buffer), num_rendered), num_rendered)
+    sl = view(sample_binning_buffer, L.pigs_sample_list(_ptr(sample_binning_buffer)), N)
+    return pl, pt, sl
+
+
+# ---- neighbour aggregation (ext.cpp:29-31) ----------------------------------------------------------
+def preprocess_aggregate(means, conics, radii, debug):
+    """AggregateNeighborsPreprocessCUDA (aggregate_neighbors.cu:323-367).  Returns
+    (indices i64[M], ranges i64[P], dists f32[M,D], densities f32[M], inv_total_densities f32[P])."""
+    L = _lib.lib()
+    means = _f32c(means, "means")
+    conics = _f32c(conics, "conics")
+    radii = _f32c(radii, "radii")
+    P, D = means.size(0), means.size(-1)
+    dev = means.device
+    ws = _bytes(max(int(L.pigs_neighbor_workspace_bytes(P, D)), 16), dev)
+    counts = torch.zeros(P, dtype=torch.int64, device=dev)
+    st = _stream()
+    check(L.pigs_neighbors_count(P, D, _ptr(means), _ptr(radii), _ptr(counts), _ptr(ws), st), "pigs_neighbors_count")
+    ranges = counts.cumsum(0)
+    length = int(ranges[-1].item()) if P > 0 else 0
+    indices = torch.full((length,), -1, dtype=torch.int64, device=dev)
+    dists = torch.zeros((length, D), dtype=torch.float32, device=dev)
+    densities = torch.zeros((length,), dtype=torch.float32, device=dev)
+    inv_total = torch.zeros((P,), dtype=torch.float32, device=dev)
+    check(L.pigs_neighbors_fill(P, D, _ptr(means), _ptr(conics), _ptr(radii), _ptr(ranges), _ptr(indices), _ptr(dists),
+                                _ptr(densities), _ptr(inv_total), _ptr(ws), st), "pigs_neighbors_fill")
+    if debug:
+        torch.cuda.synchronize()
+    return indices, ranges, dists, densities, inv_total
+
+
+def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                        densities, inv_total_densities, debug):
+    """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415).  Returns
+    (weights, embeddings, factors [M], neighbor_features [P,L])."""
+    L_ = _lib.lib()
+    features = _f32c(features, "features")
+    transform = _f32c(transform, "transform")
+    queries = _f32c(queries, "queries")
+    keys = _f32c(keys, "keys")
+    frequencies = _f32c(frequencies, "frequencies")
+    dt = _f32c(distance_transform, "distance_transform")
+    dists = _f32c(dists, "dists")
+    densities = _f32c(densities, "densities")
+    inv_total = _f32c(inv_total_densities, "inv_total_densities")
+    indices = indices.contiguous()
+    ranges = ranges.contiguous()
+    P, D, L = features.size(0), dists.size(-1), features.size(-1)
+    K, E = queries.size(-1), dt.size(-1) // 2
+    dev = features.device
+    weights = torch.zeros_like(densities)
+    embeddings = torch.zeros_like(densities)
+    factors = torch.zeros_like(densities)
+    out = torch.zeros((P, L), dtype=torch.float32, device=dev)
+    if P > 0:
+        check(L_.pigs_aggregate_forward(P, D, L, K, E, _ptr(features), _ptr(transform), _ptr(queries), _ptr(keys),
+                                        _ptr(frequencies), _ptr(dt), _ptr(indices), _ptr(ranges), _ptr(dists),
+                                        _ptr(densities), _ptr(inv_total), _ptr(weights), _ptr(embeddings), _ptr(factors),
+                                        _ptr(out), _stream()), "pigs_aggregate_forward")
+    if debug:
+        torch.cuda.synchronize()
+    return weights, embeddings, factors, out
+
+
+def aggregate_neighbors_backward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
+                                 dists, densities, weights, embeddings, factors, inv_total_densities,
+                                 dL_dneighbor_features, debug):
+    """AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475)."""
+    L_ = _lib.lib()
+    features = _f32c(features, "features")
+    transform = _f32c(transform, "transform")
+    queries = _f32c(queries, "queries")
+    keys = _f32c(keys, "keys")
+    frequencies = _f32c(frequencies, "frequencies")
+    dt = _f32c(distance_transform, "distance_transform")
+    dists = _f32c(dists, "dists")
+    g = _f32c(dL_dneighbor_features, "dL_dneighbor_features")
+    P, D, L = features.size(0), dists.size(-1), features.size(-1)
+    K, E = queries.size(-1), dt.size(-1) // 2
+    M = densities.numel()
+    dev = features.device
+    gf = torch.zeros_like(features)
+    gt = torch.zeros_like(transform)
+    gq = torch.zeros_like(queries)
+    gk = torch.zeros_like(keys)
+    gfr = torch.zeros_like(frequencies)
+    gdt = torch.zeros_like(dt)
+    if P > 0:
+        ws = _bytes(max(int(L_.pigs_aggregate_backward_workspace_bytes(P, L, K, E)), 16), dev)
+        check(L_.pigs_aggregate_backward(P, D, L, K, E, M, _ptr(features), _ptr(transform), _ptr(queries), _ptr(keys),
+                                         _ptr(frequencies), _ptr(dt), _ptr(indices.contiguous()), _ptr(ranges.contiguous()),
+                                         _ptr(dists), _ptr(_f32c(densities, "densities")), _ptr(_f32c(weights, "weights")),
+                                         _ptr(_f32c(embeddings, "embeddings")), _ptr(_f32c(factors, "factors")),
+                                         _ptr(_f32c(inv_total_densities, "inv_total_densities")), _ptr(g), _ptr(gf),
+                                         _ptr(gt), _ptr(gq), _ptr(gk), _ptr(gfr), _ptr(gdt), _ptr(ws), _stream()),
+              "pigs_aggregate_backward")
+    if debug:
+        torch.cuda.synchronize()
+    return gf, gt, gq, gk, gfr, gdt

@@ -1,0 +1,237 @@
+"""pigs_b200 — B200-native (sm_100a) implementation of kr4b/pigs' differentiable Gaussian-mixture
+sampling path, behind the reference's own Python API.
+
+Public surface = diff-gaussian-sampling/diff_gaussian_sampling/__init__.py (reference), name for name:
+  GaussianSampler(debug) with .preprocess / .sample_gaussians / .sample_gaussians_derivative /
+  .sample_gaussians_laplacian / .sample_gaussians_third_derivative / .preprocess_aggregate /
+  .aggregate_neighbors, and the module-level functions sample_gaussians(...), ...,
+  preprocess_gaussians, preprocess_aggregate, aggregate_neighbors.
+Extensions (additive, keyword-only): GaussianSampler(debug, fused=...), .sample_fused(mask), .pair_count().
+
+Everything below the API is hand-written CUDA in libpigs_b200.so (include/pigs_b200.h); there is no
+CPU or PyTorch fallback.
+"""
+import os
+
+import torch
+
+from . import _C
+from ._C import FN_DERIV, FN_HESS, FN_THIRD, FN_VALUE
+
+__all__ = [
+    "GaussianSampler", "sample_gaussians", "sample_gaussians_derivative", "sample_gaussians_laplacian",
+    "sample_gaussians_third_derivative", "aggregate_neighbors", "preprocess_gaussians", "preprocess_aggregate",
+    "FN_VALUE", "FN_DERIV", "FN_HESS", "FN_THIRD",
+]
+
+
+def cpu_deep_copy_tuple(input_tuple):
+    return tuple(item.cpu().clone() if isinstance(item, torch.Tensor) else item for item in input_tuple)
+
+
+def call_debug(func, debug, name, *args):
+    """Reference debug semantics (__init__.py:38-50): with debug on, inputs are copied to the CPU before the
+    call and dumped to snapshot_<name>.dump if it raises; the native side synchronises after each launch."""
+    if debug:
+        cpu_args = cpu_deep_copy_tuple(args)
+        try:
+            results = func(*args)
+        except Exception as ex:
+            torch.save(cpu_args, "snapshot_{}.dump".format(name))
+            print("\nAn error occured in {}. Please forward snapshot_{}.dump for debugging.".format(name, name))
+            raise ex
+    else:
+        results = func(*args)
+    return results
+
+
+def preprocess_gaussians(means, values, covariances, conics, samples, debug):
+    return call_debug(_C.preprocess_gaussians, debug, "preprocess", means, values, covariances, conics, samples, debug)
+
+
+def preprocess_aggregate(means, conics, radii, debug):
+    return call_debug(_C.preprocess_aggregate, debug, "preprocess_agg", means, conics, radii, debug)
+
+
+class _SampleFused(torch.autograd.Function):
+    """One autograd node for any subset of {value, derivative, Hessian, third}: one fused forward kernel,
+    one fused backward kernel.  Inputs are kept on ctx (not save_for_backward) so that, like the
+    reference's separate nodes, each output can be back-propagated in its own backward() call."""
+
+    @staticmethod
+    def forward(ctx, mask, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
+                sample_ranges, debug):
+        args = (means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
+                sample_ranges, debug)
+        outs = call_debug(lambda *a: _C.sample_forward(mask, *a), debug, "fw%d" % mask, *args)
+        ctx.mask = mask
+        ctx.args = args
+        return tuple(o for o in outs if o is not None)
+
+    @staticmethod
+    def backward(ctx, *grad_outs):
+        mask = ctx.mask
+        means, values, conics, samples, num_rendered, bb, sbb, ranges, sample_ranges, debug = ctx.args
+        grads, it = [None] * 4, iter(grad_outs)
+        live = 0
+        for k in range(4):
+            if mask & (1 << k):
+                g = next(it)
+                if g is not None:
+                    grads[k] = g
+                    live |= 1 << k
+        if live == 0:
+            return (None,) * 11
+        dm, dv, dc = call_debug(lambda *a: _C.sample_backward(live, *a), debug, "bw%d" % mask, means, values, conics,
+                                samples, num_rendered, grads, bb, sbb, ranges, sample_ranges, debug)
+        return (None, dm, dv, dc, None, None, None, None, None, None, None)
+
+
+def _sample_mask(mask, *args):
+    return _SampleFused.apply(mask, *args)
+
+
+# module-level functions, reference signatures (__init__.py:21-36): the first positional parameter is
+# called `debug` there but receives `means`; args = (means, values, conics, samples, num_rendered,
+# binning_buffer, sample_binning_buffer, ranges, sample_ranges, debug)
+def sample_gaussians(debug, *args):
+    return _sample_mask(FN_VALUE, debug, *args)[0]
+
+
+def sample_gaussians_derivative(debug, *args):
+    return _sample_mask(FN_DERIV, debug, *args)[0]
+
+
+def sample_gaussians_laplacian(debug, *args):
+    return _sample_mask(FN_HESS, debug, *args)[0]
+
+
+def sample_gaussians_third_derivative(debug, *args):
+    return _sample_mask(FN_THIRD, debug, *args)[0]
+
+
+class _AggregateNeighbors(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                densities, inv_total_densities, debug):
+        args = (features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+                inv_total_densities, debug)
+        weights, embeddings, factors, neighbor_features = call_debug(_C.aggregate_neighbors, debug, "aggregate", *args)
+        ctx.args = args
+        ctx.saved = (weights, embeddings, factors)
+        return neighbor_features
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        (features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+         inv_total_densities, debug) = ctx.args
+        weights, embeddings, factors = ctx.saved
+        grads = call_debug(_C.aggregate_neighbors_backward, debug, "aggregate_bw", features, transform, queries, keys,
+                           frequencies, distance_transform, indices, ranges, dists, densities, weights, embeddings,
+                           factors, inv_total_densities, grad_out, debug)
+        return tuple(grads) + (None,) * 6
+
+
+def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                        densities, inv_total_densities, debug):
+    return _AggregateNeighbors.apply(features, transform, queries, keys, frequencies, distance_transform, indices,
+                                     ranges, dists, densities, inv_total_densities, debug)
+
+
+_BIT_OF = {"u": FN_VALUE, "du": FN_DERIV, "ddu": FN_HESS, "dddu": FN_THIRD}
+
+
+class GaussianSampler:
+    """Stateful sampler, reference API (__init__.py:214-317).
+
+    fused (extension): True / False / "auto" (default, env PIGS_B200_FUSE=0 disables).  The reference's
+    callers ask for u, grad u and the Hessian in three calls after one preprocess(); with fusion on, the
+    sampler remembers which outputs were requested during the previous preprocess() cycle and, on the
+    first request of the next cycle, evaluates that whole set in ONE kernel (and back-propagates it in
+    one), handing out the cached pieces.  Results are identical to the unfused calls."""
+
+    def __init__(self, debug, fused="auto"):
+        self.debug = debug
+        if fused == "auto":
+            fused = os.environ.get("PIGS_B200_FUSE", "1") != "0"
+        self.fused = bool(fused)
+        self._plan = 0      # mask requested during the previous cycle
+        self._seen = 0      # mask requested so far in this cycle
+        self._cache = {}    # bit -> tensor produced by a fused call in this cycle
+
+    def preprocess(self, means, values, covariances, conics, samples, bounds=None):
+        debug = self.debug
+        if bounds is None:
+            res = preprocess_gaussians(means, values, covariances, conics, samples, debug)
+        else:
+            res = call_debug(lambda *a: _C.preprocess_gaussians(*a, bounds=bounds), debug, "preprocess", means, values,
+                             covariances, conics, samples, debug)
+        num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii = res
+        self.means = means
+        self.values = values
+        self.conics = conics
+        self.samples = samples
+        self.num_rendered = num_rendered
+        self.binning_buffer = binning_buffer
+        self.sample_binning_buffer = sample_binning_buffer
+        self.ranges = ranges
+        self.sample_ranges = sample_ranges
+        self.radii = radii
+        self._sample_state = (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges)
+        self._plan, self._seen, self._cache = self._seen, 0, {}
+
+    def _args(self):
+        nr, bb, sbb, rg, srg = self._sample_state
+        return (self.means, self.values, self.conics, self.samples, nr, bb, sbb, rg, srg, self.debug)
+
+    def sample_fused(self, mask):
+        """(extension) evaluate every function in `mask` with one fused kernel; returns a tuple in
+        (value, derivative, Hessian, third) order restricted to the requested ones."""
+        return _sample_mask(mask, *self._args())
+
+    def _request(self, bit):
+        self._seen |= bit
+        if bit in self._cache:
+            return self._cache.pop(bit)
+        if self.fused and (self._plan & bit) and self._plan != bit and not self._cache:
+            outs = iter(self.sample_fused(self._plan))
+            for k in range(4):
+                if self._plan & (1 << k):
+                    self._cache[1 << k] = next(outs)
+            return self._cache.pop(bit)
+        return self.sample_fused(bit)[0]
+
+    def sample_gaussians(self):
+        return self._request(FN_VALUE)
+
+    def sample_gaussians_derivative(self):
+        return self._request(FN_DERIV)
+
+    def sample_gaussians_laplacian(self):
+        return self._request(FN_HESS)
+
+    def sample_gaussians_third_derivative(self):
+        return self._request(FN_THIRD)
+
+    def pair_count(self):
+        """(extension) size of the reference pair set: sum over tiles of n_samples(tile) * n_gaussians(tile)."""
+        ranges, sample_ranges = self._sample_state[3], self._sample_state[4]
+        b = ranges.numel() // 8 - 1
+        if b <= 0:
+            return 0
+        g = ranges.view(torch.int32)[: 2 * b].view(b, 2).to(torch.int64)
+        s = sample_ranges.view(torch.int32)[: 2 * b].view(b, 2).to(torch.int64)
+        return int(((g[:, 1] - g[:, 0]) * (s[:, 1] - s[:, 0])).sum().item())
+
+    def preprocess_aggregate(self):
+        indices, ranges, dists, densities, inv_total_densities = preprocess_aggregate(self.means, self.conics, self.radii,
+                                                                                       self.debug)
+        self.indices = indices
+        self.ranges = ranges  # NB: like the reference (__init__.py:298) this overwrites the tile ranges attribute
+        self.dists = dists
+        self.densities = densities
+        self.inv_total_densities = inv_total_densities
+
+    def aggregate_neighbors(self, features, transform, queries, keys, frequencies, distance_transform):
+        return aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, self.indices,
+                                   self.ranges, self.dists, self.densities, self.inv_total_densities, self.debug)

@@ -1,0 +1,95 @@
+"""ctypes loader for libpigs_b200.so (the C ABI in include/pigs_b200.h).
+
+There is no CPU fallback and no alternative backend: if the shared library is missing or a CUDA
+call fails, a RuntimeError is raised.
+"""
+import ctypes
+import os
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "libpigs_b200.so")
+_lib = None
+
+c_void_p, c_int, c_int64, c_size_t, c_uint = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t, ctypes.c_uint
+
+
+class PigsHeader(ctypes.Structure):
+    """Mirror of `struct pigs_header` (include/pigs_b200.h)."""
+    _fields_ = [
+        ("magic", ctypes.c_uint32),
+        ("D", ctypes.c_int32),
+        ("grid", ctypes.c_int32 * 2),
+        ("blocks", ctypes.c_int32),
+        ("nslots", ctypes.c_int32),
+        ("min_b", ctypes.c_float * 2),
+        ("max_b", ctypes.c_float * 2),
+        ("P", ctypes.c_int64),
+        ("N", ctypes.c_int64),
+        ("num_rendered", ctypes.c_int64),
+        ("reserved", ctypes.c_uint32 * 48),
+    ]
+
+
+HEADER_BYTES = ctypes.sizeof(PigsHeader)
+assert HEADER_BYTES == 256, HEADER_BYTES
+
+# name -> (restype, argtypes); every symbol include/pigs_b200.h declares
+SIGNATURES = {
+    "pigs_version": (c_int, []),
+    "pigs_last_error": (ctypes.c_char_p, []),
+    "pigs_set_grid_recip_mode": (None, [c_int]),
+    "pigs_sample_bounds": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
+    "pigs_geom_workspace_bytes": (c_size_t, [c_int64]),
+    "pigs_preprocess_count": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "pigs_binning_bytes": (c_size_t, [c_int64, c_int]),
+    "pigs_sample_binning_bytes": (c_size_t, [c_int64, c_int, c_int]),
+    "pigs_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
+    "pigs_preprocess_bin": (c_int, [c_int64, c_int, c_int64, c_int, c_int64] + [c_void_p] * 10),
+    "pigs_point_list": (c_void_p, [c_void_p]),
+    "pigs_point_tiles": (c_void_p, [c_void_p, c_int64]),
+    "pigs_sample_list": (c_void_p, [c_void_p]),
+    "pigs_eval_workspace_bytes": (c_size_t, [c_int64, c_int64, c_int, c_int, c_int, c_uint]),
+    "pigs_sample_forward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 13 + [c_size_t, c_void_p]),
+    "pigs_sample_backward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 16 + [c_size_t, c_void_p]),
+    "pigs_launch_count": (c_int64, []),
+    "pigs_neighbor_workspace_bytes": (c_size_t, [c_int64, c_int]),
+    "pigs_neighbors_count": (c_int, [c_int64, c_int] + [c_void_p] * 5),
+    "pigs_neighbors_fill": (c_int, [c_int64, c_int] + [c_void_p] * 10),
+    "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
+    "pigs_aggregate_backward_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
+    "pigs_aggregate_backward": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64] + [c_void_p] * 23),
+    "pigs_microbench_ffma": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
+    "pigs_microbench_ex2": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
+}
+
+
+def build(verbose=False):
+    """Compile pigs_b200/csrc/*.cu for sm_100a into pigs_b200/libpigs_b200.so (nvcc, in-tree)."""
+    cmd = ["make", "-C", os.path.join(_HERE, "csrc"), "-j8"]
+    if not verbose:
+        cmd.append("-s")
+    subprocess.run(cmd, check=True)
+
+
+def lib():
+    """The loaded library; raises RuntimeError when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            raise RuntimeError(
+                f"{_SO} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                "(nvcc, sm_100a). pigs_b200 has no CPU or PyTorch fallback.")
+        L = ctypes.CDLL(_SO)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the .so does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc, what):
+    if rc != 0:
+        msg = lib().pigs_last_error()
+        raise RuntimeError(f"pigs_b200: {what} failed (status {rc}): {msg.decode() if msg else ''}")

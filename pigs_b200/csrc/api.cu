@@ -1,0 +1,240 @@
+// api.cu — extern "C" entry points of the evaluation path (see include/pigs_b200.h) and the roofline
+// microbenchmarks.  Host logic only: resolve the opaque buffers, split the request into natively
+// compiled (mask, channel-group) kernels, stage, launch.  No host synchronisation anywhere.
+#include "layouts.cuh"
+
+using namespace pigs;
+
+namespace {
+
+// function masks with a dedicated kernel; anything else inside {V,D,H} runs the fused 7-kernel with
+// the unwanted outputs/upstreams left NULL.
+unsigned native_low_mask(unsigned m)
+{
+    m &= 7u;
+    if (m == 0u || m == 1u || m == 2u || m == 4u) return m;
+    return 7u;
+}
+
+int max_sv4(int D, int C)
+{
+    int m = 0;
+    const unsigned masks[5] = {1u, 2u, 4u, 7u, 8u};
+    for (unsigned k : masks) {
+        int v = srec_v4(D, C, k);
+        if (v > m) m = v;
+    }
+    return m;
+}
+
+int resolve(EvalCall& c, int64_t P, int D, int64_t N, int C, int blocks, int64_t R, const float* means, const float* values,
+            const float* conics, const float* samples, const void* binning_buffer, const void* sample_binning_buffer,
+            const void* ranges, const void* sample_ranges)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(C >= 1);
+    PIGS_ARG(P > 0 && N > 0 && blocks > 0 && R >= 0);
+    PIGS_ARG(means && values && conics && samples && binning_buffer && sample_binning_buffer && ranges && sample_ranges);
+    c.D = D;
+    c.C = C;
+    c.blocks = blocks;
+    c.P = P;
+    c.N = N;
+    c.R = R;
+    c.means = means;
+    c.values = values;
+    c.conics = conics;
+    c.samples = samples;
+    BinLayout b(const_cast<void*>(binning_buffer), R);
+    SampleBinLayout s(const_cast<void*>(sample_binning_buffer), N, blocks, D);
+    c.list = b.list;
+    c.tiles = b.tiles;
+    c.slist = s.list;
+    c.bbox = s.bbox;
+    c.ranges = (const uint2*)ranges;
+    c.sample_ranges = (const uint2*)sample_ranges;
+    return 0;
+}
+
+uint32_t split_hint(int64_t stationary, uint32_t chunk, int blocks)
+{
+    const int64_t target = (int64_t)num_sms() * 48;
+    const int64_t base = stationary / chunk + blocks;
+    int64_t s = (target + base - 1) / base;
+    if (s < 1) s = 1;
+    if (s > 256) s = 256;
+    return (uint32_t)s;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pigs_version(void) { return 100; }
+const char* pigs_last_error(void) { return g_err; }
+void pigs_set_grid_recip_mode(int recip) { g_recip_mode = recip ? 1 : 0; }
+int64_t pigs_launch_count(void) { return g_launches; }
+
+size_t pigs_eval_workspace_bytes(int64_t num_rendered, int64_t N, int blocks, int D, int C, unsigned fn_mask)
+{
+    (void)fn_mask;
+    const int Cg = C >= 2 ? 2 : 1;
+    return EvalWs(nullptr, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg)).bytes;
+}
+
+int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, int blocks, int64_t num_rendered,
+                        const float* means, const float* values, const float* conics, const float* samples,
+                        const void* binning_buffer, const void* sample_binning_buffer, const void* ranges,
+                        const void* sample_ranges, float* out_u, float* out_du, float* out_ddu, float* out_dddu,
+                        void* workspace, size_t workspace_bytes, void* stream)
+{
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~15u) == 0);
+    EvalCall c;
+    int rc = resolve(c, P, D, N, C, blocks, num_rendered, means, values, conics, samples, binning_buffer,
+                     sample_binning_buffer, ranges, sample_ranges);
+    if (rc) return rc;
+    PIGS_ARG(workspace && workspace_bytes >= pigs_eval_workspace_bytes(num_rendered, N, blocks, D, C, fn_mask));
+    PIGS_ARG(!(fn_mask & PIGS_FN_VALUE) || out_u);
+    PIGS_ARG(!(fn_mask & PIGS_FN_DERIV) || out_du);
+    PIGS_ARG(!(fn_mask & PIGS_FN_HESS) || out_ddu);
+    PIGS_ARG(!(fn_mask & PIGS_FN_THIRD) || out_dddu);
+    if (num_rendered == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Cg = C >= 2 ? 2 : 1;
+    EvalWs ws(workspace, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg));
+
+    for (int ch0 = 0; ch0 < C; ch0 += 2) {
+        const int cw = (C - ch0) >= 2 ? 2 : 1;
+        rc = stage_gaussians(c, cw, ch0, ws, st);
+        if (rc) return rc;
+        unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
+        for (unsigned m : todo) {
+            if (!m) continue;
+            const uint32_t chunk = EV_THREADS * fwd_ks(D, cw, m);
+            rc = stage_worklist(c, ws, chunk, split_hint(N, chunk, blocks), 256, true, st);
+            if (rc) return rc;
+            FwdOut o;
+            o.u = (fn_mask & PIGS_FN_VALUE) ? out_u : nullptr;
+            o.du = (fn_mask & PIGS_FN_DERIV) ? out_du : nullptr;
+            o.ddu = (fn_mask & PIGS_FN_HESS) ? out_ddu : nullptr;
+            o.dddu = (fn_mask & PIGS_FN_THIRD) ? out_dddu : nullptr;
+            rc = launch_forward(c, cw, m, false, ch0, ws, o, st);
+            if (rc) return rc;
+            rc = launch_forward(c, cw, m, true, ch0, ws, o, st);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, int blocks, int64_t num_rendered,
+                         const float* means, const float* values, const float* conics, const float* samples,
+                         const void* binning_buffer, const void* sample_binning_buffer, const void* ranges,
+                         const void* sample_ranges, const float* dL_du, const float* dL_ddu, const float* dL_dddu,
+                         const float* dL_ddddu, float* dL_dmeans, float* dL_dvalues, float* dL_dconics, void* workspace,
+                         size_t workspace_bytes, void* stream)
+{
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~15u) == 0);
+    EvalCall c;
+    int rc = resolve(c, P, D, N, C, blocks, num_rendered, means, values, conics, samples, binning_buffer,
+                     sample_binning_buffer, ranges, sample_ranges);
+    if (rc) return rc;
+    PIGS_ARG(workspace && workspace_bytes >= pigs_eval_workspace_bytes(num_rendered, N, blocks, D, C, fn_mask));
+    PIGS_ARG(dL_dmeans && dL_dvalues && dL_dconics);
+    // a NULL upstream gradient is an all-zero one
+    if (!dL_du) fn_mask &= ~PIGS_FN_VALUE;
+    if (!dL_ddu) fn_mask &= ~PIGS_FN_DERIV;
+    if (!dL_dddu) fn_mask &= ~PIGS_FN_HESS;
+    if (!dL_ddddu) fn_mask &= ~PIGS_FN_THIRD;
+    if (num_rendered == 0 || fn_mask == 0) return 0;
+    cudaStream_t st = (cudaStream_t)stream;
+    const int Cg = C >= 2 ? 2 : 1;
+    EvalWs ws(workspace, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg));
+
+    for (int ch0 = 0; ch0 < C; ch0 += 2) {
+        const int cw = (C - ch0) >= 2 ? 2 : 1;
+        rc = stage_gaussians(c, cw, ch0, ws, st);
+        if (rc) return rc;
+        unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
+        for (unsigned m : todo) {
+            if (!m) continue;
+            rc = stage_samples(c, cw, m, ch0, (fn_mask & PIGS_FN_VALUE) ? dL_du : nullptr,
+                               (fn_mask & PIGS_FN_DERIV) ? dL_ddu : nullptr, (fn_mask & PIGS_FN_HESS) ? dL_dddu : nullptr,
+                               (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, ws, st);
+            if (rc) return rc;
+            const uint32_t chunk = EV_THREADS * bwd_kg(D, cw, m);
+            rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks), 128, false, st);
+            if (rc) return rc;
+            BwdOut o{dL_dmeans, dL_dvalues, dL_dconics};
+            rc = launch_backward(c, cw, m, false, ch0, ws, o, st);
+            if (rc) return rc;
+            rc = launch_backward(c, cw, m, true, ch0, ws, o, st);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// roofline microbenchmarks: register-resident FFMA and MUFU.EX2 loops (bench.py measures the peaks
+// the evaluation kernels are compared against)
+// ------------------------------------------------------------------------------------------------
+namespace pigs {
+
+constexpr int MB_ILP = 16;
+
+__global__ void __launch_bounds__(256) mb_ffma_kernel(int iters, float* sink)
+{
+    float a[MB_ILP];
+    const float b = 1.0000001f + 1e-9f * threadIdx.x, c = 1e-7f;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) a[i] = 1.0f + i * 1e-3f + threadIdx.x * 1e-6f;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int i = 0; i < MB_ILP; i++) a[i] = fmaf(a[i], b, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) s += a[i];
+    if (s == 123.456f) sink[0] = s;
+}
+
+__global__ void __launch_bounds__(256) mb_ex2_kernel(int iters, float* sink)
+{
+    float a[MB_ILP];
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) a[i] = -0.5f - i * 1e-3f - threadIdx.x * 1e-6f;
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++)
+#pragma unroll
+            for (int i = 0; i < MB_ILP; i++) a[i] = ex2_approx(a[i]) - 1.5f;  // 1 MUFU + 1 FADD
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) s += a[i];
+    if (s == 123.456f) sink[0] = s;
+}
+
+}  // namespace pigs
+
+extern "C" {
+
+int64_t pigs_microbench_ffma(int ctas, int iters, float* sink, void* stream)
+{
+    mb_ffma_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(iters, sink);
+    g_launches++;
+    return (int64_t)ctas * 256 * (int64_t)iters * 4 * MB_ILP;
+}
+int64_t pigs_microbench_ex2(int ctas, int iters, float* sink, void* stream)
+{
+    mb_ex2_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(iters, sink);
+    g_launches++;
+    return (int64_t)ctas * 256 * (int64_t)iters * 4 * MB_ILP;
+}
+
+}  // extern "C"

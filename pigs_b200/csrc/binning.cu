@@ -1,0 +1,424 @@
+// binning.cu — cutoff-radius tile binning, bit-exact with the reference's
+// (cuda_sampler/forward.cu:24-83 preprocessCUDA, auxiliary.h:21-31 getRect,
+//  sampler_impl.cu:54-189 duplicateWithKeys / identifyTileRanges / sampleWithKeys,
+//  sample_points.cu:70-77 tile grid) but with none of its host round trips inside the pipeline,
+// no device-side new/delete, 32-bit tile keys and a hand-written stable sort.
+//
+// Floating-point expressions that decide a bin are spelled with explicit round-to-nearest
+// intrinsics in the exact operation order of the reference's SASS, so
+// nvcc cannot contract or reorder them.
+#include "common.cuh"
+#include "layouts.cuh"
+
+namespace pigs {
+
+// ---------------------------------------------------------------------------------------------
+// S1: bounds
+// ---------------------------------------------------------------------------------------------
+__global__ void bounds_init(float* mm, int D)
+{
+    if (threadIdx.x < D) {
+        mm[threadIdx.x] = __int_as_float(0x7f800000);      // +inf
+        mm[D + threadIdx.x] = __int_as_float(0xff800000);  // -inf
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ samples, int64_t N, float* __restrict__ mm)
+{
+    float lo[D], hi[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        lo[d] = __int_as_float(0x7f800000);
+        hi[d] = __int_as_float(0xff800000);
+    }
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
+        if (D == 2) {
+            const float2 p = reinterpret_cast<const float2*>(samples)[i];
+            lo[0] = fminf(lo[0], p.x);
+            hi[0] = fmaxf(hi[0], p.x);
+            lo[D - 1] = fminf(lo[D - 1], p.y);
+            hi[D - 1] = fmaxf(hi[D - 1], p.y);
+        } else {
+            const float p = samples[i];
+            lo[0] = fminf(lo[0], p);
+            hi[0] = fmaxf(hi[0], p);
+        }
+    }
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+            lo[d] = fminf(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+            hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
+        }
+    }
+    __shared__ float slo[8][D], shi[8][D];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (lane == 0)
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            slo[w][d] = lo[d];
+            shi[w][d] = hi[d];
+        }
+    __syncthreads();
+    if (threadIdx.x < D) {
+        const int d = threadIdx.x;
+        float l = slo[0][d], h = shi[0][d];
+        for (int i = 1; i < 8; i++) {
+            l = fminf(l, slo[i][d]);
+            h = fmaxf(h, shi[i][d]);
+        }
+        atomic_min_float(mm + d, l + 0.0f);
+        atomic_max_float(mm + D + d, h + 0.0f);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// header / tile grid (sample_points.cu:73-74)
+// ---------------------------------------------------------------------------------------------
+__global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int64_t N, int recip, pigs_header* hdr)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    pigs_header h;
+    memset(&h, 0, sizeof(h));
+    h.magic = PIGS_MAGIC;
+    h.D = D;
+    h.grid[0] = h.grid[1] = 1;
+    h.P = P;
+    h.N = N;
+    int blocks = 1;
+    const float inv = __fdiv_rn(1.0f, PIGS_TILE_WIDTH);
+    for (int d = 0; d < D; d++) {
+        const float lo = mm[d], hi = mm[D + d];
+        const float span = __fadd_rn(__fsub_rn(hi, lo), 1e-6f);
+        const float q = recip ? __fmul_rn(span, inv) : __fdiv_rn(span, PIGS_TILE_WIDTH);
+        int g = (int)ceilf(q);
+        h.grid[d] = g;
+        h.min_b[d] = lo;
+        h.max_b[d] = hi;
+        blocks *= g;
+    }
+    h.blocks = blocks;
+    h.nslots = blocks + h.grid[0] + 2;
+    *hdr = h;
+}
+
+// ---------------------------------------------------------------------------------------------
+// S2/S3: radius, rect
+// ---------------------------------------------------------------------------------------------
+template <int D>
+__device__ __forceinline__ float gaussian_radius(const float* __restrict__ cov, bool& degenerate)
+{
+    degenerate = false;
+    if (D == 1) return __fmul_rn(3.0f, __fsqrt_rn(cov[0]));
+    const float c0 = cov[0], c1 = cov[1], c2 = cov[2];
+    const float t = __fmul_rn(c1, c1);
+    const float det = __fmaf_rn(c0, c2, -t);
+    if (det == 0.0f) {
+        degenerate = true;
+        return 0.0f;
+    }
+    const float mid = __fmul_rn(0.5f, __fadd_rn(c0, c2));
+    const float disc = __fmaf_rn(mid, mid, -det);
+    const double root = __dsqrt_rn(fmax(1e-6, (double)disc));
+    const float lambda = __double2float_rn(__dadd_rn((double)mid, root));
+    return __fmul_rn(3.0f, __fsqrt_rn(lambda));
+}
+
+__device__ __forceinline__ void tile_rect(float p, float off, float r, int& lo, int& hi)
+{
+    const float c = __fsub_rn(p, off);
+    lo = (int)floorf(__fdiv_rn(__fsub_rn(c, r), PIGS_TILE_WIDTH));
+    hi = (int)ceilf(__fdiv_rn(__fadd_rn(c, r), PIGS_TILE_WIDTH));
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) count_kernel(int64_t P, const float* __restrict__ means,
+                                                    const float* __restrict__ cov, const pigs_header* __restrict__ hdr,
+                                                    float* __restrict__ radii, uint32_t* __restrict__ touched)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    constexpr int K = D * (D + 1) / 2;
+    bool degenerate;
+    const float r = gaussian_radius<D>(cov + g * K, degenerate);
+    uint32_t n = 0;
+    if (!degenerate) {
+        int lo, hi;
+        tile_rect(means[g * D], hdr->min_b[0], r, lo, hi);
+        n = (uint32_t)min(hi - lo, hdr->grid[0]);
+        if (D == 2) {
+            tile_rect(means[g * D + 1], hdr->min_b[1], r, lo, hi);
+            n = (uint32_t)min(hi - lo, hdr->grid[1]) * n;
+        }
+    }
+    radii[g] = n ? r : 0.0f;
+    touched[g] = n;
+}
+
+// total -> header.num_rendered
+__global__ void store_total(const uint32_t* __restrict__ offsets, int64_t P, pigs_header* hdr)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) hdr->num_rendered = (int64_t)offsets[P];
+}
+
+__device__ __forceinline__ int wrap_tile(int x, int g) { return x < 0 ? g + (x % g) : x % g; }
+
+// S4: one (tile, id) pair per covered tile, id-major (sampler_impl.cu:54-129)
+template <int D>
+__global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __restrict__ means,
+                                                   const float* __restrict__ radii, const uint32_t* __restrict__ offsets,
+                                                   const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
+                                                   uint32_t* __restrict__ vals)
+{
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= P) return;
+    const float r = radii[g];
+    if (!(r > 0.0f)) return;
+    uint32_t off = offsets[g];
+    const int g0 = hdr->grid[0], g1 = hdr->grid[1];
+    int lo0, hi0, lo1 = 0, hi1 = 1;
+    tile_rect(means[g * D], hdr->min_b[0], r, lo0, hi0);
+    if (hi0 - lo0 >= g0) {
+        lo0 = 0;
+        hi0 = g0;
+    }
+    if (D == 2) {
+        tile_rect(means[g * D + 1], hdr->min_b[1], r, lo1, hi1);
+        if (hi1 - lo1 >= g1) {
+            lo1 = 0;
+            hi1 = g1;
+        }
+    }
+    for (int y = lo1; y < hi1; y++) {
+        const int ty = D == 2 ? wrap_tile(y, g1) : 0;
+        for (int x = lo0; x < hi0; x++) {
+            const int tx = wrap_tile(x, g0);
+            keys[off] = (uint32_t)(ty * g0 + tx);
+            vals[off] = (uint32_t)g;
+            off++;
+        }
+    }
+}
+
+// S6: tile of each sample (sampler_impl.cu:155-189) + per-tile bounding box of the samples
+template <int D>
+__global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float* __restrict__ samples,
+                                                         const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
+                                                         uint32_t* __restrict__ vals, float* __restrict__ bbox /* [nslots][2*D] */)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int g0 = hdr->grid[0];
+    float x[D];
+    int t[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        x[d] = samples[i * D + d];
+        const int q = (int)__fdiv_rn(__fsub_rn(x[d], hdr->min_b[d]), PIGS_TILE_WIDTH);
+        t[d] = min(hdr->grid[d], max(0, q));
+    }
+    const uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+    keys[i] = tile;
+    vals[i] = (uint32_t)i;
+    // warp-aggregated bbox update: lanes sharing a tile reduce among themselves first
+    const uint32_t active = __activemask();
+    const uint32_t peers = __match_any_sync(active, tile);
+    float lo[D], hi[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) lo[d] = hi[d] = x[d] + 0.0f;
+    const int lane = threadIdx.x & 31;
+    // butterfly restricted to peers: iterate over set bits (at most 32, typically one or two groups)
+    if (peers == active) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const float a = __shfl_xor_sync(active, lo[d], o);
+                const float b = __shfl_xor_sync(active, hi[d], o);
+                // lanes outside `active` return undefined values: guard with the mask
+                if ((active >> (lane ^ o)) & 1u) {
+                    lo[d] = fminf(lo[d], a);
+                    hi[d] = fmaxf(hi[d], b);
+                }
+            }
+        if (lane == (__ffs(peers) - 1))
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                atomic_min_float(bbox + (size_t)tile * 2 * D + d, lo[d]);
+                atomic_max_float(bbox + (size_t)tile * 2 * D + D + d, hi[d]);
+            }
+    } else {
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            atomic_min_float(bbox + (size_t)tile * 2 * D + d, lo[d]);
+            atomic_max_float(bbox + (size_t)tile * 2 * D + D + d, hi[d]);
+        }
+    }
+}
+
+__global__ void bbox_init(float* bbox, int64_t nslots, int D)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nslots * 2 * D) return;
+    const int k = (int)(i % (2 * D));
+    bbox[i] = k < D ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+}
+
+// S7: identifyTileRanges (sampler_impl.cu:134-151) on the sorted 32-bit tile keys
+__global__ void __launch_bounds__(256) ranges_kernel(int64_t L, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges,
+                                                     int max_slot)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= L) return;
+    const uint32_t cur = keys[i];
+    if (i == 0) {
+        if ((int)cur <= max_slot) ranges[cur].x = 0;
+    } else {
+        const uint32_t prev = keys[i - 1];
+        if (cur != prev) {
+            if ((int)prev <= max_slot) ranges[prev].y = (uint32_t)i;
+            if ((int)cur <= max_slot) ranges[cur].x = (uint32_t)i;
+        }
+    }
+    if (i == L - 1 && (int)cur <= max_slot) ranges[cur].y = (uint32_t)L;
+}
+
+static int bit_length(uint32_t n)
+{
+    int b = 0;
+    while (n) {
+        b++;
+        n >>= 1;
+    }
+    return b;
+}
+
+}  // namespace pigs
+
+using namespace pigs;
+
+extern "C" {
+
+int pigs_sample_bounds(const float* samples, int64_t N, int D, float* d_minmax, void* stream)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(N > 0 && samples && d_minmax);
+    cudaStream_t st = (cudaStream_t)stream;
+    bounds_init<<<1, 32, 0, st>>>(d_minmax, D);
+    PIGS_LAUNCH_CHECK();
+    int64_t nb = (N + 255) / 256;
+    const int cap = num_sms() * 8;
+    if (nb > cap) nb = cap;
+    if (D == 2)
+        bounds_kernel<2><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax);
+    else
+        bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+size_t pigs_geom_workspace_bytes(int64_t P) { return GeomLayout(nullptr, P).bytes; }
+
+int pigs_preprocess_count(int64_t P, int D, int64_t N, const float* means, const float* covariances,
+                          const float* d_minmax, float* radii, void* geom_ws, void* stream)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(P > 0 && N > 0 && means && covariances && d_minmax && radii && geom_ws);
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomLayout g(geom_ws, P);
+    grid_kernel<<<1, 32, 0, st>>>(d_minmax, D, P, N, g_recip_mode, g.hdr);
+    PIGS_LAUNCH_CHECK();
+    const unsigned nb = (unsigned)((P + 255) / 256);
+    if (D == 2)
+        count_kernel<2><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched);
+    else
+        count_kernel<1><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched);
+    PIGS_LAUNCH_CHECK();
+    int rc = exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st);
+    if (rc) return rc;
+    store_total<<<1, 32, 0, st>>>(g.touched, P, g.hdr);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+size_t pigs_binning_bytes(int64_t num_rendered, int blocks)
+{
+    (void)blocks;
+    return BinLayout(nullptr, num_rendered).bytes;
+}
+size_t pigs_sample_binning_bytes(int64_t N, int blocks, int D) { return SampleBinLayout(nullptr, N, blocks, D).bytes; }
+size_t pigs_sort_workspace_bytes(int64_t num_rendered, int64_t N)
+{
+    const int64_t n = num_rendered > N ? num_rendered : N;
+    return sort_ws_bytes(n) + 2 * align_up((size_t)(n > 0 ? n : 1) * sizeof(uint32_t));
+}
+
+int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_rendered, const float* means,
+                        const float* samples, const float* radii, const void* geom_ws, void* binning_buffer,
+                        void* sample_binning_buffer, void* ranges, void* sample_ranges, void* sort_ws, void* stream)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(P > 0 && N > 0 && blocks > 0 && num_rendered >= 0);
+    PIGS_ARG(means && samples && radii && geom_ws && binning_buffer && sample_binning_buffer && ranges && sample_ranges &&
+             sort_ws);
+    cudaStream_t st = (cudaStream_t)stream;
+    GeomLayout g(const_cast<void*>(geom_ws), P);
+    BinLayout b(binning_buffer, num_rendered);
+    SampleBinLayout s(sample_binning_buffer, N, blocks, D);
+    const int64_t nmax = num_rendered > N ? num_rendered : N;
+    Carver c(sort_ws);
+    uint32_t* keys_u = c.take<uint32_t>((size_t)(nmax > 0 ? nmax : 1));
+    uint32_t* vals_u = c.take<uint32_t>((size_t)(nmax > 0 ? nmax : 1));
+    char* sws = c.take<char>(sort_ws_bytes(nmax));
+    // tile ids are <= blocks + grid[0] (alias slots) <= 2*blocks
+    const int bits = bit_length((uint32_t)(2 * blocks + 1));
+
+    PIGS_CHECK(cudaMemcpyAsync(b.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
+    PIGS_CHECK(cudaMemcpyAsync(s.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
+    PIGS_CHECK(cudaMemsetAsync(ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+    PIGS_CHECK(cudaMemsetAsync(sample_ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+
+    if (num_rendered > 0) {
+        const unsigned nb = (unsigned)((P + 255) / 256);
+        if (D == 2)
+            emit_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, g.touched, g.hdr, keys_u, vals_u);
+        else
+            emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.touched, g.hdr, keys_u, vals_u);
+        PIGS_LAUNCH_CHECK();
+        int rc = stable_sort_pairs_u32(keys_u, vals_u, b.tiles, b.list, num_rendered, bits, sws, st);
+        if (rc) return rc;
+        ranges_kernel<<<(unsigned)((num_rendered + 255) / 256), 256, 0, st>>>(num_rendered, b.tiles, (uint2*)ranges, blocks);
+        PIGS_LAUNCH_CHECK();
+    }
+    {
+        const int64_t nslots = 2 * (int64_t)blocks + 4;
+        bbox_init<<<(unsigned)((nslots * 2 * D + 255) / 256), 256, 0, st>>>(s.bbox, nslots, D);
+        PIGS_LAUNCH_CHECK();
+        const unsigned nb = (unsigned)((N + 255) / 256);
+        if (D == 2)
+            sample_key_kernel<2><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox);
+        else
+            sample_key_kernel<1><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox);
+        PIGS_LAUNCH_CHECK();
+        int rc = stable_sort_pairs_u32(keys_u, vals_u, s.tiles, s.list, N, bits, sws, st);
+        if (rc) return rc;
+        ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, s.tiles, (uint2*)sample_ranges, blocks);
+        PIGS_LAUNCH_CHECK();
+    }
+    return 0;
+}
+
+const uint32_t* pigs_point_list(const void* binning_buffer) { return BinLayout(const_cast<void*>(binning_buffer), 1).list; }
+const uint32_t* pigs_point_tiles(const void* binning_buffer, int64_t num_rendered)
+{
+    return BinLayout(const_cast<void*>(binning_buffer), num_rendered).tiles;
+}
+const uint32_t* pigs_sample_list(const void* sample_binning_buffer)
+{
+    return SampleBinLayout(const_cast<void*>(sample_binning_buffer), 1, 1, 1).list;
+}
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// common.cuh — shared device/host helpers for libpigs_b200 (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include "../../include/pigs_b200.h"
+
+#define PIGS_MAGIC 0x53474950u  // 'PIGS'
+#define PIGS_ALIGN 128
+static_assert(sizeof(pigs_header) == 256, "pigs_header must be 256 bytes");
+
+namespace pigs {
+
+extern thread_local char g_err[512];
+extern int64_t g_launches;
+extern int g_recip_mode;
+
+int set_error(int code, const char* what, const char* file, int line);
+
+#define PIGS_CHECK(expr)                                                           \
+    do {                                                                           \
+        cudaError_t _e = (expr);                                                   \
+        if (_e != cudaSuccess) return pigs::set_error((int)_e, #expr, __FILE__, __LINE__); \
+    } while (0)
+
+#define PIGS_LAUNCH_CHECK()                                                        \
+    do {                                                                           \
+        pigs::g_launches++;                                                        \
+        cudaError_t _e = cudaGetLastError();                                       \
+        if (_e != cudaSuccess) return pigs::set_error((int)_e, "kernel launch", __FILE__, __LINE__); \
+    } while (0)
+
+#define PIGS_ARG(cond)                                                             \
+    do {                                                                           \
+        if (!(cond)) return pigs::set_error(-1, "bad argument: " #cond, __FILE__, __LINE__); \
+    } while (0)
+
+static inline size_t align_up(size_t x, size_t a = PIGS_ALIGN) { return (x + a - 1) / a * a; }
+
+// carve typed sub-arrays out of a byte buffer (128-B aligned, like the reference's `obtain`,
+// cuda_sampler/sampler_impl.h:25-31, but with our own layouts)
+struct Carver {
+    char* p;
+    size_t used;
+    explicit Carver(void* base) : p((char*)base), used(0) {}
+    template <typename T>
+    T* take(size_t count)
+    {
+        used = align_up(used);
+        T* r = p ? (T*)(p + used) : nullptr;
+        used += count * sizeof(T);
+        return r;
+    }
+    size_t total() const { return align_up(used); }
+};
+
+int num_sms();
+
+// ---------------------------------------------------------------------------------------------
+// exclusive scan of u32 (three small kernels; n up to 2^31).  out may alias in.  out[n] = total if
+// write_total.  ws: scan_ws_bytes(n).
+size_t scan_ws_bytes(int64_t n);
+int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_total, void* ws, cudaStream_t st);
+
+// stable LSD radix sort of (key u32, value u32) pairs on the low `bits` bits of the key.
+// keys_in/vals_in are clobbered when more than one pass is needed (ping-pong); result lands in
+// keys_out/vals_out.  ws: sort_ws_bytes(n).
+size_t sort_ws_bytes(int64_t n);
+int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, int64_t n,
+                          int bits, void* ws, cudaStream_t st);
+
+// ---------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+__device__ __forceinline__ void atomic_min_float(float* addr, float v)
+{
+    // works on the raw bit pattern for any mix of signs as long as *addr was initialised to +inf
+    if (v >= 0.0f)
+        atomicMin((int*)addr, __float_as_int(v));
+    else
+        atomicMax((unsigned int*)addr, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_float(float* addr, float v)
+{
+    if (v >= 0.0f)
+        atomicMax((int*)addr, __float_as_int(v));
+    else
+        atomicMin((unsigned int*)addr, __float_as_uint(v));
+}
+__device__ __forceinline__ float ex2_approx(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+#endif
+
+}  // namespace pigs

@@ -1,0 +1,205 @@
+// eval_fwd.cu — fused value / gradient / Hessian (/ third-derivative) evaluation of the mixture at
+// every sample (replaces the four renderCUDA<F> instantiations of cuda_sampler/forward.cu:88-343).
+//
+// Design (B200, sm_100a):
+//   * persistent grid (2 CTAs x 256 threads per SM), work items pulled from a device-side list with
+//     one atomic per item: an item is (tile, chunk of 256*KS samples, slice of the tile's Gaussians).
+//     The reference runs ONE CTA per tile — 16 CTAs on a [-1,1]^2 domain.
+//   * each thread keeps KS samples and their accumulators in registers;
+//   * the tile's Gaussians stream through shared memory as packed float4 records (pack.cu),
+//     double-buffered; every record is read with broadcast LDS.128 and reused for KS pairs;
+//   * exp() is one MUFU.EX2 (ex2.approx.ftz) with -log2(e)/2 folded into the argument;
+//   * each output element is written once per item with a fire-and-forget RED.ADD (the reference does
+//     a global read-modify-write per pair per component, forward.cu:175,182,...).
+// The path is FP32-FMA-issue bound (no dense contraction => no tensor cores).
+#include "layouts.cuh"
+
+namespace pigs {
+
+constexpr int FWD_GB = 256;  // Gaussian records per shared-memory batch
+
+template <int D, int C, unsigned MASK, bool GENERAL>
+__global__ void __launch_bounds__(EV_THREADS, 2)
+    eval_fwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
+                    const float4* __restrict__ recs, const uint32_t* __restrict__ slist,
+                    const float* __restrict__ samples, int Ctot, int ch0, float* __restrict__ out_u,
+                    float* __restrict__ out_du, float* __restrict__ out_ddu, float* __restrict__ out_dddu)
+{
+    constexpr int NV = grec_v4(D, C);
+    constexpr int NA = nacc(D, MASK);
+    constexpr int KS = fwd_ks(D, C, MASK);
+    constexpr int SEG = GENERAL ? 1 : 0;
+    __shared__ float4 sm[2][FWD_GB * NV];
+    __shared__ WorkItem s_item;
+    __shared__ int s_valid;
+    const int tid = threadIdx.x;
+
+    for (;;) {
+        if (tid == 0) {
+            const uint32_t i = atomicAdd(&wh->counter[SEG], 1u);
+            s_valid = i < wh->items[SEG];
+            if (s_valid) s_item = decode_item(segs + (size_t)SEG * blocks, blocks, i, EV_THREADS * KS, true);
+        }
+        __syncthreads();
+        if (!s_valid) break;
+        const WorkItem it = s_item;
+
+        // ---- stationary operand: KS samples per thread, strided by the CTA width (coalesced) ----
+        float x[KS][D];
+        uint32_t sid[KS];
+        float acc[KS][C][NA];
+#pragma unroll
+        for (int s = 0; s < KS; s++) {
+            const uint32_t idx = tid + s * EV_THREADS;
+            sid[s] = idx < it.s_count ? slist[it.s_begin + idx] : 0xffffffffu;
+#pragma unroll
+            for (int d = 0; d < D; d++) x[s][d] = sid[s] != 0xffffffffu ? samples[(size_t)sid[s] * D + d] : 0.0f;
+#pragma unroll
+            for (int ch = 0; ch < C; ch++)
+#pragma unroll
+                for (int k = 0; k < NA; k++) acc[s][ch][k] = 0.0f;
+        }
+
+        // ---- streamed operand: Gaussian records through shared memory, double-buffered ----
+        const float4* __restrict__ src = recs + (size_t)it.g_begin * NV;
+        const uint32_t total_v4 = it.g_count * NV;
+        const int nbatch = (it.g_count + FWD_GB - 1) / FWD_GB;
+        float4 pre[NV];
+#pragma unroll
+        for (int k = 0; k < NV; k++) {
+            const uint32_t o = tid + k * EV_THREADS;
+            pre[k] = o < total_v4 ? src[o] : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int k = 0; k < NV; k++) sm[0][tid + k * EV_THREADS] = pre[k];
+        __syncthreads();
+
+        for (int b = 0; b < nbatch; b++) {
+            const int buf = b & 1;
+            if (b + 1 < nbatch) {
+#pragma unroll
+                for (int k = 0; k < NV; k++) {
+                    const uint32_t o = (uint32_t)(b + 1) * FWD_GB * NV + tid + k * EV_THREADS;
+                    pre[k] = o < total_v4 ? src[o] : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+            }
+            int cnt = min((int)FWD_GB, (int)it.g_count - b * FWD_GB);
+            cnt = (cnt + 1) & ~1;  // zero-padded records contribute exactly 0
+            const float4* __restrict__ batch = sm[buf];
+#pragma unroll 2
+            for (int j = 0; j < cnt; j++) {
+                const GaussReg<D, C> g = load_gauss<D, C>(batch + j * NV);
+#pragma unroll
+                for (int s = 0; s < KS; s++) {
+                    PairGeom<D, GENERAL> pg;
+                    pg.compute(g, x[s]);
+                    float f[NA];
+                    pair_factors<D, MASK>(pg.a, g.c, f);
+#pragma unroll
+                    for (int ch = 0; ch < C; ch++) {
+                        const float w = g.v[ch] * pg.alpha;
+#pragma unroll
+                        for (int k = 0; k < NA; k++) {
+                            if (k == 0 && (MASK & PIGS_FN_VALUE))
+                                acc[s][ch][0] += w;
+                            else
+                                acc[s][ch][k] = fmaf(w, f[k], acc[s][ch][k]);
+                        }
+                    }
+                }
+            }
+            if (b + 1 < nbatch) {
+#pragma unroll
+                for (int k = 0; k < NV; k++) sm[buf ^ 1][tid + k * EV_THREADS] = pre[k];
+            }
+            __syncthreads();
+        }
+
+        // ---- epilogue: one RED.ADD per output element per item ----
+#pragma unroll
+        for (int s = 0; s < KS; s++) {
+            if (sid[s] == 0xffffffffu) continue;
+            const size_t id = sid[s];
+#pragma unroll
+            for (int ch = 0; ch < C; ch++) {
+                const int c = ch0 + ch;
+                int k = 0;
+                if constexpr ((MASK & PIGS_FN_VALUE) != 0) {
+                    if (out_u) atomicAdd(out_u + id * Ctot + c, acc[s][ch][k]);
+                    k++;
+                }
+                if constexpr ((MASK & PIGS_FN_DERIV) != 0) {
+#pragma unroll
+                    for (int d = 0; d < D; d++) {
+                        if (out_du) atomicAdd(out_du + (id * D + d) * Ctot + c, acc[s][ch][k]);
+                        k++;
+                    }
+                }
+                if constexpr ((MASK & PIGS_FN_HESS) != 0) {
+                    if constexpr (D == 1) {
+                        if (out_ddu) atomicAdd(out_ddu + id * Ctot + c, acc[s][ch][k]);
+                        k++;
+                    } else {
+                        if (out_ddu) {
+                            float* o = out_ddu + id * 4 * Ctot + c;
+                            atomicAdd(o, acc[s][ch][k]);
+                            atomicAdd(o + Ctot, acc[s][ch][k + 1]);
+                            atomicAdd(o + 2 * Ctot, acc[s][ch][k + 1]);
+                            atomicAdd(o + 3 * Ctot, acc[s][ch][k + 2]);
+                        }
+                        k += 3;
+                    }
+                }
+                if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
+                    if constexpr (D == 1) {
+                        if (out_dddu) atomicAdd(out_dddu + id * Ctot + c, acc[s][ch][k]);
+                        k++;
+                    } else {
+                        if (out_dddu) {
+                            // flat [x|y]^3 index -> unique component (forward.cu:264-271)
+                            float* o = out_dddu + id * 8 * Ctot + c;
+                            atomicAdd(o, acc[s][ch][k]);
+                            atomicAdd(o + 1 * Ctot, acc[s][ch][k + 1]);
+                            atomicAdd(o + 2 * Ctot, acc[s][ch][k + 1]);
+                            atomicAdd(o + 3 * Ctot, acc[s][ch][k + 2]);
+                            atomicAdd(o + 4 * Ctot, acc[s][ch][k + 1]);
+                            atomicAdd(o + 5 * Ctot, acc[s][ch][k + 2]);
+                            atomicAdd(o + 6 * Ctot, acc[s][ch][k + 2]);
+                            atomicAdd(o + 7 * Ctot, acc[s][ch][k + 3]);
+                        }
+                        k += 4;
+                    }
+                }
+            }
+        }
+        __syncthreads();  // s_item / sm reuse
+    }
+}
+
+template <int D, int C, unsigned MASK>
+static int launch_fwd_t(const EvalCall& c, bool general, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
+{
+    const int grid = num_sms() * 2;
+    if (general)
+        eval_fwd_kernel<D, C, MASK, true><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist, c.samples,
+                                                                       c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+    else
+        eval_fwd_kernel<D, C, MASK, false><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist,
+                                                                        c.samples, c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int launch_forward(const EvalCall& c, int C, unsigned mask, bool general, int ch0, const EvalWs& ws, FwdOut out,
+                   cudaStream_t st)
+{
+#define FW(D_, C_, M_) \
+    if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, general, ch0, ws, out, st);
+#define FW_ALL(D_, C_) FW(D_, C_, 1u) FW(D_, C_, 2u) FW(D_, C_, 4u) FW(D_, C_, 7u) FW(D_, C_, 8u)
+    FW_ALL(2, 1) FW_ALL(2, 2) FW_ALL(1, 1) FW_ALL(1, 2)
+#undef FW_ALL
+#undef FW
+    return set_error(-1, "unsupported (D, C, mask)", __FILE__, __LINE__);
+}
+
+}  // namespace pigs

@@ -1,0 +1,274 @@
+// pack.cu — per-call staging for the evaluation kernels:
+//   * classify every (tile, Gaussian) list entry as FAST or GENERAL,
+//   * stable-partition each tile's list into [fast | general] and write the Gaussian parameters as
+//     packed float4 records in that order (what the evaluation kernels stream through shared memory),
+//   * gather the sorted samples' coordinates and upstream gradients into float4 records (backward),
+//   * build the device-side work lists.
+// All HBM-bound, a few bytes per list entry; no host synchronisation.
+#include "eval_common.cuh"
+#include "layouts.cuh"
+
+namespace pigs {
+
+// FAST  <=>  conic safely positive definite  AND  for every sample of the tile |mu - x| <= 1 in every
+// dimension (so the reference's torus wrap, forward.cu:149-157, is the identity and power <= 0).
+// fl(mu - x) is monotone in x, so testing the two ends of the tile's sample bounding box is exact.
+template <int D>
+__global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __restrict__ list,
+                                                   const uint32_t* __restrict__ tiles, const float* __restrict__ means,
+                                                   const float* __restrict__ conics, const float* __restrict__ bbox,
+                                                   uint32_t* __restrict__ flags)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= R) return;
+    const uint32_t id = list[e], t = tiles[e];
+    bool fast;
+    if constexpr (D == 1) {
+        fast = conics[id] > 0.0f;
+    } else {
+        const float c0 = conics[3 * (size_t)id], c1 = conics[3 * (size_t)id + 1], c2 = conics[3 * (size_t)id + 2];
+        const float cc = c0 * c2;
+        fast = (c0 > 0.0f) && (c2 > 0.0f) && (cc - c1 * c1 >= 1e-4f * cc) && (cc < 3.0e38f);
+    }
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        const float m = means[(size_t)id * D + d];
+        const float xlo = bbox[(size_t)t * 2 * D + d], xhi = bbox[(size_t)t * 2 * D + D + d];
+        const float Xa = m - xhi, Xb = m - xlo;
+        fast = fast && (Xa >= -1.0f) && (Xb <= 1.0f);
+    }
+    flags[e] = fast ? 0u : 1u;
+}
+
+// gen_prefix = exclusive scan of flags (with total at [R]).  Writes records in partitioned order.
+template <int D, int C>
+__global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32_t* __restrict__ list,
+                                                         const uint32_t* __restrict__ tiles,
+                                                         const uint32_t* __restrict__ gen_prefix,
+                                                         const uint2* __restrict__ ranges, int blocks,
+                                                         const float* __restrict__ means, const float* __restrict__ values,
+                                                         const float* __restrict__ conics, int Ctot, int ch0,
+                                                         float4* __restrict__ recs, uint32_t* __restrict__ rec_id,
+                                                         uint32_t* __restrict__ nfast)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= R) return;
+    const uint32_t id = list[e], t = tiles[e];
+    if ((int)t >= blocks) return;  // alias slots are never evaluated (the reference launches `blocks` CTAs)
+    const uint2 r = ranges[t];
+    const uint32_t gen_before = gen_prefix[e] - gen_prefix[r.x];
+    const uint32_t gen_total = gen_prefix[r.y] - gen_prefix[r.x];
+    const uint32_t nf = (r.y - r.x) - gen_total;
+    const bool general = gen_prefix[e + 1] != gen_prefix[e];
+    const uint32_t pos = general ? r.x + nf + gen_before : r.x + (uint32_t)(e - r.x) - gen_before;
+    if (e == r.x) nfast[t] = nf;
+    constexpr int NV = grec_v4(D, C);
+    float f[NV * 4];
+#pragma unroll
+    for (int i = 0; i < NV * 4; i++) f[i] = 0.0f;
+#pragma unroll
+    for (int d = 0; d < D; d++) f[d] = means[(size_t)id * D + d];
+#pragma unroll
+    for (int k = 0; k < nconic(D); k++) f[D + k] = conics[(size_t)id * nconic(D) + k];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) f[D + nconic(D) + ch] = values[(size_t)id * Ctot + ch0 + ch];
+#pragma unroll
+    for (int i = 0; i < NV; i++) recs[(size_t)pos * NV + i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
+    rec_id[pos] = id;
+}
+
+// sample records for the backward pass: [x(D)] then per channel the upstream weights of the unique
+// components, symmetric duplicates summed (backward.cu:244-247,269: dL_dGxy + dL_dGyx, etc.)
+template <int D, int C, unsigned MASK>
+__global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint32_t* __restrict__ slist,
+                                                           const float* __restrict__ samples,
+                                                           const float* __restrict__ gV, const float* __restrict__ gD,
+                                                           const float* __restrict__ gH, const float* __restrict__ gT,
+                                                           int Ctot, int ch0, float4* __restrict__ srecs)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const size_t sid = slist[i];
+    constexpr int SV = srec_v4(D, C, MASK);
+    constexpr int NA = nacc(D, MASK);
+    float f[SV * 4];
+#pragma unroll
+    for (int k = 0; k < SV * 4; k++) f[k] = 0.0f;
+#pragma unroll
+    for (int d = 0; d < D; d++) f[d] = samples[sid * D + d];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) {
+        int k = D + ch * NA;
+        const int c = ch0 + ch;
+        if constexpr ((MASK & PIGS_FN_VALUE) != 0) {
+            f[k++] = gV ? gV[sid * Ctot + c] : 0.0f;
+        }
+        if constexpr ((MASK & PIGS_FN_DERIV) != 0) {
+#pragma unroll
+            for (int d = 0; d < D; d++) f[k++] = gD ? gD[(sid * D + d) * Ctot + c] : 0.0f;
+        }
+        if constexpr ((MASK & PIGS_FN_HESS) != 0) {
+            if constexpr (D == 1) {
+                f[k++] = gH ? gH[sid * Ctot + c] : 0.0f;
+            } else {
+                const float* g = gH + sid * 4 * Ctot + c;
+                f[k++] = gH ? g[0] : 0.0f;
+                f[k++] = gH ? g[Ctot] + g[2 * Ctot] : 0.0f;
+                f[k++] = gH ? g[3 * Ctot] : 0.0f;
+            }
+        }
+        if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
+            if constexpr (D == 1) {
+                f[k++] = gT ? gT[sid * Ctot + c] : 0.0f;
+            } else {
+                const float* g = gT + sid * 8 * Ctot + c;
+                f[k++] = gT ? g[0] : 0.0f;
+                f[k++] = gT ? g[Ctot] + g[2 * Ctot] + g[4 * Ctot] : 0.0f;
+                f[k++] = gT ? g[3 * Ctot] + g[5 * Ctot] + g[6 * Ctot] : 0.0f;
+                f[k++] = gT ? g[7 * Ctot] : 0.0f;
+            }
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < SV; k++) srecs[(size_t)i * SV + k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
+}
+
+// One CTA.  For every tile: the fast and general segments and how many work items each yields.
+//   forward : stationary = samples in chunks of `chunk`, streamed = Gaussians split `split_hint` ways
+//   backward: stationary = Gaussians in chunks of `chunk`, streamed = samples split `split_hint` ways
+__global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* __restrict__ ranges,
+                                                       const uint2* __restrict__ sample_ranges,
+                                                       const uint32_t* __restrict__ nfast, uint32_t chunk,
+                                                       uint32_t split_hint, uint32_t min_stream, int stream_is_gauss,
+                                                       TileSeg* __restrict__ segs /* [2][blocks] */, WorkHeader* __restrict__ wh)
+{
+    __shared__ uint32_t s_scan[256];
+    __shared__ uint32_t s_carry[2];
+    __shared__ unsigned long long s_pairs;
+    if (threadIdx.x == 0) {
+        s_carry[0] = s_carry[1] = 0;
+        s_pairs = 0ull;
+    }
+    __syncthreads();
+    unsigned long long my_pairs = 0;
+    for (int base = 0; base < blocks; base += 256) {
+        const int t = base + threadIdx.x;
+        TileSeg sg[2];
+        uint32_t items[2] = {0, 0};
+        if (t < blocks) {
+            const uint2 gr = ranges[t], sr = sample_ranges[t];
+            const uint32_t G = gr.y - gr.x, S = sr.y - sr.x;
+            const uint32_t nf = (G > 0) ? nfast[t] : 0;
+            my_pairs += (unsigned long long)G * S;
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+                sg[k].g_begin = k == 0 ? gr.x : gr.x + nf;
+                sg[k].g_count = k == 0 ? nf : G - nf;
+                sg[k].s_begin = sr.x;
+                sg[k].s_count = S;
+                const uint32_t stat_n = stream_is_gauss ? sg[k].s_count : sg[k].g_count;
+                const uint32_t strm_n = stream_is_gauss ? sg[k].g_count : sg[k].s_count;
+                uint32_t split = 1;
+                if (stat_n > 0 && strm_n > 0) {
+                    split = min(split_hint, (strm_n + min_stream - 1) / min_stream);
+                    if (split < 1) split = 1;
+                    items[k] = ((stat_n + chunk - 1) / chunk) * split;
+                }
+                sg[k].split = split;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            // block exclusive scan of items[k]
+            s_scan[threadIdx.x] = items[k];
+            __syncthreads();
+            for (int o = 1; o < 256; o <<= 1) {
+                uint32_t v = threadIdx.x >= o ? s_scan[threadIdx.x - o] : 0;
+                __syncthreads();
+                s_scan[threadIdx.x] += v;
+                __syncthreads();
+            }
+            const uint32_t incl = s_scan[threadIdx.x];
+            const uint32_t carry = s_carry[k];
+            if (t < blocks) {
+                sg[k].item_begin = carry + incl - items[k];
+                segs[(size_t)k * blocks + t] = sg[k];
+            }
+            __syncthreads();
+            if (threadIdx.x == 255) s_carry[k] = carry + incl;
+            __syncthreads();
+        }
+    }
+    atomicAdd(&s_pairs, my_pairs);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        wh->counter[0] = wh->counter[1] = 0;
+        wh->items[0] = s_carry[0];
+        wh->items[1] = s_carry[1];
+        wh->pairs = s_pairs;
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side staging entry points (called from api.cu)
+// ---------------------------------------------------------------------------------------------
+int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStream_t st)
+{
+    const int64_t R = c.R;
+    const unsigned nb = (unsigned)((R + 255) / 256);
+    if (c.D == 2)
+        flag_kernel<2><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags);
+    else
+        flag_kernel<1><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags);
+    PIGS_LAUNCH_CHECK();
+    int rc = exclusive_scan_u32(ws.flags, ws.flags, R, true, ws.scan_ws, st);
+    if (rc) return rc;
+    PIGS_CHECK(cudaMemsetAsync(ws.nfast, 0, (size_t)(c.blocks + 1) * sizeof(uint32_t), st));
+#define PACK(D_, C_)                                                                                                  \
+    pack_gauss_kernel<D_, C_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, c.ranges, c.blocks, c.means, c.values, \
+                                                  c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
+    if (c.D == 2 && C == 1)
+        PACK(2, 1);
+    else if (c.D == 2 && C == 2)
+        PACK(2, 2);
+    else if (c.D == 1 && C == 1)
+        PACK(1, 1);
+    else
+        PACK(1, 2);
+#undef PACK
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int stage_worklist(const EvalCall& c, const EvalWs& ws, uint32_t chunk, uint32_t split_hint, uint32_t min_stream,
+                   bool stream_is_gauss, cudaStream_t st)
+{
+    worklist_kernel<<<1, 256, 0, st>>>(c.blocks, c.ranges, c.sample_ranges, ws.nfast, chunk, split_hint, min_stream,
+                                       stream_is_gauss ? 1 : 0, ws.segs, ws.wh);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+template <int D, int C, unsigned MASK>
+static int stage_samples_t(const EvalCall& c, int ch0, const float* gV, const float* gD, const float* gH, const float* gT,
+                           const EvalWs& ws, cudaStream_t st)
+{
+    pack_samples_kernel<D, C, MASK><<<(unsigned)((c.N + 255) / 256), 256, 0, st>>>(c.N, c.slist, c.samples, gV, gD, gH, gT,
+                                                                                    c.C, ch0, ws.srecs);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float* gV, const float* gD, const float* gH,
+                  const float* gT, const EvalWs& ws, cudaStream_t st)
+{
+#define SS(D_, C_, M_) \
+    if (c.D == D_ && C == C_ && mask == M_) return stage_samples_t<D_, C_, M_>(c, ch0, gV, gD, gH, gT, ws, st);
+#define SS_ALL(D_, C_) SS(D_, C_, 1u) SS(D_, C_, 2u) SS(D_, C_, 4u) SS(D_, C_, 7u) SS(D_, C_, 8u)
+    SS_ALL(2, 1) SS_ALL(2, 2) SS_ALL(1, 1) SS_ALL(1, 2)
+#undef SS_ALL
+#undef SS
+    return set_error(-1, "unsupported (D, C, mask)", __FILE__, __LINE__);
+}
+
+}  // namespace pigs

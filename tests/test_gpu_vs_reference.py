@@ -1,0 +1,92 @@
+"""GPU parity against the LIVE unmodified reference CUDA extension (oracle/_ref/_C.so, built here by
+oracle/build_ref.sh and shipped to the GPU box with the snapshot).  Bit-exact binning, 1e-5 norm-wise values and
+gradients.  Skipped when the prebuilt reference is absent."""
+import numpy as np
+import pytest
+
+from tests import refcuda
+from tests.fixtures import RECIPES
+from tests.helpers import TOL, rel_err, to_dev, upstream
+
+pytestmark = pytest.mark.gpu
+NAMES = list(RECIPES)
+
+
+def _both(name):
+    import torch
+    from pigs_b200 import GaussianSampler
+    if not refcuda.available():
+        pytest.skip("oracle/_ref/_C.so not built")
+    rec = RECIPES[name]()
+    d = to_dev(rec)
+    ref = refcuda.RefSampler(False)
+    ref.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    ours = GaussianSampler(False, fused=False)
+    ours.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    return rec, d, ref, ours, torch
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_binning_bit_exact_vs_reference(name):
+    from pigs_b200 import _C
+    rec, d, ref, ours, torch = _both(name)
+    N = rec["samples"].shape[0]
+    assert ours.num_rendered == ref.num_rendered
+    assert torch.equal(ours.radii.view(torch.int32), ref.radii.view(torch.int32))
+    assert torch.equal(ours.ranges, ref.ranges)
+    assert torch.equal(ours.sample_ranges, ref.sample_ranges)
+    pl, pt, sl = _C.point_lists(ours.num_rendered, ours.binning_buffer, ours.sample_binning_buffer, N)
+    assert torch.equal(pl, ref.point_list())
+    assert torch.equal(sl, ref.sample_point_list())
+
+
+@pytest.mark.parametrize("name", NAMES)
+@pytest.mark.parametrize("fn", [0, 1, 2, 3])
+def test_forward_backward_vs_reference(name, fn):
+    rec, d, ref, ours, torch = _both(name)
+    want = ref.forward(fn)
+    got = ours.sample_fused(1 << fn)[0]
+    assert got.shape == want.shape
+    assert rel_err(got.cpu().numpy(), want.cpu().numpy()) <= TOL
+    g = torch.from_numpy(upstream(rec, fn)).cuda()
+    wm, wv, wc = ref.backward(fn, g)
+    from pigs_b200 import _C
+    grads = [None] * 4
+    grads[fn] = g
+    nr, bb, sbb, rg, srg = ours._sample_state
+    gm, gv, gc = _C.sample_backward(1 << fn, d["means"], d["values"], d["conics"], d["samples"], nr, grads, bb, sbb, rg,
+                                    srg, False)
+    for a, b, nm in ((gm, wm, "means"), (gv, wv, "values"), (gc, wc, "conics")):
+        assert rel_err(a.cpu().numpy(), b.cpu().numpy()) <= TOL, nm
+
+
+def test_tile_grid_arithmetic_matches_torch_cuda():
+    """sample_points.cu:73 evaluates (max-min+1e-6f)/0.51f with torch CUDA ops; find spans where IEEE division and
+    multiply-by-reciprocal disagree after ceil and check the library follows torch."""
+    import torch
+    from pigs_b200 import GaussianSampler
+    if not torch.cuda.is_available():
+        pytest.skip("no cuda")
+    inv = np.float32(1.0) / np.float32(0.51)
+    cands = []
+    for k in range(1, 4000):
+        base = np.float32(0.51) * np.float32(k)
+        for off in range(-3, 4):
+            span = np.nextafter(base, np.float32(np.inf if off > 0 else -np.inf), dtype=np.float32) if off else base
+            for _ in range(abs(off) - 1):
+                span = np.nextafter(span, np.float32(np.inf if off > 0 else -np.inf), dtype=np.float32)
+            x = np.float32(span + np.float32(1e-6))
+            if np.ceil(np.float32(x * inv)) != np.ceil(np.float32(x / np.float32(0.51))):
+                cands.append(float(span))
+    cands = cands[:20]
+    if not cands:
+        pytest.skip("no discriminating span found")
+    for span in cands:
+        samples = torch.tensor([[0.0], [span]], device="cuda", dtype=torch.float32)
+        mn, mx = samples.min(0)[0], samples.max(0)[0]
+        want = int(torch.ceil((mx - mn + 1e-6) / 0.51).to(torch.int32).prod().item())
+        s = GaussianSampler(False)
+        means = torch.tensor([[span / 2]], device="cuda")
+        cov = torch.tensor([[1e-4]], device="cuda")
+        s.preprocess(means, torch.ones(1, 1, device="cuda"), cov, 1.0 / cov, samples)
+        assert s.ranges.numel() // 8 - 1 == want, span
