@@ -155,7 +155,7 @@ def test_degenerate_gaussians_are_dropped(torch_mod):
     """det == 0 covariance -> radius 0, no tile keys (forward.cu:55-57); NaN-free outputs."""
     torch = torch_mod
     rec = RECIPES["derivatives"]()
-    rec["covariances"][3] = [0.04, 0.04, 0.04]
+    rec["covariances"][3] = [0.25, 0.25, 0.25]  # exact products: det == 0
     rec["covariances"][7] = 0.0
     st = oracle_state(rec)
     s, d = _sampler(rec)

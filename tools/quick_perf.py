@@ -70,6 +70,10 @@ def ref_perf(P, N):
     if not refcuda.available():
         print("reference CUDA not available")
         return
+    # the reference allocates with device-side new[] in every thread (forward.cu:63-64, sampler_impl.cu:166):
+    # raise the device malloc heap or it returns NULL beyond ~1e5 resident threads
+    rt = ctypes.CDLL("libcudart.so.12")
+    print("cudaDeviceSetLimit(MallocHeapSize, 2 GiB) ->", rt.cudaDeviceSetLimit(2, ctypes.c_size_t(2 << 30)))
     rec = synthetic(P, N, seed=0)
     d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
     r = refcuda.RefSampler(False)
@@ -85,8 +89,10 @@ def ref_perf(P, N):
 
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0))
+    if "--ref" in sys.argv:
+        ref_perf(20_000, 200_000)
+        sys.exit(0)
     micro()
     perf(100_000, 1_000_000, "C2")
     if "--big" in sys.argv:
         perf(1_000_000, 4_000_000, "C3")
-    ref_perf(20_000, 200_000)
