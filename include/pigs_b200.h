@@ -110,6 +110,13 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
  * of the last forward/backward work list (device scalar, int64) */
 int64_t pigs_launch_count(void);
 
+/* Optional device timing of the evaluation kernels (bench.py roofline).  While on, the forward /
+ * backward evaluation launches of every pigs_sample_forward / pigs_sample_backward call are
+ * bracketed by cudaEvents on the call's stream.  pigs_kernel_timing_read(which = 0 forward |
+ * 1 backward) synchronises on those events, returns their summed duration and count and clears them. */
+void pigs_set_kernel_timing(int on);
+int pigs_kernel_timing_read(int which, float *ms_sum, int *launches);
+
 /* ---- neighbour lists + aggregation (aggregate_neighbors.cu:18-475) ------------------------------ */
 size_t pigs_neighbor_workspace_bytes(int64_t P, int D);
 /* stage A: per-Gaussian neighbour counts (findCollisions semantics) -> counts int64[P] */

@@ -53,6 +53,8 @@ SIGNATURES = {
     "pigs_sample_forward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 13 + [c_size_t, c_void_p]),
     "pigs_sample_backward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 16 + [c_size_t, c_void_p]),
     "pigs_launch_count": (c_int64, []),
+    "pigs_set_kernel_timing": (None, [c_int]),
+    "pigs_kernel_timing_read": (c_int, [c_int, c_void_p, c_void_p]),
     "pigs_neighbor_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_neighbors_count": (c_int, [c_int64, c_int] + [c_void_p] * 5),
     "pigs_neighbors_fill": (c_int, [c_int64, c_int] + [c_void_p] * 10),

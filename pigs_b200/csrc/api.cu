@@ -3,9 +3,52 @@
 // compiled (mask, channel-group) kernels, stage, launch.  No host synchronisation anywhere.
 #include "layouts.cuh"
 
+#include <vector>
+
 using namespace pigs;
 
 namespace {
+
+// ---- optional device timing of the evaluation kernels (bench.py roofline) ------------------------
+struct TimedLaunch {
+    cudaEvent_t a, b;
+    int which;  // 0 forward, 1 backward
+};
+bool g_timing = false;
+std::vector<TimedLaunch> g_timed;
+std::vector<cudaEvent_t> g_event_pool;
+
+cudaEvent_t take_event()
+{
+    cudaEvent_t e = nullptr;
+    if (!g_event_pool.empty()) {
+        e = g_event_pool.back();
+        g_event_pool.pop_back();
+    } else {
+        cudaEventCreate(&e);
+    }
+    return e;
+}
+
+struct ScopedKernelTimer {
+    bool on;
+    TimedLaunch t;
+    cudaStream_t st;
+    ScopedKernelTimer(int which, cudaStream_t s) : on(g_timing), st(s)
+    {
+        if (!on) return;
+        t.a = take_event();
+        t.b = take_event();
+        t.which = which;
+        cudaEventRecord(t.a, st);
+    }
+    ~ScopedKernelTimer()
+    {
+        if (!on) return;
+        cudaEventRecord(t.b, st);
+        g_timed.push_back(t);
+    }
+};
 
 // function masks with a dedicated kernel; anything else inside {V,D,H} runs the fused 7-kernel with
 // the unwanted outputs/upstreams left NULL.
@@ -75,6 +118,36 @@ const char* pigs_last_error(void) { return g_err; }
 void pigs_set_grid_recip_mode(int recip) { g_recip_mode = recip ? 1 : 0; }
 int64_t pigs_launch_count(void) { return g_launches; }
 
+void pigs_set_kernel_timing(int on)
+{
+    g_timing = on != 0;
+}
+
+int pigs_kernel_timing_read(int which, float* ms_sum, int* launches)
+{
+    PIGS_ARG(ms_sum && launches);
+    float sum = 0.f;
+    int n = 0;
+    std::vector<TimedLaunch> keep;
+    for (const TimedLaunch& t : g_timed) {
+        if (t.which != which) {
+            keep.push_back(t);
+            continue;
+        }
+        PIGS_CHECK(cudaEventSynchronize(t.b));
+        float ms = 0.f;
+        PIGS_CHECK(cudaEventElapsedTime(&ms, t.a, t.b));
+        sum += ms;
+        n++;
+        g_event_pool.push_back(t.a);
+        g_event_pool.push_back(t.b);
+    }
+    g_timed.swap(keep);
+    *ms_sum = sum;
+    *launches = n;
+    return 0;
+}
+
 size_t pigs_eval_workspace_bytes(int64_t num_rendered, int64_t N, int blocks, int D, int C, unsigned fn_mask)
 {
     (void)fn_mask;
@@ -118,10 +191,13 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
             o.du = (fn_mask & PIGS_FN_DERIV) ? out_du : nullptr;
             o.ddu = (fn_mask & PIGS_FN_HESS) ? out_ddu : nullptr;
             o.dddu = (fn_mask & PIGS_FN_THIRD) ? out_dddu : nullptr;
-            rc = launch_forward(c, cw, m, false, ch0, ws, o, st);
-            if (rc) return rc;
-            rc = launch_forward(c, cw, m, true, ch0, ws, o, st);
-            if (rc) return rc;
+            {
+                ScopedKernelTimer tm(0, st);
+                rc = launch_forward(c, cw, m, false, ch0, ws, o, st);
+                if (rc) return rc;
+                rc = launch_forward(c, cw, m, true, ch0, ws, o, st);
+                if (rc) return rc;
+            }
         }
     }
     return 0;
@@ -166,10 +242,13 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
             rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks), 128, false, st);
             if (rc) return rc;
             BwdOut o{dL_dmeans, dL_dvalues, dL_dconics};
-            rc = launch_backward(c, cw, m, false, ch0, ws, o, st);
-            if (rc) return rc;
-            rc = launch_backward(c, cw, m, true, ch0, ws, o, st);
-            if (rc) return rc;
+            {
+                ScopedKernelTimer tm(1, st);
+                rc = launch_backward(c, cw, m, false, ch0, ws, o, st);
+                if (rc) return rc;
+                rc = launch_backward(c, cw, m, true, ch0, ws, o, st);
+                if (rc) return rc;
+            }
         }
     }
     return 0;

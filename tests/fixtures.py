@@ -143,3 +143,45 @@ RECIPES = {
     "wide": wide,
     "scaled": lambda: synthetic(800, 6000, seed=7, scale=2.5),
 }
+
+
+# ---- neighbour aggregation (aggregate_neighbors.cu) -------------------------------------------------
+def agg_params(P, L, K, E, D, seed=0, dt_rows=None):
+    """test_neighbor_aggregation.py:69-80 / model_pn.py:199-230: features, transform [L,L], queries/keys [P,K],
+    frequencies [(E-1)//D//2] = 10 N(0,1), distance_transform [dt_rows or L, 2E] (only row 0 is read by the kernel,
+    aggregate_neighbors.cu:185-193)."""
+    rng = np.random.default_rng(seed)
+    f = lambda *s: rng.uniform(-1, 1, s).astype(np.float32)
+    return dict(features=f(P, L), transform=f(L, L), queries=f(P, K), keys=f(P, K),
+                frequencies=(rng.normal(size=(E - 1) // D // 2) * 10).astype(np.float32),
+                distance_transform=f(dt_rows or L, 2 * E))
+
+
+def agg_grid5():
+    """test_neighbor_aggregation.py:15-27,69-80 (gradcheck branch): 5x5 grid, sigma^2 = e^-1.5, L=2, K=4, E=21."""
+    t = np.linspace(-1, 1, 5)
+    gx, gy = np.meshgrid(t, t, indexing="ij")
+    means = np.stack([gx, gy], -1).reshape(25, 2)
+    cov, con = covariances_from(np.full((25, 2), np.exp(-1.5)), np.zeros(25))
+    values = np.zeros((25, 1))
+    values[:5] = 1.0
+    rec = _pack(means, values, cov, con, _grid_samples(64))
+    rec.update(agg_params(25, 2, 4, 21, 2, seed=11))
+    return rec
+
+
+def agg_model(P=700, seed=12, D=2, **kw):
+    """model_pn.py call pattern (samples = means, model_pn.py:648): L = K = 16, E = 25, nF = 6 (1-D: 12)."""
+    rec = synthetic(P, 64, seed=seed, D=D, **kw)
+    rec["samples"] = rec["means"].copy()
+    rec.update(agg_params(P, 16, 16, 25, D, seed=seed + 100))
+    return rec
+
+
+AGG_RECIPES = {
+    "agg_grid5": agg_grid5,
+    "agg_model": agg_model,
+    "agg_model_edge": lambda: agg_model(900, seed=13, edge_fraction=0.15, anisotropy=3.0),
+    "agg_model_1d": lambda: agg_model(300, seed=14, D=1),
+    "agg_scaled": lambda: agg_model(400, seed=15, scale=2.5),
+}

@@ -35,3 +35,14 @@ def upstream(rec, fn, seed=0):
 def ranges_np(t, blocks):
     """uint8 tensor (blocks*8+8 bytes) -> [(blocks+1), 2] uint32"""
     return t.cpu().numpy().view(np.uint32).reshape(blocks + 1, 2)
+
+
+def agg_upstream(rec, seed=0):
+    """seeded N(0,1) upstream gradient of aggregate_neighbors' output [P, L]"""
+    rng = np.random.default_rng(2000 + seed)
+    return rng.normal(size=rec["features"].shape).astype(np.float32)
+
+
+AGG_KEYS = ("features", "transform", "queries", "keys", "frequencies", "distance_transform")
+# shared-parameter gradients vs the reference CUDA golden: bounded by the reference's own fp32-atomic noise
+AGG_SHARED_TOL = 1e-4
