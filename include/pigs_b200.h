@@ -149,6 +149,8 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
  * and returns the number of lane-ops executed. Timing is done by the caller with CUDA events. */
 int64_t pigs_microbench_ffma(int ctas, int iters, float *sink, void *stream);
 int64_t pigs_microbench_ex2(int ctas, int iters, float *sink, void *stream);
+/* packed fma.rn.f32x2 (FFMA2) loop; mix != 0 adds 2 MUFU.EX2 per 32 lane-FMAs.  Returns lane-FMAs executed. */
+int64_t pigs_microbench_ffma2(int ctas, int iters, int mix, float *sink, void *stream);
 
 #ifdef __cplusplus
 }

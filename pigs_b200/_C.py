@@ -155,9 +155,12 @@ def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads
     samples = _f32c(samples, "samples")
     P, D, N, C = _dims(means, values, samples)
     dev = means.device
-    dm = torch.zeros((P, D), dtype=torch.float32, device=dev)
-    dv = torch.zeros((P, C), dtype=torch.float32, device=dev)
-    dc = torch.zeros((P, D * (D + 1) // 2), dtype=torch.float32, device=dev)
+    # one flat buffer, three contiguous views: a multi-GPU caller all-reduces `flat` with one collective
+    K = D * (D + 1) // 2
+    flat = torch.zeros(P * (D + C + K), dtype=torch.float32, device=dev)
+    dm = flat[:P * D].view(P, D)
+    dv = flat[P * D:P * (D + C)].view(P, C)
+    dc = flat[P * (D + C):].view(P, K)
     g = [None if x is None else _f32c(x, "dL_dout") for x in grads]
     if P != 0 and N != 0:
         blocks = _blocks_of(ranges)
@@ -170,6 +173,14 @@ def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads
         if debug:
             torch.cuda.synchronize()
     return dm, dv, dc
+
+
+def packed_base(dm):
+    """The flat [P*(D+C+K)] gradient buffer that sample_backward's three results are views of."""
+    base = dm._base
+    if base is None:
+        raise RuntimeError("not a view returned by sample_backward")
+    return base
 
 
 def _single(bit):

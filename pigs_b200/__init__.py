@@ -60,12 +60,13 @@ class _SampleFused(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, mask, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
-                sample_ranges, debug):
+                sample_ranges, debug, reduce=None):
         args = (means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
                 sample_ranges, debug)
         outs = call_debug(lambda *a: _C.sample_forward(mask, *a), debug, "fw%d" % mask, *args)
         ctx.mask = mask
         ctx.args = args
+        ctx.reduce = reduce  # sharded sampler: callable applied to the packed gradient buffer (NCCL all-reduce)
         return tuple(o for o in outs if o is not None)
 
     @staticmethod
@@ -81,10 +82,12 @@ class _SampleFused(torch.autograd.Function):
                     grads[k] = g
                     live |= 1 << k
         if live == 0:
-            return (None,) * 11
+            return (None,) * 12
         dm, dv, dc = call_debug(lambda *a: _C.sample_backward(live, *a), debug, "bw%d" % mask, means, values, conics,
                                 samples, num_rendered, grads, bb, sbb, ranges, sample_ranges, debug)
-        return (None, dm, dv, dc, None, None, None, None, None, None, None)
+        if ctx.reduce is not None:
+            ctx.reduce(_C.packed_base(dm))  # dm, dv, dc are views of one flat buffer: one collective
+        return (None, dm, dv, dc, None, None, None, None, None, None, None, None)
 
 
 def _sample_mask(mask, *args):
@@ -182,6 +185,11 @@ class GaussianSampler:
 
     def _args(self):
         nr, bb, sbb, rg, srg = self._sample_state
+        reduce = getattr(self, "_reduce", None)
+        if reduce is not None:
+            group = self.group
+            return (self.means, self.values, self.conics, self.samples, nr, bb, sbb, rg, srg, self.debug,
+                    lambda flat: reduce(flat, group))
         return (self.means, self.values, self.conics, self.samples, nr, bb, sbb, rg, srg, self.debug)
 
     def sample_fused(self, mask):

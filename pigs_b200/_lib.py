@@ -63,6 +63,7 @@ SIGNATURES = {
     "pigs_aggregate_backward": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64] + [c_void_p] * 23),
     "pigs_microbench_ffma": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
     "pigs_microbench_ex2": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
+    "pigs_microbench_ffma2": (c_int64, [c_int, c_int, c_int, c_void_p, c_void_p]),
 }
 
 

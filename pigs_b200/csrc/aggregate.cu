@@ -1,11 +1,956 @@
-// aggregate.cu — neighbour lists + neighbour aggregation (placeholder; implemented in a later commit)
+// aggregate.cu — neighbour lists and neighbour feature aggregation for model_pn.py
+// (replaces aggregate_neighbors.cu:18-475 of the reference: findCollisions, preprocess,
+//  aggregateNeighbors, aggregateNeighborsBackward and their torch host wrappers).
+//
+// Neighbour search.  The reference tests all P^2 pairs into a dense P x P bool matrix (1 TB at
+// P = 1M).  Here the Gaussians are bucketed into a uniform grid (stable sort by cell, so every cell
+// list is ascending in id); a warp owns one Gaussian, enumerates only the cells that can hold a
+// neighbour under the reference's (asymmetric, period-2) torus distance and applies the reference's
+// exact fp32/fp64 test to every candidate, so the accepted set is identical.  The row is then put in
+// ascending id order (shared-memory bitonic sort; rows beyond its capacity go through a per-CTA bitmap
+// over ids) which reproduces the reference's CSR bit for bit.
+//
+// Aggregation.  One warp per Gaussian; lanes over neighbour slots for the per-slot scalars (query.key,
+// Fourier embedding), lanes over feature channels for the row accumulation.  The transform is applied
+// ONCE per Gaussian (z . T) instead of once per neighbour (L^2 FMAs each in the reference); the backward
+// reduces the shared-parameter gradients (transform, frequencies, distance_transform) in shared memory
+// and issues one atomic per address per CTA (the reference: one per neighbour per channel).
 #include "common.cuh"
-using namespace pigs;
-extern "C" {
-size_t pigs_neighbor_workspace_bytes(int64_t, int) { return 0; }
-int pigs_neighbors_count(int64_t, int, const float*, const float*, int64_t*, void*, void*) { return set_error(-2, "not implemented", __FILE__, __LINE__); }
-int pigs_neighbors_fill(int64_t, int, const float*, const float*, const float*, const int64_t*, int64_t*, float*, float*, float*, void*, void*) { return set_error(-2, "not implemented", __FILE__, __LINE__); }
-int pigs_aggregate_forward(int64_t, int, int, int, int, const float*, const float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*, const float*, const float*, const float*, float*, float*, float*, float*, void*) { return set_error(-2, "not implemented", __FILE__, __LINE__); }
-size_t pigs_aggregate_backward_workspace_bytes(int64_t, int, int, int) { return 0; }
-int pigs_aggregate_backward(int64_t, int, int, int, int, int64_t, const float*, const float*, const float*, const float*, const float*, const float*, const int64_t*, const int64_t*, const float*, const float*, const float*, const float*, const float*, const float*, const float*, float*, float*, float*, float*, float*, float*, void*, void*) { return set_error(-2, "not implemented", __FILE__, __LINE__); }
+#include "eval_common.cuh"
+
+namespace pigs {
+
+constexpr int NB_THREADS = 128;            // 4 warps, one row each
+constexpr int NB_WARPS = NB_THREADS / 32;
+constexpr int NB_WARP_CAP = 2048;          // neighbours per row sorted in shared memory by one warp
+constexpr int NB_MAX_SPANS = 6;            // merged cell intervals per dimension (direct + torus images)
+constexpr int NB_BIG_CTAS = 64;            // persistent CTAs (one id-bitmap each) for rows beyond NB_WARP_CAP
+constexpr int NB_BIG_THREADS = 256;
+
+struct NbGrid {
+    float lo[2], hi[2];    // bounding box of the valid means
+    float inv_h[2];
+    int n[2];
+    int ncells;
+    float rmax;            // max effective radius (radii * 0.2)
+    uint32_t big_count;    // rows routed to the bitmap path
+    uint32_t big_next;
+    int pad[4];
+};
+
+struct NbLayout {
+    NbGrid* grid;
+    float* reff;          // [P] float(radii * 0.2)
+    uint32_t *keys_a, *vals_a, *keys_b, *vals_b;  // [P]
+    char* sort_ws;
+    uint32_t* cell_start;  // [ncells_max + 2]
+    float4* srec;          // [P] sorted by (cell, id): {mx, my, reff, id bits}
+    uint32_t* big_list;    // [P]
+    uint32_t* bitmaps;     // [NB_BIG_CTAS][words]
+    int64_t ncells_max, words;
+    size_t bytes;
+    NbLayout(void* base, int64_t P, int D)
+    {
+        const int64_t Pn = P > 0 ? P : 1;
+        ncells_max = cells_cap(P, D);
+        words = (Pn + 31) / 32;
+        Carver c(base);
+        grid = c.take<NbGrid>(1);
+        reff = c.take<float>((size_t)Pn);
+        keys_a = c.take<uint32_t>((size_t)Pn);
+        vals_a = c.take<uint32_t>((size_t)Pn);
+        keys_b = c.take<uint32_t>((size_t)Pn);
+        vals_b = c.take<uint32_t>((size_t)Pn);
+        sort_ws = c.take<char>(sort_ws_bytes(Pn));
+        cell_start = c.take<uint32_t>((size_t)ncells_max + 2);
+        srec = c.take<float4>((size_t)Pn);
+        big_list = c.take<uint32_t>((size_t)Pn);
+        bitmaps = c.take<uint32_t>((size_t)NB_BIG_CTAS * words);
+        bytes = c.total();
+    }
+    static int per_dim_cap(int64_t P, int D)
+    {
+        const int64_t budget = 2 * (P > 0 ? P : 1) + 1024;
+        if (D == 1) return (int)(budget < (1 << 22) ? budget : (1 << 22));
+        int n = 1;
+        while ((int64_t)(n + 1) * (n + 1) <= budget && n < 2048) n++;
+        return n;
+    }
+    static int64_t cells_cap(int64_t P, int D)
+    {
+        const int64_t n = per_dim_cap(P, D);
+        return D == 1 ? n : n * n;
+    }
+};
+
+// ---- stage 0: effective radii, bounding box of the valid means, max radius -----------------------
+__global__ void nb_init_kernel(NbGrid* g)
+{
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        for (int d = 0; d < 2; d++) {
+            g->lo[d] = __int_as_float(0x7f800000);
+            g->hi[d] = __int_as_float(0xff800000);
+            g->inv_h[d] = 0.f;
+            g->n[d] = 1;
+        }
+        g->ncells = 1;
+        g->rmax = 0.f;
+        g->big_count = 0;
+        g->big_next = 0;
+    }
 }
+
+template <int D>
+__global__ void __launch_bounds__(256) nb_prepare_kernel(int64_t P, const float* __restrict__ means,
+                                                         const float* __restrict__ radii, float* __restrict__ reff,
+                                                         NbGrid* __restrict__ g)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    float lo[D], hi[D], rm = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        lo[d] = __int_as_float(0x7f800000);
+        hi[d] = __int_as_float(0xff800000);
+    }
+    if (i < P) {
+        // aggregate_neighbors.cu:28: `radii[idx] * 0.2` is a double product rounded to FLOAT
+        const float r = __double2float_rn((double)radii[i] * 0.2);
+        reff[i] = r;
+        if (!((double)r < 1e-6)) {
+            rm = r;
+#pragma unroll
+            for (int d = 0; d < D; d++) lo[d] = hi[d] = means[i * D + d] + 0.0f;
+        }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        rm = fmaxf(rm, __shfl_xor_sync(0xffffffffu, rm, o));
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            lo[d] = fminf(lo[d], __shfl_xor_sync(0xffffffffu, lo[d], o));
+            hi[d] = fmaxf(hi[d], __shfl_xor_sync(0xffffffffu, hi[d], o));
+        }
+    }
+    if ((threadIdx.x & 31) == 0 && rm > 0.f) {
+        atomic_max_float(&g->rmax, rm);
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            atomic_min_float(&g->lo[d], lo[d]);
+            atomic_max_float(&g->hi[d], hi[d]);
+        }
+    }
+}
+
+__global__ void nb_grid_kernel(NbGrid* g, int D, int per_dim_cap)
+{
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    int ncells = 1;
+    for (int d = 0; d < D; d++) {
+        const float ext = g->hi[d] - g->lo[d];
+        int n = 1;
+        float inv_h = 0.f;
+        if (g->rmax > 0.f && ext > 0.f && ext < 3.0e38f) {
+            const float h = fmaxf(g->rmax, ext / (float)per_dim_cap);
+            const float q = ext / h;
+            n = q >= (float)per_dim_cap ? per_dim_cap : max(1, (int)q);
+            inv_h = (float)n / ext;
+        }
+        g->n[d] = n;
+        g->inv_h[d] = inv_h;
+        ncells *= n;
+    }
+    g->ncells = ncells;
+}
+
+__device__ __forceinline__ int nb_cell(float x, float lo, float inv_h, int n)
+{
+    const float c = floorf((x - lo) * inv_h);
+    return c >= (float)(n - 1) ? n - 1 : (c > 0.f ? (int)c : 0);  // NaN -> 0
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) nb_key_kernel(int64_t P, const float* __restrict__ means,
+                                                     const float* __restrict__ reff, const NbGrid* __restrict__ g,
+                                                     uint32_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    uint32_t key = (uint32_t)g->ncells;  // invalid Gaussians sort behind every cell
+    if (!((double)reff[i] < 1e-6)) {
+        int c = nb_cell(means[i * D], g->lo[0], g->inv_h[0], g->n[0]);
+        if (D == 2) c += g->n[0] * nb_cell(means[i * D + 1], g->lo[1], g->inv_h[1], g->n[1]);
+        key = (uint32_t)c;
+    }
+    keys[i] = key;
+    vals[i] = (uint32_t)i;
+}
+
+// cell_start[c] = first sorted position with key >= c, for c in [0, ncells + 1]
+__global__ void __launch_bounds__(256) nb_cell_start_kernel(int64_t P, const uint32_t* __restrict__ keys,
+                                                            const NbGrid* __restrict__ g, uint32_t* __restrict__ cell_start)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t cur = keys[i];
+    const uint32_t first = i == 0 ? 0u : keys[i - 1] + 1u;
+    for (uint32_t c = first; c <= cur; c++) cell_start[c] = (uint32_t)i;
+    if (i == P - 1)
+        for (uint32_t c = cur + 1u; c <= (uint32_t)g->ncells + 1u; c++) cell_start[c] = (uint32_t)P;
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) nb_gather_kernel(int64_t P, const uint32_t* __restrict__ ids,
+                                                        const float* __restrict__ means, const float* __restrict__ reff,
+                                                        float4* __restrict__ srec)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    const uint32_t id = ids[i];
+    srec[i] = make_float4(means[(size_t)id * D], D == 2 ? means[(size_t)id * D + 1] : 0.f, reff[id], __uint_as_float(id));
+}
+
+// ---- candidate enumeration -------------------------------------------------------------------------
+// Reference distance per dimension (aggregate_neighbors.cu:43-49), dx = other - mine:
+//   dx_eff = (FLOAT) min((double)dx, fabs(2.0 - fmod(fabs((double)dx), 2.0)))
+// For dx <= 1 this is dx itself (negative offsets never wrap); for dx > 1 it is the distance up to the
+// next multiple of 2.  A neighbour needs |dx_eff| <= r_i + r_j <= T in every dimension, i.e. per
+// dimension other in [mine - T, mine + T]  or  other in [mine + 2k - T, mine + 2k), k = 1, 2, ...
+struct Spans {
+    int n;
+    int lo[NB_MAX_SPANS], hi[NB_MAX_SPANS];
+};
+
+__device__ __forceinline__ void span_add(Spans& s, int lo, int hi, int ncell)
+{
+    if (s.n > 0 && lo <= s.hi[s.n - 1] + 1) {  // starts are generated in ascending order: merge with the last
+        if (hi > s.hi[s.n - 1]) s.hi[s.n - 1] = hi;
+        return;
+    }
+    if (s.n == NB_MAX_SPANS) {  // too many torus images (domain much wider than the period): scan everything
+        s.n = 1;
+        s.lo[0] = 0;
+        s.hi[0] = ncell - 1;
+        return;
+    }
+    s.lo[s.n] = lo;
+    s.hi[s.n] = hi;
+    s.n++;
+}
+
+__device__ __forceinline__ void dim_spans(float mine, float T, const NbGrid& g, int d, Spans& s)
+{
+    const float pad = 1e-4f * T + 1e-6f * (1.0f + fabsf(mine) + fabsf(g.lo[d]) + fabsf(g.hi[d]));
+    const float Tp = T + pad;
+    const int n = g.n[d];
+    s.n = 0;
+    span_add(s, nb_cell(mine - Tp, g.lo[d], g.inv_h[d], n), nb_cell(mine + Tp, g.lo[d], g.inv_h[d], n), n);
+    for (int k = 1; k < 64; k++) {
+        const float a = mine + 2.0f * (float)k - Tp;
+        if (a > g.hi[d]) break;
+        span_add(s, nb_cell(a, g.lo[d], g.inv_h[d], n), nb_cell(mine + 2.0f * (float)k + pad, g.lo[d], g.inv_h[d], n), n);
+        if (s.n == 1 && s.lo[0] == 0 && s.hi[0] == n - 1) break;
+    }
+}
+
+// the reference's collision test, operation for operation (findCollisions, aggregate_neighbors.cu:40-53;
+// `dist += dx * dx` is an FFMA in its SASS)
+template <int D>
+__device__ __forceinline__ bool nb_collides(const float* mi, float ri, const float* mj, float rj)
+{
+    float dist = 0.0f;
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        float dx = __fsub_rn(mj[d], mi[d]);
+        if (dx > 1.0f) dx = __double2float_rn(fmin((double)dx, fabs(2.0 - fmod(fabs((double)dx), 2.0))));
+        dist = __fmaf_rn(dx, dx, dist);
+    }
+    const float rad = __fadd_rn(ri, rj);
+    return !(dist > __fmul_rn(rad, rad));
+}
+
+// Calls f(sorted position p, record) for every candidate of row record `me`; the calling group has
+// `stride` threads with index `t`.  f is invoked group-uniformly (p may be >= end: valid = false).
+template <int D, typename F>
+__device__ __forceinline__ void nb_for_candidates(const float4 me, const NbGrid& g, const uint32_t* __restrict__ cell_start,
+                                                  const float4* __restrict__ srec, int t, int stride, F f)
+{
+    const float T = me.z + g.rmax;
+    Spans sx, sy;
+    dim_spans(me.x, T, g, 0, sx);
+    if (D == 2)
+        dim_spans(me.y, T, g, 1, sy);
+    else {
+        sy.n = 1;
+        sy.lo[0] = sy.hi[0] = 0;
+    }
+    for (int iy = 0; iy < sy.n; iy++)
+        for (int cy = sy.lo[iy]; cy <= sy.hi[iy]; cy++)
+            for (int ix = 0; ix < sx.n; ix++) {
+                const uint32_t b = cell_start[cy * g.n[0] + sx.lo[ix]];
+                const uint32_t e = cell_start[cy * g.n[0] + sx.hi[ix] + 1];
+                for (uint32_t base = b; base < e; base += stride) {
+                    const uint32_t p = base + t;
+                    const bool valid = p < e;
+                    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (valid) o = srec[p];
+                    f(valid, o);
+                }
+            }
+}
+
+// ---- stage A: counts -------------------------------------------------------------------------------
+template <int D>
+__global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const NbGrid* __restrict__ gp,
+                                                              const uint32_t* __restrict__ cell_start,
+                                                              const float4* __restrict__ srec, int64_t* __restrict__ counts)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t r = (int64_t)blockIdx.x * NB_WARPS + (threadIdx.x >> 5);
+    const NbGrid g = *gp;
+    if (r >= (int64_t)cell_start[g.ncells]) return;  // invalid rows keep count 0
+    const float4 me = srec[r];
+    const float mi[2] = {me.x, me.y};
+    uint32_t cnt = 0;
+    nb_for_candidates<D>(me, g, cell_start, srec, lane, 32, [&](bool valid, const float4& o) {
+        const float mj[2] = {o.x, o.y};
+        if (valid && nb_collides<D>(mi, me.z, mj, o.z)) cnt++;
+    });
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+    if (lane == 0) counts[__float_as_uint(me.w)] = (int64_t)cnt;
+}
+
+// ---- stage B: fill ---------------------------------------------------------------------------------
+// outputs of one CSR slot (preprocess, aggregate_neighbors.cu:82-126), returns the density (0 if skipped)
+template <int D>
+__device__ __forceinline__ float nb_emit_slot(int64_t slot, uint32_t j, const float* mi, float inv_r,
+                                              const float* __restrict__ means, const float* __restrict__ conics,
+                                              int64_t* __restrict__ indices, float* __restrict__ dists,
+                                              float* __restrict__ densities)
+{
+    float X[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) X[d] = torus_wrap(__fsub_rn(means[(size_t)j * D + d], mi[d]));
+    float power;
+    if (D == 1) {
+        const float c0 = conics[j];
+        power = __double2float_rn(-0.5 * (double)c0 * (double)X[0] * (double)X[0]);
+    } else {
+        const float c0 = conics[(size_t)j * 3], c1 = conics[(size_t)j * 3 + 1], c2 = conics[(size_t)j * 3 + 2];
+        const float a = __fmul_rn(__fmul_rn(c0, X[0]), X[0]);
+        const float q = __fmaf_rn(__fmul_rn(c2, X[D - 1]), X[D - 1], a);
+        const float m = __fmul_rn(__fmul_rn(c1, X[0]), X[D - 1]);
+        power = __double2float_rn(-0.5 * (double)q - (double)m);
+    }
+#pragma unroll
+    for (int d = 0; d < D; d++) dists[slot * D + d] = __fmul_rn(X[d], inv_r);
+    if (power > 0.0f) {  // skipped by the reference: index stays -1, density 0
+        indices[slot] = -1;
+        densities[slot] = 0.0f;
+        return 0.0f;
+    }
+    const float dens = expf(power);
+    densities[slot] = dens;
+    indices[slot] = (int64_t)j;
+    return dens;
+}
+
+__device__ __forceinline__ float nb_inv_radius(float radius)
+{
+    // aggregate_neighbors.cu:74-75: my_radius = radii * 0.333 (double -> FLOAT); 1.0 / (my_radius + 1e-6) -> FLOAT
+    const float my_radius = __double2float_rn((double)radius * 0.333);
+    return __double2float_rn(1.0 / ((double)my_radius + 1e-6));
+}
+
+template <int D>
+__global__ void __launch_bounds__(NB_THREADS) nb_fill_kernel(int64_t P, NbGrid* __restrict__ gp,
+                                                             const uint32_t* __restrict__ cell_start,
+                                                             const float4* __restrict__ srec, const float* __restrict__ means,
+                                                             const float* __restrict__ conics, const float* __restrict__ radii,
+                                                             const int64_t* __restrict__ ranges, int64_t* __restrict__ indices,
+                                                             float* __restrict__ dists, float* __restrict__ densities,
+                                                             float* __restrict__ inv_total, uint32_t* __restrict__ big_list)
+{
+    __shared__ uint32_t s_buf[NB_WARPS][NB_WARP_CAP];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t r = (int64_t)blockIdx.x * NB_WARPS + w;
+    if (r >= P) return;
+    const NbGrid g = *gp;
+    const float4 me = srec[r];
+    const uint32_t id = __float_as_uint(me.w);
+    if (r >= (int64_t)cell_start[g.ncells]) {  // no neighbours: total density 0 (aggregate_neighbors.cu:124-125)
+        if (lane == 0) inv_total[id] = __double2float_rn(1.0 / (0.0 + 1e-6));
+        return;
+    }
+    const int64_t start = id == 0 ? 0 : ranges[id - 1];
+    const int64_t n = ranges[id] - start;
+    if (n > NB_WARP_CAP) {
+        if (lane == 0) big_list[atomicAdd(&gp->big_count, 1u)] = (uint32_t)r;
+        return;
+    }
+    const float mi[2] = {me.x, me.y};
+    uint32_t* buf = s_buf[w];
+    uint32_t cnt = 0;
+    nb_for_candidates<D>(me, g, cell_start, srec, lane, 32, [&](bool valid, const float4& o) {
+        const float mj[2] = {o.x, o.y};
+        const bool ok = valid && nb_collides<D>(mi, me.z, mj, o.z);
+        const uint32_t m = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            const uint32_t pos = cnt + __popc(m & ((1u << lane) - 1u));
+            if (pos < NB_WARP_CAP) buf[pos] = __float_as_uint(o.w);
+        }
+        cnt += __popc(m);
+    });
+    // ascending neighbour id (the reference scans i = 0..P-1): bitonic sort of the padded row
+    uint32_t n2 = 1;
+    while (n2 < cnt) n2 <<= 1;
+    for (uint32_t i = cnt + lane; i < n2; i += 32) buf[i] = 0xffffffffu;
+    __syncwarp();
+    for (uint32_t k = 2; k <= n2; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = lane; t < (n2 >> 1); t += 32) {
+                const uint32_t i0 = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const uint32_t i1 = i0 | j;
+                const uint32_t a = buf[i0], b = buf[i1];
+                const bool up = (i0 & k) == 0;
+                if ((a > b) == up) {
+                    buf[i0] = b;
+                    buf[i1] = a;
+                }
+            }
+            __syncwarp();
+        }
+    const float inv_r = nb_inv_radius(radii[id]);
+    float total = 0.0f;
+    for (uint32_t s = lane; s < cnt; s += 32)
+        total += nb_emit_slot<D>(start + s, buf[s], mi, inv_r, means, conics, indices, dists, densities);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+    if (lane == 0) inv_total[id] = __double2float_rn(1.0 / ((double)total + 1e-6));
+}
+
+// rows with more than NB_WARP_CAP neighbours: a persistent CTA marks the accepted ids in a bitmap over
+// [0, P) and emits them in ascending order with a block-wide prefix sum of the word popcounts
+template <int D>
+__global__ void __launch_bounds__(NB_BIG_THREADS) nb_fill_big_kernel(int64_t P, NbGrid* __restrict__ gp,
+                                                                     const uint32_t* __restrict__ cell_start,
+                                                                     const float4* __restrict__ srec,
+                                                                     const float* __restrict__ means,
+                                                                     const float* __restrict__ conics,
+                                                                     const float* __restrict__ radii,
+                                                                     const int64_t* __restrict__ ranges,
+                                                                     int64_t* __restrict__ indices, float* __restrict__ dists,
+                                                                     float* __restrict__ densities, float* __restrict__ inv_total,
+                                                                     const uint32_t* __restrict__ big_list,
+                                                                     uint32_t* __restrict__ bitmaps, int64_t words)
+{
+    __shared__ uint32_t s_scan[NB_BIG_THREADS];
+    __shared__ uint32_t s_row, s_base;
+    __shared__ float s_total;
+    const NbGrid g = *gp;
+    uint32_t* bm = bitmaps + (size_t)blockIdx.x * words;
+    const int tid = threadIdx.x;
+    for (;;) {
+        __syncthreads();
+        if (tid == 0) {
+            s_row = atomicAdd(&gp->big_next, 1u);
+            s_base = 0;
+            s_total = 0.0f;
+        }
+        __syncthreads();
+        if (s_row >= g.big_count) break;
+        const float4 me = srec[big_list[s_row]];
+        const uint32_t id = __float_as_uint(me.w);
+        const float mi[2] = {me.x, me.y};
+        for (int64_t wd = tid; wd < words; wd += NB_BIG_THREADS) bm[wd] = 0u;
+        __syncthreads();
+        nb_for_candidates<D>(me, g, cell_start, srec, tid, NB_BIG_THREADS, [&](bool valid, const float4& o) {
+            const float mj[2] = {o.x, o.y};
+            if (valid && nb_collides<D>(mi, me.z, mj, o.z)) {
+                const uint32_t j = __float_as_uint(o.w);
+                atomicOr(&bm[j >> 5], 1u << (j & 31));
+            }
+        });
+        __syncthreads();
+        const int64_t start = id == 0 ? 0 : ranges[id - 1];
+        const float inv_r = nb_inv_radius(radii[id]);
+        float total = 0.0f;
+        for (int64_t w0 = 0; w0 < words; w0 += NB_BIG_THREADS) {
+            const int64_t wd = w0 + tid;
+            uint32_t bits = wd < words ? bm[wd] : 0u;
+            const uint32_t c = __popc(bits);
+            s_scan[tid] = c;
+            __syncthreads();
+            for (int o = 1; o < NB_BIG_THREADS; o <<= 1) {
+                const uint32_t v = tid >= o ? s_scan[tid - o] : 0u;
+                __syncthreads();
+                s_scan[tid] += v;
+                __syncthreads();
+            }
+            int64_t slot = start + s_base + s_scan[tid] - c;
+            while (bits) {
+                const uint32_t b = __ffs(bits) - 1;
+                bits &= bits - 1;
+                total += nb_emit_slot<D>(slot++, (uint32_t)(wd * 32 + b), mi, inv_r, means, conics, indices, dists, densities);
+            }
+            __syncthreads();
+            if (tid == NB_BIG_THREADS - 1) s_base += s_scan[tid];
+            __syncthreads();
+        }
+        atomicAdd(&s_total, total);
+        __syncthreads();
+        if (tid == 0) inv_total[id] = __double2float_rn(1.0 / ((double)s_total + 1e-6));
+    }
+}
+
+// ====================================================================================================
+// aggregation (aggregate_neighbors.cu:129-321)
+// ====================================================================================================
+constexpr int AG_THREADS = 256;
+constexpr int AG_WARPS = AG_THREADS / 32;
+constexpr int AG_MAX_L = 128, AG_MAX_K = 128;
+
+// sin / cos of (frequency * pi * X).  The reference evaluates the argument and sin/cos in double
+// (`sin(frequencies[e] * M_PI * X[d])`, aggregate_neighbors.cu:181-182); here the product f*X is formed
+// exactly as p + e (two floats), reduced modulo 2 exactly, and fed to sincospif: abs error ~2e-7.
+__device__ __forceinline__ void sincos_fpx(float f, float X, float& s, float& c)
+{
+    const float p = __fmul_rn(f, X);
+    const float e = __fmaf_rn(f, X, -p);
+    const float r = __fsub_rn(p, 2.0f * rintf(0.5f * p));
+    sincospif(__fadd_rn(r, e), &s, &c);
+}
+
+struct AggDims {
+    int D, L, K, E, nF, stride;  // stride = (E-1)/D, nF = stride/2
+};
+
+__global__ void __launch_bounds__(AG_THREADS)
+    agg_forward_kernel(int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
+                       const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
+                       const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
+                       const float* __restrict__ dists, const float* __restrict__ densities,
+                       const float* __restrict__ inv_total, float* __restrict__ weights, float* __restrict__ embeddings,
+                       float* __restrict__ factors, float* __restrict__ out)
+{
+    extern __shared__ float sm[];
+    const int D = dm.D, L = dm.L, K = dm.K, E = dm.E, nF = dm.nF, stride = dm.stride;
+    float* s_dt = sm;                 // [2E]
+    float* s_fr = s_dt + 2 * E;       // [nF]
+    float* wbase = s_fr + nF;
+    const int per_warp = K + L + 3 * 32;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* s_q = wbase + (size_t)w * per_warp;  // [K]
+    float* s_z = s_q + K;                       // [L]
+    float* s_dwe = s_z + L;                     // [32]
+    float* s_dwf = s_dwe + 32;                  // [32]
+    int* s_j = (int*)(s_dwf + 32);              // [32]
+    for (int i = threadIdx.x; i < 2 * E; i += AG_THREADS) s_dt[i] = dt[i];
+    for (int i = threadIdx.x; i < nF; i += AG_THREADS) s_fr[i] = freqs[i];
+    __syncthreads();
+
+    for (int64_t row = (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {
+        const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
+        for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
+        const float inv = inv_total[row];
+        float z[AG_MAX_L / 32];
+#pragma unroll
+        for (int a = 0; a < AG_MAX_L / 32; a++) z[a] = 0.0f;
+        __syncwarp();
+        for (int64_t chunk = start; chunk < end; chunk += 32) {
+            const int64_t s = chunk + lane;
+            const int64_t j = s < end ? indices[s] : -1;
+            float dwe = 0.0f, dwf = 0.0f;
+            if (j >= 0) {
+                const float* key = keys + j * K;
+                float wgt = 0.0f;
+                for (int k = 0; k < K; k++) wgt = fmaf(s_q[k], key[k], wgt);
+                float emb = 0.0f, fac = 0.0f;
+                for (int d = 0; d < D; d++) {
+                    const float X = dists[s * D + d];
+                    for (int e = 0; e < nF; e++) {
+                        float sn, cs;
+                        sincos_fpx(s_fr[e], X, sn, cs);
+                        const int i0 = d * stride + 2 * e;
+                        emb = fmaf(s_dt[i0], sn, emb);
+                        emb = fmaf(s_dt[i0 + 1], cs, emb);
+                        fac = fmaf(s_dt[E + i0], sn, fac);
+                        fac = fmaf(s_dt[E + i0 + 1], cs, fac);
+                    }
+                }
+                emb += s_dt[E - 1];
+                fac += s_dt[2 * E - 1];
+                weights[s] = wgt;
+                embeddings[s] = emb;
+                factors[s] = fac;
+                const float dw = inv * densities[s] * wgt;
+                dwf = dw * fac;
+                dwe = dw * emb;
+            }
+            s_dwe[lane] = dwe;
+            s_dwf[lane] = dwf;
+            s_j[lane] = (int)j;
+            __syncwarp();
+            const int cnt = (int)min((int64_t)32, end - chunk);
+            for (int t = 0; t < cnt; t++) {
+                const int jj = s_j[t];
+                if (jj < 0) continue;
+                const float a0 = s_dwe[t], a1 = s_dwf[t];
+                const float* f = features + (size_t)jj * L;
+#pragma unroll
+                for (int a = 0; a < AG_MAX_L / 32; a++)
+                    if (a * 32 + lane < L) z[a] += fmaf(a1, f[a * 32 + lane], a0);
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int a = 0; a < AG_MAX_L / 32; a++)
+            if (a * 32 + lane < L) s_z[a * 32 + lane] = z[a];
+        __syncwarp();
+        // out_i = z . T  (the reference applies T inside the neighbour loop, :201-206)
+        for (int b = lane; b < L; b += 32) {
+            float acc = 0.0f;
+            for (int a = 0; a < L; a++) acc = fmaf(s_z[a], transform[a * L + b], acc);
+            out[row * L + b] = acc;
+        }
+        __syncwarp();
+    }
+}
+
+// Backward.  Per row i with upstream g_i:  st = T g_i,  A = sum(st),  and per neighbour slot (j):
+//   B = st . feat_j,  dc = density * inv_total_i,  dcw = dc * weight,  TE = dc * (emb * A + fac * B)
+//   dL/dfeat_j   += dcw * fac * st                 dL/dkey_j += q_i * TE      dL/dq_i += key_j * TE
+//   dL/dT[a][b]  += g_i[b] * sum_s w_s * dc_s * (emb_s + fac_s * feat_j[a])
+//   dL/ddt, dL/dfreq: the per-slot sums over channels collapse to A and B (reference :266-281)
+// Shared-parameter gradients are accumulated per lane in shared-memory columns (no conflicts), reduced
+// once per CTA, then one atomic per address per CTA.
+__global__ void __launch_bounds__(AG_THREADS)
+    agg_backward_kernel(int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
+                        const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
+                        const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
+                        const float* __restrict__ dists, const float* __restrict__ densities,
+                        const float* __restrict__ weights, const float* __restrict__ embeddings,
+                        const float* __restrict__ factors, const float* __restrict__ inv_total,
+                        const float* __restrict__ gout, float* __restrict__ g_features, float* __restrict__ g_transform,
+                        float* __restrict__ g_queries, float* __restrict__ g_keys, float* __restrict__ g_freqs,
+                        float* __restrict__ g_dt)
+{
+    extern __shared__ float sm[];
+    const int D = dm.D, L = dm.L, K = dm.K, E = dm.E, nF = dm.nF, stride = dm.stride;
+    const int ncol = 2 * E + nF;
+    float* s_dt = sm;                     // [2E]
+    float* s_fr = s_dt + 2 * E;           // [nF]
+    float* s_gt = s_fr + nF;              // [L*L]  CTA accumulator of dL/dT
+    float* wbase = s_gt + L * L;
+    const int per_warp = K + 3 * L + 6 * 32 + ncol * 32;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    float* s_q = wbase + (size_t)w * per_warp;  // [K]
+    float* s_st = s_q + K;                      // [L]
+    float* s_g = s_st + L;                      // [L]
+    float* s_wz = s_g + L;                      // [L]
+    float* s_te = s_wz + L;                     // [32] x5 + j
+    float* s_c1 = s_te + 32;
+    float* s_w = s_c1 + 32;
+    float* s_dce = s_w + 32;
+    float* s_dcf = s_dce + 32;
+    int* s_j = (int*)(s_dcf + 32);
+    float* s_col = (float*)(s_j + 32);          // [ncol][32] per-lane partial sums of dL/ddt, dL/dfreq
+    for (int i = threadIdx.x; i < 2 * E; i += AG_THREADS) s_dt[i] = dt[i];
+    for (int i = threadIdx.x; i < nF; i += AG_THREADS) s_fr[i] = freqs[i];
+    for (int i = threadIdx.x; i < L * L; i += AG_THREADS) s_gt[i] = 0.0f;
+    for (int i = lane; i < ncol * 32; i += 32) s_col[i] = 0.0f;
+    __syncthreads();
+    const float PI = 3.14159265358979323846f;
+
+    for (int64_t row = (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {
+        const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
+        if (end == start) continue;
+        for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
+        for (int b = lane; b < L; b += 32) s_g[b] = gout[row * L + b];
+        __syncwarp();
+        float Apart = 0.0f;
+        for (int a = lane; a < L; a += 32) {
+            float acc = 0.0f;
+            for (int b = 0; b < L; b++) acc = fmaf(transform[a * L + b], s_g[b], acc);
+            s_st[a] = acc;
+            Apart += acc;
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) Apart += __shfl_xor_sync(0xffffffffu, Apart, o);
+        const float A = Apart;
+        const float inv = inv_total[row];
+        float wz[AG_MAX_L / 32], gq[AG_MAX_K / 32];
+#pragma unroll
+        for (int a = 0; a < AG_MAX_L / 32; a++) wz[a] = 0.0f;
+#pragma unroll
+        for (int k = 0; k < AG_MAX_K / 32; k++) gq[k] = 0.0f;
+        __syncwarp();
+        for (int64_t chunk = start; chunk < end; chunk += 32) {
+            const int64_t s = chunk + lane;
+            const int64_t j = s < end ? indices[s] : -1;
+            float te = 0.f, c1 = 0.f, wgt = 0.f, dce = 0.f, dcf = 0.f;
+            if (j >= 0) {
+                const float* f = features + j * L;
+                float B = 0.0f;
+                for (int a = 0; a < L; a++) B = fmaf(s_st[a], f[a], B);
+                wgt = weights[s];
+                const float emb = embeddings[s], fac = factors[s];
+                const float dc = densities[s] * inv;
+                const float dcw = dc * wgt;
+                dce = dc * emb;
+                dcf = dc * fac;
+                te = fmaf(dce, A, dcf * B);
+                c1 = dcw * fac;
+                const float dA = dcw * A, dB = dcw * B;
+                for (int d = 0; d < D; d++) {
+                    const float X = dists[s * D + d];
+                    for (int e = 0; e < nF; e++) {
+                        float sn, cs;
+                        sincos_fpx(s_fr[e], X, sn, cs);
+                        const int i0 = d * stride + 2 * e;
+                        s_col[(i0)*32 + lane] += dA * sn;
+                        s_col[(E + i0) * 32 + lane] += dB * sn;
+                        s_col[(i0 + 1) * 32 + lane] += dA * cs;
+                        s_col[(E + i0 + 1) * 32 + lane] += dB * cs;
+                        const float ts = fmaf(s_dt[E + i0], dB, s_dt[i0] * dA);
+                        const float tc = fmaf(s_dt[E + i0 + 1], dB, s_dt[i0 + 1] * dA);
+                        s_col[(2 * E + e) * 32 + lane] += PI * X * fmaf(cs, ts, -sn * tc);
+                    }
+                }
+                s_col[(E - 1) * 32 + lane] += dA;
+                s_col[(2 * E - 1) * 32 + lane] += dB;
+            }
+            s_te[lane] = te;
+            s_c1[lane] = c1;
+            s_w[lane] = wgt;
+            s_dce[lane] = dce;
+            s_dcf[lane] = dcf;
+            s_j[lane] = (int)j;
+            __syncwarp();
+            const int cnt = (int)min((int64_t)32, end - chunk);
+            for (int t = 0; t < cnt; t++) {
+                const int jj = s_j[t];
+                if (jj < 0) continue;
+                const float t_te = s_te[t], t_c1 = s_c1[t], t_w = s_w[t], t_dce = s_dce[t], t_dcf = s_dcf[t];
+                const float* f = features + (size_t)jj * L;
+#pragma unroll
+                for (int a = 0; a < AG_MAX_L / 32; a++) {
+                    const int ai = a * 32 + lane;
+                    if (ai < L) {
+                        atomicAdd(g_features + (size_t)jj * L + ai, t_c1 * s_st[ai]);
+                        wz[a] = fmaf(t_w, fmaf(t_dcf, f[ai], t_dce), wz[a]);
+                    }
+                }
+                const float* key = keys + (size_t)jj * K;
+#pragma unroll
+                for (int k = 0; k < AG_MAX_K / 32; k++) {
+                    const int ki = k * 32 + lane;
+                    if (ki < K) {
+                        gq[k] = fmaf(key[ki], t_te, gq[k]);
+                        atomicAdd(g_keys + (size_t)jj * K + ki, s_q[ki] * t_te);
+                    }
+                }
+            }
+            __syncwarp();
+        }
+#pragma unroll
+        for (int k = 0; k < AG_MAX_K / 32; k++)
+            if (k * 32 + lane < K) g_queries[row * K + k * 32 + lane] = gq[k];
+#pragma unroll
+        for (int a = 0; a < AG_MAX_L / 32; a++)
+            if (a * 32 + lane < L) s_wz[a * 32 + lane] = wz[a];
+        __syncwarp();
+        for (int b = lane; b < L; b += 32) {
+            const float gb = s_g[b];
+            for (int a = 0; a < L; a++) atomicAdd(&s_gt[a * L + b], s_wz[a] * gb);
+        }
+        __syncwarp();
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < L * L; i += AG_THREADS)
+        if (s_gt[i] != 0.0f) atomicAdd(g_transform + i, s_gt[i]);
+    for (int i = threadIdx.x; i < ncol; i += AG_THREADS) {
+        float acc = 0.0f;
+        for (int ww = 0; ww < AG_WARPS; ww++) {
+            const float* col = wbase + (size_t)ww * per_warp + (K + 3 * L + 6 * 32) + i * 32;
+            for (int l = 0; l < 32; l++) acc += col[l];
+        }
+        if (acc != 0.0f) atomicAdd(i < 2 * E ? g_dt + i : g_freqs + (i - 2 * E), acc);
+    }
+}
+
+}  // namespace pigs
+
+using namespace pigs;
+
+namespace {
+
+int bit_len(uint32_t n)
+{
+    int b = 0;
+    while (n) {
+        b++;
+        n >>= 1;
+    }
+    return b;
+}
+
+size_t agg_fwd_smem(int L, int K, int E, int nF) { return sizeof(float) * (2 * E + nF + (size_t)AG_WARPS * (K + L + 3 * 32)); }
+size_t agg_bwd_smem(int L, int K, int E, int nF)
+{
+    return sizeof(float) * (2 * E + nF + (size_t)L * L + (size_t)AG_WARPS * (K + 3 * L + 6 * 32 + (2 * E + nF) * 32));
+}
+
+int agg_dims(AggDims& dm, int D, int L, int K, int E)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(L >= 1 && L <= AG_MAX_L);
+    PIGS_ARG(K >= 1 && K <= AG_MAX_K);
+    PIGS_ARG(E >= 1);
+    dm.D = D;
+    dm.L = L;
+    dm.K = K;
+    dm.E = E;
+    dm.stride = (E - 1) / D;
+    dm.nF = (E - 1) / D / 2;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t pigs_neighbor_workspace_bytes(int64_t P, int D) { return NbLayout(nullptr, P, D == 1 ? 1 : 2).bytes; }
+
+int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radii, int64_t* counts, void* workspace,
+                         void* stream)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(P > 0 && P < (1ll << 31) && means && radii && counts && workspace);
+    cudaStream_t st = (cudaStream_t)stream;
+    NbLayout w(workspace, P, D);
+    const unsigned nb = (unsigned)((P + 255) / 256);
+    PIGS_CHECK(cudaMemsetAsync(counts, 0, (size_t)P * sizeof(int64_t), st));
+    nb_init_kernel<<<1, 32, 0, st>>>(w.grid);
+    PIGS_LAUNCH_CHECK();
+    if (D == 2)
+        nb_prepare_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, w.reff, w.grid);
+    else
+        nb_prepare_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, w.reff, w.grid);
+    PIGS_LAUNCH_CHECK();
+    nb_grid_kernel<<<1, 32, 0, st>>>(w.grid, D, NbLayout::per_dim_cap(P, D));
+    PIGS_LAUNCH_CHECK();
+    if (D == 2)
+        nb_key_kernel<2><<<nb, 256, 0, st>>>(P, means, w.reff, w.grid, w.keys_a, w.vals_a);
+    else
+        nb_key_kernel<1><<<nb, 256, 0, st>>>(P, means, w.reff, w.grid, w.keys_a, w.vals_a);
+    PIGS_LAUNCH_CHECK();
+    // stable sort by cell id: every cell's list stays ascending in Gaussian id
+    const int bits = bit_len((uint32_t)w.ncells_max + 1u);
+    int rc = stable_sort_pairs_u32(w.keys_a, w.vals_a, w.keys_b, w.vals_b, P, bits, w.sort_ws, st);
+    if (rc) return rc;
+    nb_cell_start_kernel<<<nb, 256, 0, st>>>(P, w.keys_b, w.grid, w.cell_start);
+    PIGS_LAUNCH_CHECK();
+    if (D == 2)
+        nb_gather_kernel<2><<<nb, 256, 0, st>>>(P, w.vals_b, means, w.reff, w.srec);
+    else
+        nb_gather_kernel<1><<<nb, 256, 0, st>>>(P, w.vals_b, means, w.reff, w.srec);
+    PIGS_LAUNCH_CHECK();
+    const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
+    if (D == 2)
+        nb_count_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts);
+    else
+        nb_count_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conics, const float* radii,
+                        const int64_t* ranges, int64_t* indices, float* dists, float* densities,
+                        float* inv_total_densities, void* workspace, void* stream)
+{
+    PIGS_ARG(D == 1 || D == 2);
+    PIGS_ARG(P > 0 && means && conics && radii && ranges && inv_total_densities && workspace);
+    cudaStream_t st = (cudaStream_t)stream;
+    NbLayout w(workspace, P, D);
+    const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
+    if (D == 2) {
+        nb_fill_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
+                                                      dists, densities, inv_total_densities, w.big_list);
+        PIGS_LAUNCH_CHECK();
+        nb_fill_big_kernel<2><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
+                                                                      ranges, indices, dists, densities, inv_total_densities,
+                                                                      w.big_list, w.bitmaps, w.words);
+    } else {
+        nb_fill_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
+                                                      dists, densities, inv_total_densities, w.big_list);
+        PIGS_LAUNCH_CHECK();
+        nb_fill_big_kernel<1><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
+                                                                      ranges, indices, dists, densities, inv_total_densities,
+                                                                      w.big_list, w.bitmaps, w.words);
+    }
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+                           const float* queries, const float* keys, const float* frequencies,
+                           const float* distance_transform, const int64_t* indices, const int64_t* ranges,
+                           const float* dists, const float* densities, const float* inv_total_densities, float* weights,
+                           float* embeddings, float* factors, float* neighbor_features, void* stream)
+{
+    AggDims dm;
+    int rc = agg_dims(dm, D, L, K, E);
+    if (rc) return rc;
+    PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
+             neighbor_features);
+    PIGS_ARG(dm.nF == 0 || frequencies);
+    const size_t smem = agg_fwd_smem(L, K, E, dm.nF);
+    PIGS_ARG(smem <= 200 * 1024);
+    PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    const int64_t cap = (int64_t)num_sms() * 16;
+    if (grid > cap) grid = cap;
+    agg_forward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+        P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+        inv_total_densities, weights, embeddings, factors, neighbor_features);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+size_t pigs_aggregate_backward_workspace_bytes(int64_t P, int L, int K, int E)
+{
+    (void)P, (void)L, (void)K, (void)E;
+    return 0;  // all partial sums live in shared memory
+}
+
+int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, const float* features,
+                            const float* transform, const float* queries, const float* keys, const float* frequencies,
+                            const float* distance_transform, const int64_t* indices, const int64_t* ranges,
+                            const float* dists, const float* densities, const float* weights, const float* embeddings,
+                            const float* factors, const float* inv_total_densities, const float* dL_dneighbor_features,
+                            float* dL_dfeatures, float* dL_dtransform, float* dL_dqueries, float* dL_dkeys,
+                            float* dL_dfrequencies, float* dL_ddistance_transform, void* workspace, void* stream)
+{
+    (void)M, (void)workspace;
+    AggDims dm;
+    int rc = agg_dims(dm, D, L, K, E);
+    if (rc) return rc;
+    PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
+             dL_dneighbor_features && dL_dfeatures && dL_dtransform && dL_dqueries && dL_dkeys && dL_ddistance_transform);
+    PIGS_ARG(dm.nF == 0 || (frequencies && dL_dfrequencies));
+    const size_t smem = agg_bwd_smem(L, K, E, dm.nF);
+    PIGS_ARG(smem <= 200 * 1024);
+    PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    const int64_t cap = (int64_t)num_sms() * 2;
+    if (grid > cap) grid = cap;
+    agg_backward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+        P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities, weights,
+        embeddings, factors, inv_total_densities, dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
+        dL_dfrequencies, dL_ddistance_transform);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

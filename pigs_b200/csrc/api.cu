@@ -299,9 +299,64 @@ __global__ void __launch_bounds__(256) mb_ex2_kernel(int iters, float* sink)
     if (s == 123.456f) sink[0] = s;
 }
 
+// packed FP32x2 (Blackwell FFMA2): 2 FMAs per lane per instruction
+__device__ __forceinline__ unsigned long long mb_pack(float a, float b)
+{
+    unsigned long long r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+    return r;
+}
+__device__ __forceinline__ unsigned long long mb_fma2(unsigned long long a, unsigned long long b, unsigned long long c)
+{
+    unsigned long long d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+
+// MIX = 0: FFMA2 only.  MIX = 1: per 16 FFMA2 (32 lane-FMAs) two MUFU.EX2 — the ratio of the fused forward.
+template <int MIX>
+__global__ void __launch_bounds__(256) mb_ffma2_kernel(int iters, float* sink)
+{
+    unsigned long long a[MB_ILP];
+    float m0 = -0.5f - threadIdx.x * 1e-6f, m1 = -0.25f - threadIdx.x * 1e-6f;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) a[i] = mb_pack(1.0f + i * 1e-3f + threadIdx.x * 1e-6f, 0.5f + i * 1e-3f);
+    // distinct (non-uniform) multiplicands so operands come from the vector register file like in the real kernels
+    const unsigned long long b = mb_pack(1.0000001f + 1e-9f * threadIdx.x, 0.9999999f), c = mb_pack(1e-7f * threadIdx.x, 2e-7f);
+    for (int it = 0; it < iters; it++) {
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+#pragma unroll
+            for (int i = 0; i < MB_ILP; i++) a[i] = mb_fma2(a[i], b, c);
+            if (MIX) {
+                m0 = ex2_approx(m0) - 1.5f;
+                m1 = ex2_approx(m1) - 1.5f;
+            }
+        }
+    }
+    float s = m0 + m1;
+#pragma unroll
+    for (int i = 0; i < MB_ILP; i++) {
+        float lo, hi;
+        asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(a[i]));
+        s += lo + hi;
+    }
+    if (s == 123.456f) sink[0] = s;
+}
+
 }  // namespace pigs
 
 extern "C" {
+
+int64_t pigs_microbench_ffma2(int ctas, int iters, int mix, float* sink, void* stream)
+{
+    if (mix)
+        mb_ffma2_kernel<1><<<ctas, 256, 0, (cudaStream_t)stream>>>(iters, sink);
+    else
+        mb_ffma2_kernel<0><<<ctas, 256, 0, (cudaStream_t)stream>>>(iters, sink);
+    g_launches++;
+    return (int64_t)ctas * 256 * (int64_t)iters * 4 * MB_ILP * 2;  // lane-FMAs
+}
 
 int64_t pigs_microbench_ffma(int ctas, int iters, float* sink, void* stream)
 {

@@ -142,7 +142,14 @@ __device__ __forceinline__ GaussReg<D, C> load_gauss(const float4* __restrict__ 
 // reference torus wrap, forward.cu:149-157 (period 2 hard-wired)
 __device__ __forceinline__ float torus_wrap(float X)
 {
-    if (fabsf(X) > 1.0f) X = (X >= 0.0f) ? fmodf(X, 2.0f) - 2.0f : fmodf(X, 2.0f) + 2.0f;
+    const float ax = fabsf(X);
+    if (ax > 1.0f) {
+        // 1 < |X| < 2: fmod(X, 2) == X exactly, so the wrap is X -/+ 2 (exact); the fmod path only beyond
+        if (ax < 2.0f)
+            X = X - copysignf(2.0f, X);
+        else
+            X = (X >= 0.0f) ? fmodf(X, 2.0f) - 2.0f : fmodf(X, 2.0f) + 2.0f;
+    }
     return X;
 }
 

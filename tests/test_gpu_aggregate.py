@@ -1,0 +1,146 @@
+"""GPU parity of the neighbour-list build and neighbour aggregation (pigs_b200 through the reference-shaped API /
+C ABI) against the CPU oracle, the committed reference-CUDA goldens and — when oracle/_ref/_C.so is present —
+the live reference extension.  Bit-exact: indices, ranges.  1e-5 norm-wise: dists, densities, inv_total,
+aggregation outputs and gradients (shared-parameter gradients vs the REFERENCE: AGG_SHARED_TOL, its own
+fp32-atomic noise floor; vs the float64-accumulating oracle: 1e-5)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pigs_oracle as po
+from tests import refcuda
+from tests.fixtures import AGG_RECIPES, agg_params, covariances_from, synthetic, _pack
+from tests.helpers import AGG_KEYS, AGG_SHARED_TOL, TOL, agg_upstream, oracle_state, rel_err, to_dev
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _prep(rec):
+    from pigs_b200 import GaussianSampler
+    d = to_dev(rec)
+    s = GaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    s.preprocess_aggregate()
+    return s, d
+
+
+def _check_lists(s, want):
+    idx, rng, dists, dens, inv = want
+    np.testing.assert_array_equal(s.ranges.cpu().numpy(), rng)
+    np.testing.assert_array_equal(s.indices.cpu().numpy(), idx)
+    assert tuple(s.dists.shape) == dists.shape
+    assert rel_err(s.dists.cpu().numpy(), dists) <= TOL
+    assert rel_err(s.densities.cpu().numpy(), dens) <= TOL
+    assert rel_err(s.inv_total_densities.cpu().numpy(), inv) <= TOL
+
+
+@pytest.mark.parametrize("name", list(AGG_RECIPES))
+def test_neighbor_lists_bit_exact_vs_oracle_and_golden(name):
+    rec = AGG_RECIPES[name]()
+    st = oracle_state(rec)
+    s, d = _prep(rec)
+    _check_lists(s, po.neighbors(rec["means"], rec["conics"], st["radii"]))
+    g = np.load(os.path.join(GOLD, "refcuda_%s.npz" % name))
+    _check_lists(s, (g["indices"], g["ranges"], g["dists"], g["densities"], g["inv_total"]))
+
+
+@pytest.mark.parametrize("name", list(AGG_RECIPES))
+def test_aggregate_forward_backward(name):
+    import torch
+    rec = AGG_RECIPES[name]()
+    st = oracle_state(rec)
+    s, d = _prep(rec)
+    idx, rng, dists, dens, inv = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    a = [rec[k] for k in AGG_KEYS]
+    w, e, f, out = po.aggregate_forward(*a, idx, rng, dists, dens, inv)
+    up = agg_upstream(rec)
+    want = po.aggregate_backward(*a, idx, rng, dists, dens, w, e, f, inv, up)
+    t = [d[k].clone().requires_grad_(True) for k in AGG_KEYS]
+    got = s.aggregate_neighbors(*t)
+    assert rel_err(got.detach().cpu().numpy(), out) <= TOL
+    got.backward(torch.from_numpy(up).cuda())
+    g = np.load(os.path.join(GOLD, "refcuda_%s.npz" % name))
+    assert rel_err(got.detach().cpu().numpy(), g["out"]) <= TOL
+    for x, wv, key in zip(t, want, AGG_KEYS):
+        assert x.grad is not None, key
+        assert rel_err(x.grad.cpu().numpy(), wv) <= TOL, key
+        tol = AGG_SHARED_TOL if key in ("transform", "frequencies", "distance_transform") else TOL
+        assert rel_err(x.grad.cpu().numpy(), g["grad_" + key]) <= tol, key
+    # saved per-slot products (the reference returns them from the forward, aggregate_neighbors.cu:414)
+    from pigs_b200 import _C
+    wq, eq, fq, _ = _C.aggregate_neighbors(*[d[k] for k in AGG_KEYS], s.indices, s.ranges, s.dists, s.densities,
+                                           s.inv_total_densities, False)
+    for x, wv in ((wq, w), (eq, e), (fq, f)):
+        assert rel_err(x.cpu().numpy(), wv) <= TOL
+
+
+def _dense_cluster(P=2600, seed=3):
+    """every Gaussian neighbours (almost) every other: rows beyond the shared-memory sort capacity -> bitmap path"""
+    rng = np.random.default_rng(seed)
+    means = rng.uniform(-0.2, 0.2, (P, 2))
+    cov, con = covariances_from(np.exp(rng.uniform(-1.2, -0.8, (P, 2))), rng.normal(0, 0.2, P))
+    return _pack(means, rng.uniform(-1, 1, (P, 1)), cov, con, means.copy())
+
+
+@pytest.mark.parametrize("make", [_dense_cluster, lambda: synthetic(20000, 64, seed=9),
+                                  lambda: synthetic(6000, 64, seed=10, edge_fraction=0.3, scale=1.0),
+                                  lambda: synthetic(3000, 64, seed=11, D=1),
+                                  lambda: synthetic(3000, 64, seed=12, scale=2.5)])
+def test_neighbor_lists_larger_sets(make):
+    rec = make()
+    rec["samples"] = rec["means"].copy()
+    st = oracle_state(rec)
+    s, d = _prep(rec)
+    want = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    _check_lists(s, want)
+
+
+def test_degenerate_rows_have_no_neighbours():
+    rec = AGG_RECIPES["agg_model"]()
+    rec["covariances"][5] = 0.0   # det == 0 -> radius 0 -> skipped row and column (aggregate_neighbors.cu:29,38)
+    rec["covariances"][77] = [0.25, 0.25, 0.25]
+    st = oracle_state(rec)
+    s, d = _prep(rec)
+    want = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    _check_lists(s, want)
+    assert float(s.inv_total_densities[5]) == pytest.approx(1e6, rel=1e-6)
+
+
+@pytest.mark.parametrize("name", ["agg_model", "agg_model_1d", "agg_grid5"])
+def test_vs_live_reference(name):
+    import torch
+    if not refcuda.available():
+        pytest.skip("oracle/_ref/_C.so not built")
+    rec = AGG_RECIPES[name]()
+    s, d = _prep(rec)
+    ref = refcuda.RefSampler(False)
+    ref.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    indices, ranges, dists, densities, inv_total = ref.preprocess_aggregate()
+    assert torch.equal(s.indices, indices) and torch.equal(s.ranges, ranges)
+    a = [d[k] for k in AGG_KEYS]
+    w, e, f, out = ref.C.aggregate_neighbors(*a, indices, ranges, dists, densities, inv_total, False)
+    got = s.aggregate_neighbors(*a)
+    assert rel_err(got.cpu().numpy(), out.cpu().numpy()) <= TOL
+
+
+def test_generic_sizes():
+    """L, K, E away from the model's 16/16/25 (runtime-sized kernel): L=40, K=7, E=13."""
+    import torch
+    rec = synthetic(500, 64, seed=31)
+    rec["samples"] = rec["means"].copy()
+    rec.update(agg_params(500, 40, 7, 13, 2, seed=32, dt_rows=1))
+    st = oracle_state(rec)
+    s, d = _prep(rec)
+    idx, rng, dists, dens, inv = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    a = [rec[k] for k in AGG_KEYS]
+    w, e, f, out = po.aggregate_forward(*a, idx, rng, dists, dens, inv)
+    up = agg_upstream(rec)
+    want = po.aggregate_backward(*a, idx, rng, dists, dens, w, e, f, inv, up)
+    t = [d[k].clone().requires_grad_(True) for k in AGG_KEYS]
+    got = s.aggregate_neighbors(*t)
+    assert rel_err(got.detach().cpu().numpy(), out) <= TOL
+    got.backward(torch.from_numpy(up).cuda())
+    for x, wv, key in zip(t, want, AGG_KEYS):
+        assert rel_err(x.grad.cpu().numpy(), wv) <= TOL, key

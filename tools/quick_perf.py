@@ -33,7 +33,8 @@ def micro():
     sink = torch.zeros(4, device="cuda")
     st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     sms = torch.cuda.get_device_properties(0).multi_processor_count
-    for name, f in (("ffma", L.pigs_microbench_ffma), ("ex2", L.pigs_microbench_ex2)):
+    f2 = lambda mix: (lambda c, i, s, t: L.pigs_microbench_ffma2(c, i, mix, s, t))
+    for name, f in (("ffma", L.pigs_microbench_ffma), ("ex2", L.pigs_microbench_ex2), ("ffma2", f2(0)), ("ffma2+mufu", f2(1))):
         for ctas_per_sm in (4, 8):
             ops = [0]
 
