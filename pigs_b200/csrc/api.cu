@@ -193,10 +193,10 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
             o.dddu = (fn_mask & PIGS_FN_THIRD) ? out_dddu : nullptr;
             {
                 ScopedKernelTimer tm(0, st);
-                rc = launch_forward(c, cw, m, false, ch0, ws, o, st);
-                if (rc) return rc;
-                rc = launch_forward(c, cw, m, true, ch0, ws, o, st);
-                if (rc) return rc;
+                for (int mode = 0; mode < EV_NSEG; mode++) {
+                    rc = launch_forward(c, cw, m, mode, ch0, ws, o, st);
+                    if (rc) return rc;
+                }
             }
         }
     }
@@ -244,10 +244,10 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
             BwdOut o{dL_dmeans, dL_dvalues, dL_dconics};
             {
                 ScopedKernelTimer tm(1, st);
-                rc = launch_backward(c, cw, m, false, ch0, ws, o, st);
-                if (rc) return rc;
-                rc = launch_backward(c, cw, m, true, ch0, ws, o, st);
-                if (rc) return rc;
+                for (int mode = 0; mode < EV_NSEG; mode++) {
+                    rc = launch_backward(c, cw, m, mode, ch0, ws, o, st);
+                    if (rc) return rc;
+                }
             }
         }
     }

@@ -16,7 +16,7 @@ namespace pigs {
 
 constexpr int BWD_SB = 128;  // sample records per shared-memory batch
 
-template <int D, int C, unsigned MASK, bool GENERAL>
+template <int D, int C, unsigned MASK, int MODE>
 __global__ void __launch_bounds__(EV_THREADS, 2)
     eval_bwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
                     const float4* __restrict__ recs, const uint32_t* __restrict__ rec_id,
@@ -29,7 +29,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
     constexpr int NA = nacc(D, MASK);
     constexpr int KG = bwd_kg(D, C, MASK);
     constexpr int NC = nconic(D);
-    constexpr int SEG = GENERAL ? 1 : 0;
+    constexpr int SEG = MODE;
     constexpr int LD_PER_THREAD = (BWD_SB * SV + EV_THREADS - 1) / EV_THREADS;
     __shared__ float4 sm[2][BWD_SB * SV];
     __shared__ WorkItem s_item;
@@ -107,7 +107,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 load_v4<SV>(batch + s * SV, r);
 #pragma unroll
                 for (int j = 0; j < KG; j++) {
-                    PairGeom<D, GENERAL> pg;
+                    PairGeom<D, MODE> pg;
                     pg.compute(g[j], r);
                     float f[NA];
                     pair_factors<D, MASK>(pg.a, g[j].c, f);
@@ -133,10 +133,14 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                             for (int k = 0; k < NC; k++) E[k] = fmaf(g[j].v[ch], Ec[k], E[k]);
                         }
                     }
-                    const float w = (C == 1) ? g[j].v[0] * pg.alpha : pg.alpha;
+                    // Gradient accumulation.  With r = p - S X:  dL/dmu = w C r  (because a = C X and C is
+                    // symmetric: C p - S a = C (p - S X)), so only alpha*r is accumulated per pair and the
+                    // conic (and, for one channel, the value v) is applied ONCE per Gaussian in the epilogue.
+                    // dL/dConic_ij += w (e_i X_j sym + E_ij),  e = p - S X / 2.
+                    const float w = pg.alpha;
                     if constexpr (D == 1) {
                         const float X = pg.X[0], a = pg.a[0], c0 = g[j].c[0];
-                        dm[j][0] = fmaf(w, fmaf(c0, p[0], -S * a), dm[j][0]);
+                        dm[j][0] = fmaf(w, fmaf(-S, X, p[0]), dm[j][0]);
                         if constexpr (MASK == PIGS_FN_THIRD) {
                             // backward.cu:326-329 as written: with T the (value-weighted) upstream weight,
                             // dconic += (2X^2 - 2a^2 X - (2Xa - X)X^2/2 + (a^2 - c)aX^2/2) * T * alpha
@@ -157,12 +161,9 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                             dc[j][0] = fmaf(w, fmaf(e, X, E[0]), dc[j][0]);
                         }
                     } else {
-                        const float X0 = pg.X[0], X1 = pg.X[1], a1 = pg.a[0], a2 = pg.a[1];
-                        const float c0 = g[j].c[0], c1 = g[j].c[1], c2 = g[j].c[2];
-                        const float Cp1 = fmaf(c1, p[1], c0 * p[0]);
-                        const float Cp2 = fmaf(c2, p[1], c1 * p[0]);
-                        dm[j][0] = fmaf(w, fmaf(-S, a1, Cp1), dm[j][0]);
-                        dm[j][1] = fmaf(w, fmaf(-S, a2, Cp2), dm[j][1]);
+                        const float X0 = pg.X[0], X1 = pg.X[1];
+                        dm[j][0] = fmaf(w, fmaf(-S, X0, p[0]), dm[j][0]);
+                        dm[j][1] = fmaf(w, fmaf(-S, X1, p[1]), dm[j][1]);
                         const float hS = -0.5f * S;
                         const float e1 = fmaf(hS, X0, p[0]);
                         const float e2 = fmaf(hS, X1, p[1]);
@@ -187,10 +188,15 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
         for (int j = 0; j < KG; j++) {
             if (!act[j]) continue;
             const size_t id = rec_id[it.g_begin + tid + j * EV_THREADS];
+            const float vs = (C == 1) ? g[j].v[0] : 1.0f;  // C > 1: v is already inside S, p, E
+            if constexpr (D == 1) {
+                atomicAdd(dmeans + id, vs * (g[j].c[0] * dm[j][0]));
+            } else {
+                atomicAdd(dmeans + id * 2, vs * fmaf(g[j].c[1], dm[j][1], g[j].c[0] * dm[j][0]));
+                atomicAdd(dmeans + id * 2 + 1, vs * fmaf(g[j].c[2], dm[j][1], g[j].c[1] * dm[j][0]));
+            }
 #pragma unroll
-            for (int d = 0; d < D; d++) atomicAdd(dmeans + id * D + d, dm[j][d]);
-#pragma unroll
-            for (int k = 0; k < NC; k++) atomicAdd(dconics + id * NC + k, dc[j][k]);
+            for (int k = 0; k < NC; k++) atomicAdd(dconics + id * NC + k, vs * dc[j][k]);
 #pragma unroll
             for (int ch = 0; ch < C; ch++) atomicAdd(dvalues + id * Ctot + ch0 + ch, dv[j][ch]);
         }
@@ -198,25 +204,31 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
     }
 }
 
-template <int D, int C, unsigned MASK>
-static int launch_bwd_t(const EvalCall& c, bool general, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
+template <int D, int C, unsigned MASK, int MODE>
+static void launch_bwd_m(const EvalCall& c, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
 {
-    const int grid = num_sms() * 2;
-    if (general)
-        eval_bwd_kernel<D, C, MASK, true><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, ws.rec_id, ws.srecs,
-                                                                       c.C, ch0, o.dmeans, o.dvalues, o.dconics);
+    eval_bwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, ws.rec_id, ws.srecs,
+                                                                           c.C, ch0, o.dmeans, o.dvalues, o.dconics);
+}
+
+template <int D, int C, unsigned MASK>
+static int launch_bwd_t(const EvalCall& c, int mode, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
+{
+    if (mode == EV_FAST)
+        launch_bwd_m<D, C, MASK, EV_FAST>(c, ch0, ws, o, st);
+    else if (mode == EV_SHIFT)
+        launch_bwd_m<D, C, MASK, EV_SHIFT>(c, ch0, ws, o, st);
     else
-        eval_bwd_kernel<D, C, MASK, false><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, ws.rec_id,
-                                                                        ws.srecs, c.C, ch0, o.dmeans, o.dvalues, o.dconics);
+        launch_bwd_m<D, C, MASK, EV_GENERAL>(c, ch0, ws, o, st);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
 
-int launch_backward(const EvalCall& c, int C, unsigned mask, bool general, int ch0, const EvalWs& ws, BwdOut out,
+int launch_backward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, BwdOut out,
                     cudaStream_t st)
 {
 #define BW(D_, C_, M_) \
-    if (c.D == D_ && C == C_ && mask == M_) return launch_bwd_t<D_, C_, M_>(c, general, ch0, ws, out, st);
+    if (c.D == D_ && C == C_ && mask == M_) return launch_bwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
 #define BW_ALL(D_, C_) BW(D_, C_, 1u) BW(D_, C_, 2u) BW(D_, C_, 4u) BW(D_, C_, 7u) BW(D_, C_, 8u)
     BW_ALL(2, 1) BW_ALL(2, 2) BW_ALL(1, 1) BW_ALL(1, 2)
 #undef BW_ALL

@@ -32,8 +32,8 @@ __host__ __device__ constexpr int nacc(int D, unsigned mask)
            ((mask & PIGS_FN_HESS) ? nsym(D, PIGS_FN_HESS) : 0) + ((mask & PIGS_FN_THIRD) ? nsym(D, PIGS_FN_THIRD) : 0);
 }
 __host__ __device__ constexpr int nconic(int D) { return D * (D + 1) / 2; }
-// Gaussian record: D means, D(D+1)/2 conics, C values, padded to float4s
-__host__ __device__ constexpr int grec_floats(int D, int C) { return D + nconic(D) + C; }
+// Gaussian record: D means, D(D+1)/2 conics, C values, 1 wrap-shift code (SHIFT instances), padded to float4s
+__host__ __device__ constexpr int grec_floats(int D, int C) { return D + nconic(D) + C + 1; }
 __host__ __device__ constexpr int grec_v4(int D, int C) { return (grec_floats(D, C) + 3) / 4; }
 // sample record (backward): D coords + C * nacc upstream weights, padded to float4s
 __host__ __device__ constexpr int srec_floats(int D, int C, unsigned mask) { return D + C * nacc(D, mask); }
@@ -44,8 +44,12 @@ __host__ __device__ constexpr int bwd_kg(int D, int C, unsigned mask) { return 4
 
 // ---- work lists --------------------------------------------------------------------------------
 // Built on the device by worklist_kernel (pack.cu); decoded by every CTA of the persistent
-// evaluation kernels.  seg 0 = "fast" Gaussians (no torus wrap possible inside the tile and a
-// safely positive-definite conic), seg 1 = "general" Gaussians (per-pair wrap + power>0 test).
+// evaluation kernels.  Every (tile, Gaussian) instance is in one of three classes (pack.cu flag_kernel):
+//   seg 0 FAST    : no torus wrap possible for any sample of the tile, safely positive-definite conic
+//   seg 1 SHIFT   : per dimension the reference's wrap is the SAME constant (0, -2 or +2) for every sample
+//                   of the tile, so X = fl(mu - x) + shift reproduces forward.cu:149-157 exactly
+//   seg 2 GENERAL : anything else — per-pair wrap (fmod) and the power > 0 skip
+constexpr int EV_FAST = 0, EV_SHIFT = 1, EV_GENERAL = 2, EV_NSEG = 3;
 struct TileSeg {
     uint32_t g_begin, g_count;  // packed-record range
     uint32_t s_begin, s_count;  // sorted-sample range
@@ -54,10 +58,10 @@ struct TileSeg {
 };
 
 struct WorkHeader {
-    uint32_t counter[2];  // dynamic work counters per seg
-    uint32_t items[2];    // total items per seg
+    uint32_t counter[4];  // dynamic work counters per seg
+    uint32_t items[4];    // total items per seg
     unsigned long long pairs;
-    uint32_t pad[10];
+    uint32_t pad[6];
 };
 
 struct WorkItem {
@@ -108,7 +112,16 @@ struct GaussReg {
     float m[D];
     float c[nconic(D)];
     float v[C];
+    float sh[D];  // SHIFT class: constant wrap per dimension (0, -2, +2); unused otherwise
 };
+
+// wrap-shift code stored (as int bits) in the record slot behind the values: 2 bits per dimension,
+// 0 -> 0, 1 -> -2 (1 < X < 2), 2 -> +2 (-2 < X < -1)
+__host__ __device__ __forceinline__ float shift_of_code(int code, int d)
+{
+    const int k = (code >> (2 * d)) & 3;
+    return k == 0 ? 0.0f : (k == 1 ? -2.0f : 2.0f);
+}
 
 template <int NV>
 __device__ __forceinline__ void load_v4(const float4* __restrict__ src, float* __restrict__ f)
@@ -136,6 +149,9 @@ __device__ __forceinline__ GaussReg<D, C> load_gauss(const float4* __restrict__ 
     for (int k = 0; k < nconic(D); k++) g.c[k] = f[D + k];
 #pragma unroll
     for (int ch = 0; ch < C; ch++) g.v[ch] = f[D + nconic(D) + ch];
+    const int code = __float_as_int(f[D + nconic(D) + C]);
+#pragma unroll
+    for (int d = 0; d < D; d++) g.sh[d] = shift_of_code(code, d);
     return g;
 }
 
@@ -155,8 +171,9 @@ __device__ __forceinline__ float torus_wrap(float X)
 
 // geometry of one pair: offsets X, a = Conic X, alpha.  On the GENERAL path alpha = 0 when the
 // reference would skip the pair (power > 0, forward.cu:171).
-template <int D, bool GENERAL>
+template <int D, int MODE>
 struct PairGeom {
+    static constexpr bool GENERAL = MODE == EV_GENERAL;
     float X[D], a[D], alpha;
     template <int C>
     __device__ __forceinline__ void compute(const GaussReg<D, C>& g, const float* __restrict__ x)
@@ -164,6 +181,7 @@ struct PairGeom {
 #pragma unroll
         for (int d = 0; d < D; d++) {
             X[d] = g.m[d] - x[d];
+            if constexpr (MODE == EV_SHIFT) X[d] = __fadd_rn(X[d], g.sh[d]);  // never contracted into the subtract
             if constexpr (GENERAL) X[d] = torus_wrap(X[d]);
         }
         float q;

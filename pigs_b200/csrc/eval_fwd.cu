@@ -18,7 +18,7 @@ namespace pigs {
 
 constexpr int FWD_GB = 256;  // Gaussian records per shared-memory batch
 
-template <int D, int C, unsigned MASK, bool GENERAL>
+template <int D, int C, unsigned MASK, int MODE>
 __global__ void __launch_bounds__(EV_THREADS, 2)
     eval_fwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
                     const float4* __restrict__ recs, const uint32_t* __restrict__ slist,
@@ -28,7 +28,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
     constexpr int NV = grec_v4(D, C);
     constexpr int NA = nacc(D, MASK);
     constexpr int KS = fwd_ks(D, C, MASK);
-    constexpr int SEG = GENERAL ? 1 : 0;
+    constexpr int SEG = MODE;
     __shared__ float4 sm[2][FWD_GB * NV];
     __shared__ WorkItem s_item;
     __shared__ int s_valid;
@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 const GaussReg<D, C> g = load_gauss<D, C>(batch + j * NV);
 #pragma unroll
                 for (int s = 0; s < KS; s++) {
-                    PairGeom<D, GENERAL> pg;
+                    PairGeom<D, MODE> pg;
                     pg.compute(g, x[s]);
                     float f[NA];
                     pair_factors<D, MASK>(pg.a, g.c, f);
@@ -176,25 +176,31 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
     }
 }
 
-template <int D, int C, unsigned MASK>
-static int launch_fwd_t(const EvalCall& c, bool general, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
+template <int D, int C, unsigned MASK, int MODE>
+static void launch_fwd_m(const EvalCall& c, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
 {
-    const int grid = num_sms() * 2;
-    if (general)
-        eval_fwd_kernel<D, C, MASK, true><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist, c.samples,
-                                                                       c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+    eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist, c.samples,
+                                                                           c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+}
+
+template <int D, int C, unsigned MASK>
+static int launch_fwd_t(const EvalCall& c, int mode, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
+{
+    if (mode == EV_FAST)
+        launch_fwd_m<D, C, MASK, EV_FAST>(c, ch0, ws, o, st);
+    else if (mode == EV_SHIFT)
+        launch_fwd_m<D, C, MASK, EV_SHIFT>(c, ch0, ws, o, st);
     else
-        eval_fwd_kernel<D, C, MASK, false><<<grid, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist,
-                                                                        c.samples, c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+        launch_fwd_m<D, C, MASK, EV_GENERAL>(c, ch0, ws, o, st);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
 
-int launch_forward(const EvalCall& c, int C, unsigned mask, bool general, int ch0, const EvalWs& ws, FwdOut out,
+int launch_forward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, FwdOut out,
                    cudaStream_t st)
 {
 #define FW(D_, C_, M_) \
-    if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, general, ch0, ws, out, st);
+    if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
 #define FW_ALL(D_, C_) FW(D_, C_, 1u) FW(D_, C_, 2u) FW(D_, C_, 4u) FW(D_, C_, 7u) FW(D_, C_, 8u)
     FW_ALL(2, 1) FW_ALL(2, 2) FW_ALL(1, 1) FW_ALL(1, 2)
 #undef FW_ALL

@@ -67,10 +67,12 @@ struct EvalCall {
 // per-call workspace (torch-owned, sized by pigs_eval_workspace_bytes)
 struct EvalWs {
     WorkHeader* wh;
-    uint32_t* flags;   // [R+1] general flags -> exclusive prefix
+    uint32_t* flags;   // [R+2] GENERAL flags -> exclusive prefix
+    uint32_t* flags1;  // [R+2] SHIFT flags   -> exclusive prefix
+    uint32_t* scode;   // [R]   wrap-shift code per instance
     char* scan_ws;
-    uint32_t* nfast;   // [blocks+1]
-    TileSeg* segs;     // [2][blocks]
+    uint32_t* nfast;   // [2][blocks+1]: number of FAST, then of SHIFT instances per tile
+    TileSeg* segs;     // [EV_NSEG][blocks]
     float4* recs;      // [R][grec_v4]
     uint32_t* rec_id;  // [R]
     float4* srecs;     // [N][srec_v4]   (backward only)
@@ -80,9 +82,11 @@ struct EvalWs {
         Carver c(base);
         wh = c.take<WorkHeader>(1);
         flags = c.take<uint32_t>((size_t)R + 2);
+        flags1 = c.take<uint32_t>((size_t)R + 2);
+        scode = c.take<uint32_t>((size_t)(R > 0 ? R : 1));
         scan_ws = c.take<char>(scan_ws_bytes(R));
-        nfast = c.take<uint32_t>((size_t)blocks + 1);
-        segs = c.take<TileSeg>((size_t)2 * blocks);
+        nfast = c.take<uint32_t>((size_t)2 * (blocks + 1));
+        segs = c.take<TileSeg>((size_t)EV_NSEG * blocks);
         recs = c.take<float4>((size_t)(R > 0 ? R : 1) * gv4);
         rec_id = c.take<uint32_t>((size_t)(R > 0 ? R : 1));
         srecs = c.take<float4>((size_t)(N > 0 ? N : 1) * sv4);
@@ -100,12 +104,12 @@ int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float*
 struct FwdOut {
     float *u, *du, *ddu, *dddu;
 };
-int launch_forward(const EvalCall& c, int C, unsigned mask, bool general, int ch0, const EvalWs& ws, FwdOut out,
+int launch_forward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, FwdOut out,
                    cudaStream_t st);
 struct BwdOut {
     float *dmeans, *dvalues, *dconics;
 };
-int launch_backward(const EvalCall& c, int C, unsigned mask, bool general, int ch0, const EvalWs& ws, BwdOut out,
+int launch_backward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, BwdOut out,
                     cudaStream_t st);
 
 }  // namespace pigs

@@ -10,41 +10,62 @@
 
 namespace pigs {
 
-// FAST  <=>  conic safely positive definite  AND  for every sample of the tile |mu - x| <= 1 in every
-// dimension (so the reference's torus wrap, forward.cu:149-157, is the identity and power <= 0).
-// fl(mu - x) is monotone in x, so testing the two ends of the tile's sample bounding box is exact.
+// Classification of every (tile, Gaussian) list entry (classes: eval_common.cuh).
+// fl(mu - x) is monotone in x, so testing the two ends of the tile's sample bounding box is exact:
+//   FAST  : conic safely positive definite and |mu - x| <= 1 in every dimension for every sample of the tile
+//           (the reference's torus wrap, forward.cu:149-157, is the identity and power <= 0)
+//   SHIFT : conic safely PD and per dimension EITHER |X| <= 1 for all samples, OR 1 < X < 2 for all (wrap = X - 2
+//           exactly, fmod(X,2) == X), OR -2 < X < -1 for all (wrap = X + 2)
+//   GENERAL otherwise.
 template <int D>
 __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __restrict__ list,
                                                    const uint32_t* __restrict__ tiles, const float* __restrict__ means,
                                                    const float* __restrict__ conics, const float* __restrict__ bbox,
-                                                   uint32_t* __restrict__ flags)
+                                                   uint32_t* __restrict__ flags_general, uint32_t* __restrict__ flags_shift,
+                                                   uint32_t* __restrict__ scode)
 {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= R) return;
     const uint32_t id = list[e], t = tiles[e];
-    bool fast;
+    bool pd;
     if constexpr (D == 1) {
-        fast = conics[id] > 0.0f;
+        pd = conics[id] > 0.0f;
     } else {
         const float c0 = conics[3 * (size_t)id], c1 = conics[3 * (size_t)id + 1], c2 = conics[3 * (size_t)id + 2];
         const float cc = c0 * c2;
-        fast = (c0 > 0.0f) && (c2 > 0.0f) && (cc - c1 * c1 >= 1e-4f * cc) && (cc < 3.0e38f);
+        pd = (c0 > 0.0f) && (c2 > 0.0f) && (cc - c1 * c1 >= 1e-4f * cc) && (cc < 3.0e38f);
     }
+    bool ok = pd;
+    uint32_t code = 0;
 #pragma unroll
     for (int d = 0; d < D; d++) {
         const float m = means[(size_t)id * D + d];
         const float xlo = bbox[(size_t)t * 2 * D + d], xhi = bbox[(size_t)t * 2 * D + D + d];
-        const float Xa = m - xhi, Xb = m - xlo;
-        fast = fast && (Xa >= -1.0f) && (Xb <= 1.0f);
+        const float Xa = m - xhi, Xb = m - xlo;  // Xa <= X <= Xb for every sample of the tile
+        uint32_t k = 3;
+        if (Xa >= -1.0f && Xb <= 1.0f)
+            k = 0;
+        else if (Xa > 1.0f && Xb < 2.0f)
+            k = 1;
+        else if (Xa > -2.0f && Xb < -1.0f)
+            k = 2;
+        if (k == 3) ok = false;
+        code |= (k & 3u) << (2 * d);
     }
-    flags[e] = fast ? 0u : 1u;
+    const bool general = !ok;
+    flags_general[e] = general ? 1u : 0u;
+    flags_shift[e] = (!general && code != 0u) ? 1u : 0u;
+    scode[e] = general ? 0u : code;
 }
 
-// gen_prefix = exclusive scan of flags (with total at [R]).  Writes records in partitioned order.
+// gen_prefix / shift_prefix = exclusive scans of the two flag arrays (with totals at [R]).  Writes the
+// records in partitioned order [fast | shift | general] within each tile (stable within each class).
 template <int D, int C>
 __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32_t* __restrict__ list,
                                                          const uint32_t* __restrict__ tiles,
                                                          const uint32_t* __restrict__ gen_prefix,
+                                                         const uint32_t* __restrict__ shift_prefix,
+                                                         const uint32_t* __restrict__ scode,
                                                          const uint2* __restrict__ ranges, int blocks,
                                                          const float* __restrict__ means, const float* __restrict__ values,
                                                          const float* __restrict__ conics, int Ctot, int ch0,
@@ -58,10 +79,18 @@ __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32
     const uint2 r = ranges[t];
     const uint32_t gen_before = gen_prefix[e] - gen_prefix[r.x];
     const uint32_t gen_total = gen_prefix[r.y] - gen_prefix[r.x];
-    const uint32_t nf = (r.y - r.x) - gen_total;
+    const uint32_t sh_before = shift_prefix[e] - shift_prefix[r.x];
+    const uint32_t sh_total = shift_prefix[r.y] - shift_prefix[r.x];
+    const uint32_t nf = (r.y - r.x) - gen_total - sh_total;
     const bool general = gen_prefix[e + 1] != gen_prefix[e];
-    const uint32_t pos = general ? r.x + nf + gen_before : r.x + (uint32_t)(e - r.x) - gen_before;
-    if (e == r.x) nfast[t] = nf;
+    const bool shift = shift_prefix[e + 1] != shift_prefix[e];
+    const uint32_t before = (uint32_t)(e - r.x);
+    const uint32_t pos = general ? r.x + nf + sh_total + gen_before
+                                 : (shift ? r.x + nf + sh_before : r.x + before - gen_before - sh_before);
+    if (e == r.x) {
+        nfast[t] = nf;
+        nfast[blocks + 1 + t] = sh_total;
+    }
     constexpr int NV = grec_v4(D, C);
     float f[NV * 4];
 #pragma unroll
@@ -72,6 +101,7 @@ __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32
     for (int k = 0; k < nconic(D); k++) f[D + k] = conics[(size_t)id * nconic(D) + k];
 #pragma unroll
     for (int ch = 0; ch < C; ch++) f[D + nconic(D) + ch] = values[(size_t)id * Ctot + ch0 + ch];
+    f[D + nconic(D) + C] = __int_as_float((int)scode[e]);
 #pragma unroll
     for (int i = 0; i < NV; i++) recs[(size_t)pos * NV + i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
     rec_id[pos] = id;
@@ -133,37 +163,43 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
     for (int k = 0; k < SV; k++) srecs[(size_t)i * SV + k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
 }
 
-// One CTA.  For every tile: the fast and general segments and how many work items each yields.
+// One CTA.  For every tile: the FAST / SHIFT / GENERAL segments and how many work items each yields.
 //   forward : stationary = samples in chunks of `chunk`, streamed = Gaussians split `split_hint` ways
 //   backward: stationary = Gaussians in chunks of `chunk`, streamed = samples split `split_hint` ways
 __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* __restrict__ ranges,
                                                        const uint2* __restrict__ sample_ranges,
                                                        const uint32_t* __restrict__ nfast, uint32_t chunk,
                                                        uint32_t split_hint, uint32_t min_stream, int stream_is_gauss,
-                                                       TileSeg* __restrict__ segs /* [2][blocks] */, WorkHeader* __restrict__ wh)
+                                                       TileSeg* __restrict__ segs /* [EV_NSEG][blocks] */,
+                                                       WorkHeader* __restrict__ wh)
 {
     __shared__ uint32_t s_scan[256];
-    __shared__ uint32_t s_carry[2];
+    __shared__ uint32_t s_carry[EV_NSEG];
     __shared__ unsigned long long s_pairs;
     if (threadIdx.x == 0) {
-        s_carry[0] = s_carry[1] = 0;
+        for (int k = 0; k < EV_NSEG; k++) s_carry[k] = 0;
         s_pairs = 0ull;
     }
     __syncthreads();
     unsigned long long my_pairs = 0;
     for (int base = 0; base < blocks; base += 256) {
         const int t = base + threadIdx.x;
-        TileSeg sg[2];
-        uint32_t items[2] = {0, 0};
+        TileSeg sg[EV_NSEG];
+        uint32_t items[EV_NSEG];
+#pragma unroll
+        for (int k = 0; k < EV_NSEG; k++) items[k] = 0;
         if (t < blocks) {
             const uint2 gr = ranges[t], sr = sample_ranges[t];
             const uint32_t G = gr.y - gr.x, S = sr.y - sr.x;
             const uint32_t nf = (G > 0) ? nfast[t] : 0;
+            const uint32_t ns = (G > 0) ? nfast[blocks + 1 + t] : 0;
             my_pairs += (unsigned long long)G * S;
+            const uint32_t begin[EV_NSEG] = {gr.x, gr.x + nf, gr.x + nf + ns};
+            const uint32_t count[EV_NSEG] = {nf, ns, G - nf - ns};
 #pragma unroll
-            for (int k = 0; k < 2; k++) {
-                sg[k].g_begin = k == 0 ? gr.x : gr.x + nf;
-                sg[k].g_count = k == 0 ? nf : G - nf;
+            for (int k = 0; k < EV_NSEG; k++) {
+                sg[k].g_begin = begin[k];
+                sg[k].g_count = count[k];
                 sg[k].s_begin = sr.x;
                 sg[k].s_count = S;
                 const uint32_t stat_n = stream_is_gauss ? sg[k].s_count : sg[k].g_count;
@@ -178,7 +214,7 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
             }
         }
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < EV_NSEG; k++) {
             // block exclusive scan of items[k]
             s_scan[threadIdx.x] = items[k];
             __syncthreads();
@@ -202,9 +238,10 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
     atomicAdd(&s_pairs, my_pairs);
     __syncthreads();
     if (threadIdx.x == 0) {
-        wh->counter[0] = wh->counter[1] = 0;
-        wh->items[0] = s_carry[0];
-        wh->items[1] = s_carry[1];
+        for (int k = 0; k < EV_NSEG; k++) {
+            wh->counter[k] = 0;
+            wh->items[k] = s_carry[k];
+        }
         wh->pairs = s_pairs;
     }
 }
@@ -217,16 +254,18 @@ int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStr
     const int64_t R = c.R;
     const unsigned nb = (unsigned)((R + 255) / 256);
     if (c.D == 2)
-        flag_kernel<2><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags);
+        flag_kernel<2><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags, ws.flags1, ws.scode);
     else
-        flag_kernel<1><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags);
+        flag_kernel<1><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags, ws.flags1, ws.scode);
     PIGS_LAUNCH_CHECK();
     int rc = exclusive_scan_u32(ws.flags, ws.flags, R, true, ws.scan_ws, st);
     if (rc) return rc;
-    PIGS_CHECK(cudaMemsetAsync(ws.nfast, 0, (size_t)(c.blocks + 1) * sizeof(uint32_t), st));
+    rc = exclusive_scan_u32(ws.flags1, ws.flags1, R, true, ws.scan_ws, st);
+    if (rc) return rc;
+    PIGS_CHECK(cudaMemsetAsync(ws.nfast, 0, (size_t)2 * (c.blocks + 1) * sizeof(uint32_t), st));
 #define PACK(D_, C_)                                                                                                  \
-    pack_gauss_kernel<D_, C_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, c.ranges, c.blocks, c.means, c.values, \
-                                                  c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
+    pack_gauss_kernel<D_, C_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, ws.flags1, ws.scode, c.ranges, c.blocks, \
+                                                  c.means, c.values, c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
     if (c.D == 2 && C == 1)
         PACK(2, 1);
     else if (c.D == 2 && C == 2)
