@@ -193,7 +193,11 @@ struct PairGeom {
             a[1] = fmaf(g.c[2], X[1], g.c[1] * X[0]);
             q = fmaf(a[1], X[1], a[0] * X[0]);
         }
+#ifdef PIGS_DBG_NOMUFU  // issue-rate experiment only (tools/quick_perf.py --variants): same FP32 count, no MUFU
+        alpha = __fadd_rn(__fmul_rn(q, KH), 1.0f);
+#else
         alpha = ex2_approx(q * KH);
+#endif
         if constexpr (GENERAL) {
             // power = -q/2 > 0  <=>  q < 0 ; NaN falls through like the reference's comparison
             if (q < 0.0f) alpha = 0.0f;

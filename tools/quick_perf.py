@@ -9,7 +9,11 @@ import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-from pigs_b200 import GaussianSampler, _lib  # noqa: E402
+from pigs_b200 import _lib  # noqa: E402
+for _i, _a in enumerate(sys.argv):  # --lib <path>: time a debug build of the library (issue-rate experiments)
+    if _a == "--lib":
+        _lib._SO = os.path.abspath(sys.argv[_i + 1])
+from pigs_b200 import GaussianSampler  # noqa: E402
 from tests.fixtures import synthetic  # noqa: E402
 
 
@@ -93,7 +97,8 @@ if __name__ == "__main__":
     if "--ref" in sys.argv:
         ref_perf(20_000, 200_000)
         sys.exit(0)
-    micro()
+    if "--no-micro" not in sys.argv:
+        micro()
     perf(100_000, 1_000_000, "C2")
     if "--big" in sys.argv:
         perf(1_000_000, 4_000_000, "C3")
