@@ -152,7 +152,7 @@ size_t pigs_eval_workspace_bytes(int64_t num_rendered, int64_t N, int blocks, in
 {
     (void)fn_mask;
     const int Cg = C >= 2 ? 2 : 1;
-    return EvalWs(nullptr, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg)).bytes;
+    return EvalWs(nullptr, num_rendered, N, blocks, frec_v4(D, Cg), max_sv4(D, Cg)).bytes;
 }
 
 int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, int blocks, int64_t num_rendered,
@@ -174,11 +174,11 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
     if (num_rendered == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     const int Cg = C >= 2 ? 2 : 1;
-    EvalWs ws(workspace, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg));
+    EvalWs ws(workspace, num_rendered, N, blocks, frec_v4(D, Cg), max_sv4(D, Cg));
 
     for (int ch0 = 0; ch0 < C; ch0 += 2) {
         const int cw = (C - ch0) >= 2 ? 2 : 1;
-        rc = stage_gaussians(c, cw, ch0, ws, st);
+        rc = stage_gaussians(c, cw, ch0, true, ws, st);
         if (rc) return rc;
         unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
@@ -225,11 +225,11 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
     if (num_rendered == 0 || fn_mask == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     const int Cg = C >= 2 ? 2 : 1;
-    EvalWs ws(workspace, num_rendered, N, blocks, grec_v4(D, Cg), max_sv4(D, Cg));
+    EvalWs ws(workspace, num_rendered, N, blocks, frec_v4(D, Cg), max_sv4(D, Cg));
 
     for (int ch0 = 0; ch0 < C; ch0 += 2) {
         const int cw = (C - ch0) >= 2 ? 2 : 1;
-        rc = stage_gaussians(c, cw, ch0, ws, st);
+        rc = stage_gaussians(c, cw, ch0, false, ws, st);
         if (rc) return rc;
         unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {

@@ -35,6 +35,12 @@ __host__ __device__ constexpr int nconic(int D) { return D * (D + 1) / 2; }
 // Gaussian record: D means, D(D+1)/2 conics, C values, 1 wrap-shift code (SHIFT instances), padded to float4s
 __host__ __device__ constexpr int grec_floats(int D, int C) { return D + nconic(D) + C + 1; }
 __host__ __device__ constexpr int grec_v4(int D, int C) { return (grec_floats(D, C) + 3) / 4; }
+// forward record: D means, K = KH*Conic (so that log2(alpha) = X.(K X) needs no scaling multiply), M = KH^2*Conic
+// (the constant of the scaled Hessian factor a'a'^T - M with a' = K X = KH*a), C values, 1 wrap-shift code.
+// Accumulating in the scaled variables makes the gradient come out times KH, the Hessian times KH^2 and the
+// third derivative times KH^3 — constants applied once per output element in the epilogue.
+__host__ __device__ constexpr int frec_floats(int D, int C) { return D + 2 * nconic(D) + C + 1; }
+__host__ __device__ constexpr int frec_v4(int D, int C) { return (frec_floats(D, C) + 3) / 4; }
 // sample record (backward): D coords + C * nacc upstream weights, padded to float4s
 __host__ __device__ constexpr int srec_floats(int D, int C, unsigned mask) { return D + C * nacc(D, mask); }
 __host__ __device__ constexpr int srec_v4(int D, int C, unsigned mask) { return (srec_floats(D, C, mask) + 3) / 4; }
@@ -150,6 +156,38 @@ __device__ __forceinline__ GaussReg<D, C> load_gauss(const float4* __restrict__ 
 #pragma unroll
     for (int ch = 0; ch < C; ch++) g.v[ch] = f[D + nconic(D) + ch];
     const int code = __float_as_int(f[D + nconic(D) + C]);
+#pragma unroll
+    for (int d = 0; d < D; d++) g.sh[d] = shift_of_code(code, d);
+    return g;
+}
+
+// forward-kernel view of a record (layout: frec_floats)
+template <int D, int C>
+struct GaussFwd {
+    float m[D];
+    float k[nconic(D)];   // KH * conic
+    float mm[nconic(D)];  // KH^2 * conic
+    float v[C];
+    float sh[D];
+};
+
+template <int D, int C>
+__device__ __forceinline__ GaussFwd<D, C> load_gauss_fwd(const float4* __restrict__ rec)
+{
+    constexpr int NV = frec_v4(D, C);
+    constexpr int NC = nconic(D);
+    float f[NV * 4];
+    load_v4<NV>(rec, f);
+    GaussFwd<D, C> g;
+#pragma unroll
+    for (int d = 0; d < D; d++) g.m[d] = f[d];
+#pragma unroll
+    for (int k = 0; k < NC; k++) g.k[k] = f[D + k];
+#pragma unroll
+    for (int k = 0; k < NC; k++) g.mm[k] = f[D + NC + k];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) g.v[ch] = f[D + 2 * NC + ch];
+    const int code = __float_as_int(f[D + 2 * NC + C]);
 #pragma unroll
     for (int d = 0; d < D; d++) g.sh[d] = shift_of_code(code, d);
     return g;

@@ -14,9 +14,113 @@
 // The path is FP32-FMA-issue bound (no dense contraction => no tensor cores).
 #include "layouts.cuh"
 
+#ifndef PIGS_FWD_ASM_ACC
+#define PIGS_FWD_ASM_ACC 1
+#endif
+
 namespace pigs {
 
 constexpr int FWD_GB = 256;  // Gaussian records per shared-memory batch
+
+// One Gaussian against the KS samples a thread holds, written OP-MAJOR: every step is applied to all KS samples
+// before the next step starts.  On B200 an FP32 instruction that needs three register-file reads occupies the
+// dispatch port for two cycles (tools/mb_issue.cu; operands served by the reuse cache, immediates and constants
+// are free), so the order is chosen to keep the Gaussian's parameter in the same operand slot of consecutive
+// instructions (reuse-cache hits) in the geometry phase, and the pair's weight w in the accumulation phase.
+// Scaled variables: a' = K X (= KH a), e = X.a' = log2(alpha); factors in (a', M) come out times KH^order.
+template <int D, int C, unsigned MASK, int MODE, int KS, int S0, int HS>
+__device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, const float (&x)[KS][D],
+                                                 float (&acc)[KS][C][nacc(D, MASK)])
+{
+    constexpr int NA = nacc(D, MASK);
+    float X[D][HS], a[D][HS], al[HS];
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+#pragma unroll
+        for (int s = 0; s < HS; s++) X[d][s] = g.m[d] - x[S0 + s][d];
+        if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+            for (int s = 0; s < HS; s++) X[d][s] = __fadd_rn(X[d][s], g.sh[d]);  // never contracted into the subtract
+        }
+        if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+            for (int s = 0; s < HS; s++) X[d][s] = torus_wrap(X[d][s]);
+        }
+    }
+    if constexpr (D == 1) {
+#pragma unroll
+        for (int s = 0; s < HS; s++) a[0][s] = g.k[0] * X[0][s];
+#pragma unroll
+        for (int s = 0; s < HS; s++) al[s] = a[0][s] * X[0][s];
+    } else {
+#pragma unroll
+        for (int s = 0; s < HS; s++) a[0][s] = g.k[0] * X[0][s];
+#pragma unroll
+        for (int s = 0; s < HS; s++) a[1][s] = g.k[1] * X[0][s];
+#pragma unroll
+        for (int s = 0; s < HS; s++) a[0][s] = fmaf(g.k[1], X[1][s], a[0][s]);
+#pragma unroll
+        for (int s = 0; s < HS; s++) a[1][s] = fmaf(g.k[2], X[1][s], a[1][s]);
+#pragma unroll
+        for (int s = 0; s < HS; s++) al[s] = a[0][s] * X[0][s];
+#pragma unroll
+        for (int s = 0; s < HS; s++) al[s] = fmaf(a[1][s], X[1][s], al[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < HS; s++) {
+        const float e = al[s];  // = KH * q = log2(alpha)
+#ifdef PIGS_DBG_NOMUFU  // issue-rate experiment only
+        al[s] = e + 1.0f;
+#else
+        al[s] = ex2_approx(e);
+#endif
+        if constexpr (MODE == EV_GENERAL) {
+            // power = -q/2 > 0  <=>  e > 0 (KH < 0); NaN falls through like the reference's comparison (forward.cu:171)
+            if (e > 0.0f) al[s] = 0.0f;
+        }
+    }
+    // accumulation, sample-major: factors then the NA accumulators of one (sample, channel) back to back
+#pragma unroll
+    for (int s = 0; s < HS; s++) {
+        float av[D], f[NA];
+#pragma unroll
+        for (int d = 0; d < D; d++) av[d] = a[d][s];
+        pair_factors<D, MASK>(av, g.mm, f);
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) {
+            const float w = g.v[ch] * al[s];
+#pragma unroll
+            for (int k = 0; k < NA; k++) {
+#if PIGS_FWD_ASM_ACC
+                // fixed operand order: w stays in operand slot A of the whole group (reuse cache), the value
+                // accumulator goes first because its add needs only two register reads
+                if (k == 0 && (MASK & PIGS_FN_VALUE))
+                    asm volatile("add.rn.f32 %0, %1, %0;" : "+f"(acc[S0 + s][ch][0]) : "f"(w));
+                else
+                    asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc[S0 + s][ch][k]) : "f"(w), "f"(f[k]));
+#else
+                if (k == 0 && (MASK & PIGS_FN_VALUE))
+                    acc[S0 + s][ch][0] += w;
+                else
+                    acc[S0 + s][ch][k] = fmaf(w, f[k], acc[S0 + s][ch][k]);
+#endif
+            }
+        }
+    }
+}
+
+template <int D, int C, unsigned MASK, int MODE, int KS>
+__device__ __forceinline__ void fwd_one_gaussian(const GaussFwd<D, C>& g, const float (&x)[KS][D],
+                                                 float (&acc)[KS][C][nacc(D, MASK)])
+{
+#ifndef PIGS_FWD_HS
+#define PIGS_FWD_HS 8
+#endif
+    constexpr int HS = KS < PIGS_FWD_HS ? KS : PIGS_FWD_HS;
+    static_assert(KS <= 2 * HS, "two blocks cover KS");
+    fwd_gaussian_block<D, C, MASK, MODE, KS, 0, HS>(g, x, acc);
+    if constexpr (KS > HS) fwd_gaussian_block<D, C, MASK, MODE, KS, HS, HS>(g, x, acc);
+}
 
 template <int D, int C, unsigned MASK, int MODE>
 __global__ void __launch_bounds__(EV_THREADS, 2)
@@ -25,7 +129,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                     const float* __restrict__ samples, int Ctot, int ch0, float* __restrict__ out_u,
                     float* __restrict__ out_du, float* __restrict__ out_ddu, float* __restrict__ out_dddu)
 {
-    constexpr int NV = grec_v4(D, C);
+    constexpr int NV = frec_v4(D, C);
     constexpr int NA = nacc(D, MASK);
     constexpr int KS = fwd_ks(D, C, MASK);
     constexpr int SEG = MODE;
@@ -83,30 +187,12 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                     pre[k] = o < total_v4 ? src[o] : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
-            int cnt = min((int)FWD_GB, (int)it.g_count - b * FWD_GB);
-            cnt = (cnt + 1) & ~1;  // zero-padded records contribute exactly 0
+            const int cnt = min((int)FWD_GB, (int)it.g_count - b * FWD_GB);
             const float4* __restrict__ batch = sm[buf];
-#pragma unroll 2
+#pragma unroll 1
             for (int j = 0; j < cnt; j++) {
-                const GaussReg<D, C> g = load_gauss<D, C>(batch + j * NV);
-#pragma unroll
-                for (int s = 0; s < KS; s++) {
-                    PairGeom<D, MODE> pg;
-                    pg.compute(g, x[s]);
-                    float f[NA];
-                    pair_factors<D, MASK>(pg.a, g.c, f);
-#pragma unroll
-                    for (int ch = 0; ch < C; ch++) {
-                        const float w = g.v[ch] * pg.alpha;
-#pragma unroll
-                        for (int k = 0; k < NA; k++) {
-                            if (k == 0 && (MASK & PIGS_FN_VALUE))
-                                acc[s][ch][0] += w;
-                            else
-                                acc[s][ch][k] = fmaf(w, f[k], acc[s][ch][k]);
-                        }
-                    }
-                }
+                const GaussFwd<D, C> g = load_gauss_fwd<D, C>(batch + j * NV);
+                fwd_one_gaussian<D, C, MASK, MODE, KS>(g, x, acc);
             }
             if (b + 1 < nbatch) {
 #pragma unroll
@@ -115,7 +201,8 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             __syncthreads();
         }
 
-        // ---- epilogue: one RED.ADD per output element per item ----
+        // ---- epilogue: undo the KH^order scaling, one RED.ADD per output element per item ----
+        constexpr float IK1 = 1.0f / KH, IK2 = IK1 * IK1, IK3 = IK2 * IK1;
 #pragma unroll
         for (int s = 0; s < KS; s++) {
             if (sid[s] == 0xffffffffu) continue;
@@ -131,41 +218,44 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 if constexpr ((MASK & PIGS_FN_DERIV) != 0) {
 #pragma unroll
                     for (int d = 0; d < D; d++) {
-                        if (out_du) atomicAdd(out_du + (id * D + d) * Ctot + c, acc[s][ch][k]);
+                        if (out_du) atomicAdd(out_du + (id * D + d) * Ctot + c, IK1 * acc[s][ch][k]);
                         k++;
                     }
                 }
                 if constexpr ((MASK & PIGS_FN_HESS) != 0) {
                     if constexpr (D == 1) {
-                        if (out_ddu) atomicAdd(out_ddu + id * Ctot + c, acc[s][ch][k]);
+                        if (out_ddu) atomicAdd(out_ddu + id * Ctot + c, IK2 * acc[s][ch][k]);
                         k++;
                     } else {
                         if (out_ddu) {
                             float* o = out_ddu + id * 4 * Ctot + c;
-                            atomicAdd(o, acc[s][ch][k]);
-                            atomicAdd(o + Ctot, acc[s][ch][k + 1]);
-                            atomicAdd(o + 2 * Ctot, acc[s][ch][k + 1]);
-                            atomicAdd(o + 3 * Ctot, acc[s][ch][k + 2]);
+                            const float hxy = IK2 * acc[s][ch][k + 1];
+                            atomicAdd(o, IK2 * acc[s][ch][k]);
+                            atomicAdd(o + Ctot, hxy);
+                            atomicAdd(o + 2 * Ctot, hxy);
+                            atomicAdd(o + 3 * Ctot, IK2 * acc[s][ch][k + 2]);
                         }
                         k += 3;
                     }
                 }
                 if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
                     if constexpr (D == 1) {
-                        if (out_dddu) atomicAdd(out_dddu + id * Ctot + c, acc[s][ch][k]);
+                        if (out_dddu) atomicAdd(out_dddu + id * Ctot + c, IK3 * acc[s][ch][k]);
                         k++;
                     } else {
                         if (out_dddu) {
                             // flat [x|y]^3 index -> unique component (forward.cu:264-271)
                             float* o = out_dddu + id * 8 * Ctot + c;
-                            atomicAdd(o, acc[s][ch][k]);
-                            atomicAdd(o + 1 * Ctot, acc[s][ch][k + 1]);
-                            atomicAdd(o + 2 * Ctot, acc[s][ch][k + 1]);
-                            atomicAdd(o + 3 * Ctot, acc[s][ch][k + 2]);
-                            atomicAdd(o + 4 * Ctot, acc[s][ch][k + 1]);
-                            atomicAdd(o + 5 * Ctot, acc[s][ch][k + 2]);
-                            atomicAdd(o + 6 * Ctot, acc[s][ch][k + 2]);
-                            atomicAdd(o + 7 * Ctot, acc[s][ch][k + 3]);
+                            const float t0 = IK3 * acc[s][ch][k], t1 = IK3 * acc[s][ch][k + 1];
+                            const float t2 = IK3 * acc[s][ch][k + 2], t3 = IK3 * acc[s][ch][k + 3];
+                            atomicAdd(o, t0);
+                            atomicAdd(o + 1 * Ctot, t1);
+                            atomicAdd(o + 2 * Ctot, t1);
+                            atomicAdd(o + 3 * Ctot, t2);
+                            atomicAdd(o + 4 * Ctot, t1);
+                            atomicAdd(o + 5 * Ctot, t2);
+                            atomicAdd(o + 6 * Ctot, t2);
+                            atomicAdd(o + 7 * Ctot, t3);
                         }
                         k += 4;
                     }

@@ -73,7 +73,7 @@ struct EvalWs {
     char* scan_ws;
     uint32_t* nfast;   // [2][blocks+1]: number of FAST, then of SHIFT instances per tile
     TileSeg* segs;     // [EV_NSEG][blocks]
-    float4* recs;      // [R][grec_v4]
+    float4* recs;      // [R][frec_v4] (forward layout) or [R][grec_v4] (backward layout)
     uint32_t* rec_id;  // [R]
     float4* srecs;     // [N][srec_v4]   (backward only)
     size_t bytes;
@@ -94,7 +94,7 @@ struct EvalWs {
     }
 };
 
-int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStream_t st);
+int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, const EvalWs& ws, cudaStream_t st);
 int stage_worklist(const EvalCall& c, const EvalWs& ws, uint32_t chunk, uint32_t split_hint, uint32_t min_stream,
                    bool stream_is_gauss, cudaStream_t st);
 int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float* gV, const float* gD, const float* gH,

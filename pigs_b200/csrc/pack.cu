@@ -60,7 +60,7 @@ __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __
 
 // gen_prefix / shift_prefix = exclusive scans of the two flag arrays (with totals at [R]).  Writes the
 // records in partitioned order [fast | shift | general] within each tile (stable within each class).
-template <int D, int C>
+template <int D, int C, bool FWD>
 __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32_t* __restrict__ list,
                                                          const uint32_t* __restrict__ tiles,
                                                          const uint32_t* __restrict__ gen_prefix,
@@ -91,17 +91,31 @@ __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32
         nfast[t] = nf;
         nfast[blocks + 1 + t] = sh_total;
     }
-    constexpr int NV = grec_v4(D, C);
+    constexpr int NV = FWD ? frec_v4(D, C) : grec_v4(D, C);
+    constexpr int NC = nconic(D);
     float f[NV * 4];
 #pragma unroll
     for (int i = 0; i < NV * 4; i++) f[i] = 0.0f;
 #pragma unroll
     for (int d = 0; d < D; d++) f[d] = means[(size_t)id * D + d];
+    if constexpr (FWD) {
+        // forward layout (eval_common.cuh frec_floats): K = KH*conic, M = KH*K
 #pragma unroll
-    for (int k = 0; k < nconic(D); k++) f[D + k] = conics[(size_t)id * nconic(D) + k];
+        for (int k = 0; k < NC; k++) {
+            const float kk = __fmul_rn(KH, conics[(size_t)id * NC + k]);
+            f[D + k] = kk;
+            f[D + NC + k] = __fmul_rn(KH, kk);
+        }
 #pragma unroll
-    for (int ch = 0; ch < C; ch++) f[D + nconic(D) + ch] = values[(size_t)id * Ctot + ch0 + ch];
-    f[D + nconic(D) + C] = __int_as_float((int)scode[e]);
+        for (int ch = 0; ch < C; ch++) f[D + 2 * NC + ch] = values[(size_t)id * Ctot + ch0 + ch];
+        f[D + 2 * NC + C] = __int_as_float((int)scode[e]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < NC; k++) f[D + k] = conics[(size_t)id * NC + k];
+#pragma unroll
+        for (int ch = 0; ch < C; ch++) f[D + NC + ch] = values[(size_t)id * Ctot + ch0 + ch];
+        f[D + NC + C] = __int_as_float((int)scode[e]);
+    }
 #pragma unroll
     for (int i = 0; i < NV; i++) recs[(size_t)pos * NV + i] = make_float4(f[4 * i], f[4 * i + 1], f[4 * i + 2], f[4 * i + 3]);
     rec_id[pos] = id;
@@ -249,7 +263,7 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
 // ---------------------------------------------------------------------------------------------
 // host-side staging entry points (called from api.cu)
 // ---------------------------------------------------------------------------------------------
-int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStream_t st)
+int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, const EvalWs& ws, cudaStream_t st)
 {
     const int64_t R = c.R;
     const unsigned nb = (unsigned)((R + 255) / 256);
@@ -263,9 +277,16 @@ int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStr
     rc = exclusive_scan_u32(ws.flags1, ws.flags1, R, true, ws.scan_ws, st);
     if (rc) return rc;
     PIGS_CHECK(cudaMemsetAsync(ws.nfast, 0, (size_t)2 * (c.blocks + 1) * sizeof(uint32_t), st));
-#define PACK(D_, C_)                                                                                                  \
-    pack_gauss_kernel<D_, C_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, ws.flags1, ws.scode, c.ranges, c.blocks, \
-                                                  c.means, c.values, c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
+#define PACK1(D_, C_, F_)                                                                                               \
+    pack_gauss_kernel<D_, C_, F_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, ws.flags1, ws.scode, c.ranges, c.blocks, \
+                                                      c.means, c.values, c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
+#define PACK(D_, C_)       \
+    do {                   \
+        if (fwd_layout)    \
+            PACK1(D_, C_, true);  \
+        else               \
+            PACK1(D_, C_, false); \
+    } while (0)
     if (c.D == 2 && C == 1)
         PACK(2, 1);
     else if (c.D == 2 && C == 2)
@@ -275,6 +296,7 @@ int stage_gaussians(const EvalCall& c, int C, int ch0, const EvalWs& ws, cudaStr
     else
         PACK(1, 2);
 #undef PACK
+#undef PACK1
     PIGS_LAUNCH_CHECK();
     return 0;
 }

@@ -127,13 +127,14 @@ __global__ void __launch_bounds__(256) k(int iters, float* sink, const float* sr
     __shared__ float4 sm[64];
     if (threadIdx.x < 64) sm[threadIdx.x] = make_float4(src[threadIdx.x], 1.f, 2.f, 3.f);
     __syncthreads();
-    float a[N], x[N], y[N], m[4];
+    float a[N], x[N], y[N], z[N], m[4];
     const float b = 1.0000001f + 1e-9f * threadIdx.x, c = 1e-7f + src[1];
 #pragma unroll
     for (int i = 0; i < N; i++) {
         a[i] = 1.0f + i * 1e-3f + threadIdx.x * 1e-6f;
         x[i] = 1.0f + src[(threadIdx.x + i) & 511] * 1e-6f;
         y[i] = 1e-6f * src[(threadIdx.x + 37 * i + N) & 511] + 1e-7f;
+        z[i] = 1.0f + 1e-6f * src[(threadIdx.x + 41 * i + 3) & 511];
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) m[i] = -0.5f - src[(threadIdx.x + i + 99) & 511];
@@ -146,6 +147,10 @@ __global__ void __launch_bounds__(256) k(int iters, float* sink, const float* sr
                 if (MODE == 0 || MODE == 7) a[i] = fmaf(a[i], b, c);
                 if (MODE == 1 || MODE == 3 || MODE == 4 || MODE == 8 || MODE == 9) a[i] = fmaf(x[i], y[i], a[i]);
                 if (MODE == 2) a[i] = fmaf(b, y[i], a[i]);
+                if (MODE == 10) {  // shared-operand FFMA alternating with an unrelated 2-operand FMUL
+                    a[i] = fmaf(b, y[i], a[i]);
+                    x[i] = x[i] * z[i];
+                }
                 if (MODE == 5) a[i] = x[i] + a[i];
                 if (MODE == 6) a[i] = x[i] * a[i];
                 if ((MODE == 9) && (i % 4 == 0)) m[(i / 4) & 3] = ex2(m[(i / 4) & 3]);
@@ -163,7 +168,7 @@ __global__ void __launch_bounds__(256) k(int iters, float* sink, const float* sr
     }
     float s = acc4.x;
 #pragma unroll
-    for (int i = 0; i < N; i++) s += a[i];
+    for (int i = 0; i < N; i++) s += a[i] + x[i];
 #pragma unroll
     for (int i = 0; i < 4; i++) s += m[i];
     if (s == 123.456f) sink[0] = s;
@@ -236,6 +241,7 @@ int main()
     run<0>("ffma reuse (a=a*b+c)", 64, 0, sink, src, sms, mhz);
     run<1>("ffma 3 distinct regs", 64, 0, sink, src, sms, mhz);
     run<2>("ffma shared A operand", 64, 0, sink, src, sms, mhz);
+    run<10>("ffma shared A alternating w/ fmul", 128, 0, sink, src, sms, mhz);
     run<5>("fadd 2 regs", 64, 0, sink, src, sms, mhz);
     run<6>("fmul 2 regs", 64, 0, sink, src, sms, mhz);
     run<7>("ffma reuse + 1 mufu/16", 64, 4, sink, src, sms, mhz);
