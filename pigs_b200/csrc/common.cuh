@@ -86,6 +86,57 @@ __device__ __forceinline__ void atomic_max_float(float* addr, float v)
     else
         atomicMin((unsigned int*)addr, __float_as_uint(v));
 }
+// ---- packed FP32x2 (Blackwell FFMA2 / FMUL2 / FADD2): two IEEE fp32 operations per lane per instruction on a
+// 64-bit register pair.  ptxas folds pk(s, s) into a scalar-broadcast operand, negations into operand modifiers
+// and pk(imm, imm) into an immediate, so none of these helpers costs an instruction by itself.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+// pair of two scalars that live in unrelated registers, materialised ONCE in an adjacent register pair: ptxas treats
+// a plain mov.b64 as a free copy and re-packs loop-invariant pairs from their halves in every loop iteration.
+// Adding -0.0f read from memory at run time (x + (-0) == x bit-exactly for every x, signed zeros included) gives the
+// pair a defining arithmetic instruction that cannot be folded away, so it stays where it is written.
+__device__ __forceinline__ f32x2 pk2_once(float lo, float hi, float neg_zero)
+{
+    f32x2 r;
+    asm volatile("{\n\t.reg .b64 t, z;\n\tmov.b64 t, {%1, %2};\n\tmov.b64 z, {%3, %3};\n\tadd.rn.f32x2 %0, t, z;\n\t}"
+                 : "=l"(r)
+                 : "f"(lo), "f"(hi), "f"(neg_zero));
+    return r;
+}
+__device__ __forceinline__ f32x2 bc2(float s) { return pk2(s, s); }
+__device__ __forceinline__ void upk2(f32x2 v, float& lo, float& hi)
+{
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 neg2(f32x2 v)
+{
+    float lo, hi;
+    upk2(v, lo, hi);
+    return pk2(-lo, -hi);
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+    f32x2 d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
 __device__ __forceinline__ float ex2_approx(float x)
 {
     float y;

@@ -16,6 +16,279 @@ namespace pigs {
 
 constexpr int BWD_SB = 128;  // sample records per shared-memory batch
 
+#ifndef PIGS_BWD_OPMAJOR
+#define PIGS_BWD_OPMAJOR 1
+#endif
+
+// One sample record against the KG Gaussians a thread owns — 2-D, one channel, any subset of value / gradient /
+// Hessian.  Same arithmetic as the generic path below, but written OP-MAJOR over the KG Gaussians wherever an
+// operand of the sample record (warp-uniform) takes part, so that it sits in the same operand slot of consecutive
+// instructions (reuse-cache hits: an FP32 instruction needing three register-file reads costs two dispatch cycles
+// on B200, tools/mb_issue.cu), and GAUSSIAN-major where the shared operand is the pair's alpha.
+template <unsigned MASK, int MODE, int KG>
+__device__ __forceinline__ void bwd_sample_2d(const GaussReg<2, 1> (&g)[KG], const float* __restrict__ r,
+                                              float (&dm)[KG][2], float (&dc)[KG][3], float (&dv)[KG][1])
+{
+    constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0, HH = (MASK & PIGS_FN_HESS) != 0;
+    constexpr int OD = 2 + (HV ? 1 : 0), OH = OD + (HD ? 2 : 0);
+    const float x0 = r[0], x1 = r[1];
+    const float gu = HV ? r[2] : 0.0f;
+    const float g0 = HD ? r[OD] : 0.0f, g1 = HD ? r[OD + 1] : 0.0f;
+    const float G00 = HH ? r[OH] : 0.0f, G01 = HH ? r[OH + 1] : 0.0f, G11 = HH ? r[OH + 2] : 0.0f;
+    float X0[KG], X1[KG], a0[KG], a1[KG], al[KG], S[KG], p0[KG], p1[KG];
+#pragma unroll
+    for (int j = 0; j < KG; j++) X0[j] = g[j].m[0] - x0;
+#pragma unroll
+    for (int j = 0; j < KG; j++) X1[j] = g[j].m[1] - x1;
+    if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+        for (int j = 0; j < KG; j++) X0[j] = __fadd_rn(X0[j], g[j].sh[0]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) X1[j] = __fadd_rn(X1[j], g[j].sh[1]);
+    }
+    if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+        for (int j = 0; j < KG; j++) {
+            X0[j] = torus_wrap(X0[j]);
+            X1[j] = torus_wrap(X1[j]);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < KG; j++) a0[j] = g[j].c[0] * X0[j];
+#pragma unroll
+    for (int j = 0; j < KG; j++) a1[j] = g[j].c[1] * X0[j];
+#pragma unroll
+    for (int j = 0; j < KG; j++) a0[j] = fmaf(g[j].c[1], X1[j], a0[j]);
+#pragma unroll
+    for (int j = 0; j < KG; j++) a1[j] = fmaf(g[j].c[2], X1[j], a1[j]);
+#pragma unroll
+    for (int j = 0; j < KG; j++) al[j] = a0[j] * X0[j];
+#pragma unroll
+    for (int j = 0; j < KG; j++) al[j] = fmaf(a1[j], X1[j], al[j]);
+#pragma unroll
+    for (int j = 0; j < KG; j++) {
+        const float q = al[j];
+        al[j] = ex2_approx(q * KH);
+        if constexpr (MODE == EV_GENERAL) {
+            if (q < 0.0f) al[j] = 0.0f;  // power > 0: the reference skips the pair (backward.cu:81)
+        }
+    }
+    // S = sum_w G_w f_w and p = dS/da, the sample's upstream weights staying in one operand slot across the KG Gaussians
+#pragma unroll
+    for (int j = 0; j < KG; j++) S[j] = HD ? fmaf(g0, a0[j], gu) : gu;
+    if constexpr (HD) {
+#pragma unroll
+        for (int j = 0; j < KG; j++) S[j] = fmaf(g1, a1[j], S[j]);
+    }
+    if constexpr (HH) {
+        float h[KG];
+#pragma unroll
+        for (int j = 0; j < KG; j++) h[j] = fmaf(a0[j], a0[j], -g[j].c[0]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) S[j] = fmaf(G00, h[j], S[j]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) h[j] = fmaf(a0[j], a1[j], -g[j].c[1]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) S[j] = fmaf(G01, h[j], S[j]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) h[j] = fmaf(a1[j], a1[j], -g[j].c[2]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) S[j] = fmaf(G11, h[j], S[j]);
+        const float G00x2 = G00 + G00, G11x2 = G11 + G11;
+#pragma unroll
+        for (int j = 0; j < KG; j++) p0[j] = fmaf(G00x2, a0[j], g0);
+#pragma unroll
+        for (int j = 0; j < KG; j++) p1[j] = fmaf(G11x2, a1[j], g1);
+#pragma unroll
+        for (int j = 0; j < KG; j++) p0[j] = fmaf(G01, a1[j], p0[j]);
+#pragma unroll
+        for (int j = 0; j < KG; j++) p1[j] = fmaf(G01, a0[j], p1[j]);
+    } else {
+#pragma unroll
+        for (int j = 0; j < KG; j++) {
+            p0[j] = g0;
+            p1[j] = g1;
+        }
+    }
+    // per Gaussian: r = p - S X (-> dL/dmu = w C r, conic applied in the epilogue), e = p - S X / 2,
+    // dConic_ij += alpha (e_i X_j sym + E_ij), E = -G; the six accumulations share alpha
+#pragma unroll
+    for (int j = 0; j < KG; j++) {
+        const float Sj = S[j], hS = -0.5f * Sj;
+        float r0, r1, e1, e2;
+        if constexpr (HD || HH) {
+            r0 = fmaf(-Sj, X0[j], p0[j]);
+            e1 = fmaf(hS, X0[j], p0[j]);
+            r1 = fmaf(-Sj, X1[j], p1[j]);
+            e2 = fmaf(hS, X1[j], p1[j]);
+        } else {
+            r0 = -Sj * X0[j];
+            e1 = hS * X0[j];
+            r1 = -Sj * X1[j];
+            e2 = hS * X1[j];
+        }
+        float T0, T1, T2;
+        if constexpr (HH) {
+            T0 = fmaf(e1, X0[j], -G00);
+            T1 = fmaf(e1, X1[j], fmaf(e2, X0[j], -G01));
+            T2 = fmaf(e2, X1[j], -G11);
+        } else {
+            T0 = e1 * X0[j];
+            T1 = fmaf(e1, X1[j], e2 * X0[j]);
+            T2 = e2 * X1[j];
+        }
+        const float w = al[j];
+        dv[j][0] = fmaf(w, Sj, dv[j][0]);
+        dm[j][0] = fmaf(w, r0, dm[j][0]);
+        dm[j][1] = fmaf(w, r1, dm[j][1]);
+        dc[j][0] = fmaf(w, T0, dc[j][0]);
+        dc[j][1] = fmaf(w, T1, dc[j][1]);
+        dc[j][2] = fmaf(w, T2, dc[j][2]);
+    }
+}
+
+#ifndef PIGS_BWD_PACKED
+#define PIGS_BWD_PACKED 1
+#endif
+
+// The KG Gaussians a thread owns, as KG/2 register PAIRS (2-D, one channel): parameters and gradient accumulators.
+template <int KP>
+struct GaussPairs {
+    f32x2 m0[KP], m1[KP], c0[KP], c1[KP], c2[KP], sh0[KP], sh1[KP], v[KP];
+    f32x2 dv[KP], dm0[KP], dm1[KP], dc0[KP], dc1[KP], dc2[KP];
+};
+
+// One sample record against the Gaussian pairs of a thread, in packed FP32x2 arithmetic (same IEEE operations per
+// lane as the scalar path).  Why packed: on B200 an FP32 instruction with three register operands that are not in
+// the operand-reuse cache takes two dispatch cycles, and with the Gaussians stationary most of this kernel's FMAs
+// are of that kind (two per-pair temporaries plus an accumulator or a Gaussian parameter).  One FFMA2 on three
+// register pairs does TWO such FMAs in three cycles and needs no reuse-cache luck (tools/mb_issue.cu).  The sample
+// record's values are warp-uniform scalars and enter as broadcast operands.
+template <unsigned MASK, int MODE, int KP>
+__device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const float* __restrict__ r)
+{
+    constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0, HH = (MASK & PIGS_FN_HESS) != 0;
+    constexpr int OD = 2 + (HV ? 1 : 0), OH = OD + (HD ? 2 : 0);
+    const float x0 = r[0], x1 = r[1];
+    const float gu = HV ? r[2] : 0.0f;
+    const float g0 = HD ? r[OD] : 0.0f, g1 = HD ? r[OD + 1] : 0.0f;
+    const float G00 = HH ? r[OH] : 0.0f, G01 = HH ? r[OH + 1] : 0.0f, G11 = HH ? r[OH + 2] : 0.0f;
+    f32x2 X0[KP], X1[KP], a0[KP], a1[KP], al[KP], S[KP], p0[KP], p1[KP];
+#pragma unroll
+    for (int k = 0; k < KP; k++) X0[k] = add2(G.m0[k], bc2(-x0));
+#pragma unroll
+    for (int k = 0; k < KP; k++) X1[k] = add2(G.m1[k], bc2(-x1));
+    if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) X0[k] = add2(X0[k], G.sh0[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) X1[k] = add2(X1[k], G.sh1[k]);
+    }
+    if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) {
+            float lo, hi;
+            upk2(X0[k], lo, hi);
+            X0[k] = pk2(torus_wrap(lo), torus_wrap(hi));
+            upk2(X1[k], lo, hi);
+            X1[k] = pk2(torus_wrap(lo), torus_wrap(hi));
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KP; k++) a0[k] = mul2(G.c0[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a1[k] = mul2(G.c1[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a0[k] = fma2(G.c1[k], X1[k], a0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a1[k] = fma2(G.c2[k], X1[k], a1[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) al[k] = mul2(a0[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) al[k] = fma2(a1[k], X1[k], al[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) {
+        float qlo, qhi;
+        upk2(al[k], qlo, qhi);
+        float alo = ex2_approx(qlo * KH), ahi = ex2_approx(qhi * KH);
+        if constexpr (MODE == EV_GENERAL) {
+            if (qlo < 0.0f) alo = 0.0f;  // power > 0: the reference skips the pair (backward.cu:81)
+            if (qhi < 0.0f) ahi = 0.0f;
+        }
+        al[k] = pk2(alo, ahi);
+    }
+#pragma unroll
+    for (int k = 0; k < KP; k++) S[k] = HD ? fma2(bc2(g0), a0[k], bc2(gu)) : bc2(gu);
+    if constexpr (HD) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) S[k] = fma2(bc2(g1), a1[k], S[k]);
+    }
+    if constexpr (HH) {
+        f32x2 h[KP];
+#pragma unroll
+        for (int k = 0; k < KP; k++) h[k] = fma2(a0[k], a0[k], neg2(G.c0[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) S[k] = fma2(bc2(G00), h[k], S[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) h[k] = fma2(a0[k], a1[k], neg2(G.c1[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) S[k] = fma2(bc2(G01), h[k], S[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) h[k] = fma2(a1[k], a1[k], neg2(G.c2[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) S[k] = fma2(bc2(G11), h[k], S[k]);
+        const float G00x2 = G00 + G00, G11x2 = G11 + G11;
+#pragma unroll
+        for (int k = 0; k < KP; k++) p0[k] = fma2(bc2(G00x2), a0[k], bc2(g0));
+#pragma unroll
+        for (int k = 0; k < KP; k++) p1[k] = fma2(bc2(G11x2), a1[k], bc2(g1));
+#pragma unroll
+        for (int k = 0; k < KP; k++) p0[k] = fma2(bc2(G01), a1[k], p0[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) p1[k] = fma2(bc2(G01), a0[k], p1[k]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < KP; k++) {
+            p0[k] = bc2(g0);
+            p1[k] = bc2(g1);
+        }
+    }
+    // r = p - S X (-> dL/dmu = w C r, conic applied in the epilogue), e = p - S X / 2,
+    // dConic_ij += alpha (e_i X_j sym + E_ij), E = -G
+#pragma unroll
+    for (int k = 0; k < KP; k++) {
+        const f32x2 Sk = S[k], hS = mul2(Sk, bc2(-0.5f));
+        f32x2 r0, r1, e1, e2, T0, T1, T2;
+        if constexpr (HD || HH) {
+            r0 = fma2(neg2(Sk), X0[k], p0[k]);
+            e1 = fma2(hS, X0[k], p0[k]);
+            r1 = fma2(neg2(Sk), X1[k], p1[k]);
+            e2 = fma2(hS, X1[k], p1[k]);
+        } else {
+            r0 = mul2(neg2(Sk), X0[k]);
+            e1 = mul2(hS, X0[k]);
+            r1 = mul2(neg2(Sk), X1[k]);
+            e2 = mul2(hS, X1[k]);
+        }
+        if constexpr (HH) {
+            T0 = fma2(e1, X0[k], bc2(-G00));
+            T1 = fma2(e1, X1[k], fma2(e2, X0[k], bc2(-G01)));
+            T2 = fma2(e2, X1[k], bc2(-G11));
+        } else {
+            T0 = mul2(e1, X0[k]);
+            T1 = fma2(e1, X1[k], mul2(e2, X0[k]));
+            T2 = mul2(e2, X1[k]);
+        }
+        const f32x2 w = al[k];
+        G.dv[k] = fma2(w, Sk, G.dv[k]);
+        G.dm0[k] = fma2(w, r0, G.dm0[k]);
+        G.dm1[k] = fma2(w, r1, G.dm1[k]);
+        G.dc0[k] = fma2(w, T0, G.dc0[k]);
+        G.dc1[k] = fma2(w, T1, G.dc1[k]);
+        G.dc2[k] = fma2(w, T2, G.dc2[k]);
+    }
+}
+
 template <int D, int C, unsigned MASK, int MODE>
 __global__ void __launch_bounds__(EV_THREADS, 2)
     eval_bwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
@@ -72,6 +345,26 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             for (int ch = 0; ch < C; ch++) dv[j][ch] = 0.0f;
         }
 
+        // packed view of the stationary Gaussians (2-D, one channel)
+        constexpr bool PACKED = PIGS_BWD_PACKED && D == 2 && C == 1 && (MASK & PIGS_FN_THIRD) == 0 && (KG % 2) == 0;
+        GaussPairs<PACKED ? KG / 2 : 1> GP;
+        if constexpr (PACKED) {
+            const float nz = __uint_as_float(wh->neg_zero);
+#pragma unroll
+            for (int k = 0; k < KG / 2; k++) {
+                const GaussReg<D, C>&ga = g[2 * k], &gb = g[2 * k + 1];
+                GP.m0[k] = pk2_once(ga.m[0], gb.m[0], nz);
+                GP.m1[k] = pk2_once(ga.m[D - 1], gb.m[D - 1], nz);
+                GP.c0[k] = pk2_once(ga.c[0], gb.c[0], nz);
+                GP.c1[k] = pk2_once(ga.c[NC > 1 ? 1 : 0], gb.c[NC > 1 ? 1 : 0], nz);
+                GP.c2[k] = pk2_once(ga.c[NC - 1], gb.c[NC - 1], nz);
+                GP.sh0[k] = pk2_once(ga.sh[0], gb.sh[0], nz);
+                GP.sh1[k] = pk2_once(ga.sh[D - 1], gb.sh[D - 1], nz);
+                GP.v[k] = pk2_once(ga.v[0], gb.v[0], nz);
+                GP.dv[k] = GP.dm0[k] = GP.dm1[k] = GP.dc0[k] = GP.dc1[k] = GP.dc2[k] = bc2(0.0f);
+            }
+        }
+
         // ---- streamed operand: sample records through shared memory ----
         const float4* __restrict__ src = srecs + (size_t)it.s_begin * SV;
         const uint32_t total_v4 = it.s_count * SV;
@@ -105,6 +398,14 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             for (int s = 0; s < cnt; s++) {
                 float r[SV * 4];
                 load_v4<SV>(batch + s * SV, r);
+                if constexpr (PACKED) {
+                    bwd_sample_2d_packed<MASK, MODE, KG / 2>(GP, r);
+                    continue;
+                }
+                if constexpr (PIGS_BWD_OPMAJOR && D == 2 && C == 1 && (MASK & PIGS_FN_THIRD) == 0) {
+                    bwd_sample_2d<MASK, MODE, KG>(g, r, dm, dc, dv);
+                    continue;
+                }
 #pragma unroll
                 for (int j = 0; j < KG; j++) {
                     PairGeom<D, MODE> pg;
@@ -183,17 +484,41 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             __syncthreads();
         }
 
+        // conic / value of each owned Gaussian for the epilogue (the packed path keeps no scalar copy alive in the loop)
+        float ec[KG][NC], ev[KG];
+        if constexpr (PACKED) {
+#pragma unroll
+            for (int k = 0; k < KG / 2; k++) {
+                upk2(GP.dv[k], dv[2 * k][0], dv[2 * k + 1][0]);
+                upk2(GP.dm0[k], dm[2 * k][0], dm[2 * k + 1][0]);
+                upk2(GP.dm1[k], dm[2 * k][D - 1], dm[2 * k + 1][D - 1]);
+                upk2(GP.dc0[k], dc[2 * k][0], dc[2 * k + 1][0]);
+                upk2(GP.dc1[k], dc[2 * k][NC > 1 ? 1 : 0], dc[2 * k + 1][NC > 1 ? 1 : 0]);
+                upk2(GP.dc2[k], dc[2 * k][NC - 1], dc[2 * k + 1][NC - 1]);
+                upk2(GP.c0[k], ec[2 * k][0], ec[2 * k + 1][0]);
+                upk2(GP.c1[k], ec[2 * k][NC > 1 ? 1 : 0], ec[2 * k + 1][NC > 1 ? 1 : 0]);
+                upk2(GP.c2[k], ec[2 * k][NC - 1], ec[2 * k + 1][NC - 1]);
+                upk2(GP.v[k], ev[2 * k], ev[2 * k + 1]);
+            }
+        } else {
+#pragma unroll
+            for (int j = 0; j < KG; j++) {
+#pragma unroll
+                for (int k = 0; k < NC; k++) ec[j][k] = g[j].c[k];
+                ev[j] = g[j].v[0];
+            }
+        }
         // ---- epilogue: one RED.ADD per Gaussian parameter per item ----
 #pragma unroll
         for (int j = 0; j < KG; j++) {
             if (!act[j]) continue;
             const size_t id = rec_id[it.g_begin + tid + j * EV_THREADS];
-            const float vs = (C == 1) ? g[j].v[0] : 1.0f;  // C > 1: v is already inside S, p, E
+            const float vs = (C == 1) ? ev[j] : 1.0f;  // C > 1: v is already inside S, p, E
             if constexpr (D == 1) {
-                atomicAdd(dmeans + id, vs * (g[j].c[0] * dm[j][0]));
+                atomicAdd(dmeans + id, vs * (ec[j][0] * dm[j][0]));
             } else {
-                atomicAdd(dmeans + id * 2, vs * fmaf(g[j].c[1], dm[j][1], g[j].c[0] * dm[j][0]));
-                atomicAdd(dmeans + id * 2 + 1, vs * fmaf(g[j].c[2], dm[j][1], g[j].c[1] * dm[j][0]));
+                atomicAdd(dmeans + id * 2, vs * fmaf(ec[j][1], dm[j][1], ec[j][0] * dm[j][0]));
+                atomicAdd(dmeans + id * 2 + 1, vs * fmaf(ec[j][2], dm[j][1], ec[j][1] * dm[j][0]));
             }
 #pragma unroll
             for (int k = 0; k < NC; k++) atomicAdd(dconics + id * NC + k, vs * dc[j][k]);

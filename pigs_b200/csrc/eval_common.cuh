@@ -67,7 +67,8 @@ struct WorkHeader {
     uint32_t counter[4];  // dynamic work counters per seg
     uint32_t items[4];    // total items per seg
     unsigned long long pairs;
-    uint32_t pad[6];
+    uint32_t neg_zero;  // bit pattern of -0.0f: a run-time addend ptxas cannot fold (pk2_once)
+    uint32_t pad[5];
 };
 
 struct WorkItem {

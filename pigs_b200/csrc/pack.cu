@@ -257,6 +257,7 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
             wh->items[k] = s_carry[k];
         }
         wh->pairs = s_pairs;
+        wh->neg_zero = 0x80000000u;
     }
 }
 
