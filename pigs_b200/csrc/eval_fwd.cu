@@ -14,8 +14,8 @@
 // The path is FP32-FMA-issue bound (no dense contraction => no tensor cores).
 #include "layouts.cuh"
 
-#ifndef PIGS_FWD_ASM_ACC
-#define PIGS_FWD_ASM_ACC 1
+#ifndef PIGS_FWD_PACKED
+#define PIGS_FWD_PACKED 1
 #endif
 
 namespace pigs {
@@ -30,10 +30,55 @@ constexpr int FWD_GB = 256;  // Gaussian records per shared-memory batch
 // Scaled variables: a' = K X (= KH a), e = X.a' = log2(alpha); factors in (a', M) come out times KH^order.
 template <int D, int C, unsigned MASK, int MODE, int KS, int S0, int HS>
 __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, const float (&x)[KS][D],
-                                                 float (&acc)[KS][C][nacc(D, MASK)])
+                                                   const f32x2 (&xp)[D][(KS + 1) / 2], float (&acc)[KS][C][nacc(D, MASK)])
 {
     constexpr int NA = nacc(D, MASK);
+    constexpr bool PACKED = PIGS_FWD_PACKED && D == 2 && (HS % 2) == 0 && (S0 % 2) == 0;
     float X[D][HS], a[D][HS], al[HS];
+    if constexpr (PACKED) {
+        // geometry in packed FP32x2 over sample pairs: the Gaussian's parameters enter as scalar-broadcast operands,
+        // so no instruction reads three register pairs except the last FMA of the quadratic form (3 cycles per 2)
+        constexpr int HP = HS / 2, P0 = S0 / 2;
+        f32x2 X0[HP], X1[HP], A0[HP], A1[HP], E[HP];
+#pragma unroll
+        for (int p = 0; p < HP; p++) X0[p] = add2(bc2(g.m[0]), neg2(xp[0][P0 + p]));
+#pragma unroll
+        for (int p = 0; p < HP; p++) X1[p] = add2(bc2(g.m[1]), neg2(xp[1][P0 + p]));
+        if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+            for (int p = 0; p < HP; p++) X0[p] = add2(X0[p], bc2(g.sh[0]));
+#pragma unroll
+            for (int p = 0; p < HP; p++) X1[p] = add2(X1[p], bc2(g.sh[1]));
+        }
+        if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+            for (int p = 0; p < HP; p++) {
+                float lo, hi;
+                upk2(X0[p], lo, hi);
+                X0[p] = pk2(torus_wrap(lo), torus_wrap(hi));
+                upk2(X1[p], lo, hi);
+                X1[p] = pk2(torus_wrap(lo), torus_wrap(hi));
+            }
+        }
+#pragma unroll
+        for (int p = 0; p < HP; p++) A0[p] = mul2(bc2(g.k[0]), X0[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) A1[p] = mul2(bc2(g.k[1]), X0[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) A0[p] = fma2(bc2(g.k[1]), X1[p], A0[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) A1[p] = fma2(bc2(g.k[2]), X1[p], A1[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) E[p] = mul2(A0[p], X0[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) E[p] = fma2(A1[p], X1[p], E[p]);
+#pragma unroll
+        for (int p = 0; p < HP; p++) {
+            upk2(A0[p], a[0][2 * p], a[0][2 * p + 1]);
+            upk2(A1[p], a[1][2 * p], a[1][2 * p + 1]);
+            upk2(E[p], al[2 * p], al[2 * p + 1]);
+        }
+    } else {
 #pragma unroll
     for (int d = 0; d < D; d++) {
 #pragma unroll
@@ -66,6 +111,7 @@ __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, cons
 #pragma unroll
         for (int s = 0; s < HS; s++) al[s] = fmaf(a[1][s], X[1][s], al[s]);
     }
+    }
 #pragma unroll
     for (int s = 0; s < HS; s++) {
         const float e = al[s];  // = KH * q = log2(alpha)
@@ -91,19 +137,10 @@ __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, cons
             const float w = g.v[ch] * al[s];
 #pragma unroll
             for (int k = 0; k < NA; k++) {
-#if PIGS_FWD_ASM_ACC
-                // fixed operand order: w stays in operand slot A of the whole group (reuse cache), the value
-                // accumulator goes first because its add needs only two register reads
-                if (k == 0 && (MASK & PIGS_FN_VALUE))
-                    asm volatile("add.rn.f32 %0, %1, %0;" : "+f"(acc[S0 + s][ch][0]) : "f"(w));
-                else
-                    asm volatile("fma.rn.f32 %0, %1, %2, %0;" : "+f"(acc[S0 + s][ch][k]) : "f"(w), "f"(f[k]));
-#else
                 if (k == 0 && (MASK & PIGS_FN_VALUE))
                     acc[S0 + s][ch][0] += w;
                 else
                     acc[S0 + s][ch][k] = fmaf(w, f[k], acc[S0 + s][ch][k]);
-#endif
             }
         }
     }
@@ -111,15 +148,15 @@ __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, cons
 
 template <int D, int C, unsigned MASK, int MODE, int KS>
 __device__ __forceinline__ void fwd_one_gaussian(const GaussFwd<D, C>& g, const float (&x)[KS][D],
-                                                 float (&acc)[KS][C][nacc(D, MASK)])
+                                                 const f32x2 (&xp)[D][(KS + 1) / 2], float (&acc)[KS][C][nacc(D, MASK)])
 {
 #ifndef PIGS_FWD_HS
 #define PIGS_FWD_HS 8
 #endif
     constexpr int HS = KS < PIGS_FWD_HS ? KS : PIGS_FWD_HS;
     static_assert(KS <= 2 * HS, "two blocks cover KS");
-    fwd_gaussian_block<D, C, MASK, MODE, KS, 0, HS>(g, x, acc);
-    if constexpr (KS > HS) fwd_gaussian_block<D, C, MASK, MODE, KS, HS, HS>(g, x, acc);
+    fwd_gaussian_block<D, C, MASK, MODE, KS, 0, HS>(g, x, xp, acc);
+    if constexpr (KS > HS) fwd_gaussian_block<D, C, MASK, MODE, KS, HS, HS>(g, x, xp, acc);
 }
 
 template <int D, int C, unsigned MASK, int MODE>
@@ -164,6 +201,15 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 for (int k = 0; k < NA; k++) acc[s][ch][k] = 0.0f;
         }
 
+        f32x2 xp[D][(KS + 1) / 2];
+        if constexpr (PIGS_FWD_PACKED && D == 2 && (KS % 2) == 0) {
+            const float nz = __uint_as_float(wh->neg_zero);
+#pragma unroll
+            for (int d = 0; d < D; d++)
+#pragma unroll
+                for (int p = 0; p < KS / 2; p++) xp[d][p] = pk2_once(x[2 * p][d], x[2 * p + 1][d], nz);
+        }
+
         // ---- streamed operand: Gaussian records through shared memory, double-buffered ----
         const float4* __restrict__ src = recs + (size_t)it.g_begin * NV;
         const uint32_t total_v4 = it.g_count * NV;
@@ -192,7 +238,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
 #pragma unroll 1
             for (int j = 0; j < cnt; j++) {
                 const GaussFwd<D, C> g = load_gauss_fwd<D, C>(batch + j * NV);
-                fwd_one_gaussian<D, C, MASK, MODE, KS>(g, x, acc);
+                fwd_one_gaussian<D, C, MASK, MODE, KS>(g, x, xp, acc);
             }
             if (b + 1 < nbatch) {
 #pragma unroll
