@@ -44,6 +44,21 @@ WORKLOADS = {
 METRIC = "gaussian_point_evals_per_s_fwd_bwd_grad_hessian"
 UNIT = "pairs/s"
 LANE_OPS_FWD, LANE_OPS_BWD = 19, 45  # algorithmic FP32 lane-ops per pair
+EXEC_OPS_FWD, EXEC_OPS_BWD = 19.0, 36.5  # FP32 lane-ops per pair the kernels actually execute (SASS count)
+
+
+def ncu_traffic():
+    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary (profiles/), or None.
+    bench.py cannot measure DRAM traffic itself; the summary is of the same command (tools/gpu_round.sh)."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_eval_c3.json")))
+        for k in d["kernels"]:
+            if "eval_bwd_kernel<2, 1, 7, 0>" in k["kernel"] and "dram_read_bytes" in k:
+                return {"dram_bytes_per_launch": k["dram_read_bytes"] + k["dram_write_bytes"],
+                        "kernel": "eval_bwd_kernel<2,1,7,FAST> at C3, 1 GPU", "source": "profiles/r01_ncu_eval_c3.json"}
+    except Exception:
+        pass
+    return None
 
 
 def parse_args():
@@ -339,7 +354,11 @@ def run_ours(args):
                      "peak_measured_ex2": peaks["ex2"], "lane_ops_per_pair": LANE_OPS_BWD,
                      "fwd_plus_bwd": {"achieved": ach_all, "frac": ach_all / peak if ach_all else None,
                                       "lane_ops_per_pair": LANE_OPS_FWD + LANE_OPS_BWD},
-                     "traffic": None},
+                     "executed_lane_ops_per_pair": EXEC_OPS_BWD,
+                     "frac_executed": (ach_bwd * EXEC_OPS_BWD / LANE_OPS_BWD) / peak if ach_bwd else None,
+                     "traffic": (ncu_traffic() or {}).get("dram_bytes_per_launch"),
+                     "traffic_note": (ncu_traffic() or {}).get("kernel", "no committed ncu summary") + "; " +
+                                     (ncu_traffic() or {}).get("source", "")},
         "clocks": ck,
     }
     if e2e:

@@ -203,58 +203,60 @@ __global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __res
     }
 }
 
-// S6: tile of each sample (sampler_impl.cu:155-189) + per-tile bounding box of the samples
-template <int D>
+// S6: tile of each sample (sampler_impl.cu:155-189) + per-tile bounding box of the samples.
+// SMEM = true (few tile slots, the usual 4x4 grid): the boxes are reduced in shared memory by a grid-stride CTA and
+// merged with one global atomic per slot component per CTA — with uniformly scattered samples every lane of a warp
+// hits a different tile, so per-sample global atomics on a few dozen addresses serialise (6.8 ms at 4M samples).
+template <int D, bool SMEM>
 __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float* __restrict__ samples,
                                                          const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
-                                                         uint32_t* __restrict__ vals, float* __restrict__ bbox /* [nslots][2*D] */)
+                                                         uint32_t* __restrict__ vals, float* __restrict__ bbox /* [nslots][2*D] */,
+                                                         int nslots)
 {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= N) return;
+    extern __shared__ float s_box[];  // [nslots][2*D]
+    if constexpr (SMEM) {
+        for (int k = threadIdx.x; k < nslots * 2 * D; k += blockDim.x)
+            s_box[k] = (k % (2 * D)) < D ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+        __syncthreads();
+    }
     const int g0 = hdr->grid[0];
-    float x[D];
-    int t[D];
+    float mn[D];
+    int gr[D];
 #pragma unroll
     for (int d = 0; d < D; d++) {
-        x[d] = samples[i * D + d];
-        const int q = (int)__fdiv_rn(__fsub_rn(x[d], hdr->min_b[d]), PIGS_TILE_WIDTH);
-        t[d] = min(hdr->grid[d], max(0, q));
+        mn[d] = hdr->min_b[d];
+        gr[d] = hdr->grid[d];
     }
-    const uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
-    keys[i] = tile;
-    vals[i] = (uint32_t)i;
-    // warp-aggregated bbox update: lanes sharing a tile reduce among themselves first
-    const uint32_t active = __activemask();
-    const uint32_t peers = __match_any_sync(active, tile);
-    float lo[D], hi[D];
-#pragma unroll
-    for (int d = 0; d < D; d++) lo[d] = hi[d] = x[d] + 0.0f;
-    const int lane = threadIdx.x & 31;
-    // butterfly restricted to peers: iterate over set bits (at most 32, typically one or two groups)
-    if (peers == active) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1)
-#pragma unroll
-            for (int d = 0; d < D; d++) {
-                const float a = __shfl_xor_sync(active, lo[d], o);
-                const float b = __shfl_xor_sync(active, hi[d], o);
-                // lanes outside `active` return undefined values: guard with the mask
-                if ((active >> (lane ^ o)) & 1u) {
-                    lo[d] = fminf(lo[d], a);
-                    hi[d] = fmaxf(hi[d], b);
-                }
-            }
-        if (lane == (__ffs(peers) - 1))
-#pragma unroll
-            for (int d = 0; d < D; d++) {
-                atomic_min_float(bbox + (size_t)tile * 2 * D + d, lo[d]);
-                atomic_max_float(bbox + (size_t)tile * 2 * D + D + d, hi[d]);
-            }
-    } else {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
+        float x[D];
+        int t[D];
 #pragma unroll
         for (int d = 0; d < D; d++) {
-            atomic_min_float(bbox + (size_t)tile * 2 * D + d, lo[d]);
-            atomic_max_float(bbox + (size_t)tile * 2 * D + D + d, hi[d]);
+            x[d] = samples[i * D + d];
+            const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
+            t[d] = min(gr[d], max(0, q));
+        }
+        const uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+        keys[i] = tile;
+        vals[i] = (uint32_t)i;
+        float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
+#pragma unroll
+        for (int d = 0; d < D; d++) {
+            const float v = x[d] + 0.0f;  // -0 -> +0 so the integer-ordered atomics below are consistent
+            // the boxes only ever grow, so a stale read can at worst let a redundant atomic through
+            if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
+            if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
+        }
+    }
+    if constexpr (SMEM) {
+        __syncthreads();
+        for (int k = threadIdx.x; k < nslots * 2 * D; k += blockDim.x) {
+            const float v = s_box[k];
+            if ((k % (2 * D)) < D) {
+                if (v != __int_as_float(0x7f800000)) atomic_min_float(bbox + k, v);
+            } else {
+                if (v != __int_as_float(0xff800000)) atomic_max_float(bbox + k, v);
+            }
         }
     }
 }
@@ -397,11 +399,18 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
         const int64_t nslots = 2 * (int64_t)blocks + 4;
         bbox_init<<<(unsigned)((nslots * 2 * D + 255) / 256), 256, 0, st>>>(s.bbox, nslots, D);
         PIGS_LAUNCH_CHECK();
-        const unsigned nb = (unsigned)((N + 255) / 256);
-        if (D == 2)
-            sample_key_kernel<2><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox);
+        const int64_t nb_all = (N + 255) / 256;
+        const size_t box_bytes = (size_t)nslots * 2 * D * sizeof(float);
+        const bool smem = box_bytes <= 32 * 1024;
+        const unsigned nb = (unsigned)(smem ? (nb_all < (int64_t)num_sms() * 8 ? nb_all : (int64_t)num_sms() * 8) : nb_all);
+        if (D == 2 && smem)
+            sample_key_kernel<2, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+        else if (D == 2)
+            sample_key_kernel<2, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+        else if (smem)
+            sample_key_kernel<1, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
         else
-            sample_key_kernel<1><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox);
+            sample_key_kernel<1, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
         PIGS_LAUNCH_CHECK();
         int rc = stable_sort_pairs_u32(keys_u, vals_u, s.tiles, s.list, N, bits, sws, st);
         if (rc) return rc;

@@ -18,7 +18,7 @@ cat $OUT/quick_perf.log | tail -12
 # launch list of the same bench command (per-launch times are cold-cache and serialised)
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_c3.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > $OUT/ncu_launch.log 2>&1; echo "ncu launch exit $?"
-# full capture of the evaluation kernels at C2 (same kernels, 30x shorter replays)
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:eval_ -c 6 -o $OUT/eval_c2_full -f \
-    python bench.py --workload C2 --steps 1 --warmup 0 --no-cpu-baseline --no-e2e > $OUT/ncu_full.log 2>&1; echo "ncu full exit $?"
+# full capture of the six evaluation kernels of one C3 step (the bench workload itself)
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:eval_ -c 6 -o $OUT/eval_c3_full -f \
+    python bench.py --steps 1 --warmup 0 --no-cpu-baseline --no-e2e > $OUT/ncu_full.log 2>&1; echo "ncu full exit $?"
 ls -la $OUT
