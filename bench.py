@@ -286,6 +286,14 @@ def run_ours(args):
         kt[nm] = (ms.value / max(n.value, 1), n.value)
     ms_per_step = total_ms / args.steps
     value = pairs / (ms_per_step * 1e-3)
+    # per-rank kernel times and pair counts (load balance of the sample shards; rank 0 prints them)
+    per_rank = torch.tensor([kt["fwd"][0], kt["bwd"][0], float(pairs_local)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        gathered = [torch.zeros_like(per_rank) for _ in range(world)]
+        dist.all_gather(gathered, per_rank)
+        per_rank_rows = [[float(v) for v in g.tolist()] for g in gathered]
+    else:
+        per_rank_rows = [[float(v) for v in per_rank.tolist()]]
     launches_t = torch.tensor([launches], device="cuda", dtype=torch.int64)
     if world > 1:
         dist.all_reduce(launches_t)
@@ -346,7 +354,9 @@ def run_ours(args):
                    "parallelism": "points sharded x%d, Gaussians replicated" % world, "l2": flush_note()},
         "pde_step_ms": ms_per_step,
         "gpu_launches": int(launches_t.item()),
-        "kernel_ms": {"eval_fwd": fwd_ms, "eval_bwd": bwd_ms, "other_per_step": ms_per_step - fwd_ms - bwd_ms},
+        "kernel_ms": {"eval_fwd": fwd_ms, "eval_bwd": bwd_ms, "other_per_step": ms_per_step - fwd_ms - bwd_ms,
+                      "per_rank_fwd_bwd_ms": [[round(r[0], 3), round(r[1], 3)] for r in per_rank_rows],
+                      "per_rank_pairs": [int(r[2]) for r in per_rank_rows]},
         "roofline": {"bound": "fp32", "kernel": "eval_bwd_kernel<2,1,7,*> (fused backward evaluation)",
                      "achieved": ach_bwd, "peak": peak, "unit": "T lane-op/s", "frac": ach_bwd / peak if ach_bwd else None,
                      "peak_source": "%d SMs x 128 FP32 lanes x %.0f MHz (clocks.max.sm); MEASURED_PEAKS.json has no FP32 figure" % (sms, fmax / 1e6),
