@@ -144,6 +144,18 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
                             float *dL_dqueries, float *dL_dkeys, float *dL_dfrequencies,
                             float *dL_ddistance_transform, void *workspace, void *stream);
 
+/* ---- covariance / conic construction ---------------------------------------
+ * Replaces the torch chain of gaussians.py:163-193 `build_covariances(s, t)` (tanh, sqrt(prod), diag_embed, indexed
+ * assignment, batched torch.inverse, flatten to [xx, xy, yy]) that feeds GaussianSampler.preprocess in every driver.
+ * scaling [P, D], transform [P, 1] (ignored for D = 1) -> covariances, conics [P, D(D+1)/2].
+ * Backward: upstream gradients of the two flattened outputs (either may be NULL = zero) -> dL/dscaling [P, D],
+ * dL/dtransform [P, 1]; equals torch.autograd through the reference chain. */
+int pigs_build_covariances_forward(int64_t P, int D, const float *scaling, const float *transform, float *covariances,
+                                   float *conics, void *stream);
+int pigs_build_covariances_backward(int64_t P, int D, const float *scaling, const float *transform,
+                                    const float *dL_dcovariances, const float *dL_dconics, float *dL_dscaling,
+                                    float *dL_dtransform, void *stream);
+
 /* ---- roofline microbenchmarks (bench.py): register-resident FFMA / MUFU.EX2 loops ---------------
  * Each launches `ctas` CTAs x 256 threads running `iters` iterations of 64 independent ops per thread
  * and returns the number of lane-ops executed. Timing is done by the caller with CUDA events. */

@@ -244,3 +244,51 @@ def aggregate_backward(features, transform, queries, keys, frequencies, distance
                                       _p(_f32(factors)), _p(_f32(inv_total)), _p(_f32(dL_dout)), _p(gf), _p(gt),
                                       _p(gq), _p(gk), _p(gfr), _p(gdt))
     return gf, gt, gq, gk, gfr, gdt
+
+
+# ---------------------------------------------------------------------------------------------------------
+# covariance / conic construction — numpy float64 restatement of gaussians.py:163-193
+# ---------------------------------------------------------------------------------------------------------
+def build_covariances(s, t):
+    """gaussians.py:164 tau = tanh(t) * sqrt(prod(s)); :165-177 Sigma = [[s0, tau], [tau, s1]];
+    :181 conic = inverse(Sigma); :186-189 flatten [0, 1, 3].  Returns float64 (cov, conic), [P, 3] (2-D) or [P, 1]."""
+    s = np.asarray(s, np.float64)
+    if s.shape[-1] == 1:
+        return s.copy(), 1.0 / s
+    t = np.asarray(t, np.float64).reshape(-1)
+    tau = np.tanh(t) * np.sqrt(s[:, 0] * s[:, 1])
+    det = s[:, 0] * s[:, 1] - tau * tau
+    cov = np.stack([s[:, 0], tau, s[:, 1]], 1)
+    con = np.stack([s[:, 1] / det, -tau / det, s[:, 0] / det], 1)
+    return cov, con
+
+
+def build_covariances_backward(s, t, g_cov, g_con):
+    """Gradient of the chain above as torch.autograd computes it for the reference: dL/dSigma = -K^T G K^T with the
+    flattened conic gradient placed at entries [0,0], [0,1], [1,1] (gaussians.py:181,186-189), both off-diagonal
+    entries of Sigma being the same tau (:176-177).  float64; returns (dL/ds [P, D], dL/dt [P, 1])."""
+    s = np.asarray(s, np.float64)
+    g_cov = np.asarray(g_cov, np.float64)
+    g_con = np.asarray(g_con, np.float64)
+    if s.shape[-1] == 1:
+        return g_cov - g_con / (s * s), np.zeros((s.shape[0], 1))
+    t = np.asarray(t, np.float64).reshape(-1)
+    P = s.shape[0]
+    u = np.tanh(t)
+    r = np.sqrt(s[:, 0] * s[:, 1])
+    tau = u * r
+    Sig = np.empty((P, 2, 2))
+    Sig[:, 0, 0], Sig[:, 1, 1] = s[:, 0], s[:, 1]
+    Sig[:, 0, 1] = Sig[:, 1, 0] = tau
+    K = np.linalg.inv(Sig)
+    G = np.zeros((P, 2, 2))
+    G[:, 0, 0], G[:, 0, 1], G[:, 1, 1] = g_con[:, 0], g_con[:, 1], g_con[:, 2]
+    KT = np.transpose(K, (0, 2, 1))
+    dS = -KT @ G @ KT
+    dS[:, 0, 0] += g_cov[:, 0]
+    dS[:, 0, 1] += g_cov[:, 1]
+    dS[:, 1, 1] += g_cov[:, 2]
+    dtau = dS[:, 0, 1] + dS[:, 1, 0]
+    ds0 = dS[:, 0, 0] + dtau * u * s[:, 1] / (2 * r)
+    ds1 = dS[:, 1, 1] + dtau * u * s[:, 0] / (2 * r)
+    return np.stack([ds0, ds1], 1), (dtau * (1 - u * u) * r).reshape(-1, 1)

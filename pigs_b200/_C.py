@@ -318,3 +318,31 @@ def aggregate_neighbors_backward(features, transform, queries, keys, frequencies
     if debug:
         torch.cuda.synchronize()
     return gf, gt, gq, gk, gfr, gdt
+
+
+def build_covariances(scaling, transform):
+    """(scaling [P, D], transform [P, 1]) -> flattened (covariances, conics) [P, D(D+1)/2]; gaussians.py:163-193."""
+    L = _lib.lib()
+    scaling = _f32c(scaling, "scaling")
+    P, D = scaling.shape[0], scaling.shape[-1]
+    transform = _f32c(transform, "transform") if D > 1 else None
+    n = D * (D + 1) // 2
+    cov = torch.empty((P, n), dtype=torch.float32, device=scaling.device)
+    con = torch.empty((P, n), dtype=torch.float32, device=scaling.device)
+    check(L.pigs_build_covariances_forward(P, D, _ptr(scaling), _ptr(transform), _ptr(cov), _ptr(con), _stream()),
+          "pigs_build_covariances_forward")
+    return cov, con
+
+
+def build_covariances_backward(scaling, transform, g_cov, g_con):
+    L = _lib.lib()
+    scaling = _f32c(scaling, "scaling")
+    P, D = scaling.shape[0], scaling.shape[-1]
+    transform = _f32c(transform, "transform") if D > 1 else None
+    g_cov = None if g_cov is None else _f32c(g_cov, "dL_dcovariances")
+    g_con = None if g_con is None else _f32c(g_con, "dL_dconics")
+    ds = torch.empty_like(scaling)
+    dt = torch.empty((P, 1), dtype=torch.float32, device=scaling.device)
+    check(L.pigs_build_covariances_backward(P, D, _ptr(scaling), _ptr(transform), _ptr(g_cov), _ptr(g_con), _ptr(ds),
+                                            _ptr(dt), _stream()), "pigs_build_covariances_backward")
+    return ds, dt

@@ -61,6 +61,8 @@ SIGNATURES = {
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
     "pigs_aggregate_backward_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "pigs_aggregate_backward": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64] + [c_void_p] * 23),
+    "pigs_build_covariances_forward": (c_int, [c_int64, c_int] + [c_void_p] * 5),
+    "pigs_build_covariances_backward": (c_int, [c_int64, c_int] + [c_void_p] * 7),
     "pigs_microbench_ffma": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
     "pigs_microbench_ex2": (c_int64, [c_int, c_int, c_void_p, c_void_p]),
     "pigs_microbench_ffma2": (c_int64, [c_int, c_int, c_int, c_void_p, c_void_p]),
