@@ -1,0 +1,93 @@
+"""Parity at BASELINE.json's FULL sizes (C2 = 100K x 1M, C4 = 500K anisotropic torus x 2M, C3 = 1M x 4M), where the
+CPU oracle cannot evaluate the whole pair set (C3: 5.1e11 pairs):
+
+  * binning bit-exact against the oracle on the whole input (the oracle's binning is O(P + N));
+  * values / gradient / Hessian of a random SUBSET of the samples against the oracle run on that subset with the
+    tile grid pinned to the full problem's bounds — per-sample results depend on the other samples only through
+    the grid, so these rows must equal the full run's rows;
+  * parameter gradients for an upstream gradient that is non-zero on that subset only, against the oracle's backward
+    over the subset (the CUDA backward still walks the full pair set);
+  * the adjoint identity <u(v), G> = <v, dL/dv(G)> over ALL samples (u is linear in the values), which ties the
+    full-size forward to the full-size backward without any oracle.
+"""
+import numpy as np
+import pytest
+
+from oracle import pigs_oracle as po
+from tests.fixtures import synthetic
+from tests.helpers import TOL, ranges_np, rel_err
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = {
+    "C2": (100_000, 1_000_000, {}, 600),
+    "C4": (500_000, 2_000_000, dict(edge_fraction=0.1, anisotropy=4.0), 300),
+    "C3": (1_000_000, 4_000_000, {}, 240),
+}
+
+
+@pytest.mark.timeout(900)
+@pytest.mark.parametrize("name", list(CONFIGS))
+def test_full_size_against_oracle_subset(name):
+    import torch
+
+    from pigs_b200 import GaussianSampler, _C
+    P, N, kw, nsub = CONFIGS[name]
+    rec = synthetic(P, N, seed=0, **kw)
+    st = po.preprocess(rec["means"], rec["covariances"], rec["samples"])
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    for k in ("means", "values", "conics"):
+        d[k].requires_grad_(True)
+    s = GaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    # ---- binning, whole input, bit-exact ----
+    assert s.num_rendered == st["num_rendered"]
+    np.testing.assert_array_equal(s.radii.cpu().numpy(), st["radii"])
+    np.testing.assert_array_equal(ranges_np(s.ranges, st["blocks"]), st["ranges"])
+    np.testing.assert_array_equal(ranges_np(s.sample_ranges, st["blocks"]), st["sample_ranges"])
+    pl, _, sl = _C.point_lists(s.num_rendered, s.binning_buffer, s.sample_binning_buffer, N)
+    np.testing.assert_array_equal(pl.cpu().numpy().view(np.uint32), st["point_list"])
+    np.testing.assert_array_equal(sl.cpu().numpy().view(np.uint32), st["sample_list"])
+    assert s.pair_count() == po.pair_count(st)
+
+    # ---- forward on everything; a subset of rows against the oracle ----
+    outs = s.sample_fused(7)
+    rng = np.random.default_rng(5)
+    sub = np.sort(rng.choice(N, nsub, replace=False))
+    sub_samples = np.ascontiguousarray(rec["samples"][sub])
+    st_sub = po.preprocess(rec["means"], rec["covariances"], sub_samples, bounds=(st["min_b"], st["max_b"]))
+    np.testing.assert_array_equal(st_sub["grid"], st["grid"])
+    ups_sub, full_ups = [], []
+    for fn, got in enumerate(outs):
+        want = po.forward(fn, st_sub, rec["means"], rec["values"], rec["conics"], sub_samples)
+        e = rel_err(got.detach()[torch.from_numpy(sub).cuda()].cpu().numpy(), want)
+        assert e <= TOL, (name, "forward", fn, e)
+        g = rng.normal(size=want.shape).astype(np.float32)
+        ups_sub.append(g)
+        full = torch.zeros_like(got)
+        full[torch.from_numpy(sub).cuda()] = torch.from_numpy(g).cuda()
+        full_ups.append(full)
+
+    # ---- backward: upstream non-zero on the subset only == oracle backward over the subset ----
+    sum((o * g).sum() for o, g in zip(outs, full_ups)).backward()
+    want = [np.zeros_like(rec[k], dtype=np.float64) for k in ("means", "values", "conics")]
+    for fn in range(3):
+        for acc, part in zip(want, po.backward(fn, st_sub, rec["means"], rec["values"], rec["conics"], sub_samples,
+                                               ups_sub[fn])):
+            acc += part.reshape(acc.shape)
+    for k, w in zip(("means", "values", "conics"), want):
+        e = rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w)
+        assert e <= TOL, (name, "backward", k, e)
+
+    # ---- adjoint identity over ALL samples, per function ----
+    nr, bb, sbb, rg, srg = s._sample_state
+    for fn, o in enumerate(outs):
+        G = torch.randn(o.shape, device="cuda", generator=torch.Generator(device="cuda").manual_seed(fn))
+        grads = [None] * 4
+        grads[fn] = G
+        _, dv, _ = _C.sample_backward(1 << fn, d["means"].detach(), d["values"].detach(), d["conics"].detach(),
+                                      d["samples"], nr, grads, bb, sbb, rg, srg, False)
+        lhs = (o.detach().double() * G.double()).sum().item()
+        rhs = (d["values"].detach().double() * dv.double()).sum().item()
+        scale = (o.detach().double().abs() * G.double().abs()).sum().item()
+        assert abs(lhs - rhs) <= 1e-5 * scale, (name, "adjoint", fn, lhs, rhs, scale)
