@@ -133,6 +133,9 @@ int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float *f
                            const int64_t *indices, const int64_t *ranges, const float *dists,
                            const float *densities, const float *inv_total_densities, float *weights,
                            float *embeddings, float *factors, float *neighbor_features, void *stream);
+/* Library-level option (default 1): sizes L = K = 16, E = 25 (model_pn.py:44-49) run kernels specialised for them
+ * (aggregate16.cu); 0 forces the generic kernels (same results within rounding; tests compare the two). */
+void pigs_set_aggregate_specialised(int on);
 size_t pigs_aggregate_backward_workspace_bytes(int64_t P, int L, int K, int E);
 int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, const float *features,
                             const float *transform, const float *queries, const float *keys,

@@ -781,9 +781,26 @@ __global__ void __launch_bounds__(AG_THREADS)
 
 }  // namespace pigs
 
+namespace pigs {
+// aggregate16.cu: kernels specialised for L = K = 16, E = 25 (model_pn.py); return 1 if handled, 0 to fall back
+int launch_aggregate16_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+                               const float* queries, const float* keys, const float* freqs, const float* dt,
+                               const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
+                               const float* inv_total, float* weights, float* embeddings, float* factors, float* out,
+                               cudaStream_t st);
+int launch_aggregate16_backward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+                                const float* queries, const float* keys, const float* freqs, const float* dt,
+                                const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
+                                const float* weights, const float* embeddings, const float* factors, const float* inv_total,
+                                const float* gout, float* g_features, float* g_transform, float* g_queries, float* g_keys,
+                                float* g_freqs, float* g_dt, cudaStream_t st);
+}  // namespace pigs
+
 using namespace pigs;
 
 namespace {
+
+bool g_agg_fast = true;  // pigs_set_aggregate_specialised(0): always run the generic kernels (tests compare both)
 
 int bit_len(uint32_t n)
 {
@@ -893,6 +910,8 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
     return 0;
 }
 
+void pigs_set_aggregate_specialised(int on) { g_agg_fast = on != 0; }
+
 int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                            const float* queries, const float* keys, const float* frequencies,
                            const float* distance_transform, const int64_t* indices, const int64_t* ranges,
@@ -905,6 +924,12 @@ int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* f
     PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
              neighbor_features);
     PIGS_ARG(dm.nF == 0 || frequencies);
+    if (g_agg_fast && frequencies && weights && embeddings && factors && indices && dists && densities) {
+        rc = launch_aggregate16_forward(P, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
+                                        indices, ranges, dists, densities, inv_total_densities, weights, embeddings, factors,
+                                        neighbor_features, (cudaStream_t)stream);
+        if (rc != 0) return rc == 1 ? 0 : rc;
+    }
     const size_t smem = agg_fwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
     PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -939,6 +964,13 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
     PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
              dL_dneighbor_features && dL_dfeatures && dL_dtransform && dL_dqueries && dL_dkeys && dL_ddistance_transform);
     PIGS_ARG(dm.nF == 0 || (frequencies && dL_dfrequencies));
+    if (g_agg_fast && frequencies && dL_dfrequencies) {
+        rc = launch_aggregate16_backward(P, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
+                                         indices, ranges, dists, densities, weights, embeddings, factors, inv_total_densities,
+                                         dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
+                                         dL_dfrequencies, dL_ddistance_transform, (cudaStream_t)stream);
+        if (rc != 0) return rc == 1 ? 0 : rc;
+    }
     const size_t smem = agg_bwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
     PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

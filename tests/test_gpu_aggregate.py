@@ -46,8 +46,17 @@ def test_neighbor_lists_bit_exact_vs_oracle_and_golden(name):
     _check_lists(s, (g["indices"], g["ranges"], g["dists"], g["densities"], g["inv_total"]))
 
 
+@pytest.fixture(params=["specialised", "generic"])
+def agg_path(request):
+    """L = K = 16, E = 25 recipes run aggregate16.cu by default; 'generic' forces aggregate.cu's kernels for them too."""
+    from pigs_b200 import _lib
+    _lib.lib().pigs_set_aggregate_specialised(1 if request.param == "specialised" else 0)
+    yield request.param
+    _lib.lib().pigs_set_aggregate_specialised(1)
+
+
 @pytest.mark.parametrize("name", list(AGG_RECIPES))
-def test_aggregate_forward_backward(name):
+def test_aggregate_forward_backward(name, agg_path):
     import torch
     rec = AGG_RECIPES[name]()
     st = oracle_state(rec)
