@@ -15,6 +15,7 @@ tail -c 3000 $OUT/bench_c3.json
 timeout 600 python bench.py --impl reference > $OUT/bench_reference_arm.json 2> $OUT/bench_ref.err; echo "ref arm exit $?"
 timeout 600 python tools/quick_perf.py --big > $OUT/quick_perf.log 2>&1; echo "quick exit $?"
 cat $OUT/quick_perf.log | tail -12
+timeout 600 python tools/bench_hbm.py > $OUT/hbm_kernels.json 2> $OUT/hbm.err; echo "hbm exit $?"
 # launch list of the same bench command (per-launch times are cold-cache and serialised)
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_c3.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > $OUT/ncu_launch.log 2>&1; echo "ncu launch exit $?"
