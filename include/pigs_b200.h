@@ -34,6 +34,12 @@ extern "C" {
 #define PIGS_FN_DERIV 2u /* grad u   -> [N, D, C]       */
 #define PIGS_FN_HESS 4u  /* Hessian  -> [N, D, D, C]    */
 #define PIGS_FN_THIRD 8u /* 3rd der. -> [N, D, D, D, C] */
+/* Extension: the Laplacian = trace of the Hessian -> [N, C], what pde_rhs consumes
+ * (model_pn.py:613-625 `uxx[:,0,0] + uxx[:,1,1]`).  Mutually exclusive with PIGS_FN_HESS; it uses the Hessian's
+ * argument slots: out_ddu / dL_dddu then hold [N, C] instead of [N, D, D, C].  Same pair arithmetic as the Hessian
+ * (sum formed once per sample in the epilogue), so lap == H_00 + H_11 of the PIGS_FN_HESS result up to the order of
+ * the per-item atomic adds; the [N,D,D,C] tensor and its upstream gradient never touch HBM. */
+#define PIGS_FN_LAPL 16u
 
 /* Device-resident header written by pigs_preprocess_count at the start of `geom_ws` and copied to
  * the start of `binning_buffer` by pigs_preprocess_bin.  The host reads it back ONCE per preprocess
@@ -158,6 +164,26 @@ int pigs_build_covariances_forward(int64_t P, int D, const float *scaling, const
 int pigs_build_covariances_backward(int64_t P, int D, const float *scaling, const float *transform,
                                     const float *dL_dcovariances, const float *dL_dconics, float *dL_dscaling,
                                     float *dL_dtransform, void *stream);
+
+/* ---- PDE right-hand side + residual loss -------------------------------------
+ * Replaces the torch chain behind the sampler in the PDE drivers: model_pn.py:612-625 `pde_rhs` and :822-834
+ * `rhs = dt * pde_rhs(...)`, `pde_loss += mean((ut - rhs)**2)`.  Inputs are the sampler's outputs u [N, C],
+ * ux [N, D, C], lap [N, C] (PIGS_FN_LAPL: the trace the reference takes of its Hessian) and ut [N, C].
+ *   DIFFUSION rhs = lap ; BURGERS rhs = nu*lap - u*ux[:,0] ; WAVE (C == 2) rhs = (u1, 10*lap0 - 0.1*u1)
+ *   r = ut - dt*rhs ; loss = mean(r^2)  (WAVE: 0.01*mean(r0^2) + mean(r1^2))
+ * forward: writes the device scalar `loss` (deterministic two-stage reduction) and, if non-NULL, residual [N, C].
+ * backward: dL_dloss is a device scalar; every output pointer may be NULL (not wanted); dL_dux is fully written
+ * for BURGERS (components other than [:,0] are zero) and untouched otherwise. No host synchronisation. */
+#define PIGS_PDE_DIFFUSION 1
+#define PIGS_PDE_BURGERS 3
+#define PIGS_PDE_WAVE 4 /* numbering = model_pn.py:13-19 `Problem` enum.auto() values */
+size_t pigs_pde_residual_workspace_bytes(int64_t N, int C);
+int pigs_pde_residual_forward(int problem, int64_t N, int D, int C, float nu, float dt, const float *u, const float *ux,
+                              const float *lap, const float *ut, float *residual, float *loss, void *workspace,
+                              void *stream);
+int pigs_pde_residual_backward(int problem, int64_t N, int D, int C, float nu, float dt, const float *u, const float *ux,
+                               const float *lap, const float *ut, const float *dL_dloss, float *dL_du, float *dL_dux,
+                               float *dL_dlap, float *dL_dut, void *stream);
 
 /* ---- roofline microbenchmarks (bench.py): register-resident FFMA / MUFU.EX2 loops ---------------
  * Each launches `ctas` CTAs x 256 threads running `iters` iterations of 64 independent ops per thread

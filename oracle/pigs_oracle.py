@@ -292,3 +292,72 @@ def build_covariances_backward(s, t, g_cov, g_con):
     ds0 = dS[:, 0, 0] + dtau * u * s[:, 1] / (2 * r)
     ds1 = dS[:, 1, 1] + dtau * u * s[:, 0] / (2 * r)
     return np.stack([ds0, ds1], 1), (dtau * (1 - u * u) * r).reshape(-1, 1)
+
+
+# ---- Laplacian + PDE residual -------------------------------------------------
+PDE_DIFFUSION, PDE_BURGERS, PDE_WAVE = 1, 3, 4  # model_pn.py:13-19 Problem enum values
+
+
+def laplacian(st, means, values, conics, samples):
+    """`uxx[:,0,0] + uxx[:,1,1]` of the reference's Hessian output (model_pn.py:613-614), [N, C]."""
+    H = forward(FN_HESS, st, means, values, conics, samples)
+    D = st["D"]
+    out = H[:, 0, 0, :].copy() if D == 2 else H.reshape(H.shape[0], -1).copy()
+    if D == 2:
+        out = out + H[:, 1, 1, :]
+    return out.astype(np.float32)
+
+
+def laplacian_backward(st, means, values, conics, samples, dL_dlap):
+    """autograd of the trace: the upstream gradient goes on the diagonal of the Hessian's, zeros elsewhere."""
+    D, N = st["D"], st["N"]
+    g = _f32(dL_dlap).reshape(N, -1)
+    C = g.shape[1]
+    G = np.zeros(out_shape(FN_HESS, N, D, C), np.float32)
+    for d in range(D):
+        G[(slice(None),) + (d, d)] = g
+    return backward(FN_HESS, st, means, values, conics, samples, G)
+
+
+def pde_rhs(problem, u, ux, lap, nu):
+    """model_pn.py:612-627 pde_rhs with the trace already taken; fp32 op by op like the torch expressions."""
+    f = np.float32
+    if problem == PDE_DIFFUSION:
+        return lap.astype(f)
+    if problem == PDE_BURGERS:
+        return (f(nu) * lap - u * ux[:, 0]).astype(f)
+    if problem == PDE_WAVE:
+        return np.stack((u[..., 1], f(10) * lap[..., 0] - f(0.1) * u[..., 1]), axis=-1).astype(f)
+    raise ValueError("Unexpected PDE problem: %r" % (problem,))
+
+
+def pde_residual_loss(problem, u, ux, lap, ut, nu, dt):
+    """model_pn.py:822-837: rhs = dt * pde_rhs; loss = mean((ut - rhs)**2) (WAVE: 0.01 * mean + mean).
+    Returns (residual [N, C] fp32, loss float64-accumulated)."""
+    r = (ut - np.float32(dt) * pde_rhs(problem, u, ux, lap, nu)).astype(np.float32)
+    sq = r.astype(np.float64) ** 2
+    if problem == PDE_WAVE:
+        return r, 0.01 * sq[..., 0].mean() + sq[..., 1].mean()
+    return r, sq.mean()
+
+
+def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss):
+    """Analytic gradient of pde_residual_loss (checked against torch.autograd through the real model_pn.pde_rhs by
+    tests/golden/pde_golden.npz).  Returns (d_u, d_ux, d_lap, d_ut), float64."""
+    r, _ = pde_residual_loss(problem, u, ux, lap, ut, nu, dt)
+    r = r.astype(np.float64)
+    N = r.shape[0]
+    z = np.zeros_like
+    if problem == PDE_WAVE:
+        dr = np.stack((0.01 * 2 * r[..., 0] / N, 2 * r[..., 1] / N), -1) * g_loss
+        d_u, d_lap = z(dr), z(dr)
+        d_u[..., 1] = -dt * dr[..., 0] + 0.1 * dt * dr[..., 1]
+        d_lap[..., 0] = -10.0 * dt * dr[..., 1]
+        return d_u, (None if ux is None else np.zeros(ux.shape)), d_lap, dr
+    dr = 2 * r / r.size * g_loss
+    drhs = -dt * dr
+    if problem == PDE_DIFFUSION:
+        return z(dr), (None if ux is None else np.zeros(ux.shape)), drhs, dr
+    d_ux = np.zeros(ux.shape)
+    d_ux[:, 0] = -u * drhs
+    return -ux[:, 0] * drhs, d_ux, nu * drhs, dr

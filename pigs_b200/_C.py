@@ -17,6 +17,7 @@ from . import _lib
 from ._lib import HEADER_BYTES, PigsHeader, check
 
 FN_VALUE, FN_DERIV, FN_HESS, FN_THIRD = 1, 2, 4, 8
+FN_LAPL = 16  # extension (include/pigs_b200.h PIGS_FN_LAPL): trace of the Hessian, [N, C]; excludes FN_HESS
 
 _pinned = {}
 
@@ -120,8 +121,8 @@ def _blocks_of(ranges):
 
 def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
                    sample_ranges, debug):
-    """Fused forward for any subset of {value, derivative, Hessian, third}.  Returns a 4-tuple with
-    None for the functions not requested."""
+    """Fused forward for any subset of {value, derivative, Hessian | Laplacian, third}.  Returns a 4-tuple with
+    None for the functions not requested; with FN_LAPL slot 2 holds the Laplacian [N, C] instead of the Hessian."""
     L = _lib.lib()
     means = _f32c(means, "means")
     values = _f32c(values, "values")
@@ -129,8 +130,12 @@ def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binnin
     samples = _f32c(samples, "samples")
     P, D, N, C = _dims(means, values, samples)
     dev = means.device
+    if (fn_mask & FN_LAPL) and (fn_mask & FN_HESS):
+        raise RuntimeError("FN_LAPL and FN_HESS are mutually exclusive (they share an output slot)")
     shp = lambda k: (N,) + (D,) * k + (C,)
     outs = [torch.zeros(shp(k), dtype=torch.float32, device=dev) if fn_mask & (1 << k) else None for k in range(4)]
+    if fn_mask & FN_LAPL:
+        outs[2] = torch.zeros((N, C), dtype=torch.float32, device=dev)
     if P != 0 and N != 0:
         blocks = _blocks_of(ranges)
         ws_bytes = L.pigs_eval_workspace_bytes(num_rendered, N, blocks, D, C, fn_mask)
@@ -146,8 +151,8 @@ def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binnin
 
 def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads, binning_buffer, sample_binning_buffer,
                     ranges, sample_ranges, debug):
-    """Fused backward; `grads` is a 4-tuple of upstream gradients (None = zero).  Returns
-    (dL_dmeans [P,D], dL_dvalues [P,C], dL_dconics [P,D(D+1)/2])."""
+    """Fused backward; `grads` is a 4-tuple of upstream gradients (None = zero; with FN_LAPL slot 2 is the
+    Laplacian's [N, C] gradient).  Returns (dL_dmeans [P,D], dL_dvalues [P,C], dL_dconics [P,D(D+1)/2])."""
     L = _lib.lib()
     means = _f32c(means, "means")
     values = _f32c(values, "values")
@@ -346,3 +351,55 @@ def build_covariances_backward(scaling, transform, g_cov, g_con):
     check(L.pigs_build_covariances_backward(P, D, _ptr(scaling), _ptr(transform), _ptr(g_cov), _ptr(g_con), _ptr(ds),
                                             _ptr(dt), _stream()), "pigs_build_covariances_backward")
     return ds, dt
+
+
+# ---- PDE right-hand side + residual loss (model_pn.py:612-625, 822-834) ------------
+PDE_DIFFUSION, PDE_BURGERS, PDE_WAVE = 1, 3, 4  # model_pn.py:13-19 Problem enum values
+
+
+def _pde_args(problem, u, ux, lap, ut):
+    lap = _f32c(lap, "lap")
+    ut = _f32c(ut, "ut")
+    N = lap.shape[0]
+    C = lap.numel() // max(N, 1)
+    if ut.numel() != lap.numel():
+        raise RuntimeError("ut and lap must hold N*C elements each")
+    u = None if u is None else _f32c(u, "u")
+    ux = None if ux is None else _f32c(ux, "ux")
+    D = 2 if ux is None else ux.numel() // max(N * C, 1)
+    if problem in (PDE_BURGERS, PDE_WAVE) and (u is None or u.numel() != lap.numel()):
+        raise RuntimeError("u [N, C] is required for this problem")
+    if problem == PDE_BURGERS and (ux is None or D not in (1, 2)):
+        raise RuntimeError("ux [N, D, C] is required for BURGERS")
+    return N, D if D in (1, 2) else 2, C, u, ux, lap, ut
+
+
+def pde_residual_forward(problem, u, ux, lap, ut, nu, dt, want_residual=False):
+    """-> (loss: 0-dim device tensor, residual [N, C] or None)."""
+    L = _lib.lib()
+    N, D, C, u, ux, lap, ut = _pde_args(problem, u, ux, lap, ut)
+    dev = lap.device
+    loss = torch.zeros((), dtype=torch.float32, device=dev)
+    res = torch.empty_like(lap) if want_residual else None
+    if N > 0:
+        ws = _bytes(max(int(L.pigs_pde_residual_workspace_bytes(N, C)), 16), dev)
+        check(L.pigs_pde_residual_forward(problem, N, D, C, float(nu), float(dt), _ptr(u), _ptr(ux), _ptr(lap), _ptr(ut),
+                                          _ptr(res), _ptr(loss), _ptr(ws), _stream()), "pigs_pde_residual_forward")
+    return loss, res
+
+
+def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss, need=(True, True, True, True)):
+    """-> (dL_du, dL_dux, dL_dlap, dL_dut), None where not needed or identically absent (DIFFUSION: u, ux)."""
+    L = _lib.lib()
+    N, D, C, u, ux, lap, ut = _pde_args(problem, u, ux, lap, ut)
+    g_loss = _f32c(g_loss, "dL_dloss").reshape(1)
+    uses_u = problem in (PDE_BURGERS, PDE_WAVE)
+    d_u = torch.empty_like(u) if (need[0] and uses_u) else None
+    d_ux = torch.empty_like(ux) if (need[1] and problem == PDE_BURGERS) else None
+    d_lap = torch.empty_like(lap) if need[2] else None
+    d_ut = torch.empty_like(ut) if need[3] else None
+    if N > 0:
+        check(L.pigs_pde_residual_backward(problem, N, D, C, float(nu), float(dt), _ptr(u), _ptr(ux), _ptr(lap), _ptr(ut),
+                                           _ptr(g_loss), _ptr(d_u), _ptr(d_ux), _ptr(d_lap), _ptr(d_ut), _stream()),
+              "pigs_pde_residual_backward")
+    return d_u, d_ux, d_lap, d_ut

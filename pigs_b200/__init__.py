@@ -6,7 +6,8 @@ Public surface = diff-gaussian-sampling/diff_gaussian_sampling/__init__.py (refe
   .sample_gaussians_laplacian / .sample_gaussians_third_derivative / .preprocess_aggregate /
   .aggregate_neighbors, and the module-level functions sample_gaussians(...), ...,
   preprocess_gaussians, preprocess_aggregate, aggregate_neighbors.
-Extensions (additive, keyword-only): GaussianSampler(debug, fused=...), .sample_fused(mask), .pair_count().
+Extensions (additive, keyword-only): GaussianSampler(debug, fused=...), .sample_fused(mask), .pair_count(),
+.sample_laplacian() (trace of the Hessian, [N, C] — what model_pn.py:613-625 pde_rhs consumes; pigs_b200/pde.py).
 
 Everything below the API is hand-written CUDA in libpigs_b200.so (include/pigs_b200.h); there is no
 CPU or PyTorch fallback.
@@ -16,12 +17,12 @@ import os
 import torch
 
 from . import _C
-from ._C import FN_DERIV, FN_HESS, FN_THIRD, FN_VALUE
+from ._C import FN_DERIV, FN_HESS, FN_LAPL, FN_THIRD, FN_VALUE
 
 __all__ = [
     "GaussianSampler", "sample_gaussians", "sample_gaussians_derivative", "sample_gaussians_laplacian",
     "sample_gaussians_third_derivative", "aggregate_neighbors", "preprocess_gaussians", "preprocess_aggregate",
-    "FN_VALUE", "FN_DERIV", "FN_HESS", "FN_THIRD",
+    "FN_VALUE", "FN_DERIV", "FN_HESS", "FN_THIRD", "FN_LAPL",
 ]
 
 
@@ -76,11 +77,12 @@ class _SampleFused(torch.autograd.Function):
         grads, it = [None] * 4, iter(grad_outs)
         live = 0
         for k in range(4):
-            if mask & (1 << k):
+            bit = _slot_bit(mask, k)
+            if bit:
                 g = next(it)
                 if g is not None:
                     grads[k] = g
-                    live |= 1 << k
+                    live |= bit
         if live == 0:
             return (None,) * 12
         dm, dv, dc = call_debug(lambda *a: _C.sample_backward(live, *a), debug, "bw%d" % mask, means, values, conics,
@@ -88,6 +90,14 @@ class _SampleFused(torch.autograd.Function):
         if ctx.reduce is not None:
             ctx.reduce(_C.packed_base(dm))  # dm, dv, dc are views of one flat buffer: one collective
         return (None, dm, dv, dc, None, None, None, None, None, None, None, None)
+
+
+def _slot_bit(mask, k):
+    """The function bit of `mask` whose output sits in slot k of the (value, derivative, Hessian | Laplacian, third)
+    4-tuple, or 0."""
+    if k == 2 and (mask & FN_LAPL):
+        return FN_LAPL
+    return mask & (1 << k)
 
 
 def _sample_mask(mask, *args):
@@ -182,6 +192,8 @@ class GaussianSampler:
         self.radii = radii
         self._sample_state = (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges)
         self._plan, self._seen, self._cache = self._seen, 0, {}
+        if (self._plan & FN_HESS) and (self._plan & FN_LAPL):
+            self._plan &= ~FN_LAPL  # shared output slot: the Laplacian request then runs on its own
 
     def _args(self):
         nr, bb, sbb, rg, srg = self._sample_state
@@ -204,8 +216,9 @@ class GaussianSampler:
         if self.fused and (self._plan & bit) and self._plan != bit and not self._cache:
             outs = iter(self.sample_fused(self._plan))
             for k in range(4):
-                if self._plan & (1 << k):
-                    self._cache[1 << k] = next(outs)
+                b = _slot_bit(self._plan, k)
+                if b:
+                    self._cache[b] = next(outs)
             return self._cache.pop(bit)
         return self.sample_fused(bit)[0]
 
@@ -220,6 +233,14 @@ class GaussianSampler:
 
     def sample_gaussians_third_derivative(self):
         return self._request(FN_THIRD)
+
+    def sample_laplacian(self):
+        """(extension) Laplacian of the mixture at every sample, [N, C]: the trace
+        `uxx[:,0,0] + uxx[:,1,1]` that pde_rhs takes of sample_gaussians_laplacian()'s [N, D, D, C] Hessian
+        (model_pn.py:613-625), formed in the evaluation kernel's epilogue so neither the Hessian nor its upstream
+        gradient goes through HBM.  Not combinable with sample_gaussians_laplacian() in one preprocess cycle's
+        fused plan (the two share an output slot); asking for both simply runs them unfused."""
+        return self._request(FN_LAPL)
 
     def pair_count(self):
         """(extension) size of the reference pair set: sum over tiles of n_samples(tile) * n_gaussians(tile)."""

@@ -161,7 +161,10 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
                         const void* sample_ranges, float* out_u, float* out_du, float* out_ddu, float* out_dddu,
                         void* workspace, size_t workspace_bytes, void* stream)
 {
-    PIGS_ARG(fn_mask != 0 && (fn_mask & ~15u) == 0);
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~31u) == 0);
+    PIGS_ARG(!((fn_mask & PIGS_FN_HESS) && (fn_mask & PIGS_FN_LAPL)));  // they share out_ddu
+    const int lap = (fn_mask & PIGS_FN_LAPL) ? 1 : 0;
+    if (lap) fn_mask = (fn_mask & ~PIGS_FN_LAPL) | PIGS_FN_HESS;  // same kernels; the epilogue writes the trace
     EvalCall c;
     int rc = resolve(c, P, D, N, C, blocks, num_rendered, means, values, conics, samples, binning_buffer,
                      sample_binning_buffer, ranges, sample_ranges);
@@ -191,6 +194,7 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
             o.du = (fn_mask & PIGS_FN_DERIV) ? out_du : nullptr;
             o.ddu = (fn_mask & PIGS_FN_HESS) ? out_ddu : nullptr;
             o.dddu = (fn_mask & PIGS_FN_THIRD) ? out_dddu : nullptr;
+            o.lap = lap;
             {
                 ScopedKernelTimer tm(0, st);
                 for (int mode = 0; mode < EV_NSEG; mode++) {
@@ -210,7 +214,10 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
                          const float* dL_ddddu, float* dL_dmeans, float* dL_dvalues, float* dL_dconics, void* workspace,
                          size_t workspace_bytes, void* stream)
 {
-    PIGS_ARG(fn_mask != 0 && (fn_mask & ~15u) == 0);
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~31u) == 0);
+    PIGS_ARG(!((fn_mask & PIGS_FN_HESS) && (fn_mask & PIGS_FN_LAPL)));  // they share dL_dddu
+    const bool lap = (fn_mask & PIGS_FN_LAPL) != 0;
+    if (lap) fn_mask = (fn_mask & ~PIGS_FN_LAPL) | PIGS_FN_HESS;  // d lap / d H = I, applied while packing the samples
     EvalCall c;
     int rc = resolve(c, P, D, N, C, blocks, num_rendered, means, values, conics, samples, binning_buffer,
                      sample_binning_buffer, ranges, sample_ranges);
@@ -236,7 +243,7 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
             if (!m) continue;
             rc = stage_samples(c, cw, m, ch0, (fn_mask & PIGS_FN_VALUE) ? dL_du : nullptr,
                                (fn_mask & PIGS_FN_DERIV) ? dL_ddu : nullptr, (fn_mask & PIGS_FN_HESS) ? dL_dddu : nullptr,
-                               (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, ws, st);
+                               (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, lap, ws, st);
             if (rc) return rc;
             const uint32_t chunk = EV_THREADS * bwd_kg(D, cw, m);
             rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks), 128, false, st);

@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
     eval_fwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
                     const float4* __restrict__ recs, const uint32_t* __restrict__ slist,
                     const float* __restrict__ samples, int Ctot, int ch0, float* __restrict__ out_u,
-                    float* __restrict__ out_du, float* __restrict__ out_ddu, float* __restrict__ out_dddu)
+                    float* __restrict__ out_du, float* __restrict__ out_ddu, float* __restrict__ out_dddu, int lap)
 {
     constexpr int NV = frec_v4(D, C);
     constexpr int NA = nacc(D, MASK);
@@ -273,7 +273,10 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                         if (out_ddu) atomicAdd(out_ddu + id * Ctot + c, IK2 * acc[s][ch][k]);
                         k++;
                     } else {
-                        if (out_ddu) {
+                        if (out_ddu && lap) {
+                            // PIGS_FN_LAPL: trace of the Hessian, one element per (sample, channel)
+                            atomicAdd(out_ddu + id * Ctot + c, IK2 * (acc[s][ch][k] + acc[s][ch][k + 2]));
+                        } else if (out_ddu) {
                             float* o = out_ddu + id * 4 * Ctot + c;
                             const float hxy = IK2 * acc[s][ch][k + 1];
                             atomicAdd(o, IK2 * acc[s][ch][k]);
@@ -316,7 +319,7 @@ template <int D, int C, unsigned MASK, int MODE>
 static void launch_fwd_m(const EvalCall& c, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
 {
     eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist, c.samples,
-                                                                           c.C, ch0, o.u, o.du, o.ddu, o.dddu);
+                                                                           c.C, ch0, o.u, o.du, o.ddu, o.dddu, o.lap);
 }
 
 template <int D, int C, unsigned MASK>

@@ -97,12 +97,14 @@ struct EvalWs {
 int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, const EvalWs& ws, cudaStream_t st);
 int stage_worklist(const EvalCall& c, const EvalWs& ws, uint32_t chunk, uint32_t split_hint, uint32_t min_stream,
                    bool stream_is_gauss, cudaStream_t st);
+// lap: gH is the upstream gradient of the Laplacian [N, C] (PIGS_FN_LAPL) instead of the Hessian's [N, D, D, C]
 int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float* gV, const float* gD, const float* gH,
-                  const float* gT, const EvalWs& ws, cudaStream_t st);
+                  const float* gT, bool lap, const EvalWs& ws, cudaStream_t st);
 
 // evaluation launchers (eval_fwd.cu / eval_bwd.cu); C is the channel-group width (1 or 2)
 struct FwdOut {
     float *u, *du, *ddu, *dddu;
+    int lap;  // 1: ddu is the Laplacian [N, C] (PIGS_FN_LAPL), 0: the Hessian [N, D, D, C]
 };
 int launch_forward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, FwdOut out,
                    cudaStream_t st);

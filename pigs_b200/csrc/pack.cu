@@ -128,7 +128,7 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
                                                            const float* __restrict__ samples,
                                                            const float* __restrict__ gV, const float* __restrict__ gD,
                                                            const float* __restrict__ gH, const float* __restrict__ gT,
-                                                           int Ctot, int ch0, float4* __restrict__ srecs)
+                                                           int Ctot, int ch0, int lap, float4* __restrict__ srecs)
 {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
@@ -155,10 +155,17 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
             if constexpr (D == 1) {
                 f[k++] = gH ? gH[sid * Ctot + c] : 0.0f;
             } else {
-                const float* g = gH + sid * 4 * Ctot + c;
-                f[k++] = gH ? g[0] : 0.0f;
-                f[k++] = gH ? g[Ctot] + g[2 * Ctot] : 0.0f;
-                f[k++] = gH ? g[3 * Ctot] : 0.0f;
+                if (lap) {  // d lap / d H = identity: the Laplacian's upstream gradient on the diagonal
+                    const float gl = gH ? gH[sid * Ctot + c] : 0.0f;
+                    f[k++] = gl;
+                    f[k++] = 0.0f;
+                    f[k++] = gl;
+                } else {
+                    const float* g = gH + sid * 4 * Ctot + c;
+                    f[k++] = gH ? g[0] : 0.0f;
+                    f[k++] = gH ? g[Ctot] + g[2 * Ctot] : 0.0f;
+                    f[k++] = gH ? g[3 * Ctot] : 0.0f;
+                }
             }
         }
         if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
@@ -313,19 +320,19 @@ int stage_worklist(const EvalCall& c, const EvalWs& ws, uint32_t chunk, uint32_t
 
 template <int D, int C, unsigned MASK>
 static int stage_samples_t(const EvalCall& c, int ch0, const float* gV, const float* gD, const float* gH, const float* gT,
-                           const EvalWs& ws, cudaStream_t st)
+                           bool lap, const EvalWs& ws, cudaStream_t st)
 {
     pack_samples_kernel<D, C, MASK><<<(unsigned)((c.N + 255) / 256), 256, 0, st>>>(c.N, c.slist, c.samples, gV, gD, gH, gT,
-                                                                                    c.C, ch0, ws.srecs);
+                                                                                    c.C, ch0, lap ? 1 : 0, ws.srecs);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
 
 int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float* gV, const float* gD, const float* gH,
-                  const float* gT, const EvalWs& ws, cudaStream_t st)
+                  const float* gT, bool lap, const EvalWs& ws, cudaStream_t st)
 {
 #define SS(D_, C_, M_) \
-    if (c.D == D_ && C == C_ && mask == M_) return stage_samples_t<D_, C_, M_>(c, ch0, gV, gD, gH, gT, ws, st);
+    if (c.D == D_ && C == C_ && mask == M_) return stage_samples_t<D_, C_, M_>(c, ch0, gV, gD, gH, gT, lap, ws, st);
 #define SS_ALL(D_, C_) SS(D_, C_, 1u) SS(D_, C_, 2u) SS(D_, C_, 4u) SS(D_, C_, 7u) SS(D_, C_, 8u)
     SS_ALL(2, 1) SS_ALL(2, 2) SS_ALL(1, 1) SS_ALL(1, 2)
 #undef SS_ALL

@@ -1,0 +1,82 @@
+"""PDE right-hand side + residual loss of kr4b/pigs' `model_pn.py` as ONE fused CUDA pass each way (SURVEY.md §8f
+rank 2), fed by the sampler's Laplacian output (`GaussianSampler.sample_laplacian()`, the trace `uxx[:,0,0] +
+uxx[:,1,1]` the reference takes of its [N, D, D, C] Hessian):
+
+    model_pn.py:612-625  pde_rhs:   DIFFUSION lap | BURGERS nu*lap - u*ux[:,0] | WAVE (u1, 10*lap0 - 0.1*u1)
+    model_pn.py:822-834  rhs = dt * pde_rhs(...);  pde_loss += mean((ut - rhs)**2)   (WAVE: 0.01*mean + mean)
+
+    loss = pde_residual_loss(Problem.BURGERS, u, ux, lap, ut, dt, nu)     # 0-dim tensor, differentiable
+
+A maintainer switches `compute_loss` to it by replacing the two lines above.  POISSON (its
+reference code reads an undefined `t`, model_pn.py:620) and NAVIER_STOKES (third derivatives) are left on torch.
+No CPU path: CUDA fp32 tensors only.
+"""
+import enum
+
+import torch
+
+from . import _C
+
+
+class Problem(enum.Enum):
+    """model_pn.py:13-19 (same member order, so the values agree)."""
+    DIFFUSION = enum.auto()
+    POISSON = enum.auto()
+    BURGERS = enum.auto()
+    WAVE = enum.auto()
+    NAVIER_STOKES = enum.auto()
+    TEST = enum.auto()
+
+
+_NATIVE = {Problem.DIFFUSION.value: _C.PDE_DIFFUSION, Problem.BURGERS.value: _C.PDE_BURGERS, Problem.WAVE.value: _C.PDE_WAVE}
+
+
+def _code(problem):
+    v = problem.value if isinstance(problem, enum.Enum) else int(problem)
+    if v not in _NATIVE:
+        raise ValueError("Unexpected PDE problem for the fused residual: %r" % (problem,))
+    return _NATIVE[v]
+
+
+class _ResidualLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, code, u, ux, lap, ut, nu, dt):
+        loss, _ = _C.pde_residual_forward(code, u, ux, lap, ut, nu, dt)
+        ctx.code, ctx.nu, ctx.dt = code, nu, dt
+        ctx.save_for_backward(*[t for t in (u, ux, lap, ut) if t is not None])
+        ctx.has = (u is not None, ux is not None)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        it = iter(ctx.saved_tensors)
+        u = next(it) if ctx.has[0] else None
+        ux = next(it) if ctx.has[1] else None
+        lap, ut = next(it), next(it)
+        need = (ctx.needs_input_grad[1], ctx.needs_input_grad[2], ctx.needs_input_grad[3], ctx.needs_input_grad[4])
+        d_u, d_ux, d_lap, d_ut = _C.pde_residual_backward(ctx.code, u, ux, lap, ut, ctx.nu, ctx.dt, g, need)
+
+        def shaped(d, like):
+            return None if d is None else d.reshape(like.shape)
+
+        return (None, shaped(d_u, u) if u is not None else None, shaped(d_ux, ux) if ux is not None else None,
+                shaped(d_lap, lap), shaped(d_ut, ut), None, None)
+
+
+def pde_residual_loss(problem, u, ux, lap, ut, dt, nu=0.0):
+    """mean((ut - dt * pde_rhs)**2) for DIFFUSION / BURGERS, 0.01*mean(r0**2) + mean(r1**2) for WAVE
+    (model_pn.py:822-841).  u, lap, ut: [N, C]; ux: [N, D, C] (may be None for DIFFUSION / WAVE)."""
+    code = _code(problem)
+    if code != _C.PDE_BURGERS:
+        ux = None
+    if code == _C.PDE_DIFFUSION:
+        u = None
+    return _ResidualLoss.apply(code, u, ux, lap, ut, float(nu), float(dt))
+
+
+def pde_residual(problem, u, ux, lap, ut, dt, nu=0.0):
+    """(no autograd) the residual ut - dt * pde_rhs itself, [N, C], and its loss."""
+    code = _code(problem)
+    loss, res = _C.pde_residual_forward(code, None if code == _C.PDE_DIFFUSION else u,
+                                        ux if code == _C.PDE_BURGERS else None, lap, ut, nu, dt, want_residual=True)
+    return res, loss

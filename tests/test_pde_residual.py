@@ -1,0 +1,191 @@
+"""Laplacian output + PDE right-hand side / residual loss (model_pn.py:612-625, 822-837).
+CPU: the oracle restatement against goldens produced by the real model_pn.Model.pde_rhs + torch.autograd
+(tests/golden/make_pde_golden.py).
+GPU (-m gpu): PIGS_FN_LAPL through GaussianSampler.sample_laplacian() against the trace of the oracle's Hessian
+(forward and backward, alone and inside the fused plan), and the fused residual kernels (pigs_b200.pde -> C ABI)
+against the oracle and the goldens."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pigs_oracle as po
+from tests.fixtures import synthetic
+from tests.helpers import TOL, oracle_state, rel_err, upstream
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "pde_golden.npz")
+CASES = ("diffusion", "diffusion_c3", "burgers", "burgers_c2", "wave")
+
+
+def _case(name):
+    z = np.load(GOLD)
+    return {k.split("/", 1)[1]: z[k] for k in z.files if k.startswith(name + "/")}
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_oracle_matches_reference_golden(name):
+    c = _case(name)
+    prob, nu, dt = int(c["problem"]), float(c["nu"]), float(c["dt"])
+    r, loss = po.pde_residual_loss(prob, c["u"], c["ux"], c["lap"], c["ut"], nu, dt)
+    assert rel_err(r, c["residual"]) <= TOL
+    assert abs(loss - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    d_u, d_ux, d_lap, d_ut = po.pde_residual_backward(prob, c["u"], c["ux"], c["lap"], c["ut"], nu, dt, float(c["up"]))
+    assert rel_err(d_lap, c["d_lap"]) <= TOL
+    assert rel_err(d_ut, c["d_ut"]) <= TOL
+    assert rel_err(d_u, c["d_u"]) <= TOL
+    assert rel_err(d_ux, c["d_ux"]) <= TOL
+
+
+def test_problem_enum_matches_reference_values():
+    from pigs_b200._C import PDE_BURGERS, PDE_DIFFUSION, PDE_WAVE  # import of the glue only; no library call
+    from pigs_b200.pde import Problem
+    assert (Problem.DIFFUSION.value, Problem.BURGERS.value, Problem.WAVE.value) == (PDE_DIFFUSION, PDE_BURGERS, PDE_WAVE)
+    assert (po.PDE_DIFFUSION, po.PDE_BURGERS, po.PDE_WAVE) == (PDE_DIFFUSION, PDE_BURGERS, PDE_WAVE)
+    for name in CASES:  # the goldens carry the value of the real model_pn.Problem member
+        want = {"diffusion": PDE_DIFFUSION, "burgers": PDE_BURGERS, "wave": PDE_WAVE}[name.split("_")[0]]
+        assert int(_case(name)["problem"]) == want
+
+
+def test_oracle_laplacian_is_trace_and_adjoint():
+    rec = synthetic(300, 2000, seed=5)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    H = po.forward(po.FN_HESS, st, *a)
+    lap = po.laplacian(st, *a)
+    np.testing.assert_array_equal(lap, H[:, 0, 0] + H[:, 1, 1])
+    g = np.random.default_rng(0).normal(size=lap.shape).astype(np.float32)
+    dm, dv, dc = po.laplacian_backward(st, *a, g)
+    # <dlap/dv . g> == <lap, g> because lap is linear in the values
+    assert abs((dv * rec["values"]).sum() - (lap.astype(np.float64) * g).sum()) <= 1e-4 * np.abs(lap * g).sum()
+
+
+# ------------------------------------------------------------------------------------------------ GPU
+def _sampler(rec, **kw):
+    import torch
+
+    from diff_gaussian_sampling import GaussianSampler
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    for k in ("means", "values", "conics"):
+        d[k].requires_grad_(True)
+    s = GaussianSampler(False, **kw)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    return s, d
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("shape", [dict(P=3000, N=20000), dict(P=800, N=5000, C=2), dict(P=500, N=3000, D=1),
+                                   dict(P=2000, N=9000, edge_fraction=0.2, anisotropy=4.0)])
+def test_laplacian_forward_backward_matches_oracle(shape):
+    import torch
+    kw = dict(shape)
+    rec = synthetic(kw.pop("P"), kw.pop("N"), seed=11, **kw)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    s, d = _sampler(rec)
+    lap = s.sample_laplacian()
+    want = po.laplacian(st, *a)
+    assert lap.shape == want.shape
+    assert rel_err(lap.detach().cpu().numpy(), want) <= TOL
+    g = upstream(rec, 0, seed=3).reshape(want.shape)
+    (lap * torch.from_numpy(g).cuda()).sum().backward()
+    for k, w in zip(("means", "values", "conics"), po.laplacian_backward(st, *a, g)):
+        assert rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w) <= TOL, k
+
+
+@pytest.mark.gpu
+def test_laplacian_in_fused_plan_equals_unfused():
+    """u + grad u + Laplacian requested as three calls: the second preprocess cycle runs them as ONE kernel."""
+    import torch
+    rec = synthetic(4000, 30000, seed=12)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    s, d = _sampler(rec, fused=True)
+    for cycle in range(2):
+        if cycle:
+            s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        u, ux, lap = s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_laplacian()
+    assert u.grad_fn is ux.grad_fn is lap.grad_fn  # one autograd node -> one fused backward
+    assert rel_err(u.detach().cpu().numpy(), po.forward(0, st, *a)) <= TOL
+    assert rel_err(ux.detach().cpu().numpy(), po.forward(1, st, *a)) <= TOL
+    assert rel_err(lap.detach().cpu().numpy(), po.laplacian(st, *a)) <= TOL
+    gs = [upstream(rec, 0), upstream(rec, 1), upstream(rec, 0, seed=9)]
+    (u * torch.from_numpy(gs[0]).cuda()).sum().add((ux * torch.from_numpy(gs[1]).cuda()).sum()).add(
+        (lap * torch.from_numpy(gs[2]).cuda()).sum()).backward()
+    want = [np.zeros(rec[k].shape, np.float64) for k in ("means", "values", "conics")]
+    parts = (po.backward(0, st, *a, gs[0]), po.backward(1, st, *a, gs[1]), po.laplacian_backward(st, *a, gs[2]))
+    for part in parts:
+        for acc, p in zip(want, part):
+            acc += p.reshape(acc.shape)
+    for k, w in zip(("means", "values", "conics"), want):
+        assert rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w) <= TOL, k
+
+
+@pytest.mark.gpu
+def test_laplacian_and_hessian_in_one_cycle_run_unfused():
+    rec = synthetic(1000, 6000, seed=13)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    s, d = _sampler(rec, fused=True)
+    for cycle in range(2):
+        if cycle:
+            s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        H, lap = s.sample_gaussians_laplacian(), s.sample_laplacian()
+    assert rel_err(H.detach().cpu().numpy(), po.forward(2, st, *a)) <= TOL
+    assert rel_err(lap.detach().cpu().numpy(), po.laplacian(st, *a)) <= TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", CASES)
+def test_residual_cuda_matches_oracle_and_golden(name):
+    import torch
+
+    from pigs_b200 import pde
+    c = _case(name)
+    prob, nu, dt = int(c["problem"]), float(c["nu"]), float(c["dt"])
+    t = {k: torch.from_numpy(c[k]).cuda().requires_grad_(True) for k in ("u", "ux", "lap", "ut")}
+    loss = pde.pde_residual_loss(pde.Problem(prob), t["u"], t["ux"], t["lap"], t["ut"], dt, nu)
+    r_want, loss_want = po.pde_residual_loss(prob, c["u"], c["ux"], c["lap"], c["ut"], nu, dt)
+    assert abs(float(loss.detach()) - loss_want) <= TOL * abs(loss_want)
+    assert abs(float(loss.detach()) - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    res, loss2 = pde.pde_residual(pde.Problem(prob), t["u"].detach(), t["ux"].detach(), t["lap"].detach(),
+                                  t["ut"].detach(), dt, nu)
+    assert float(loss2) == float(loss.detach())  # deterministic two-stage reduction
+    assert rel_err(res.cpu().numpy(), r_want) <= TOL
+    assert rel_err(res.cpu().numpy(), c["residual"]) <= TOL
+    (loss * float(c["up"])).backward()
+    want = po.pde_residual_backward(prob, c["u"], c["ux"], c["lap"], c["ut"], nu, dt, float(c["up"]))
+    for k, w in zip(("u", "ux", "lap", "ut"), want):
+        got = t[k].grad
+        got = np.zeros(c[k].shape, np.float32) if got is None else got.cpu().numpy()
+        assert rel_err(got, w) <= TOL, k
+        assert rel_err(got, c["d_" + k]) <= TOL, k
+
+
+@pytest.mark.gpu
+def test_residual_large_and_chain_through_sampler():
+    """End to end like compute_loss: sampler (u, grad u, Laplacian fused) -> fused Burgers residual loss -> backward
+    to the Gaussian parameters, against the oracle chain."""
+    import torch
+
+    from pigs_b200 import pde
+    rec = synthetic(3000, 50000, seed=14)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    nu, dt = 0.02, 0.05
+    ut = (0.1 * np.random.default_rng(3).normal(size=(rec["samples"].shape[0], 1))).astype(np.float32)
+    s, d = _sampler(rec)
+    u, ux, lap = s.sample_fused(1 | 2 | 16)
+    loss = pde.pde_residual_loss(pde.Problem.BURGERS, u, ux, lap, torch.from_numpy(ut).cuda(), dt, nu)
+    loss.backward()
+    uo, uxo, lo = po.forward(0, st, *a), po.forward(1, st, *a), po.laplacian(st, *a)
+    _, loss_want = po.pde_residual_loss(po.PDE_BURGERS, uo, uxo, lo, ut, nu, dt)
+    assert abs(float(loss.detach()) - loss_want) <= TOL * abs(loss_want)
+    g_u, g_ux, g_lap, _ = po.pde_residual_backward(po.PDE_BURGERS, uo, uxo, lo, ut, nu, dt, 1.0)
+    want = [np.zeros(rec[k].shape, np.float64) for k in ("means", "values", "conics")]
+    parts = (po.backward(0, st, *a, g_u.astype(np.float32)), po.backward(1, st, *a, g_ux.astype(np.float32)),
+             po.laplacian_backward(st, *a, g_lap.astype(np.float32)))
+    for part in parts:
+        for acc, p in zip(want, part):
+            acc += p.reshape(acc.shape)
+    for k, w in zip(("means", "values", "conics"), want):
+        assert rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w) <= 2 * TOL, k
