@@ -56,7 +56,12 @@ typedef struct pigs_header {
     float max_b[2];
     int64_t P, N;
     int64_t num_rendered;  /* Gaussian/tile instances (sampler_impl.cu:256-257) */
-    uint32_t reserved[48]; /* pad to 256 bytes */
+    /* culled mode only (pigs_preprocess_count_culled); zero / reference values otherwise */
+    float tile_width;      /* width of the tiles the lists are built on: 0.51f, or 0.51f / subdiv */
+    float cull_sigmas;     /* 0 = reference pair set */
+    int32_t subdiv;        /* k: every reference tile is cut k x k; 0 or 1 = reference tiles */
+    int32_t ref_grid[2];   /* the reference's grid (S1); grid[] above is then k * ref_grid[] */
+    uint32_t reserved[43]; /* pad to 256 bytes */
 } pigs_header;
 
 int pigs_version(void);
@@ -78,6 +83,19 @@ int pigs_preprocess_count(int64_t P, int D, int64_t N, const float *means, const
                           const float *d_minmax, float *radii /* [P] out */, void *geom_ws,
                           void *stream);
 /* after this call the first sizeof(pigs_header) bytes of geom_ws hold the header (device memory) */
+
+/* Opt-in CULLED mode — NOT the reference's pair set, a subset of it.  The reference evaluates
+ * every (Gaussian, sample) pair whose 0.51-wide tile is in the Gaussian's tile rectangle (S8): at C3 about 128 K
+ * Gaussians per sample, of which < 10 K lie within 6 sigma.  Here every reference tile is cut into subdiv x subdiv fine
+ * tiles and a (Gaussian, fine tile) instance is kept iff the reference emits the parent tile AND the fine tile lies
+ * within r_c = cull_sigmas * sqrt(lambda_max(Sigma)) of the mean in every dimension (period-2 wrap, no 1e-6 floor).
+ * Every dropped pair is farther than cull_sigmas standard deviations and contributes < exp(-cull_sigmas^2 / 2) of its
+ * value.  `radii` keeps the reference radii.  Everything downstream (pigs_preprocess_bin, forward, backward) reads the
+ * parameters from the header and is otherwise unchanged; blocks / ranges / lists are the fine ones.  bench and tests
+ * report this mode separately, with its own pair count and its measured deviation from the exact mode. */
+int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float *means, const float *covariances,
+                                 const float *d_minmax, float *radii, void *geom_ws, int subdiv,
+                                 float cull_sigmas, void *stream);
 
 /* ---- preprocess stage B: key emission, stable sort by tile, ranges; sample binning ---------------
  * (sampler_impl.cu:54-189, 259-327).  Sizes are functions of the header values read back by the host. */

@@ -51,8 +51,11 @@ def out_shape(fn, N, D, C):
     return (N,) + (D,) * fn + (C,)
 
 
-def preprocess(means, covariances, samples, recip_mode=1, bounds=None):
+def preprocess(means, covariances, samples, recip_mode=1, bounds=None, cull=None):
     """PreprocessCUDA (sample_points.cu:37-98) + Sampler::preprocess (sampler_impl.cu:216-330).
+    cull=(sigmas, k) (NOT reference semantics): the product's opt-in culled binning — the reference pair set
+    intersected with a per-dimension `sigmas`-sigma box test on k x k sub-tiles of every reference tile; the returned
+    grid / blocks / lists / ranges are then the fine ones, `radii` stays the reference's (see pigs_oracle.c).
 
     Returns a dict with min_b, max_b, grid, blocks, radii, touched, num_rendered, point_list,
     ranges [(blocks+1),2] u32, sample_list, sample_tiles, sample_ranges.  `bounds=(min_b,max_b)`
@@ -77,6 +80,8 @@ def preprocess(means, covariances, samples, recip_mode=1, bounds=None):
     radii = np.zeros(P, np.float32)
     touched = np.zeros(P, np.uint32)
     L.pigs_oracle_radii(_i64(P), _int(D), _p(means), _p(cov), _p(min_b), _p(grid), _p(radii), _p(touched))
+    if cull is not None:
+        return _preprocess_culled(L, cull, means, cov, samples, P, D, N, min_b, max_b, grid, blocks, radii)
     R = int(touched.astype(np.int64).sum())
     point_list = np.zeros(max(R, 1), np.uint32)
     ranges = np.zeros((blocks + 1, 2), np.uint32)
@@ -93,6 +98,26 @@ def preprocess(means, covariances, samples, recip_mode=1, bounds=None):
     return dict(P=P, D=D, N=N, min_b=min_b, max_b=max_b, grid=grid, blocks=blocks, radii=radii, touched=touched,
                 num_rendered=R, point_list=point_list[:R], ranges=ranges, sample_list=sample_list[:N],
                 sample_tiles=sample_tiles[:N], sample_ranges=sample_ranges)
+
+
+def _preprocess_culled(L, cull, means, cov, samples, P, D, N, min_b, max_b, ref_grid, ref_blocks, radii):
+    sig, k = float(cull[0]), int(cull[1])
+    L.pigs_oracle_bin_gaussians_culled.restype = ctypes.c_int64
+    args = (_i64(P), _int(D), _p(means), _p(cov), _p(radii), _p(min_b), _p(ref_grid), _int(k), ctypes.c_float(sig))
+    R = L.pigs_oracle_bin_gaussians_culled(*args, None, None)
+    blocks = ref_blocks * (k ** D)
+    point_list = np.zeros(max(R, 1), np.uint32)
+    ranges = np.zeros((blocks + 1, 2), np.uint32)
+    R2 = L.pigs_oracle_bin_gaussians_culled(*args, _p(point_list), _p(ranges))
+    assert R2 == R
+    sample_list = np.zeros(max(N, 1), np.uint32)
+    sample_tiles = np.zeros(max(N, 1), np.uint32)
+    sample_ranges = np.zeros((blocks + 1, 2), np.uint32)
+    L.pigs_oracle_bin_samples_culled(_i64(N), _int(D), _p(samples), _p(min_b), _p(ref_grid), _int(k), _p(sample_list),
+                                     _p(sample_tiles), _p(sample_ranges))
+    return dict(P=P, D=D, N=N, min_b=min_b, max_b=max_b, grid=(ref_grid * k).astype(np.int32), ref_grid=ref_grid,
+                blocks=blocks, radii=radii, num_rendered=int(R), point_list=point_list[:R], ranges=ranges,
+                sample_list=sample_list[:N], sample_tiles=sample_tiles[:N], sample_ranges=sample_ranges)
 
 
 def pair_count(st):

@@ -75,11 +75,13 @@ def read_header(buf):
     return PigsHeader.from_buffer_copy(host.numpy().tobytes())
 
 
-def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None):
+def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, cull=None):
     """PreprocessCUDA (sample_points.cu:37-98).  Returns
     (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii).
     `bounds` (device float32[2*D], optional, extension) overrides the sample bounding box — used by
-    the multi-GPU sampler so every rank bins on the global tile grid."""
+    the multi-GPU sampler so every rank bins on the global tile grid.
+    `cull` = (sigmas, subdiv) (optional, extension): the opt-in culled mode of include/pigs_b200.h
+    pigs_preprocess_count_culled — a SUBSET of the reference's pair set, not the reference's result."""
     L = _lib.lib()
     means = _f32c(means, "means")
     P, D, N, C = _dims(means, values, samples)
@@ -98,8 +100,12 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
     st = _stream()
     mm = sample_bounds(samples, D) if bounds is None else _f32c(bounds, "bounds")
     geom = _bytes(L.pigs_geom_workspace_bytes(P), dev)
-    check(L.pigs_preprocess_count(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom), st),
-          "pigs_preprocess_count")
+    if cull is None:
+        check(L.pigs_preprocess_count(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom), st),
+              "pigs_preprocess_count")
+    else:
+        check(L.pigs_preprocess_count_culled(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom),
+                                             int(cull[1]), float(cull[0]), st), "pigs_preprocess_count_culled")
     h = read_header(geom)
     blocks, R = int(h.blocks), int(h.num_rendered)
     binning = _bytes(L.pigs_binning_bytes(R, blocks), dev)

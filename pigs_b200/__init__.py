@@ -163,8 +163,13 @@ class GaussianSampler:
     first request of the next cycle, evaluates that whole set in ONE kernel (and back-propagates it in
     one), handing out the cached pieces.  Results are identical to the unfused calls."""
 
-    def __init__(self, debug, fused="auto"):
+    def __init__(self, debug, fused="auto", cull=None):
         self.debug = debug
+        # (extension, SURVEY 8f rank 3) opt-in culled mode: cull = sigmas or (sigmas, subdiv).  A SUBSET of the
+        # reference's pair set: every reference tile is cut subdiv x subdiv and pairs whose fine tile is farther than
+        # `sigmas` standard deviations (major axis) from the mean are dropped, each worth < exp(-sigmas^2/2) of its
+        # value.  Default None = the reference's pair set, the mode every parity claim is made in.
+        self.cull = cull
         if fused == "auto":
             fused = os.environ.get("PIGS_B200_FUSE", "1") != "0"
         self.fused = bool(fused)
@@ -174,11 +179,12 @@ class GaussianSampler:
 
     def preprocess(self, means, values, covariances, conics, samples, bounds=None):
         debug = self.debug
-        if bounds is None:
+        cull = self._cull_params(covariances, means.shape[-1]) if self.cull is not None else None
+        if bounds is None and cull is None:
             res = preprocess_gaussians(means, values, covariances, conics, samples, debug)
         else:
-            res = call_debug(lambda *a: _C.preprocess_gaussians(*a, bounds=bounds), debug, "preprocess", means, values,
-                             covariances, conics, samples, debug)
+            res = call_debug(lambda *a: _C.preprocess_gaussians(*a, bounds=bounds, cull=cull), debug, "preprocess", means,
+                             values, covariances, conics, samples, debug)
         num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii = res
         self.means = means
         self.values = values
@@ -194,6 +200,19 @@ class GaussianSampler:
         self._plan, self._seen, self._cache = self._seen, 0, {}
         if (self._plan & FN_HESS) and (self._plan & FN_LAPL):
             self._plan &= ~FN_LAPL  # shared output slot: the Laplacian request then runs on its own
+
+    def _cull_params(self, covariances, D):
+        """(sigmas, subdiv).  Without an explicit subdivision: fine tiles about half as wide as the mean cut radius
+        (1 <= subdiv <= 16), which keeps the overshoot of the box test moderate without exploding the instance count.
+        Costs one extra device->host scalar read per preprocess."""
+        if isinstance(self.cull, (tuple, list)):
+            return float(self.cull[0]), int(self.cull[1])
+        sig = float(self.cull)
+        K = D * (D + 1) // 2
+        cov = covariances.detach().reshape(-1, K)
+        var = cov[:, 0] if D == 1 else torch.maximum(cov[:, 0], cov[:, 2])
+        rc = sig * float(var.sqrt().mean().item()) if cov.shape[0] else 1.0
+        return sig, int(min(16, max(1, round(2.0 * 0.51 / max(rc, 1e-6)))))
 
     def _args(self):
         nr, bb, sbb, rg, srg = self._sample_state

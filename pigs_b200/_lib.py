@@ -27,7 +27,11 @@ class PigsHeader(ctypes.Structure):
         ("P", ctypes.c_int64),
         ("N", ctypes.c_int64),
         ("num_rendered", ctypes.c_int64),
-        ("reserved", ctypes.c_uint32 * 48),
+        ("tile_width", ctypes.c_float),
+        ("cull_sigmas", ctypes.c_float),
+        ("subdiv", ctypes.c_int32),
+        ("ref_grid", ctypes.c_int32 * 2),
+        ("reserved", ctypes.c_uint32 * 43),
     ]
 
 
@@ -42,6 +46,8 @@ SIGNATURES = {
     "pigs_sample_bounds": (c_int, [c_void_p, c_int64, c_int, c_void_p, c_void_p]),
     "pigs_geom_workspace_bytes": (c_size_t, [c_int64]),
     "pigs_preprocess_count": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "pigs_preprocess_count_culled": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
+                                             c_int, ctypes.c_float, c_void_p]),
     "pigs_binning_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_sample_binning_bytes": (c_size_t, [c_int64, c_int, c_int]),
     "pigs_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),

@@ -78,7 +78,8 @@ __global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ s
 // ---------------------------------------------------------------------------------------------
 // header / tile grid (sample_points.cu:73-74)
 // ---------------------------------------------------------------------------------------------
-__global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int64_t N, int recip, pigs_header* hdr)
+__global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int64_t N, int recip, int subdiv, float cull,
+                            pigs_header* hdr)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     pigs_header h;
@@ -95,11 +96,17 @@ __global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int6
         const float span = __fadd_rn(__fsub_rn(hi, lo), 1e-6f);
         const float q = recip ? __fmul_rn(span, inv) : __fdiv_rn(span, PIGS_TILE_WIDTH);
         int g = (int)ceilf(q);
+        h.ref_grid[d] = g;
+        if (subdiv > 1) g *= subdiv;  // culled mode: every reference tile cut subdiv x subdiv
         h.grid[d] = g;
         h.min_b[d] = lo;
         h.max_b[d] = hi;
         blocks *= g;
     }
+    if (D == 1) h.ref_grid[1] = 1;
+    h.subdiv = subdiv > 1 ? subdiv : 1;
+    h.cull_sigmas = subdiv > 1 ? cull : 0.0f;
+    h.tile_width = subdiv > 1 ? __fdiv_rn(PIGS_TILE_WIDTH, (float)subdiv) : PIGS_TILE_WIDTH;
     h.blocks = blocks;
     h.nslots = blocks + h.grid[0] + 2;
     *hdr = h;
@@ -134,10 +141,79 @@ __device__ __forceinline__ void tile_rect(float p, float off, float r, int& lo, 
     hi = (int)ceilf(__fdiv_rn(__fadd_rn(c, r), PIGS_TILE_WIDTH));
 }
 
+// ---- culled mode (include/pigs_b200.h pigs_preprocess_count_culled) -----------------------------------
+__device__ __forceinline__ int wrap_tile(int x, int g) { return x < 0 ? g + (x % g) : x % g; }
+
+template <int D>
+__device__ __forceinline__ float cull_radius(const float* __restrict__ cov, float sigmas)
+{
+    if (D == 1) return __fmul_rn(sigmas, __fsqrt_rn(cov[0]));
+    const float c0 = cov[0], c1 = cov[1], c2 = cov[2];
+    const float det = __fmaf_rn(c0, c2, -__fmul_rn(c1, c1));
+    const float mid = __fmul_rn(0.5f, __fadd_rn(c0, c2));
+    const float disc = __fmaf_rn(mid, mid, -det);
+    const double root = __dsqrt_rn(fmax(0.0, (double)disc));
+    const float lambda = __double2float_rn(__dadd_rn((double)mid, root));
+    return __fmul_rn(sigmas, __fsqrt_rn(lambda));
+}
+
+// distance from m (any of its period-2 images) to the interval [a, b]
+__device__ __forceinline__ float torus_interval_dist(float m, float a, float b)
+{
+    float best = __int_as_float(0x7f800000);
+#pragma unroll
+    for (int s = -1; s <= 1; s++) {
+        const float ms = __fadd_rn(m, 2.0f * (float)s);
+        const float dd = fmaxf(0.0f, fmaxf(__fsub_rn(a, ms), __fsub_rn(ms, b)));
+        best = fminf(best, dd);
+    }
+    return best;
+}
+
+// one dimension of one Gaussian: the reference rect [lo, hi) in reference tiles and the test for fine column j of
+// reference column x
+struct CullDim {
+    int lo, hi, g, k;
+    float mu, min_b, rc, h;
+    __device__ __forceinline__ void init(float mu_, float min_b_, float r_ref, float rc_, int g_, int k_, float h_)
+    {
+        mu = mu_;
+        min_b = min_b_;
+        rc = rc_;
+        g = g_;
+        k = k_;
+        h = h_;
+        const float c = __fsub_rn(mu, min_b);
+        lo = (int)floorf(__fdiv_rn(__fsub_rn(c, r_ref), PIGS_TILE_WIDTH));
+        hi = (int)ceilf(__fdiv_rn(__fadd_rn(c, r_ref), PIGS_TILE_WIDTH));
+        if (hi - lo >= g) {
+            lo = 0;
+            hi = g;
+        }
+    }
+    __device__ __forceinline__ bool kept(int x, int j, int& fx) const
+    {
+        const int tx = wrap_tile(x, g);
+        if (tx >= g) return false;  // the reference's alias slot: never evaluated there either
+        fx = k * tx + j;
+        const float a = __fadd_rn(min_b, __fmul_rn((float)fx, h));
+        const float b = __fadd_rn(min_b, __fmul_rn((float)(fx + 1), h));
+        return torus_interval_dist(mu, a, b) <= rc;
+    }
+    __device__ __forceinline__ int count() const
+    {
+        int n = 0, fx;
+        for (int x = lo; x < hi; x++)
+            for (int j = 0; j < k; j++) n += kept(x, j, fx) ? 1 : 0;
+        return n;
+    }
+};
+
 template <int D>
 __global__ void __launch_bounds__(256) count_kernel(int64_t P, const float* __restrict__ means,
                                                     const float* __restrict__ cov, const pigs_header* __restrict__ hdr,
-                                                    float* __restrict__ radii, uint32_t* __restrict__ touched)
+                                                    float* __restrict__ radii, uint32_t* __restrict__ touched,
+                                                    float* __restrict__ cull_r)
 {
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= P) return;
@@ -148,13 +224,26 @@ __global__ void __launch_bounds__(256) count_kernel(int64_t P, const float* __re
     if (!degenerate) {
         int lo, hi;
         tile_rect(means[g * D], hdr->min_b[0], r, lo, hi);
-        n = (uint32_t)min(hi - lo, hdr->grid[0]);
+        n = (uint32_t)min(hi - lo, hdr->ref_grid[0]);
         if (D == 2) {
             tile_rect(means[g * D + 1], hdr->min_b[1], r, lo, hi);
-            n = (uint32_t)min(hi - lo, hdr->grid[1]) * n;
+            n = (uint32_t)min(hi - lo, hdr->ref_grid[1]) * n;
         }
     }
-    radii[g] = n ? r : 0.0f;
+    radii[g] = n ? r : 0.0f;  // the reference radii in both modes
+    const int k = hdr->subdiv;
+    if (k > 1 && n) {
+        // culled mode: instances = kept fine columns x kept fine rows
+        const float rc = cull_radius<D>(cov + g * K, hdr->cull_sigmas);
+        cull_r[g] = rc;
+        CullDim cd;
+        cd.init(means[g * D], hdr->min_b[0], r, rc, hdr->ref_grid[0], k, hdr->tile_width);
+        n = (uint32_t)cd.count();
+        if (D == 2 && n) {
+            cd.init(means[g * D + 1], hdr->min_b[1], r, rc, hdr->ref_grid[1], k, hdr->tile_width);
+            n *= (uint32_t)cd.count();
+        }
+    }
     touched[g] = n;
 }
 
@@ -164,12 +253,53 @@ __global__ void store_total(const uint32_t* __restrict__ offsets, int64_t P, pig
     if (threadIdx.x == 0 && blockIdx.x == 0) hdr->num_rendered = (int64_t)offsets[P];
 }
 
-__device__ __forceinline__ int wrap_tile(int x, int g) { return x < 0 ? g + (x % g) : x % g; }
+// culled mode: one (fine tile, id) pair per kept fine tile, id-major
+template <int D>
+__device__ __forceinline__ void emit_culled(int64_t g, float r, const float* __restrict__ means,
+                                            const float* __restrict__ cull_r, const uint32_t* __restrict__ offsets,
+                                            const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
+                                            uint32_t* __restrict__ vals)
+{
+    uint32_t off = offsets[g];
+    const uint32_t end = offsets[g + 1];
+    if (off == end) return;
+    const int k = hdr->subdiv;
+    const float rc = cull_r[g], h = hdr->tile_width;
+    const int fg0 = hdr->grid[0];
+    CullDim cx, cy;
+    cx.init(means[g * D], hdr->min_b[0], r, rc, hdr->ref_grid[0], k, h);
+    if (D == 2) {
+        cy.init(means[g * D + 1], hdr->min_b[1], r, rc, hdr->ref_grid[1], k, h);
+        for (int y = cy.lo; y < cy.hi; y++)
+            for (int jy = 0; jy < k; jy++) {
+                int fy;
+                if (!cy.kept(y, jy, fy)) continue;
+                for (int x = cx.lo; x < cx.hi; x++)
+                    for (int jx = 0; jx < k; jx++) {
+                        int fx;
+                        if (!cx.kept(x, jx, fx)) continue;
+                        keys[off] = (uint32_t)(fy * fg0 + fx);
+                        vals[off] = (uint32_t)g;
+                        off++;
+                    }
+            }
+    } else {
+        for (int x = cx.lo; x < cx.hi; x++)
+            for (int jx = 0; jx < k; jx++) {
+                int fx;
+                if (!cx.kept(x, jx, fx)) continue;
+                keys[off] = (uint32_t)fx;
+                vals[off] = (uint32_t)g;
+                off++;
+            }
+    }
+}
 
 // S4: one (tile, id) pair per covered tile, id-major (sampler_impl.cu:54-129)
 template <int D>
 __global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __restrict__ means,
-                                                   const float* __restrict__ radii, const uint32_t* __restrict__ offsets,
+                                                   const float* __restrict__ radii, const float* __restrict__ cull_r,
+                                                   const uint32_t* __restrict__ offsets,
                                                    const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
                                                    uint32_t* __restrict__ vals)
 {
@@ -177,6 +307,10 @@ __global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __res
     if (g >= P) return;
     const float r = radii[g];
     if (!(r > 0.0f)) return;
+    if (hdr->subdiv > 1) {  // culled mode (grid-uniform branch)
+        emit_culled<D>(g, r, means, cull_r, offsets, hdr, keys, vals);
+        return;
+    }
     uint32_t off = offsets[g];
     const int g0 = hdr->grid[0], g1 = hdr->grid[1];
     int lo0, hi0, lo1 = 0, hi1 = 1;
@@ -219,13 +353,16 @@ __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float*
             s_box[k] = (k % (2 * D)) < D ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
         __syncthreads();
     }
-    const int g0 = hdr->grid[0];
+    const int g0 = hdr->ref_grid[0];
+    const int k = hdr->subdiv;
+    const float h = hdr->tile_width;
+    const int rblocks = D == 2 ? hdr->ref_grid[0] * hdr->ref_grid[1] : hdr->ref_grid[0];
     float mn[D];
     int gr[D];
 #pragma unroll
     for (int d = 0; d < D; d++) {
         mn[d] = hdr->min_b[d];
-        gr[d] = hdr->grid[d];
+        gr[d] = hdr->ref_grid[d];
     }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
         float x[D];
@@ -236,7 +373,22 @@ __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float*
             const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
             t[d] = min(gr[d], max(0, q));
         }
-        const uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+        uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+        if (k > 1) {
+            // culled mode: the reference tile (alias quirk included) cut k x k; not a real tile -> dump slot
+            const uint32_t rt = tile;
+            tile = (uint32_t)hdr->blocks;
+            if ((int)rt < rblocks) {
+                const int par[2] = {(int)(rt % (uint32_t)g0), (int)(rt / (uint32_t)g0)};
+                int f[D];
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), h) - k * par[d];
+                    f[d] = k * par[d] + min(k - 1, max(0, q));
+                }
+                tile = D == 2 ? (uint32_t)f[D - 1] * (uint32_t)hdr->grid[0] + (uint32_t)f[0] : (uint32_t)f[0];
+            }
+        }
         keys[i] = tile;
         vals[i] = (uint32_t)i;
         float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
@@ -327,17 +479,25 @@ size_t pigs_geom_workspace_bytes(int64_t P) { return GeomLayout(nullptr, P).byte
 int pigs_preprocess_count(int64_t P, int D, int64_t N, const float* means, const float* covariances,
                           const float* d_minmax, float* radii, void* geom_ws, void* stream)
 {
+    return pigs_preprocess_count_culled(P, D, N, means, covariances, d_minmax, radii, geom_ws, 1, 0.0f, stream);
+}
+
+int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float* means, const float* covariances,
+                                 const float* d_minmax, float* radii, void* geom_ws, int subdiv, float cull_sigmas,
+                                 void* stream)
+{
     PIGS_ARG(D == 1 || D == 2);
     PIGS_ARG(P > 0 && N > 0 && means && covariances && d_minmax && radii && geom_ws);
+    PIGS_ARG(subdiv >= 1 && subdiv <= 64 && (subdiv == 1 || cull_sigmas > 0.0f));
     cudaStream_t st = (cudaStream_t)stream;
     GeomLayout g(geom_ws, P);
-    grid_kernel<<<1, 32, 0, st>>>(d_minmax, D, P, N, g_recip_mode, g.hdr);
+    grid_kernel<<<1, 32, 0, st>>>(d_minmax, D, P, N, g_recip_mode, subdiv, cull_sigmas, g.hdr);
     PIGS_LAUNCH_CHECK();
     const unsigned nb = (unsigned)((P + 255) / 256);
     if (D == 2)
-        count_kernel<2><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched);
+        count_kernel<2><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched, g.cull_r);
     else
-        count_kernel<1><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched);
+        count_kernel<1><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched, g.cull_r);
     PIGS_LAUNCH_CHECK();
     int rc = exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st);
     if (rc) return rc;
@@ -386,9 +546,9 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
     if (num_rendered > 0) {
         const unsigned nb = (unsigned)((P + 255) / 256);
         if (D == 2)
-            emit_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, g.touched, g.hdr, keys_u, vals_u);
+            emit_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u);
         else
-            emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.touched, g.hdr, keys_u, vals_u);
+            emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u);
         PIGS_LAUNCH_CHECK();
         int rc = stable_sort_pairs_u32(keys_u, vals_u, b.tiles, b.list, num_rendered, bits, sws, st);
         if (rc) return rc;

@@ -8,6 +8,7 @@ struct GeomLayout {
     pigs_header* hdr;
     uint32_t* touched;  // [P+1]; becomes exclusive offsets (+ total) after the scan
     char* scan_ws;
+    float* cull_r;  // [P] culled-mode radius r_c (written only by pigs_preprocess_count_culled with subdiv > 1)
     size_t bytes;
     GeomLayout(void* base, int64_t P)
     {
@@ -15,6 +16,7 @@ struct GeomLayout {
         hdr = c.take<pigs_header>(1);
         touched = c.take<uint32_t>((size_t)P + 1);
         scan_ws = c.take<char>(scan_ws_bytes(P));
+        cull_r = c.take<float>((size_t)(P > 0 ? P : 1));
         bytes = c.total();
     }
 };

@@ -44,8 +44,8 @@ class ShardedGaussianSampler(GaussianSampler):
     grid, backward all-reduces the gradients w.r.t. means / values / conics (so every rank ends up with the
     full-batch gradient, as a single-GPU run over all samples would)."""
 
-    def __init__(self, debug, group=None, fused="auto"):
-        super().__init__(debug, fused=fused)
+    def __init__(self, debug, group=None, fused="auto", cull=None):
+        super().__init__(debug, fused=fused, cull=cull)
         self.group = group
         self._reduce = allreduce_grads
 

@@ -1,0 +1,91 @@
+"""Opt-in CULLED mode against the exact (reference pair set) mode, reported separately:
+time of the fused forward (u, grad u, Hessian) + fused backward, the TRUE pair count each mode evaluates, and the
+measured deviation of every output and parameter gradient from the exact mode (norm-wise, max|a-b| / max|b|).
+
+    python tools/bench_culled.py [C2|C3|C4 ...] > profiles/rNN_culled.json
+
+Timing: CUDA events on torch's current stream, 2 warm-ups, median of 5; working set > L2 at every size here."""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from pigs_b200 import GaussianSampler, _C  # noqa: E402
+from tests.fixtures import synthetic  # noqa: E402
+
+WORK = {"C2": (100_000, 1_000_000, {}), "C3": (1_000_000, 4_000_000, {}),
+        "C4": (500_000, 2_000_000, dict(edge_fraction=0.1, anisotropy=4.0)), "tiny": (20_000, 200_000, {})}
+
+
+def ev_time(fn, warm=2, it=5):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(it):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    return float(np.median(ts))
+
+
+def rel(a, b):
+    den = float(b.abs().max())
+    return float((a - b).abs().max()) / den if den > 0 else float(a.abs().max())
+
+
+def run(d, ups, cull):
+    s = GaussianSampler(False, fused=False, cull=cull)
+    pre = lambda: s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    t_pre = ev_time(pre)
+    nr, bb, sbb, rg, srg = s._sample_state
+    a = (d["means"], d["values"], d["conics"], d["samples"], nr)
+    fwd = lambda: _C.sample_forward(7, *a, bb, sbb, rg, srg, False)
+    bwd = lambda: _C.sample_backward(7, *a, [ups[0], ups[1], ups[2], None], bb, sbb, rg, srg, False)
+    t_f, t_b = ev_time(fwd), ev_time(bwd)
+    outs = fwd()[:3] + tuple(bwd())
+    hdr = _C.read_header(bb)
+    return dict(cull=cull, subdiv=int(hdr.subdiv), tile_width=float(hdr.tile_width), grid=[int(hdr.grid[0]), int(hdr.grid[1])],
+                blocks=int(hdr.blocks),
+                instances=int(nr), pairs=s.pair_count(), preprocess_ms=t_pre, fwd_ms=t_f, bwd_ms=t_b,
+                step_ms=t_pre + t_f + t_b), outs
+
+
+def main():
+    names = [a for a in sys.argv[1:] if a in WORK] or ["C2"]
+    out = {"gpu": torch.cuda.get_device_name(0), "outputs": ["u", "grad_u", "hessian", "dL_dmeans", "dL_dvalues", "dL_dconics"],
+           "workloads": {}}
+    for name in names:
+        P, N, kw = WORK[name]
+        rec = synthetic(P, N, seed=0, **kw)
+        d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+        g = torch.Generator(device="cuda").manual_seed(1)
+        ups = [torch.randn((N,) + (2,) * k + (1,), device="cuda", generator=g) for k in range(3)]
+        exact, ref = run(d, ups, None)
+        rows = [exact]
+        for cull in (5.0, 6.0, (6.0, 2), (6.0, 4), (6.0, 8), (6.0, 12), (6.0, 16)):
+            try:
+                row, outs = run(d, ups, cull)
+            except RuntimeError as e:  # e.g. workspace larger than memory at a too-fine grid
+                rows.append(dict(cull=cull, error=str(e)[:200]))
+                continue
+            row["deviation_from_exact"] = [rel(a, b) for a, b in zip(outs, ref)]
+            row["speedup_vs_exact"] = exact["step_ms"] / row["step_ms"]
+            row["pair_fraction"] = row["pairs"] / exact["pairs"]
+            rows.append(row)
+            del outs
+        out["workloads"][name] = {"gaussians": P, "points": N, "rows": rows}
+        del ref, d, ups
+        torch.cuda.empty_cache()
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
