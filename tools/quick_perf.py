@@ -95,7 +95,11 @@ def ref_perf(P, N):
 if __name__ == "__main__":
     print(torch.cuda.get_device_name(0))
     if "--ref" in sys.argv:
-        ref_perf(20_000, 200_000)
+        # the unmodified reference CUDA extension (oracle/_ref/_C.so) on the same GPU, next to ours at the same size
+        sizes = [(20_000, 200_000)] + ([(100_000, 1_000_000)] if "--ref-c2" in sys.argv else [])
+        for P, N in sizes:
+            ref_perf(P, N)
+            perf(P, N, "OURS at the same size")
         sys.exit(0)
     if "--no-micro" not in sys.argv:
         micro()
