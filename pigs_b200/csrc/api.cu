@@ -54,6 +54,7 @@ struct ScopedKernelTimer {
 // the unwanted outputs/upstreams left NULL.
 unsigned native_low_mask(unsigned m)
 {
+    if (m & PIGS_FN_LAPL) return (m & 3u) ? 19u : 16u;  // trace-only kernels (2-D, one channel): Laplacian (+ value + gradient)
     m &= 7u;
     if (m == 0u || m == 1u || m == 2u || m == 4u) return m;
     return 7u;
@@ -62,7 +63,7 @@ unsigned native_low_mask(unsigned m)
 int max_sv4(int D, int C)
 {
     int m = 0;
-    const unsigned masks[5] = {1u, 2u, 4u, 7u, 8u};
+    const unsigned masks[7] = {1u, 2u, 4u, 7u, 8u, 16u, 19u};
     for (unsigned k : masks) {
         int v = srec_v4(D, C, k);
         if (v > m) m = v;
@@ -183,7 +184,10 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
         const int cw = (C - ch0) >= 2 ? 2 : 1;
         rc = stage_gaussians(c, cw, ch0, true, ws, st);
         if (rc) return rc;
-        unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
+        // Laplacian: 2-D one-channel groups run the trace-only kernels (mask 16 / 19); other shapes run the Hessian
+        // kernels and form the trace in the epilogue
+        const bool lap_native = lap && D == 2 && cw == 1;
+        unsigned todo[2] = {native_low_mask(lap_native ? ((fn_mask & 3u) | PIGS_FN_LAPL) : fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
             if (!m) continue;
             const uint32_t chunk = EV_THREADS * fwd_ks(D, cw, m);
@@ -194,7 +198,7 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
             o.du = (fn_mask & PIGS_FN_DERIV) ? out_du : nullptr;
             o.ddu = (fn_mask & PIGS_FN_HESS) ? out_ddu : nullptr;
             o.dddu = (fn_mask & PIGS_FN_THIRD) ? out_dddu : nullptr;
-            o.lap = lap;
+            o.lap = (lap && !lap_native) ? 1 : 0;
             {
                 ScopedKernelTimer tm(0, st);
                 for (int mode = 0; mode < EV_NSEG; mode++) {
@@ -216,8 +220,8 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
 {
     PIGS_ARG(fn_mask != 0 && (fn_mask & ~31u) == 0);
     PIGS_ARG(!((fn_mask & PIGS_FN_HESS) && (fn_mask & PIGS_FN_LAPL)));  // they share dL_dddu
-    const bool lap = (fn_mask & PIGS_FN_LAPL) != 0;
-    if (lap) fn_mask = (fn_mask & ~PIGS_FN_LAPL) | PIGS_FN_HESS;  // d lap / d H = I, applied while packing the samples
+    bool lap = (fn_mask & PIGS_FN_LAPL) != 0;
+    if (lap) fn_mask = (fn_mask & ~PIGS_FN_LAPL) | PIGS_FN_HESS;  // d lap / d H = I (trace-only kernels, or applied while packing)
     EvalCall c;
     int rc = resolve(c, P, D, N, C, blocks, num_rendered, means, values, conics, samples, binning_buffer,
                      sample_binning_buffer, ranges, sample_ranges);
@@ -229,6 +233,7 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
     if (!dL_ddu) fn_mask &= ~PIGS_FN_DERIV;
     if (!dL_dddu) fn_mask &= ~PIGS_FN_HESS;
     if (!dL_ddddu) fn_mask &= ~PIGS_FN_THIRD;
+    lap = lap && (fn_mask & PIGS_FN_HESS);
     if (num_rendered == 0 || fn_mask == 0) return 0;
     cudaStream_t st = (cudaStream_t)stream;
     const int Cg = C >= 2 ? 2 : 1;
@@ -238,12 +243,13 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
         const int cw = (C - ch0) >= 2 ? 2 : 1;
         rc = stage_gaussians(c, cw, ch0, false, ws, st);
         if (rc) return rc;
-        unsigned todo[2] = {native_low_mask(fn_mask), fn_mask & PIGS_FN_THIRD};
+        const bool lap_native = lap && D == 2 && cw == 1;
+        unsigned todo[2] = {native_low_mask(lap_native ? ((fn_mask & 3u) | PIGS_FN_LAPL) : fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
             if (!m) continue;
             rc = stage_samples(c, cw, m, ch0, (fn_mask & PIGS_FN_VALUE) ? dL_du : nullptr,
                                (fn_mask & PIGS_FN_DERIV) ? dL_ddu : nullptr, (fn_mask & PIGS_FN_HESS) ? dL_dddu : nullptr,
-                               (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, lap, ws, st);
+                               (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, lap && !lap_native, ws, st);
             if (rc) return rc;
             const uint32_t chunk = EV_THREADS * bwd_kg(D, cw, m);
             rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks), 128, false, st);

@@ -29,12 +29,14 @@ template <unsigned MASK, int MODE, int KG>
 __device__ __forceinline__ void bwd_sample_2d(const GaussReg<2, 1> (&g)[KG], const float* __restrict__ r,
                                               float (&dm)[KG][2], float (&dc)[KG][3], float (&dv)[KG][1])
 {
-    constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0, HH = (MASK & PIGS_FN_HESS) != 0;
+    constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0;
+    constexpr bool HL = (MASK & PIGS_FN_LAPL) != 0;  // Laplacian = Hessian with G00 = G11 = gl, G01 = 0 (scalar path: as such)
+    constexpr bool HH = (MASK & PIGS_FN_HESS) != 0 || HL;
     constexpr int OD = 2 + (HV ? 1 : 0), OH = OD + (HD ? 2 : 0);
     const float x0 = r[0], x1 = r[1];
     const float gu = HV ? r[2] : 0.0f;
     const float g0 = HD ? r[OD] : 0.0f, g1 = HD ? r[OD + 1] : 0.0f;
-    const float G00 = HH ? r[OH] : 0.0f, G01 = HH ? r[OH + 1] : 0.0f, G11 = HH ? r[OH + 2] : 0.0f;
+    const float G00 = HH ? r[OH] : 0.0f, G01 = (HH && !HL) ? r[OH + 1] : 0.0f, G11 = HL ? r[OH] : (HH ? r[OH + 2] : 0.0f);
     float X0[KG], X1[KG], a0[KG], a1[KG], al[KG], S[KG], p0[KG], p1[KG];
 #pragma unroll
     for (int j = 0; j < KG; j++) X0[j] = g[j].m[0] - x0;
@@ -155,6 +157,7 @@ __device__ __forceinline__ void bwd_sample_2d(const GaussReg<2, 1> (&g)[KG], con
 template <int KP>
 struct GaussPairs {
     f32x2 m0[KP], m1[KP], c0[KP], c1[KP], c2[KP], sh0[KP], sh1[KP], v[KP];
+    f32x2 tc[KP];  // c0 + c2 (trace-only Laplacian kernels)
     f32x2 dv[KP], dm0[KP], dm1[KP], dc0[KP], dc1[KP], dc2[KP];
 };
 
@@ -168,11 +171,13 @@ template <unsigned MASK, int MODE, int KP>
 __device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const float* __restrict__ r)
 {
     constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0, HH = (MASK & PIGS_FN_HESS) != 0;
+    constexpr bool HL = (MASK & PIGS_FN_LAPL) != 0;
     constexpr int OD = 2 + (HV ? 1 : 0), OH = OD + (HD ? 2 : 0);
     const float x0 = r[0], x1 = r[1];
     const float gu = HV ? r[2] : 0.0f;
     const float g0 = HD ? r[OD] : 0.0f, g1 = HD ? r[OD + 1] : 0.0f;
     const float G00 = HH ? r[OH] : 0.0f, G01 = HH ? r[OH + 1] : 0.0f, G11 = HH ? r[OH + 2] : 0.0f;
+    const float gl = HL ? r[OH] : 0.0f;
     f32x2 X0[KP], X1[KP], a0[KP], a1[KP], al[KP], S[KP], p0[KP], p1[KP];
 #pragma unroll
     for (int k = 0; k < KP; k++) X0[k] = add2(G.m0[k], bc2(-x0));
@@ -246,6 +251,20 @@ __device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const fl
         for (int k = 0; k < KP; k++) p0[k] = fma2(bc2(G01), a1[k], p0[k]);
 #pragma unroll
         for (int k = 0; k < KP; k++) p1[k] = fma2(bc2(G01), a0[k], p1[k]);
+    } else if constexpr (HL) {
+        // trace only: S += gl (a0^2 + a1^2 - tr C), p = g + 2 gl a
+        f32x2 h[KP];
+#pragma unroll
+        for (int k = 0; k < KP; k++) h[k] = fma2(a0[k], a0[k], neg2(G.tc[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) h[k] = fma2(a1[k], a1[k], h[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) S[k] = fma2(bc2(gl), h[k], S[k]);
+        const float glx2 = gl + gl;
+#pragma unroll
+        for (int k = 0; k < KP; k++) p0[k] = fma2(bc2(glx2), a0[k], bc2(g0));
+#pragma unroll
+        for (int k = 0; k < KP; k++) p1[k] = fma2(bc2(glx2), a1[k], bc2(g1));
     } else {
 #pragma unroll
         for (int k = 0; k < KP; k++) {
@@ -259,7 +278,7 @@ __device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const fl
     for (int k = 0; k < KP; k++) {
         const f32x2 Sk = S[k], hS = mul2(Sk, bc2(-0.5f));
         f32x2 r0, r1, e1, e2, T0, T1, T2;
-        if constexpr (HD || HH) {
+        if constexpr (HD || HH || HL) {
             r0 = fma2(neg2(Sk), X0[k], p0[k]);
             e1 = fma2(hS, X0[k], p0[k]);
             r1 = fma2(neg2(Sk), X1[k], p1[k]);
@@ -274,6 +293,10 @@ __device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const fl
             T0 = fma2(e1, X0[k], bc2(-G00));
             T1 = fma2(e1, X1[k], fma2(e2, X0[k], bc2(-G01)));
             T2 = fma2(e2, X1[k], bc2(-G11));
+        } else if constexpr (HL) {
+            T0 = fma2(e1, X0[k], bc2(-gl));
+            T1 = fma2(e1, X1[k], mul2(e2, X0[k]));
+            T2 = fma2(e2, X1[k], bc2(-gl));
         } else {
             T0 = mul2(e1, X0[k]);
             T1 = fma2(e1, X1[k], mul2(e2, X0[k]));
@@ -361,6 +384,8 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 GP.sh0[k] = pk2_once(ga.sh[0], gb.sh[0], nz);
                 GP.sh1[k] = pk2_once(ga.sh[D - 1], gb.sh[D - 1], nz);
                 GP.v[k] = pk2_once(ga.v[0], gb.v[0], nz);
+                if constexpr ((MASK & PIGS_FN_LAPL) != 0)
+                    GP.tc[k] = pk2_once(ga.c[0] + ga.c[NC - 1], gb.c[0] + gb.c[NC - 1], nz);
                 GP.dv[k] = GP.dm0[k] = GP.dm1[k] = GP.dc0[k] = GP.dc1[k] = GP.dc2[k] = bc2(0.0f);
             }
         }
@@ -556,6 +581,7 @@ int launch_backward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, 
     if (c.D == D_ && C == C_ && mask == M_) return launch_bwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
 #define BW_ALL(D_, C_) BW(D_, C_, 1u) BW(D_, C_, 2u) BW(D_, C_, 4u) BW(D_, C_, 7u) BW(D_, C_, 8u)
     BW_ALL(2, 1) BW_ALL(2, 2) BW_ALL(1, 1) BW_ALL(1, 2)
+    BW(2, 1, 16u) BW(2, 1, 19u)  // trace-only Laplacian kernels
 #undef BW_ALL
 #undef BW
     return set_error(-1, "unsupported (D, C, mask)", __FILE__, __LINE__);

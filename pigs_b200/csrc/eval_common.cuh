@@ -22,14 +22,22 @@ constexpr int EV_THREADS = 256;
 
 // ---- compile-time sizes ------------------------------------------------------------------------
 // unique (symmetric) components per channel of each function
+// PIGS_FN_LAPL as a KERNEL mask bit (2-D, one channel; masks 16 and 19 = value + gradient + Laplacian): the trace of
+// the Hessian as ONE accumulator — a0^2 + a1^2 - tr(Conic) — instead of three (16 instead of 19 forward lane-ops per
+// pair, 31.5 instead of 36.5 backward).  It takes the Hessian's place in every component order; never both.
 __host__ __device__ constexpr int nsym(int D, unsigned bit)
 {
-    return bit == PIGS_FN_VALUE ? 1 : bit == PIGS_FN_DERIV ? D : bit == PIGS_FN_HESS ? D * (D + 1) / 2 : (D == 2 ? 4 : 1);
+    return bit == PIGS_FN_VALUE  ? 1
+           : bit == PIGS_FN_DERIV ? D
+           : bit == PIGS_FN_HESS  ? D * (D + 1) / 2
+           : bit == PIGS_FN_LAPL  ? 1
+                                  : (D == 2 ? 4 : 1);
 }
 __host__ __device__ constexpr int nacc(int D, unsigned mask)
 {
     return ((mask & PIGS_FN_VALUE) ? nsym(D, PIGS_FN_VALUE) : 0) + ((mask & PIGS_FN_DERIV) ? nsym(D, PIGS_FN_DERIV) : 0) +
-           ((mask & PIGS_FN_HESS) ? nsym(D, PIGS_FN_HESS) : 0) + ((mask & PIGS_FN_THIRD) ? nsym(D, PIGS_FN_THIRD) : 0);
+           ((mask & PIGS_FN_HESS) ? nsym(D, PIGS_FN_HESS) : 0) + ((mask & PIGS_FN_LAPL) ? nsym(D, PIGS_FN_LAPL) : 0) +
+           ((mask & PIGS_FN_THIRD) ? nsym(D, PIGS_FN_THIRD) : 0);
 }
 __host__ __device__ constexpr int nconic(int D) { return D * (D + 1) / 2; }
 // Gaussian record: D means, D(D+1)/2 conics, C values, 1 wrap-shift code (SHIFT instances), padded to float4s
@@ -245,7 +253,7 @@ struct PairGeom {
 };
 
 // polynomial factors f_w(a, Conic) of every requested function, unique components only, order:
-// [value][deriv d0,d1][hess 00,01,11][third 000,001,011,111]
+// [value][deriv d0,d1][hess 00,01,11 | laplacian][third 000,001,011,111]
 template <int D, unsigned MASK>
 __device__ __forceinline__ void pair_factors(const float* __restrict__ a, const float* __restrict__ c, float* __restrict__ f)
 {
@@ -263,6 +271,13 @@ __device__ __forceinline__ void pair_factors(const float* __restrict__ a, const 
             f[k++] = fmaf(a[0], a[1], -c[1]);
             f[k++] = fmaf(a[1], a[1], -c[2]);
         }
+    }
+    if constexpr ((MASK & PIGS_FN_LAPL) != 0) {
+        static_assert(!((MASK & PIGS_FN_LAPL) && (MASK & PIGS_FN_HESS)), "Laplacian takes the Hessian's place");
+        if constexpr (D == 1)
+            f[k++] = fmaf(a[0], a[0], -c[0]);
+        else
+            f[k++] = fmaf(a[0], a[0], fmaf(a[1], a[1], -(c[0] + c[2])));  // trace of a a^T - C
     }
     if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
         if constexpr (D == 1) {
@@ -317,6 +332,15 @@ __device__ __forceinline__ void upstream_spe(const float* __restrict__ G, const 
             E[2] = -g11;
             k += 3;
         }
+    }
+    if constexpr ((MASK & PIGS_FN_LAPL) != 0) {
+        const float gl = G[k];  // = G00 = G11, G01 = 0
+        S = fmaf(gl, f[k], S);
+#pragma unroll
+        for (int d = 0; d < D; d++) p[d] = fmaf(2.0f * gl, a[d], p[d]);
+        E[0] = -gl;
+        if constexpr (D == 2) E[2] = -gl;
+        k++;
     }
     if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
         if constexpr (D == 1) {

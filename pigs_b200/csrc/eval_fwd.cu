@@ -287,6 +287,10 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                         k += 3;
                     }
                 }
+                if constexpr ((MASK & PIGS_FN_LAPL) != 0) {
+                    if (out_ddu) atomicAdd(out_ddu + id * Ctot + c, IK2 * acc[s][ch][k]);
+                    k++;
+                }
                 if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
                     if constexpr (D == 1) {
                         if (out_dddu) atomicAdd(out_dddu + id * Ctot + c, IK3 * acc[s][ch][k]);
@@ -342,6 +346,7 @@ int launch_forward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, c
     if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
 #define FW_ALL(D_, C_) FW(D_, C_, 1u) FW(D_, C_, 2u) FW(D_, C_, 4u) FW(D_, C_, 7u) FW(D_, C_, 8u)
     FW_ALL(2, 1) FW_ALL(2, 2) FW_ALL(1, 1) FW_ALL(1, 2)
+    FW(2, 1, 16u) FW(2, 1, 19u)  // trace-only Laplacian kernels (PIGS_FN_LAPL as a kernel mask bit)
 #undef FW_ALL
 #undef FW
     return set_error(-1, "unsupported (D, C, mask)", __FILE__, __LINE__);

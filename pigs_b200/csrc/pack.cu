@@ -168,6 +168,9 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
                 }
             }
         }
+        if constexpr ((MASK & PIGS_FN_LAPL) != 0) {
+            f[k++] = gH ? gH[sid * Ctot + c] : 0.0f;  // gH is the Laplacian's [N, C] upstream gradient here
+        }
         if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
             if constexpr (D == 1) {
                 f[k++] = gT ? gT[sid * Ctot + c] : 0.0f;
@@ -335,6 +338,7 @@ int stage_samples(const EvalCall& c, int C, unsigned mask, int ch0, const float*
     if (c.D == D_ && C == C_ && mask == M_) return stage_samples_t<D_, C_, M_>(c, ch0, gV, gD, gH, gT, lap, ws, st);
 #define SS_ALL(D_, C_) SS(D_, C_, 1u) SS(D_, C_, 2u) SS(D_, C_, 4u) SS(D_, C_, 7u) SS(D_, C_, 8u)
     SS_ALL(2, 1) SS_ALL(2, 2) SS_ALL(1, 1) SS_ALL(1, 2)
+    SS(2, 1, 16u) SS(2, 1, 19u)
 #undef SS_ALL
 #undef SS
     return set_error(-1, "unsupported (D, C, mask)", __FILE__, __LINE__);

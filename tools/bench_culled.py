@@ -70,7 +70,12 @@ def main():
         ups = [torch.randn((N,) + (2,) * k + (1,), device="cuda", generator=g) for k in range(3)]
         exact, ref = run(d, ups, None)
         rows = [exact]
-        for cull in (5.0, 6.0, (6.0, 2), (6.0, 4), (6.0, 8), (6.0, 12), (6.0, 16)):
+        rows_spec = (5.0, 6.0, (6.0, 2), (6.0, 4), (6.0, 8), (6.0, 12), (6.0, 16))
+        if "--zero" in sys.argv:
+            # 13.3 sigma: every dropped pair has exp2(KH q) < 2^-126, which ex2.approx.ftz flushes to exactly 0 — the
+            # culled result differs from the exact mode only by the order of the atomic adds
+            rows_spec = (13.3, (13.3, 2), (13.3, 4), (13.3, 6), (13.3, 8))
+        for cull in rows_spec:
             try:
                 row, outs = run(d, ups, cull)
             except RuntimeError as e:  # e.g. workspace larger than memory at a too-fine grid
