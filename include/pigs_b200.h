@@ -203,6 +203,29 @@ int pigs_pde_residual_backward(int problem, int64_t N, int D, int C, float nu, f
                                const float *lap, const float *ut, const float *dL_dloss, float *dL_du, float *dL_dux,
                                float *dL_dlap, float *dL_dut, void *stream);
 
+/* ---- split / prune as a device-side compaction --------------------------------
+ * Replaces the torch chains that change P between steps: model_pn.py:578-610 `Model.split`, :703-716 (prune by
+ * keep_indices), test_no_mlp_1d.py:203-247 (keep + displaced clones, Adam moments of the clones zeroed).
+ * Output rows = [rows with keep != 0, in order | m appended rows per row with extend != 0, in order, child 0..m-1].
+ * keep == NULL keeps every row, extend == NULL appends nothing.
+ *   pigs_compact_count : flags + two prefix sums; the first 16 bytes of `workspace` then hold int64 {n_keep, n_extend}
+ *                        (device memory; the caller reads them back once to size the outputs)
+ *   pigs_compact_fill  : src[Pout] = parent row of every output row, Pout = n_keep + m * n_extend
+ *   pigs_gather_rows   : out[i, :] = in[src[i], :] * (i < n_keep ? 1 : appended_scale)   (W floats per row;
+ *                        appended_scale 0.5 = `u / 2` of Model.split, 0 = fresh Adam moments, 1 = plain copy)
+ *   pigs_split_means   : Model.split's means: kept rows copied, the two children of a split row at
+ *                        mu -/+ lambda_max * v_max of the parent's covariance (flattened [xx, xy, yy]; 1-D: [s]).
+ *                        The reference's order of the two children follows LAPACK's eigenvector sign; here child 0 is
+ *                        the minus side of v = normalised (lambda - c2, c1) | (c1, lambda - c0). */
+size_t pigs_compact_workspace_bytes(int64_t P);
+int pigs_compact_count(int64_t P, const uint8_t *keep, const uint8_t *extend, void *workspace, void *stream);
+int pigs_compact_fill(int64_t P, const uint8_t *keep, const uint8_t *extend, int m, const void *workspace,
+                      int64_t n_keep, int64_t *src, void *stream);
+int pigs_gather_rows(int64_t Pout, int W, int64_t n_keep, const int64_t *src, const float *in, float *out,
+                     float appended_scale, void *stream);
+int pigs_split_means(int64_t Pout, int D, int64_t n_keep, const int64_t *src, const float *means,
+                     const float *covariances, float *out_means, void *stream);
+
 /* ---- roofline microbenchmarks (bench.py): register-resident FFMA / MUFU.EX2 loops ---------------
  * Each launches `ctas` CTAs x 256 threads running `iters` iterations of 64 independent ops per thread
  * and returns the number of lane-ops executed. Timing is done by the caller with CUDA events. */

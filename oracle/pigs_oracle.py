@@ -386,3 +386,46 @@ def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss):
     d_ux = np.zeros(ux.shape)
     d_ux[:, 0] = -u * drhs
     return -ux[:, 0] * drhs, d_ux, nu * drhs, dr
+
+
+# ---- split / prune compaction ---------------------------------------------------
+def compact_plan(P, keep=None, extend=None, m=1):
+    """Parent row of every output row: kept rows in order, then m rows per extended row (model_pn.py:598-605 cat order)."""
+    keep = np.ones(P, bool) if keep is None else np.asarray(keep).reshape(-1).astype(bool)
+    ext = np.zeros(P, bool) if extend is None else np.asarray(extend).reshape(-1).astype(bool)
+    kept = np.nonzero(keep)[0]
+    return np.concatenate([kept, np.repeat(np.nonzero(ext)[0], m)]).astype(np.int64), int(kept.size), int(ext.sum())
+
+
+def split(means, scaling, transforms, u, cov, indices):
+    """Model.split, model_pn.py:578-610, with the flattened covariances [P, d(d+1)/2]: eigen-decomposition of the
+    symmetric matrix (float64), displacement = |lambda_max| * v_max, children at mu - disp, mu + disp.  The sign of
+    v_max is not defined by the reference (LAPACK's choice): compare the two children of a parent as a set
+    (`children_sorted`)."""
+    idx = np.asarray(indices).reshape(-1).astype(bool)
+    P, D = means.shape
+    src, n_keep, n_split = compact_plan(P, ~idx, idx, 2)
+    out_means = means[src].astype(np.float64)
+    par = src[n_keep:].reshape(-1, 2)[:, 0]
+    if D == 1:
+        disp = np.abs(cov[par].astype(np.float64)).reshape(-1, 1)
+    else:
+        c = cov[par].astype(np.float64)
+        A = np.stack([np.stack([c[:, 0], c[:, 1]], -1), np.stack([c[:, 1], c[:, 2]], -1)], -2)
+        w, v = np.linalg.eigh(A)
+        k = np.argmax(np.abs(w), axis=-1)
+        rows = np.arange(par.size)
+        disp = np.abs(w[rows, k])[:, None] * v[rows, :, k]
+    out_means[n_keep::2] -= disp
+    out_means[n_keep + 1::2] += disp
+    out_u = u[src].astype(np.float32)
+    out_u[n_keep:] = out_u[n_keep:] / np.float32(2.0)
+    return out_means.astype(np.float32), scaling[src], transforms[src], out_u, src, n_keep
+
+
+def children_sorted(out_means, n_keep):
+    """Rows >= n_keep grouped per parent with the two children in lexicographic order (sign-of-eigenvector free)."""
+    ch = np.asarray(out_means, np.float64)[n_keep:].reshape(-1, 2, out_means.shape[-1])
+    swap = (ch[:, 0, 0] > ch[:, 1, 0]) | ((ch[:, 0, 0] == ch[:, 1, 0]) & (ch[:, 0, -1] > ch[:, 1, -1]))
+    ch[swap] = ch[swap][:, ::-1]
+    return ch
