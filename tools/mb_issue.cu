@@ -60,6 +60,7 @@ __device__ __forceinline__ u64 add2(u64 a, u64 b)
 // PM 3: PM 0 + 8 scalar FADD per 16 FFMA2
 // PM 4: PM 0 + 8 IADD3/LOP3 per 16 FFMA2
 // PM 5: A = mul2(X, A)   PM 6: A = add2(X, A)
+// PM 8 / 9 / 10: one pair operand shared by consecutive FFMA2s (does the operand-reuse cache save the third cycle?)
 // PM 7: PM 0 + 4 MUFU per 16 FFMA2 + 4 scalar FMUL (the forward's real side-work per 2x... )
 template <int PM>
 __global__ void __launch_bounds__(256) kp(int iters, float* sink, const float* src)
@@ -88,6 +89,9 @@ __global__ void __launch_bounds__(256) kp(int iters, float* sink, const float* s
             for (int i = 0; i < N; i++) {
                 if (PM == 0 || PM == 2 || PM == 3 || PM == 4 || PM == 7) a[i] = fma2(x[i], y[i], a[i]);
                 if (PM == 1) a[i] = fma2(pk(g, g), y[i], a[i]);
+                if (PM == 8) a[i] = fma2(x[0], y[i], a[i]);            // ONE pair shared by all 16 (slot A; .reuse)
+                if (PM == 9) a[i] = fma2(x[i / 6], y[i], a[i]);        // groups of 6 share a pair (the backward's accumulate phase)
+                if (PM == 10) a[i] = fma2(x[i & 1], y[i], a[i]);       // two shared pairs alternating (interleaved k = 0 / 1)
                 if (PM == 5) a[i] = mul2(x[i], a[i]);
                 if (PM == 6) a[i] = add2(x[i], a[i]);
                 if (PM == 3 && (i & 1)) f[i >> 1] = f[i >> 1] + g;
@@ -251,6 +255,9 @@ int main()
     run<8>("ffma distinct + 1 lds128/16", 64, 4, sink, src, sms, mhz);
     runp<0>("ffma2 3 distinct pairs", 64, 0, sink, src, sms, mhz);
     runp<1>("ffma2 bcast .F32 + 2 pairs", 64, 0, sink, src, sms, mhz);
+    runp<8>("ffma2 one shared pair (reuse) + 2 pairs", 64, 0, sink, src, sms, mhz);
+    runp<9>("ffma2 shared pair per group of 6", 64, 0, sink, src, sms, mhz);
+    runp<10>("ffma2 two shared pairs alternating", 64, 0, sink, src, sms, mhz);
     runp<5>("fmul2", 64, 0, sink, src, sms, mhz);
     runp<6>("fadd2", 64, 0, sink, src, sms, mhz);
     runp<2>("ffma2 distinct + 2 mufu/16", 64, 8, sink, src, sms, mhz);
