@@ -47,7 +47,7 @@ def srcs(t):
 def hot_loop(ins):
     best = None
     for i, (a, t) in enumerate(ins):
-        m = re.search(r"BRA\s+(0x[0-9a-f]+)", t)
+        m = re.search(r"BRA(?:\.U)?\s+(?:!?U?P\d+,\s*)?(0x[0-9a-f]+)", t)
         if not m:
             continue
         tgt = int(m.group(1), 16)
