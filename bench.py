@@ -48,16 +48,19 @@ EXEC_OPS_FWD, EXEC_OPS_BWD = 19.0, 36.5  # FP32 lane-ops per pair the kernels ac
 
 
 def ncu_traffic():
-    """DRAM bytes per launch of the dominant kernel from the committed `ncu --set full` summary (profiles/), or None.
-    bench.py cannot measure DRAM traffic itself; the summary is of the same command (tools/gpu_round.sh)."""
-    try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_eval_c3.json")))
-        for k in d["kernels"]:
-            if "eval_bwd_kernel<2, 1, 7, 0>" in k["kernel"] and "dram_read_bytes" in k:
-                return {"dram_bytes_per_launch": k["dram_read_bytes"] + k["dram_write_bytes"],
-                        "kernel": "eval_bwd_kernel<2,1,7,FAST> at C3, 1 GPU", "source": "profiles/r01_ncu_eval_c3.json"}
-    except Exception:
-        pass
+    """DRAM bytes per launch of the dominant kernel from the newest committed `ncu --set full` summary (profiles/), or
+    None.  bench.py cannot measure DRAM traffic itself; the summary is of the same command (tools/gpu_round.sh)."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_eval_c3.json")), reverse=True):
+        try:
+            d = json.load(open(path))
+            for k in d["kernels"]:
+                if "eval_bwd_kernel<2, 1, 7, 0>" in k["kernel"] and k.get("dram_read_bytes") == k.get("dram_read_bytes"):
+                    return {"dram_bytes_per_launch": k["dram_read_bytes"] + k["dram_write_bytes"],
+                            "kernel": "eval_bwd_kernel<2,1,7,FAST> at C3, 1 GPU",
+                            "source": "profiles/" + os.path.basename(path)}
+        except Exception:
+            continue
     return None
 
 
