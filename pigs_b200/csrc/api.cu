@@ -3,6 +3,7 @@
 // compiled (mask, channel-group) kernels, stage, launch.  No host synchronisation anywhere.
 #include "layouts.cuh"
 
+#include <stdlib.h>
 #include <vector>
 
 using namespace pigs;
@@ -100,13 +101,27 @@ int resolve(EvalCall& c, int64_t P, int D, int64_t N, int C, int blocks, int64_t
     return 0;
 }
 
-uint32_t split_hint(int64_t stationary, uint32_t chunk, int blocks)
+// Work items per SM the list aims for.  The tail of a persistent launch is about one item long, and the backward's
+// items (1024 Gaussians x a slice of the tile's samples) are the heavier ones: measured on B200 at C3 the backward goes
+// 696.5 -> 649 ms from 48 to 768 items per SM, the forward is flat to slightly worse (profiles/r01n_split_target.log).
+int split_target_per_sm(bool backward)
 {
-    const int64_t target = (int64_t)num_sms() * 48;
+    static int v[2] = {0, 0};
+    if (v[backward] == 0) {
+        const char* e = getenv(backward ? "PIGS_SPLIT_TARGET_BWD" : "PIGS_SPLIT_TARGET_FWD");  // tuning hook
+        v[backward] = e ? atoi(e) : (backward ? 768 : 48);
+        if (v[backward] < 1) v[backward] = 48;
+    }
+    return v[backward];
+}
+
+uint32_t split_hint(int64_t stationary, uint32_t chunk, int blocks, bool backward)
+{
+    const int64_t target = (int64_t)num_sms() * split_target_per_sm(backward);
     const int64_t base = stationary / chunk + blocks;
     int64_t s = (target + base - 1) / base;
     if (s < 1) s = 1;
-    if (s > 256) s = 256;
+    if (s > 4096) s = 4096;
     return (uint32_t)s;
 }
 
@@ -191,7 +206,7 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
         for (unsigned m : todo) {
             if (!m) continue;
             const uint32_t chunk = EV_THREADS * fwd_ks(D, cw, m);
-            rc = stage_worklist(c, ws, chunk, split_hint(N, chunk, blocks), 256, true, st);
+            rc = stage_worklist(c, ws, chunk, split_hint(N, chunk, blocks, false), 256, true, st);
             if (rc) return rc;
             FwdOut o;
             o.u = (fn_mask & PIGS_FN_VALUE) ? out_u : nullptr;
@@ -252,7 +267,7 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
                                (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, lap && !lap_native, ws, st);
             if (rc) return rc;
             const uint32_t chunk = EV_THREADS * bwd_kg(D, cw, m);
-            rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks), 128, false, st);
+            rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks, true), 128, false, st);
             if (rc) return rc;
             BwdOut o{dL_dmeans, dL_dvalues, dL_dconics};
             {
