@@ -116,15 +116,20 @@ def main():
 
     # ---- neighbour search at reference semantics (C5 ii) ----
     if "--search" in sys.argv:
-        torch.cuda.synchronize()
-        a0, b0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a0.record()
-        ind, rg, ds, dn, it = _C.preprocess_aggregate(d["means"], d["conics"], radii, False)
-        b0.record()
-        torch.cuda.synchronize()
-        ms = a0.elapsed_time(b0)
+        times = []
+        for rep in range(3):  # the first run pays cudaMalloc of the ~32 GB CSR; the caching allocator serves the next ones
+            ind = rg = ds = dn = it = None
+            torch.cuda.synchronize()
+            a0, b0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a0.record()
+            ind, rg, ds, dn, it = _C.preprocess_aggregate(d["means"], d["conics"], radii, False)
+            b0.record()
+            torch.cuda.synchronize()
+            times.append(a0.elapsed_time(b0))
+        ms = min(times[1:])
+        out["neighbour_search_runs_ms"] = [round(t, 3) for t in times]
         Ms = ind.numel()
-        out["rows"].append(row("preprocess_aggregate (grid neighbour search + CSR fill, one run)", ms, 20 * Ms,
+        out["rows"].append(row("preprocess_aggregate (grid neighbour search + CSR fill incl. the torch fills of the CSR; best warm run of 2)", ms, 20 * Ms,
                                "CSR write-out 20 B/slot (idx 8, dist 8, density 4); M=%d slots = %.0f per Gaussian" % (Ms, Ms / P)))
     print(json.dumps(out, indent=1))
 
