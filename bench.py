@@ -39,6 +39,7 @@ WORKLOADS = {
     "C3": (1_000_000, 4_000_000, {}, "2-D PDE residual (u, grad u, Hessian), 1M Gaussians x 4M points"),
     "C2": (100_000, 1_000_000, {}, "2-D density fit, 100K Gaussians x 1M points"),
     "C4": (500_000, 2_000_000, dict(edge_fraction=0.1, anisotropy=4.0), "periodic torus, 500K anisotropic Gaussians x 2M points"),
+    "C1": (1_000, 10_000, dict(D=1), "1-D diffusion-style mixture, 1K Gaussians x 10K points (the reference's CPU-runnable case)"),
     "tiny": (20_000, 200_000, {}, "debug: 20K Gaussians x 200K points"),
 }
 METRIC = "gaussian_point_evals_per_s_fwd_bwd_grad_hessian"
@@ -140,7 +141,8 @@ def make_inputs(workload, rank, world):
     rec = synthetic(P, N, seed=0, **kw)
     lo, hi = shard_range(N, rank, world)
     rng = np.random.default_rng(1234)
-    ups = [rng.standard_normal((N,) + (2,) * k + (1,), dtype=np.float32) for k in range(3)]
+    D = rec["means"].shape[1]
+    ups = [rng.standard_normal((N,) + (D,) * k + (1,), dtype=np.float32) for k in range(3)]
     rec["samples"] = np.ascontiguousarray(rec["samples"][lo:hi])
     ups = [np.ascontiguousarray(u[lo:hi]) for u in ups]
     return rec, ups
@@ -177,7 +179,7 @@ def cpu_baseline(workload, budget_s=12.0):
     from oracle import dense_torch as dt
     from tests.fixtures import synthetic
     P, N, kw, _ = WORKLOADS[workload]
-    n, m = 1000, 10000  # dense intermediates are O(n*m*d*d*4 B)
+    n, m = min(P, 1000), min(N, 10000)  # dense intermediates are O(n*m*d*d*4 B)
     rec = synthetic(P, min(N, 200_000), seed=0, **kw)
     rng = np.random.default_rng(7)
     gi = np.sort(rng.choice(P, n, replace=False))
@@ -190,7 +192,7 @@ def cpu_baseline(workload, budget_s=12.0):
     best = min(times + t1)
     return {"value": pairs / best, "unit": UNIT, "cores": torch.get_num_threads(), "host_cpus": os.cpu_count(),
             "kind": "port",
-            "sample": "dense all-pairs slice of %s: %d Gaussians x %d points (2-D), u + grad u + Hessian forward and "
+            "sample": "dense all-pairs slice of %s: %d Gaussians x %d points, u + grad u + Hessian forward and "
                       "autograd backward, oracle/dense_torch.py restating gaussians.py:48-116; best of %d" %
                       (workload, n, m, len(times) + 1)}
 
@@ -217,7 +219,7 @@ def run_ours(args):
     dev = {k: v.cuda(non_blocking=True) for k, v in host.items()}
     dev_ups = [u.cuda(non_blocking=True) for u in host_ups]
     torch.cuda.synchronize()
-    D, Nl = 2, dev["samples"].shape[0]
+    D, Nl = dev["means"].shape[1], dev["samples"].shape[0]
 
     def barrier():
         if world > 1:
@@ -308,7 +310,8 @@ def run_ours(args):
         if sampler is None:
             from diff_gaussian_sampling import GaussianSampler
             sampler = GaussianSampler(False)
-        hg = torch.empty(P * 6, dtype=torch.float32).pin_memory()
+        K = D * (D + 1) // 2
+        hg = torch.empty(P * (D + 1 + K), dtype=torch.float32).pin_memory()
         hu = torch.empty((Nl, 1), dtype=torch.float32).pin_memory()
         h2d = sum(host[k].numel() * 4 for k in ("means", "values", "covariances", "conics", "samples")) + \
             sum(u.numel() * 4 for u in host_ups)
@@ -325,9 +328,9 @@ def run_ours(args):
             uxx = sampler.sample_gaussians_laplacian()
             loss = (u * gu[0]).sum() + (ux * gu[1]).sum() + (uxx * gu[2]).sum()
             loss.backward()
-            hg[:P * 2].copy_(d["means"].grad.reshape(-1), non_blocking=True)
-            hg[P * 2:P * 3].copy_(d["values"].grad.reshape(-1), non_blocking=True)
-            hg[P * 3:].copy_(d["conics"].grad.reshape(-1), non_blocking=True)
+            hg[:P * D].copy_(d["means"].grad.reshape(-1), non_blocking=True)
+            hg[P * D:P * (D + 1)].copy_(d["values"].grad.reshape(-1), non_blocking=True)
+            hg[P * (D + 1):].copy_(d["conics"].grad.reshape(-1), non_blocking=True)
             hu.copy_(u.detach(), non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
@@ -374,6 +377,10 @@ def run_ours(args):
                                      (ncu_traffic() or {}).get("source", "")},
         "clocks": ck,
     }
+    if D != 2:
+        # the lane-op counts above are the 2-D one-channel kernels'; the 1-D case (C1) is launch-bound at its size
+        out["roofline"] = {"bound": "launch latency", "note": "1-D, 1K x 10K: ~60 dependent launches of a few us each; "
+                           "no FP32 roofline is claimed for this workload", "kernel_ms": {"eval_fwd": fwd_ms, "eval_bwd": bwd_ms}}
     if e2e:
         out["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
@@ -397,7 +404,7 @@ def run_reference(args):
     from oracle import dense_torch as dt
     from tests.fixtures import synthetic
     P, N, kw, desc = WORKLOADS[args.workload]
-    n, m = 1000, 10000
+    n, m = min(P, 1000), min(N, 10000)
     rec = synthetic(P, min(N, 200_000), seed=0, **kw)
     rng = np.random.default_rng(7)
     gi = np.sort(rng.choice(P, n, replace=False))
