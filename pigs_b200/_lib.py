@@ -8,7 +8,8 @@ import os
 import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libpigs_b200.so")
+# PIGS_B200_LIB: load another build of the same library (tuning experiments: tools/*.py time variant builds)
+_SO = os.environ.get("PIGS_B200_LIB") or os.path.join(_HERE, "libpigs_b200.so")
 _lib = None
 
 c_void_p, c_int, c_int64, c_size_t, c_uint = ctypes.c_void_p, ctypes.c_int, ctypes.c_int64, ctypes.c_size_t, ctypes.c_uint

@@ -17,6 +17,17 @@
 namespace pigs {
 
 constexpr int A16_THREADS = 256;
+// resident CTAs per SM the register allocation aims for: both kernels wait on dependent gathers (ncu: long_scoreboard
+// is the dominant stall), so occupancy is what hides the latency.  Measured on B200 at P = 1M x 16 neighbours
+// (profiles/r01t_agg16_occupancy.log): forward 1.10 ms at the compiler's 128 registers (2 CTAs / SM) -> 0.82 (4) ->
+// 0.72 ms at 6 CTAs / SM (40 registers + 112 B of local memory); backward 3.30 ms at 167 registers (1 CTA / SM) ->
+// 1.82 ms at 2 (128 registers + 112 B), slower again at 3
+#ifndef A16_FWD_MINB
+#define A16_FWD_MINB 6
+#endif
+#ifndef A16_BWD_MINB
+#define A16_BWD_MINB 2
+#endif
 
 // sin(pi t), cos(pi t) for t = f * X formed exactly as p + e, reduced modulo 2 exactly (reference: double sin/cos of
 // frequencies[e] * M_PI * X[d], aggregate_neighbors.cu:181-182)
@@ -57,7 +68,7 @@ __device__ __forceinline__ void load16(const float* __restrict__ row, float* __r
 }
 
 template <int D, int NF>
-__global__ void __launch_bounds__(A16_THREADS)
+__global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
     agg_forward16_kernel(int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
                          const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                          const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
@@ -148,7 +159,7 @@ __global__ void __launch_bounds__(A16_THREADS)
 //   dL/dT[a][b] += g_i[b] sum_s w_s dc_s (emb_s + fac_s feat_j[a])
 //   dL/ddt, dL/dfreq from dA = dc w A and dB = dc w B (reference :266-281)
 template <int D, int NF>
-__global__ void __launch_bounds__(A16_THREADS)
+__global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
     agg_backward16_kernel(int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
                           const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                           const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
