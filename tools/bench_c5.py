@@ -1,0 +1,60 @@
+"""Config C5 (BASELINE.json configs[4]: model_pn.py neighbour aggregation + PDE step, 1M Gaussians, 16 neighbours) as the
+sequence of library calls one `Model.forward` + loss backward makes (model_pn.py:644-700), timed stage by stage:
+  preprocess(samples = means) -> fused u / grad u / Hessian at the means (no grad, model_pn.py:647-651)
+  -> aggregation forward + backward on a 16-regular CSR (the reference's own neighbour rule gives ~1.6 K
+     neighbours per Gaussian at this P; `_C.aggregate_neighbors` takes the CSR as plain inputs)
+The MLP between them is torch (out of scope).  python tools/bench_c5.py > profiles/rNN_c5_stages.json"""
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tools"))
+from bench_hbm import regular_csr, timed  # noqa: E402
+from pigs_b200 import GaussianSampler, _C  # noqa: E402
+from tests.fixtures import agg_params, synthetic  # noqa: E402
+
+
+def main():
+    torch.cuda.set_device(0)
+    P = 1_000_000
+    rec = synthetic(P, 16, seed=0)
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    s = GaussianSampler(False)
+    pre = lambda: s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["means"])
+    t_pre = timed(pre)
+    pairs = s.pair_count()
+    with torch.no_grad():
+        t_fwd = timed(lambda: s.sample_fused(7), it=5, warm=2)
+        t_pde = timed(lambda: s.sample_fused(1 | 2 | 16), it=5, warm=2)
+    k = 16
+    idx, rng = regular_csr(rec["means"], k)
+    indices, ranges = torch.from_numpy(idx).cuda(), torch.from_numpy(rng).cuda()
+    i_of = torch.arange(P, device="cuda").repeat_interleave(k)
+    X = d["means"][indices] - d["means"][i_of]
+    X = torch.where(X.abs() > 1, X - 2 * torch.sign(X), X)
+    dists = (X / (0.333 * s.radii[i_of] + 1e-6).unsqueeze(1)).contiguous()
+    cj = d["conics"][indices]
+    dens = torch.exp(-0.5 * (cj[:, 0] * X[:, 0] ** 2 + cj[:, 2] * X[:, 1] ** 2) - cj[:, 1] * X[:, 0] * X[:, 1]).contiguous()
+    inv_total = (1.0 / (dens.view(P, k).sum(1) + 1e-6)).contiguous()
+    ap = {kk: torch.from_numpy(v).cuda() for kk, v in agg_params(P, 16, 16, 25, 2, seed=100).items()}
+    a = (ap["features"], ap["transform"], ap["queries"], ap["keys"], ap["frequencies"], ap["distance_transform"])
+    t_af = timed(lambda: _C.aggregate_neighbors(*a, indices, ranges, dists, dens, inv_total, False))
+    w, e, f, o = _C.aggregate_neighbors(*a, indices, ranges, dists, dens, inv_total, False)
+    g = torch.randn_like(o)
+    t_ab = timed(lambda: _C.aggregate_neighbors_backward(*a, indices, ranges, dists, dens, w, e, f, inv_total, g, False))
+    out = {"gpu": torch.cuda.get_device_name(0), "gaussians": P, "samples": "the means (model_pn.py:648)",
+           "pairs_of_the_sampling_pass": pairs,
+           "ms": {"preprocess": t_pre, "sample u + grad u + Hessian (no grad)": t_fwd,
+                  "sample u + grad u + Laplacian (no grad, PIGS_FN_LAPL)": t_pde,
+                  "aggregate forward (16-regular CSR, one head)": t_af, "aggregate backward": t_ab},
+           "step_ms_hessian": t_pre + t_fwd + t_af + t_ab, "step_ms_laplacian": t_pre + t_pde + t_af + t_ab}
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
