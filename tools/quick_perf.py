@@ -112,3 +112,5 @@ if __name__ == "__main__":
     perf(100_000, 1_000_000, "C2")
     if "--big" in sys.argv:
         perf(1_000_000, 4_000_000, "C3")
+    if "--shard8" in sys.argv:
+        perf(1_000_000, 500_000, "C3 / 8 (one rank's shard at N = 8)")
