@@ -45,7 +45,7 @@ WORKLOADS = {
 METRIC = "gaussian_point_evals_per_s_fwd_bwd_grad_hessian"
 UNIT = "pairs/s"
 LANE_OPS_FWD, LANE_OPS_BWD = 19, 45  # algorithmic FP32 lane-ops per pair
-EXEC_OPS_FWD, EXEC_OPS_BWD = 19.0, 36.5  # FP32 lane-ops per pair the kernels actually execute (SASS count)
+EXEC_OPS_FWD, EXEC_OPS_BWD = 18.0, 36.5  # FP32 lane-ops per pair the kernels actually execute (SASS count, tools/sass_issue_model.py)
 
 
 def ncu_traffic():
@@ -369,7 +369,10 @@ def run_ours(args):
                      "peak_measured_ffma": peaks["ffma"], "frac_of_measured_ffma": ach_bwd / peaks["ffma"] if ach_bwd else None,
                      "peak_measured_ex2": peaks["ex2"], "lane_ops_per_pair": LANE_OPS_BWD,
                      "fwd_plus_bwd": {"achieved": ach_all, "frac": ach_all / peak if ach_all else None,
-                                      "lane_ops_per_pair": LANE_OPS_FWD + LANE_OPS_BWD},
+                                      "lane_ops_per_pair": LANE_OPS_FWD + LANE_OPS_BWD,
+                                      "executed_lane_ops_per_pair": EXEC_OPS_FWD + EXEC_OPS_BWD,
+                                      "frac_executed": (pairs_local * (EXEC_OPS_FWD + EXEC_OPS_BWD) /
+                                                        ((bwd_ms + fwd_ms) * 1e-3) / 1e12 / peak) if bwd_ms > 0 else None},
                      "executed_lane_ops_per_pair": EXEC_OPS_BWD,
                      "frac_executed": (ach_bwd * EXEC_OPS_BWD / LANE_OPS_BWD) / peak if ach_bwd else None,
                      "traffic": (ncu_traffic() or {}).get("dram_bytes_per_launch"),

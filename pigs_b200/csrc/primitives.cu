@@ -121,6 +121,34 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t* __res
     if (write_total && blockIdx.x == 0 && threadIdx.x == 0) out[n] = bsum[nb];
 }
 
+// small inputs (the reference's own drivers run 1K-40K Gaussians): ONE CTA walks the tiles with a running carry —
+// one launch instead of three; out may alias in (a tile is read into registers before it is written)
+constexpr int64_t SCAN_SMALL_MAX = 16 * SCAN_TILE;
+__global__ void __launch_bounds__(SCAN_THREADS) scan_small(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int64_t n,
+                                                           int write_total)
+{
+    uint32_t carry = 0;
+    for (int64_t tile = 0; tile < n; tile += SCAN_TILE) {
+        const int64_t base = tile + (int64_t)threadIdx.x * SCAN_ITEMS;
+        uint32_t v[SCAN_ITEMS];
+        uint32_t s = 0;
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++) {
+            v[i] = (base + i < n) ? in[base + i] : 0;
+            s += v[i];
+        }
+        uint32_t tot;
+        uint32_t ex = block_excl_scan(s, &tot) + carry;
+#pragma unroll
+        for (int i = 0; i < SCAN_ITEMS; i++) {
+            if (base + i < n) out[base + i] = ex;
+            ex += v[i];
+        }
+        carry += tot;
+    }
+    if (write_total && threadIdx.x == 0) out[n] = carry;
+}
+
 size_t scan_ws_bytes(int64_t n)
 {
     int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
@@ -132,6 +160,11 @@ int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_
     uint32_t* bsum = (uint32_t*)ws;
     if (n <= 0) {
         if (write_total) PIGS_CHECK(cudaMemsetAsync(out, 0, sizeof(uint32_t), st));
+        return 0;
+    }
+    if (n <= SCAN_SMALL_MAX) {
+        scan_small<<<1, SCAN_THREADS, 0, st>>>(in, out, n, write_total ? 1 : 0);
+        PIGS_LAUNCH_CHECK();
         return 0;
     }
     const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
