@@ -160,6 +160,10 @@ int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float *f
 /* Library-level option (default 1): sizes L = K = 16, E = 25 (model_pn.py:44-49) run kernels specialised for them
  * (aggregate16.cu); 0 forces the generic kernels (same results within rounding; tests compare the two). */
 void pigs_set_aggregate_specialised(int on);
+/* Library-level option of the neighbour search: cell_cap = candidates per grid cell the cell-cooperative kernels hold in
+ * shared memory (default and maximum 4096; 0 sends every row through the per-row kernels), cell_div = grid cells per
+ * largest effective radius (default 2).  Results do not depend on either; tests compare the paths. */
+void pigs_set_neighbor_search(int cell_cap, float cell_div);
 size_t pigs_aggregate_backward_workspace_bytes(int64_t P, int L, int K, int E);
 int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, const float *features,
                             const float *transform, const float *queries, const float *keys,

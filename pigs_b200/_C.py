@@ -250,9 +250,10 @@ def preprocess_aggregate(means, conics, radii, debug):
     check(L.pigs_neighbors_count(P, D, _ptr(means), _ptr(radii), _ptr(counts), _ptr(ws), st), "pigs_neighbors_count")
     ranges = counts.cumsum(0)
     length = int(ranges[-1].item()) if P > 0 else 0
-    indices = torch.full((length,), -1, dtype=torch.int64, device=dev)
-    dists = torch.zeros((length, D), dtype=torch.float32, device=dev)
-    densities = torch.zeros((length,), dtype=torch.float32, device=dev)
+    # every CSR slot is written by the fill kernels (skipped neighbours get index -1 / density 0 there)
+    indices = torch.empty((length,), dtype=torch.int64, device=dev)
+    dists = torch.empty((length, D), dtype=torch.float32, device=dev)
+    densities = torch.empty((length,), dtype=torch.float32, device=dev)
     inv_total = torch.zeros((P,), dtype=torch.float32, device=dev)
     check(L.pigs_neighbors_fill(P, D, _ptr(means), _ptr(conics), _ptr(radii), _ptr(ranges), _ptr(indices), _ptr(dists),
                                 _ptr(densities), _ptr(inv_total), _ptr(ws), st), "pigs_neighbors_fill")

@@ -9,6 +9,11 @@
 // exact fp32/fp64 test to every candidate, so the accepted set is identical.  The row is then put in
 // ascending id order (shared-memory bitonic sort; rows beyond its capacity go through a per-CTA bitmap
 // over ids) which reproduces the reference's CSR bit for bit.
+// Fast path (nb_cell_*): all Gaussians of one grid cell share one candidate superset (the cells reachable
+// from the cell's bounding box at the cell's largest radius).  A CTA owns the cell, sorts that superset by
+// id ONCE in shared memory, and every warp then walks it in id order for one row at a time, so accepted
+// candidates leave in ascending id order with a ballot prefix and no per-row sort.  Cells whose superset
+// does not fit in shared memory fall back to the per-row kernels.
 //
 // Aggregation.  One warp per Gaussian; lanes over neighbour slots for the per-slot scalars (query.key,
 // Fourier embedding), lanes over feature channels for the row accumulation.  The transform is applied
@@ -26,6 +31,9 @@ constexpr int NB_WARP_CAP = 2048;          // neighbours per row sorted in share
 constexpr int NB_MAX_SPANS = 6;            // merged cell intervals per dimension (direct + torus images)
 constexpr int NB_BIG_CTAS = 64;            // persistent CTAs (one id-bitmap each) for rows beyond NB_WARP_CAP
 constexpr int NB_BIG_THREADS = 256;
+constexpr int NBC_THREADS = 256;           // cell-cooperative path: 8 warps share one id-sorted candidate list
+constexpr int NBC_WARPS = NBC_THREADS / 32;
+constexpr int NBC_CAP = 4096;              // candidates per cell in shared memory (id, x, y, r: 16 B each = 64 KB)
 
 struct NbGrid {
     float lo[2], hi[2];    // bounding box of the valid means
@@ -47,6 +55,7 @@ struct NbLayout {
     float4* srec;          // [P] sorted by (cell, id): {mx, my, reff, id bits}
     uint32_t* big_list;    // [P]
     uint32_t* bitmaps;     // [NB_BIG_CTAS][words]
+    uint8_t* cell_over;    // [ncells_max + 2] 1 = candidate superset of the cell exceeds NBC_CAP: per-row kernels
     int64_t ncells_max, words;
     size_t bytes;
     NbLayout(void* base, int64_t P, int D)
@@ -66,6 +75,7 @@ struct NbLayout {
         srec = c.take<float4>((size_t)Pn);
         big_list = c.take<uint32_t>((size_t)Pn);
         bitmaps = c.take<uint32_t>((size_t)NB_BIG_CTAS * words);
+        cell_over = c.take<uint8_t>((size_t)ncells_max + 2);
         bytes = c.total();
     }
     static int per_dim_cap(int64_t P, int D)
@@ -141,7 +151,9 @@ __global__ void __launch_bounds__(256) nb_prepare_kernel(int64_t P, const float*
     }
 }
 
-__global__ void nb_grid_kernel(NbGrid* g, int D, int per_dim_cap)
+// cell edge = rmax / div (div = 2: a row's reach T <= 2 rmax spans 9-10 cells per dimension, and the
+// superset shared by a cell is only ~1.4x the accepted set)
+__global__ void nb_grid_kernel(NbGrid* g, int D, int per_dim_cap, float div)
 {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
     int ncells = 1;
@@ -150,7 +162,7 @@ __global__ void nb_grid_kernel(NbGrid* g, int D, int per_dim_cap)
         int n = 1;
         float inv_h = 0.f;
         if (g->rmax > 0.f && ext > 0.f && ext < 3.0e38f) {
-            const float h = fmaxf(g->rmax, ext / (float)per_dim_cap);
+            const float h = fmaxf(g->rmax / div, ext / (float)per_dim_cap);
             const float q = ext / h;
             n = q >= (float)per_dim_cap ? per_dim_cap : max(1, (int)q);
             inv_h = (float)n / ext;
@@ -237,17 +249,18 @@ __device__ __forceinline__ void span_add(Spans& s, int lo, int hi, int ncell)
     s.n++;
 }
 
-__device__ __forceinline__ void dim_spans(float mine, float T, const NbGrid& g, int d, Spans& s)
+// spans for every `mine` in [mlo, mhi] (a point, or the bounding box of one cell's Gaussians)
+__device__ __forceinline__ void dim_spans(float mlo, float mhi, float T, const NbGrid& g, int d, Spans& s)
 {
-    const float pad = 1e-4f * T + 1e-6f * (1.0f + fabsf(mine) + fabsf(g.lo[d]) + fabsf(g.hi[d]));
+    const float pad = 1e-4f * T + 1e-6f * (1.0f + fmaxf(fabsf(mlo), fabsf(mhi)) + fabsf(g.lo[d]) + fabsf(g.hi[d]));
     const float Tp = T + pad;
     const int n = g.n[d];
     s.n = 0;
-    span_add(s, nb_cell(mine - Tp, g.lo[d], g.inv_h[d], n), nb_cell(mine + Tp, g.lo[d], g.inv_h[d], n), n);
+    span_add(s, nb_cell(mlo - Tp, g.lo[d], g.inv_h[d], n), nb_cell(mhi + Tp, g.lo[d], g.inv_h[d], n), n);
     for (int k = 1; k < 64; k++) {
-        const float a = mine + 2.0f * (float)k - Tp;
+        const float a = mlo + 2.0f * (float)k - Tp;
         if (a > g.hi[d]) break;
-        span_add(s, nb_cell(a, g.lo[d], g.inv_h[d], n), nb_cell(mine + 2.0f * (float)k + pad, g.lo[d], g.inv_h[d], n), n);
+        span_add(s, nb_cell(a, g.lo[d], g.inv_h[d], n), nb_cell(mhi + 2.0f * (float)k + pad, g.lo[d], g.inv_h[d], n), n);
         if (s.n == 1 && s.lo[0] == 0 && s.hi[0] == n - 1) break;
     }
 }
@@ -276,9 +289,9 @@ __device__ __forceinline__ void nb_for_candidates(const float4 me, const NbGrid&
 {
     const float T = me.z + g.rmax;
     Spans sx, sy;
-    dim_spans(me.x, T, g, 0, sx);
+    dim_spans(me.x, me.x, T, g, 0, sx);
     if (D == 2)
-        dim_spans(me.y, T, g, 1, sy);
+        dim_spans(me.y, me.y, T, g, 1, sy);
     else {
         sy.n = 1;
         sy.lo[0] = sy.hi[0] = 0;
@@ -302,12 +315,15 @@ __device__ __forceinline__ void nb_for_candidates(const float4 me, const NbGrid&
 template <int D>
 __global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const NbGrid* __restrict__ gp,
                                                               const uint32_t* __restrict__ cell_start,
-                                                              const float4* __restrict__ srec, int64_t* __restrict__ counts)
+                                                              const float4* __restrict__ srec, int64_t* __restrict__ counts,
+                                                              const uint32_t* __restrict__ row_cell,
+                                                              const uint8_t* __restrict__ cell_over)
 {
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * NB_WARPS + (threadIdx.x >> 5);
     const NbGrid g = *gp;
     if (r >= (int64_t)cell_start[g.ncells]) return;  // invalid rows keep count 0
+    if (!cell_over[row_cell[r]]) return;              // counted by nb_cell_count_kernel
     const float4 me = srec[r];
     const float mi[2] = {me.x, me.y};
     uint32_t cnt = 0;
@@ -323,14 +339,13 @@ __global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const N
 // ---- stage B: fill ---------------------------------------------------------------------------------
 // outputs of one CSR slot (preprocess, aggregate_neighbors.cu:82-126), returns the density (0 if skipped)
 template <int D>
-__device__ __forceinline__ float nb_emit_slot(int64_t slot, uint32_t j, const float* mi, float inv_r,
-                                              const float* __restrict__ means, const float* __restrict__ conics,
-                                              int64_t* __restrict__ indices, float* __restrict__ dists,
-                                              float* __restrict__ densities)
+__device__ __forceinline__ float nb_emit_core(int64_t slot, uint32_t j, const float* mj, const float* mi, float inv_r,
+                                              const float* __restrict__ conics, int64_t* __restrict__ indices,
+                                              float* __restrict__ dists, float* __restrict__ densities)
 {
     float X[D];
 #pragma unroll
-    for (int d = 0; d < D; d++) X[d] = torus_wrap(__fsub_rn(means[(size_t)j * D + d], mi[d]));
+    for (int d = 0; d < D; d++) X[d] = torus_wrap(__fsub_rn(mj[d], mi[d]));
     float power;
     if (D == 1) {
         const float c0 = conics[j];
@@ -355,6 +370,18 @@ __device__ __forceinline__ float nb_emit_slot(int64_t slot, uint32_t j, const fl
     return dens;
 }
 
+template <int D>
+__device__ __forceinline__ float nb_emit_slot(int64_t slot, uint32_t j, const float* mi, float inv_r,
+                                              const float* __restrict__ means, const float* __restrict__ conics,
+                                              int64_t* __restrict__ indices, float* __restrict__ dists,
+                                              float* __restrict__ densities)
+{
+    float mj[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) mj[d] = means[(size_t)j * D + d];
+    return nb_emit_core<D>(slot, j, mj, mi, inv_r, conics, indices, dists, densities);
+}
+
 __device__ __forceinline__ float nb_inv_radius(float radius)
 {
     // aggregate_neighbors.cu:74-75: my_radius = radii * 0.333 (double -> FLOAT); 1.0 / (my_radius + 1e-6) -> FLOAT
@@ -369,7 +396,9 @@ __global__ void __launch_bounds__(NB_THREADS) nb_fill_kernel(int64_t P, NbGrid* 
                                                              const float* __restrict__ conics, const float* __restrict__ radii,
                                                              const int64_t* __restrict__ ranges, int64_t* __restrict__ indices,
                                                              float* __restrict__ dists, float* __restrict__ densities,
-                                                             float* __restrict__ inv_total, uint32_t* __restrict__ big_list)
+                                                             float* __restrict__ inv_total, uint32_t* __restrict__ big_list,
+                                                             const uint32_t* __restrict__ row_cell,
+                                                             const uint8_t* __restrict__ cell_over)
 {
     __shared__ uint32_t s_buf[NB_WARPS][NB_WARP_CAP];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
@@ -382,6 +411,7 @@ __global__ void __launch_bounds__(NB_THREADS) nb_fill_kernel(int64_t P, NbGrid* 
         if (lane == 0) inv_total[id] = __double2float_rn(1.0 / (0.0 + 1e-6));
         return;
     }
+    if (!cell_over[row_cell[r]]) return;  // filled by nb_cell_fill_kernel
     const int64_t start = id == 0 ? 0 : ranges[id - 1];
     const int64_t n = ranges[id] - start;
     if (n > NB_WARP_CAP) {
@@ -501,6 +531,261 @@ __global__ void __launch_bounds__(NB_BIG_THREADS) nb_fill_big_kernel(int64_t P, 
         __syncthreads();
         if (tid == 0) inv_total[id] = __double2float_rn(1.0 / ((double)s_total + 1e-6));
     }
+}
+
+// Conservative version of nb_collides for a whole cell: false only if NO row with mean inside the box [blo, bhi] and
+// effective radius <= rc can collide with Gaussian (mj, rj).  Per dimension dx = mj - mi ranges over [a, b]; the
+// reference distance is |dx| for dx <= 1 and at most the gap up to the next even number for dx > 1
+// (aggregate_neighbors.cu:43-49), so a lower bound is min(distance of [a, b] from 0, gap of b to the next even
+// number [0 if an even number >= 2 lies inside the part of the interval beyond 1]).
+template <int D>
+__device__ __forceinline__ bool nb_box_reach(const float* blo, const float* bhi, float rc, const float* mj, float rj)
+{
+    const float rad = rc + rj;
+    float sum = 0.f;
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        const float a = mj[d] - bhi[d], b = mj[d] - blo[d];
+        float lb = a > 0.f ? a : (b < 0.f ? -b : 0.f);
+        if (b > 1.0f) {
+            const float e = 2.0f * ceilf(0.5f * b);  // smallest even number >= b
+            const float w = (e - 2.0f >= fmaxf(a, 1.0f) && e >= 4.0f) ? 0.f : e - b;
+            lb = fminf(lb, w);
+        }
+        lb = fmaxf(lb - (1e-5f * rad + 2e-6f * (1.0f + fabsf(mj[d]) + fmaxf(fabsf(blo[d]), fabsf(bhi[d])))), 0.f);
+        sum = fmaf(lb, lb, sum);
+    }
+    return !(sum > rad * rad * 1.0001f);
+}
+
+// ---- cell-cooperative path: one CTA per grid cell ---------------------------------------------------
+struct NbCellSmem {
+    uint32_t id[NBC_CAP];  // candidate ids, ascending after the sort
+    float x[NBC_CAP], y[NBC_CAP], r[NBC_CAP];
+};
+
+// Builds the id-sorted candidate superset of cell c in shared memory.  Returns the number of candidates, 0 for a
+// cell without rows, or -1 when the superset exceeds `cap` (then cell_over[c] = 1 and the per-row kernels take over).
+template <int D>
+__device__ __forceinline__ int nbc_load_cell(uint32_t c, const NbGrid& g, const uint32_t* __restrict__ cell_start,
+                                             const float4* __restrict__ srec, const uint32_t* __restrict__ sorted_ids,
+                                             const float* __restrict__ means, const float* __restrict__ reff, int cap,
+                                             NbCellSmem& sm, float* s_red, uint32_t* s_n, uint32_t rs, uint32_t re)
+{
+    const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
+    // bounding box and largest radius of the cell's own Gaussians
+    float v[5] = {__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0xff800000),
+                  __int_as_float(0xff800000), 0.f};
+    for (uint32_t p = rs + tid; p < re; p += NBC_THREADS) {
+        const float4 o = srec[p];
+        v[0] = fminf(v[0], o.x);
+        v[1] = fminf(v[1], o.y);
+        v[2] = fmaxf(v[2], o.x);
+        v[3] = fmaxf(v[3], o.y);
+        v[4] = fmaxf(v[4], o.z);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        v[0] = fminf(v[0], __shfl_xor_sync(0xffffffffu, v[0], o));
+        v[1] = fminf(v[1], __shfl_xor_sync(0xffffffffu, v[1], o));
+        v[2] = fmaxf(v[2], __shfl_xor_sync(0xffffffffu, v[2], o));
+        v[3] = fmaxf(v[3], __shfl_xor_sync(0xffffffffu, v[3], o));
+        v[4] = fmaxf(v[4], __shfl_xor_sync(0xffffffffu, v[4], o));
+    }
+    if (lane == 0)
+        for (int k = 0; k < 5; k++) s_red[wp * 5 + k] = v[k];
+    __syncthreads();
+    for (int w2 = 0; w2 < NBC_WARPS; w2++) {
+        v[0] = fminf(v[0], s_red[w2 * 5 + 0]);
+        v[1] = fminf(v[1], s_red[w2 * 5 + 1]);
+        v[2] = fmaxf(v[2], s_red[w2 * 5 + 2]);
+        v[3] = fmaxf(v[3], s_red[w2 * 5 + 3]);
+        v[4] = fmaxf(v[4], s_red[w2 * 5 + 4]);
+    }
+    const float T = v[4] + g.rmax;
+    Spans sx, sy;
+    dim_spans(v[0], v[2], T, g, 0, sx);
+    if (D == 2)
+        dim_spans(v[1], v[3], T, g, 1, sy);
+    else {
+        sy.n = 1;
+        sy.lo[0] = sy.hi[0] = 0;
+    }
+    // ids of the Gaussians in the reachable cells that can collide with SOME point of the cell's bounding box at the
+    // cell's largest radius (conservative lower bound of the reference distance, nb_box_gap); any order, sorted below
+    const float blo[2] = {v[0], v[1]}, bhi[2] = {v[2], v[3]};
+    if (tid == 0) *s_n = 0;
+    __syncthreads();
+    for (int iy = 0; iy < sy.n; iy++)
+        for (int cy = sy.lo[iy]; cy <= sy.hi[iy]; cy++)
+            for (int ix = 0; ix < sx.n; ix++) {
+                const uint32_t b = cell_start[cy * g.n[0] + sx.lo[ix]];
+                const uint32_t e = cell_start[cy * g.n[0] + sx.hi[ix] + 1];
+                for (uint32_t base = b; base < e; base += NBC_THREADS) {
+                    const uint32_t p = base + tid;
+                    bool keep = false;
+                    float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+                    if (p < e) {
+                        o = srec[p];
+                        const float mj[2] = {o.x, o.y};
+                        keep = nb_box_reach<D>(blo, bhi, v[4], mj, o.z);
+                    }
+                    const uint32_t m = __ballot_sync(0xffffffffu, keep);
+                    uint32_t at = 0;
+                    if (lane == 0 && m) at = atomicAdd(s_n, (uint32_t)__popc(m));
+                    at = __shfl_sync(0xffffffffu, at, 0) + __popc(m & ((1u << lane) - 1u));
+                    if (keep && at < (uint32_t)cap) sm.id[at] = __float_as_uint(o.w);
+                }
+            }
+    __syncthreads();
+    const uint32_t n = *s_n;
+    if (n > (uint32_t)cap) return -1;
+    uint32_t n2 = 2;
+    while (n2 < n) n2 <<= 1;
+    for (uint32_t i = n + tid; i < n2; i += NBC_THREADS) sm.id[i] = 0xffffffffu;
+    __syncthreads();
+    for (uint32_t k = 2; k <= n2; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = tid; t < (n2 >> 1); t += NBC_THREADS) {
+                const uint32_t i0 = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                const uint32_t i1 = i0 | j;
+                const uint32_t a = sm.id[i0], b2 = sm.id[i1];
+                if ((a > b2) == ((i0 & k) == 0)) {
+                    sm.id[i0] = b2;
+                    sm.id[i1] = a;
+                }
+            }
+            __syncthreads();
+        }
+    for (uint32_t i = tid; i < n; i += NBC_THREADS) {
+        const uint32_t j = sm.id[i];
+        sm.x[i] = means[(size_t)j * D];
+        sm.y[i] = D == 2 ? means[(size_t)j * D + 1] : 0.f;
+        sm.r[i] = reff[j];
+    }
+    __syncthreads();
+    return (int)n;
+}
+
+template <int D>
+__global__ void __launch_bounds__(NBC_THREADS) nb_cell_count_kernel(const NbGrid* __restrict__ gp,
+                                                                    const uint32_t* __restrict__ cell_start,
+                                                                    const float4* __restrict__ srec,
+                                                                    const uint32_t* __restrict__ sorted_ids,
+                                                                    const float* __restrict__ means,
+                                                                    const float* __restrict__ reff, int cap,
+                                                                    uint8_t* __restrict__ cell_over, int64_t* __restrict__ counts)
+{
+    extern __shared__ __align__(16) unsigned char nbc_raw[];
+    NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
+    __shared__ float s_red[NBC_WARPS * 5];
+    __shared__ uint32_t s_n;
+    const NbGrid g = *gp;
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    for (uint32_t c = blockIdx.x; c < (uint32_t)g.ncells; c += gridDim.x) {
+        const uint32_t rs = cell_start[c], re = cell_start[c + 1];
+        if (rs == re) {
+            if (threadIdx.x == 0) cell_over[c] = 0;
+            continue;
+        }
+        __syncthreads();  // the previous cell's readers are done with shared memory
+        const int n = nbc_load_cell<D>(c, g, cell_start, srec, sorted_ids, means, reff, cap, sm, s_red, &s_n, rs, re);
+        if (threadIdx.x == 0) cell_over[c] = n < 0;
+        if (n < 0) continue;
+        for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
+            const float4 me = srec[r];
+            const float mi[2] = {me.x, me.y};
+            uint32_t cnt = 0;
+            for (int i = lane; i < n; i += 32) {
+                const float mj[2] = {sm.x[i], sm.y[i]};
+                cnt += nb_collides<D>(mi, me.z, mj, sm.r[i]);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+            if (lane == 0) counts[__float_as_uint(me.w)] = (int64_t)cnt;
+        }
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid* __restrict__ gp,
+                                                                   const uint32_t* __restrict__ cell_start,
+                                                                   const float4* __restrict__ srec,
+                                                                   const uint32_t* __restrict__ sorted_ids,
+                                                                   const float* __restrict__ means,
+                                                                   const float* __restrict__ reff, int cap,
+                                                                   const uint8_t* __restrict__ cell_over,
+                                                                   const float* __restrict__ conics,
+                                                                   const float* __restrict__ radii,
+                                                                   const int64_t* __restrict__ ranges,
+                                                                   int64_t* __restrict__ indices, float* __restrict__ dists,
+                                                                   float* __restrict__ densities, float* __restrict__ inv_total)
+{
+    extern __shared__ __align__(16) unsigned char nbc_raw[];
+    NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
+    __shared__ float s_red[NBC_WARPS * 5];
+    __shared__ uint32_t s_n;
+    const NbGrid g = *gp;
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    for (uint32_t c = blockIdx.x; c < (uint32_t)g.ncells; c += gridDim.x) {
+        const uint32_t rs = cell_start[c], re = cell_start[c + 1];
+        if (rs == re || cell_over[c]) continue;
+        __syncthreads();
+        const int n = nbc_load_cell<D>(c, g, cell_start, srec, sorted_ids, means, reff, cap, sm, s_red, &s_n, rs, re);
+        if (n < 0) continue;  // cannot happen: same inputs as the count pass
+        for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
+            const float4 me = srec[r];
+            const uint32_t id = __float_as_uint(me.w);
+            const float mi[2] = {me.x, me.y};
+            const int64_t start = id == 0 ? 0 : ranges[id - 1];
+            const float inv_r = nb_inv_radius(radii[id]);
+            float total = 0.0f;
+            uint32_t cnt = 0;
+            for (int base = 0; base < n; base += 32) {
+                const int i = base + lane;
+                bool ok = false;
+                float mj[2] = {0.f, 0.f};
+                if (i < n) {
+                    mj[0] = sm.x[i];
+                    mj[1] = sm.y[i];
+                    ok = nb_collides<D>(mi, me.z, mj, sm.r[i]);
+                }
+                const uint32_t m = __ballot_sync(0xffffffffu, ok);
+                if (ok)
+                    total += nb_emit_core<D>(start + cnt + __popc(m & lt), sm.id[i], mj, mi, inv_r, conics, indices, dists,
+                                             densities);
+                cnt += __popc(m);
+            }
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+            if (lane == 0) inv_total[id] = __double2float_rn(1.0 / ((double)total + 1e-6));
+        }
+    }
+}
+
+// run-time knobs of the neighbour search (pigs_set_neighbor_search; development and tests): cell_cap = 0 routes every
+// row through the per-row kernels, cell_div = grid cells per largest radius.  Environment defaults:
+// PIGS_NB_CELL_CAP, PIGS_NB_CELL_DIV.
+static int g_nb_cell_cap = -1;
+static float g_nb_cell_div = 0.f;
+static int nb_cell_cap()
+{
+    if (g_nb_cell_cap < 0) {
+        const char* e = getenv("PIGS_NB_CELL_CAP");
+        g_nb_cell_cap = e ? atoi(e) : NBC_CAP;
+        if (g_nb_cell_cap < 0 || g_nb_cell_cap > NBC_CAP) g_nb_cell_cap = NBC_CAP;
+    }
+    return g_nb_cell_cap;
+}
+static float nb_cell_div()
+{
+    if (g_nb_cell_div == 0.f) {
+        const char* e = getenv("PIGS_NB_CELL_DIV");
+        g_nb_cell_div = e ? (float)atof(e) : 2.0f;
+        if (!(g_nb_cell_div >= 0.25f && g_nb_cell_div <= 16.f)) g_nb_cell_div = 2.0f;
+    }
+    return g_nb_cell_div;
 }
 
 // ====================================================================================================
@@ -855,7 +1140,7 @@ int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radi
     else
         nb_prepare_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, w.reff, w.grid);
     PIGS_LAUNCH_CHECK();
-    nb_grid_kernel<<<1, 32, 0, st>>>(w.grid, D, NbLayout::per_dim_cap(P, D));
+    nb_grid_kernel<<<1, 32, 0, st>>>(w.grid, D, NbLayout::per_dim_cap(P, D), nb_cell_div());
     PIGS_LAUNCH_CHECK();
     if (D == 2)
         nb_key_kernel<2><<<nb, 256, 0, st>>>(P, means, w.reff, w.grid, w.keys_a, w.vals_a);
@@ -873,11 +1158,24 @@ int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radi
     else
         nb_gather_kernel<1><<<nb, 256, 0, st>>>(P, w.vals_b, means, w.reff, w.srec);
     PIGS_LAUNCH_CHECK();
+    // cells first (shared id-sorted candidate list), then the rows of the cells that did not fit
+    const int cap = nb_cell_cap();
+    const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
+    if (D == 2) {
+        PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
+        nb_cell_count_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means,
+                                                                               w.reff, cap, w.cell_over, counts);
+    } else {
+        PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
+        nb_cell_count_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means,
+                                                                               w.reff, cap, w.cell_over, counts);
+    }
+    PIGS_LAUNCH_CHECK();
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
     if (D == 2)
-        nb_count_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts);
+        nb_count_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over);
     else
-        nb_count_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts);
+        nb_count_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
@@ -891,16 +1189,30 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
     cudaStream_t st = (cudaStream_t)stream;
     NbLayout w(workspace, P, D);
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
+    const int cap = nb_cell_cap();
+    const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
+    if (D == 2) {
+        PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
+        nb_cell_fill_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means, w.reff,
+                                                                              cap, w.cell_over, conics, radii, ranges, indices,
+                                                                              dists, densities, inv_total_densities);
+    } else {
+        PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
+        nb_cell_fill_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means, w.reff,
+                                                                              cap, w.cell_over, conics, radii, ranges, indices,
+                                                                              dists, densities, inv_total_densities);
+    }
+    PIGS_LAUNCH_CHECK();
     if (D == 2) {
         nb_fill_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
-                                                      dists, densities, inv_total_densities, w.big_list);
+                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over);
         PIGS_LAUNCH_CHECK();
         nb_fill_big_kernel<2><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
                                                                       ranges, indices, dists, densities, inv_total_densities,
                                                                       w.big_list, w.bitmaps, w.words);
     } else {
         nb_fill_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
-                                                      dists, densities, inv_total_densities, w.big_list);
+                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over);
         PIGS_LAUNCH_CHECK();
         nb_fill_big_kernel<1><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
                                                                       ranges, indices, dists, densities, inv_total_densities,
@@ -911,6 +1223,12 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
 }
 
 void pigs_set_aggregate_specialised(int on) { g_agg_fast = on != 0; }
+
+void pigs_set_neighbor_search(int cell_cap, float cell_div)
+{
+    g_nb_cell_cap = cell_cap < 0 || cell_cap > NBC_CAP ? NBC_CAP : cell_cap;
+    g_nb_cell_div = (cell_div >= 0.25f && cell_div <= 16.f) ? cell_div : 2.0f;
+}
 
 int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                            const float* queries, const float* keys, const float* frequencies,

@@ -36,8 +36,20 @@ def _check_lists(s, want):
     assert rel_err(s.inv_total_densities.cpu().numpy(), inv) <= TOL
 
 
+@pytest.fixture(params=["cells", "rows", "mixed"])
+def nb_path(request):
+    """Neighbour search routes: 'cells' = the cell-cooperative kernels (shared id-sorted candidate list, the default),
+    'rows' = every row through the per-row kernels (sort / bitmap), 'mixed' = coarse grid with a 256-candidate
+    capacity, so dense cells overflow to the per-row kernels and sparse ones do not."""
+    from pigs_b200 import _lib
+    cap, div = {"cells": (4096, 2.0), "rows": (0, 2.0), "mixed": (256, 1.0)}[request.param]
+    _lib.lib().pigs_set_neighbor_search(cap, div)
+    yield request.param
+    _lib.lib().pigs_set_neighbor_search(4096, 2.0)
+
+
 @pytest.mark.parametrize("name", list(AGG_RECIPES))
-def test_neighbor_lists_bit_exact_vs_oracle_and_golden(name):
+def test_neighbor_lists_bit_exact_vs_oracle_and_golden(name, nb_path):
     rec = AGG_RECIPES[name]()
     st = oracle_state(rec)
     s, d = _prep(rec)
@@ -97,7 +109,7 @@ def _dense_cluster(P=2600, seed=3):
                                   lambda: synthetic(6000, 64, seed=10, edge_fraction=0.3, scale=1.0),
                                   lambda: synthetic(3000, 64, seed=11, D=1),
                                   lambda: synthetic(3000, 64, seed=12, scale=2.5)])
-def test_neighbor_lists_larger_sets(make):
+def test_neighbor_lists_larger_sets(make, nb_path):
     rec = make()
     rec["samples"] = rec["means"].copy()
     st = oracle_state(rec)
@@ -106,7 +118,7 @@ def test_neighbor_lists_larger_sets(make):
     _check_lists(s, want)
 
 
-def test_degenerate_rows_have_no_neighbours():
+def test_degenerate_rows_have_no_neighbours(nb_path):
     rec = AGG_RECIPES["agg_model"]()
     rec["covariances"][5] = 0.0   # det == 0 -> radius 0 -> skipped row and column (aggregate_neighbors.cu:29,38)
     rec["covariances"][77] = [0.25, 0.25, 0.25]
