@@ -338,14 +338,18 @@ __global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const N
 
 // ---- stage B: fill ---------------------------------------------------------------------------------
 // outputs of one CSR slot (preprocess, aggregate_neighbors.cu:82-126), returns the density (0 if skipped)
-template <int D>
+// NOWRAP: the caller knows |mj - mi| <= 1 in every dimension, where torus_wrap is the identity
+template <int D, bool NOWRAP = false>
 __device__ __forceinline__ float nb_emit_core(int64_t slot, uint32_t j, const float* mj, const float* mi, float inv_r,
                                               const float* __restrict__ conics, int64_t* __restrict__ indices,
                                               float* __restrict__ dists, float* __restrict__ densities)
 {
     float X[D];
 #pragma unroll
-    for (int d = 0; d < D; d++) X[d] = torus_wrap(__fsub_rn(mj[d], mi[d]));
+    for (int d = 0; d < D; d++) {
+        X[d] = __fsub_rn(mj[d], mi[d]);
+        if (!NOWRAP) X[d] = torus_wrap(X[d]);
+    }
     float power;
     if (D == 1) {
         const float c0 = conics[j];
@@ -560,17 +564,29 @@ __device__ __forceinline__ bool nb_box_reach(const float* blo, const float* bhi,
 
 // ---- cell-cooperative path: one CTA per grid cell ---------------------------------------------------
 struct NbCellSmem {
-    uint32_t id[NBC_CAP];  // candidate ids, ascending after the sort
+    uint32_t id[NBC_CAP];  // candidate ids (ascending after the sort of the fill pass)
     float x[NBC_CAP], y[NBC_CAP], r[NBC_CAP];
 };
 
-// Builds the id-sorted candidate superset of cell c in shared memory.  Returns the number of candidates, 0 for a
-// cell without rows, or -1 when the superset exceeds `cap` (then cell_over[c] = 1 and the per-row kernels take over).
-template <int D>
-__device__ __forceinline__ int nbc_load_cell(uint32_t c, const NbGrid& g, const uint32_t* __restrict__ cell_start,
-                                             const float4* __restrict__ srec, const uint32_t* __restrict__ sorted_ids,
-                                             const float* __restrict__ means, const float* __restrict__ reff, int cap,
-                                             NbCellSmem& sm, float* s_red, uint32_t* s_n, uint32_t rs, uint32_t re)
+struct NbCellShared {  // small static part
+    float red[NBC_WARPS * 5];
+    uint32_t n;
+    uint32_t wrap;
+    uint16_t ring[NBC_WARPS][128];
+};
+
+// Builds the candidate superset of cell c in shared memory: every Gaussian of the reachable cells that passes
+// nb_box_reach against the cell's bounding box and largest radius.  SORT = true orders it by ascending id (bitonic
+// sort of the ids, records re-read by id); SORT = false keeps arrival order (enough for counting).
+// Returns the number of candidates, or -1 when there are more than `cap` (then the per-row kernels take the cell).
+// sh.wrap == 0 afterwards iff every candidate lies within 1 of every point of the box in every dimension: then
+// neither the torus branch of the reference distance nor the wrap of the emitted offsets can trigger for this cell.
+// The list is padded to a multiple of 64 with records no row collides with when sh.wrap == 0 (x = 3e38: dx^2 = inf).
+template <int D, bool SORT>
+__device__ __forceinline__ int nbc_load_cell(const NbGrid& g, const uint32_t* __restrict__ cell_start,
+                                             const float4* __restrict__ srec, const float* __restrict__ means,
+                                             const float* __restrict__ reff, int cap, NbCellSmem& sm, NbCellShared& sh,
+                                             uint32_t rs, uint32_t re)
 {
     const int tid = threadIdx.x, lane = tid & 31, wp = tid >> 5;
     // bounding box and largest radius of the cell's own Gaussians
@@ -593,14 +609,18 @@ __device__ __forceinline__ int nbc_load_cell(uint32_t c, const NbGrid& g, const 
         v[4] = fmaxf(v[4], __shfl_xor_sync(0xffffffffu, v[4], o));
     }
     if (lane == 0)
-        for (int k = 0; k < 5; k++) s_red[wp * 5 + k] = v[k];
+        for (int k = 0; k < 5; k++) sh.red[wp * 5 + k] = v[k];
+    if (tid == 0) {
+        sh.n = 0;
+        sh.wrap = 0;
+    }
     __syncthreads();
     for (int w2 = 0; w2 < NBC_WARPS; w2++) {
-        v[0] = fminf(v[0], s_red[w2 * 5 + 0]);
-        v[1] = fminf(v[1], s_red[w2 * 5 + 1]);
-        v[2] = fmaxf(v[2], s_red[w2 * 5 + 2]);
-        v[3] = fmaxf(v[3], s_red[w2 * 5 + 3]);
-        v[4] = fmaxf(v[4], s_red[w2 * 5 + 4]);
+        v[0] = fminf(v[0], sh.red[w2 * 5 + 0]);
+        v[1] = fminf(v[1], sh.red[w2 * 5 + 1]);
+        v[2] = fmaxf(v[2], sh.red[w2 * 5 + 2]);
+        v[3] = fmaxf(v[3], sh.red[w2 * 5 + 3]);
+        v[4] = fmaxf(v[4], sh.red[w2 * 5 + 4]);
     }
     const float T = v[4] + g.rmax;
     Spans sx, sy;
@@ -611,11 +631,8 @@ __device__ __forceinline__ int nbc_load_cell(uint32_t c, const NbGrid& g, const 
         sy.n = 1;
         sy.lo[0] = sy.hi[0] = 0;
     }
-    // ids of the Gaussians in the reachable cells that can collide with SOME point of the cell's bounding box at the
-    // cell's largest radius (conservative lower bound of the reference distance, nb_box_gap); any order, sorted below
     const float blo[2] = {v[0], v[1]}, bhi[2] = {v[2], v[3]};
-    if (tid == 0) *s_n = 0;
-    __syncthreads();
+    bool wrap = false;
     for (int iy = 0; iy < sy.n; iy++)
         for (int cy = sy.lo[iy]; cy <= sy.hi[iy]; cy++)
             for (int ix = 0; ix < sx.n; ix++) {
@@ -632,56 +649,106 @@ __device__ __forceinline__ int nbc_load_cell(uint32_t c, const NbGrid& g, const 
                     }
                     const uint32_t m = __ballot_sync(0xffffffffu, keep);
                     uint32_t at = 0;
-                    if (lane == 0 && m) at = atomicAdd(s_n, (uint32_t)__popc(m));
+                    if (lane == 0 && m) at = atomicAdd(&sh.n, (uint32_t)__popc(m));
                     at = __shfl_sync(0xffffffffu, at, 0) + __popc(m & ((1u << lane) - 1u));
-                    if (keep && at < (uint32_t)cap) sm.id[at] = __float_as_uint(o.w);
+                    if (keep && at < (uint32_t)cap) {
+                        sm.id[at] = __float_as_uint(o.w);
+                        if (!SORT) {
+                            sm.x[at] = o.x;
+                            sm.y[at] = o.y;
+                            sm.r[at] = o.z;
+                        }
+                        wrap |= __fsub_rn(o.x, blo[0]) > 1.0f || __fsub_rn(o.x, bhi[0]) < -1.0f;
+                        if (D == 2) wrap |= __fsub_rn(o.y, blo[1]) > 1.0f || __fsub_rn(o.y, bhi[1]) < -1.0f;
+                    }
                 }
             }
+    if (wrap) sh.wrap = 1;
     __syncthreads();
-    const uint32_t n = *s_n;
+    const uint32_t n = sh.n;
     if (n > (uint32_t)cap) return -1;
-    uint32_t n2 = 2;
-    while (n2 < n) n2 <<= 1;
-    for (uint32_t i = n + tid; i < n2; i += NBC_THREADS) sm.id[i] = 0xffffffffu;
-    __syncthreads();
-    for (uint32_t k = 2; k <= n2; k <<= 1)
-        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-            for (uint32_t t = tid; t < (n2 >> 1); t += NBC_THREADS) {
-                const uint32_t i0 = ((t & ~(j - 1)) << 1) | (t & (j - 1));
-                const uint32_t i1 = i0 | j;
-                const uint32_t a = sm.id[i0], b2 = sm.id[i1];
-                if ((a > b2) == ((i0 & k) == 0)) {
-                    sm.id[i0] = b2;
-                    sm.id[i1] = a;
+    if (SORT) {
+        uint32_t n2 = 2;
+        while (n2 < n) n2 <<= 1;
+        for (uint32_t i = n + tid; i < n2; i += NBC_THREADS) sm.id[i] = 0xffffffffu;
+        __syncthreads();
+        for (uint32_t k = 2; k <= n2; k <<= 1)
+            for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                for (uint32_t t = tid; t < (n2 >> 1); t += NBC_THREADS) {
+                    const uint32_t i0 = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                    const uint32_t i1 = i0 | j;
+                    const uint32_t a = sm.id[i0], b2 = sm.id[i1];
+                    if ((a > b2) == ((i0 & k) == 0)) {
+                        sm.id[i0] = b2;
+                        sm.id[i1] = a;
+                    }
                 }
+                __syncthreads();
             }
-            __syncthreads();
+        for (uint32_t i = tid; i < n; i += NBC_THREADS) {
+            const uint32_t j = sm.id[i];
+            sm.x[i] = means[(size_t)j * D];
+            sm.y[i] = D == 2 ? means[(size_t)j * D + 1] : 0.f;
+            sm.r[i] = reff[j];
         }
-    for (uint32_t i = tid; i < n; i += NBC_THREADS) {
-        const uint32_t j = sm.id[i];
-        sm.x[i] = means[(size_t)j * D];
-        sm.y[i] = D == 2 ? means[(size_t)j * D + 1] : 0.f;
-        sm.r[i] = reff[j];
+    }
+    for (uint32_t i = n + tid; i < ((n + 63u) & ~63u); i += NBC_THREADS) {
+        sm.x[i] = 3.0e38f;
+        sm.y[i] = 0.f;
+        sm.r[i] = 0.f;
     }
     __syncthreads();
     return (int)n;
+}
+
+// nb_collides for rows of a cell whose candidates never take the torus branch (sh.wrap == 0): same operations, no branch
+template <int D, bool WRAP>
+__device__ __forceinline__ bool nbc_collides(const float* mi, float ri, const float* mj, float rj)
+{
+    if (WRAP) return nb_collides<D>(mi, ri, mj, rj);
+    float dist = 0.0f;
+#pragma unroll
+    for (int d = 0; d < D; d++) {
+        const float dx = __fsub_rn(mj[d], mi[d]);
+        dist = __fmaf_rn(dx, dx, dist);
+    }
+    const float rad = __fadd_rn(ri, rj);
+    return !(dist > __fmul_rn(rad, rad));
+}
+
+template <int D, bool WRAP>
+__device__ __forceinline__ void nbc_count_rows(const NbCellSmem& sm, int n, uint32_t rs, uint32_t re,
+                                               const float4* __restrict__ srec, int64_t* __restrict__ counts)
+{
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
+        const float4 me = srec[r];
+        const float mi[2] = {me.x, me.y};
+        uint32_t cnt = 0;
+        const int nn = WRAP ? n : ((n + 63) & ~63);  // the padding never collides on the branch-free path
+#pragma unroll 4
+        for (int i = lane; i < nn; i += 32) {
+            const float mj[2] = {sm.x[i], sm.y[i]};
+            cnt += nbc_collides<D, WRAP>(mi, me.z, mj, sm.r[i]);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) counts[__float_as_uint(me.w)] = (int64_t)cnt;
+    }
 }
 
 template <int D>
 __global__ void __launch_bounds__(NBC_THREADS) nb_cell_count_kernel(const NbGrid* __restrict__ gp,
                                                                     const uint32_t* __restrict__ cell_start,
                                                                     const float4* __restrict__ srec,
-                                                                    const uint32_t* __restrict__ sorted_ids,
                                                                     const float* __restrict__ means,
                                                                     const float* __restrict__ reff, int cap,
                                                                     uint8_t* __restrict__ cell_over, int64_t* __restrict__ counts)
 {
     extern __shared__ __align__(16) unsigned char nbc_raw[];
     NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
-    __shared__ float s_red[NBC_WARPS * 5];
-    __shared__ uint32_t s_n;
+    __shared__ NbCellShared sh;
     const NbGrid g = *gp;
-    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     for (uint32_t c = blockIdx.x; c < (uint32_t)g.ncells; c += gridDim.x) {
         const uint32_t rs = cell_start[c], re = cell_start[c + 1];
         if (rs == re) {
@@ -689,21 +756,70 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_count_kernel(const NbGrid
             continue;
         }
         __syncthreads();  // the previous cell's readers are done with shared memory
-        const int n = nbc_load_cell<D>(c, g, cell_start, srec, sorted_ids, means, reff, cap, sm, s_red, &s_n, rs, re);
+        const int n = nbc_load_cell<D, false>(g, cell_start, srec, means, reff, cap, sm, sh, rs, re);
         if (threadIdx.x == 0) cell_over[c] = n < 0;
         if (n < 0) continue;
-        for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
-            const float4 me = srec[r];
-            const float mi[2] = {me.x, me.y};
-            uint32_t cnt = 0;
-            for (int i = lane; i < n; i += 32) {
-                const float mj[2] = {sm.x[i], sm.y[i]};
-                cnt += nb_collides<D>(mi, me.z, mj, sm.r[i]);
+        if (sh.wrap)
+            nbc_count_rows<D, true>(sm, n, rs, re, srec, counts);
+        else
+            nbc_count_rows<D, false>(sm, n, rs, re, srec, counts);
+    }
+}
+
+// Rows of one cell: candidates are walked in ascending id; accepted ones are queued (their position in the list) in
+// a 128-entry per-warp ring (two batches of 32 per step) and leave in full groups of 32, so the CSR stores are whole-warp and consecutive.
+template <int D, bool WRAP>
+__device__ __forceinline__ void nbc_fill_rows(const NbCellSmem& sm, NbCellShared& sh, int n, uint32_t rs, uint32_t re,
+                                              const float4* __restrict__ srec, const float* __restrict__ conics,
+                                              const float* __restrict__ radii, const int64_t* __restrict__ ranges,
+                                              int64_t* __restrict__ indices, float* __restrict__ dists,
+                                              float* __restrict__ densities, float* __restrict__ inv_total)
+{
+    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    uint16_t* ring = sh.ring[wp];
+    for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
+        const float4 me = srec[r];
+        const uint32_t id = __float_as_uint(me.w);
+        const float mi[2] = {me.x, me.y};
+        const int64_t start = id == 0 ? 0 : ranges[id - 1];
+        const float inv_r = nb_inv_radius(radii[id]);
+        float total = 0.0f;
+        uint32_t cnt = 0, done = 0;  // accepted so far; emitted so far (multiple of 32)
+        const int nn = (n + 63) & ~63;
+        for (int base = 0; base < nn; base += 64) {
+            const int i0 = base + lane, i1 = i0 + 32;
+            const float a0[2] = {sm.x[i0], sm.y[i0]}, a1[2] = {sm.x[i1], sm.y[i1]};
+            bool ok0 = nbc_collides<D, WRAP>(mi, me.z, a0, sm.r[i0]);
+            bool ok1 = nbc_collides<D, WRAP>(mi, me.z, a1, sm.r[i1]);
+            if (WRAP) {  // the padding is only inert on the branch-free path
+                ok0 = ok0 && i0 < n;
+                ok1 = ok1 && i1 < n;
             }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-            if (lane == 0) counts[__float_as_uint(me.w)] = (int64_t)cnt;
+            const uint32_t m0 = __ballot_sync(0xffffffffu, ok0), m1 = __ballot_sync(0xffffffffu, ok1);
+            const uint32_t c0 = cnt + __popc(m0);
+            if (ok0) ring[(cnt + __popc(m0 & lt)) & 127u] = (uint16_t)i0;
+            if (ok1) ring[(c0 + __popc(m1 & lt)) & 127u] = (uint16_t)i1;
+            cnt = c0 + __popc(m1);
+            while (cnt - done >= 32u) {  // a group of 32 accepted candidates is complete (warp-uniform)
+                __syncwarp();
+                const int ii = ring[(done + lane) & 127u];
+                const float mj[2] = {sm.x[ii], sm.y[ii]};
+                total += nb_emit_core<D, !WRAP>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists,
+                                                densities);
+                done += 32u;
+            }
+            __syncwarp();
         }
+        if (done + lane < cnt) {
+            const int ii = ring[(done + lane) & 127u];
+            const float mj[2] = {sm.x[ii], sm.y[ii]};
+            total += nb_emit_core<D, !WRAP>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists, densities);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        if (lane == 0) inv_total[id] = __double2float_rn(1.0 / ((double)total + 1e-6));
     }
 }
 
@@ -711,7 +827,6 @@ template <int D>
 __global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid* __restrict__ gp,
                                                                    const uint32_t* __restrict__ cell_start,
                                                                    const float4* __restrict__ srec,
-                                                                   const uint32_t* __restrict__ sorted_ids,
                                                                    const float* __restrict__ means,
                                                                    const float* __restrict__ reff, int cap,
                                                                    const uint8_t* __restrict__ cell_over,
@@ -723,44 +838,18 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid*
 {
     extern __shared__ __align__(16) unsigned char nbc_raw[];
     NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
-    __shared__ float s_red[NBC_WARPS * 5];
-    __shared__ uint32_t s_n;
+    __shared__ NbCellShared sh;
     const NbGrid g = *gp;
-    const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
-    const uint32_t lt = (1u << lane) - 1u;
     for (uint32_t c = blockIdx.x; c < (uint32_t)g.ncells; c += gridDim.x) {
         const uint32_t rs = cell_start[c], re = cell_start[c + 1];
         if (rs == re || cell_over[c]) continue;
         __syncthreads();
-        const int n = nbc_load_cell<D>(c, g, cell_start, srec, sorted_ids, means, reff, cap, sm, s_red, &s_n, rs, re);
+        const int n = nbc_load_cell<D, true>(g, cell_start, srec, means, reff, cap, sm, sh, rs, re);
         if (n < 0) continue;  // cannot happen: same inputs as the count pass
-        for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
-            const float4 me = srec[r];
-            const uint32_t id = __float_as_uint(me.w);
-            const float mi[2] = {me.x, me.y};
-            const int64_t start = id == 0 ? 0 : ranges[id - 1];
-            const float inv_r = nb_inv_radius(radii[id]);
-            float total = 0.0f;
-            uint32_t cnt = 0;
-            for (int base = 0; base < n; base += 32) {
-                const int i = base + lane;
-                bool ok = false;
-                float mj[2] = {0.f, 0.f};
-                if (i < n) {
-                    mj[0] = sm.x[i];
-                    mj[1] = sm.y[i];
-                    ok = nb_collides<D>(mi, me.z, mj, sm.r[i]);
-                }
-                const uint32_t m = __ballot_sync(0xffffffffu, ok);
-                if (ok)
-                    total += nb_emit_core<D>(start + cnt + __popc(m & lt), sm.id[i], mj, mi, inv_r, conics, indices, dists,
-                                             densities);
-                cnt += __popc(m);
-            }
-#pragma unroll
-            for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
-            if (lane == 0) inv_total[id] = __double2float_rn(1.0 / ((double)total + 1e-6));
-        }
+        if (sh.wrap)
+            nbc_fill_rows<D, true>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total);
+        else
+            nbc_fill_rows<D, false>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total);
     }
 }
 
@@ -1163,12 +1252,12 @@ int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radi
     const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
     if (D == 2) {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
-        nb_cell_count_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means,
-                                                                               w.reff, cap, w.cell_over, counts);
+        nb_cell_count_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
+                                                                               cap, w.cell_over, counts);
     } else {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
-        nb_cell_count_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means,
-                                                                               w.reff, cap, w.cell_over, counts);
+        nb_cell_count_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
+                                                                               cap, w.cell_over, counts);
     }
     PIGS_LAUNCH_CHECK();
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
@@ -1193,12 +1282,12 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
     const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
     if (D == 2) {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
-        nb_cell_fill_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means, w.reff,
+        nb_cell_fill_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
                                                                               cap, w.cell_over, conics, radii, ranges, indices,
                                                                               dists, densities, inv_total_densities);
     } else {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
-        nb_cell_fill_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, w.vals_b, means, w.reff,
+        nb_cell_fill_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
                                                                               cap, w.cell_over, conics, radii, ranges, indices,
                                                                               dists, densities, inv_total_densities);
     }
