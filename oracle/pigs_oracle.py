@@ -209,6 +209,26 @@ def neighbors(means, conics, radii):
     return indices, ranges, dists, densities, inv_total
 
 
+def neighbor_rows(means, conics, radii, rows, cap=8192):
+    """`neighbors` for a sample of rows (each still scans all P candidates).  Returns counts i64[n], indices i64[n,cap]
+    (-1 beyond the count), dists f32[n,cap,D], densities f32[n,cap], inv_total f32[n]."""
+    L = lib()
+    means = _f32(means)
+    P, D = means.shape
+    conics = _f32(conics).reshape(P, D * (D + 1) // 2)
+    radii = _f32(radii).reshape(P)
+    rows = np.ascontiguousarray(rows, np.int64)
+    n = rows.shape[0]
+    counts = np.zeros(n, np.int64)
+    indices = np.full((n, cap), -1, np.int64)
+    dists = np.zeros((n, cap, D), np.float32)
+    densities = np.zeros((n, cap), np.float32)
+    inv_total = np.zeros(n, np.float32)
+    L.pigs_oracle_neighbor_rows(_i64(P), _int(D), _p(means), _p(conics), _p(radii), _i64(n), _p(rows), _i64(cap),
+                                _p(counts), _p(indices), _p(dists), _p(densities), _p(inv_total))
+    return counts, indices, dists, densities, inv_total
+
+
 def aggregate_forward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
                       densities, inv_total):
     """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415) -> aggregateNeighbors (:129-207).

@@ -31,7 +31,10 @@ constexpr int NB_WARP_CAP = 2048;          // neighbours per row sorted in share
 constexpr int NB_MAX_SPANS = 6;            // merged cell intervals per dimension (direct + torus images)
 constexpr int NB_BIG_CTAS = 64;            // persistent CTAs (one id-bitmap each) for rows beyond NB_WARP_CAP
 constexpr int NB_BIG_THREADS = 256;
-constexpr int NBC_THREADS = 256;           // cell-cooperative path: 8 warps share one id-sorted candidate list
+#ifndef PIGS_NBC_THREADS
+#define PIGS_NBC_THREADS 384
+#endif
+constexpr int NBC_THREADS = PIGS_NBC_THREADS;           // cell-cooperative path: 12 warps share one id-sorted candidate list
 constexpr int NBC_WARPS = NBC_THREADS / 32;
 constexpr int NBC_CAP = 4096;              // candidates per cell in shared memory (id, x, y, r: 16 B each = 64 KB)
 
@@ -56,6 +59,7 @@ struct NbLayout {
     uint32_t* big_list;    // [P]
     uint32_t* bitmaps;     // [NB_BIG_CTAS][words]
     uint8_t* cell_over;    // [ncells_max + 2] 1 = candidate superset of the cell exceeds NBC_CAP: per-row kernels
+    float4* cpack;         // [P] conics padded to 16 B (one aligned load per emitted neighbour), built by the fill pass
     int64_t ncells_max, words;
     size_t bytes;
     NbLayout(void* base, int64_t P, int D)
@@ -76,6 +80,7 @@ struct NbLayout {
         big_list = c.take<uint32_t>((size_t)Pn);
         bitmaps = c.take<uint32_t>((size_t)NB_BIG_CTAS * words);
         cell_over = c.take<uint8_t>((size_t)ncells_max + 2);
+        cpack = c.take<float4>((size_t)Pn);
         bytes = c.total();
     }
     static int per_dim_cap(int64_t P, int D)
@@ -339,7 +344,8 @@ __global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const N
 // ---- stage B: fill ---------------------------------------------------------------------------------
 // outputs of one CSR slot (preprocess, aggregate_neighbors.cu:82-126), returns the density (0 if skipped)
 // NOWRAP: the caller knows |mj - mi| <= 1 in every dimension, where torus_wrap is the identity
-template <int D, bool NOWRAP = false>
+// PACKED: `conics` is the float4-padded copy (NbLayout::cpack)
+template <int D, bool NOWRAP = false, bool PACKED = false>
 __device__ __forceinline__ float nb_emit_core(int64_t slot, uint32_t j, const float* mj, const float* mi, float inv_r,
                                               const float* __restrict__ conics, int64_t* __restrict__ indices,
                                               float* __restrict__ dists, float* __restrict__ densities)
@@ -352,10 +358,16 @@ __device__ __forceinline__ float nb_emit_core(int64_t slot, uint32_t j, const fl
     }
     float power;
     if (D == 1) {
-        const float c0 = conics[j];
+        const float c0 = PACKED ? conics[(size_t)j * 4] : conics[j];
         power = __double2float_rn(-0.5 * (double)c0 * (double)X[0] * (double)X[0]);
     } else {
-        const float c0 = conics[(size_t)j * 3], c1 = conics[(size_t)j * 3 + 1], c2 = conics[(size_t)j * 3 + 2];
+        float c0, c1, c2;
+        if (PACKED) {
+            const float4 c = reinterpret_cast<const float4*>(conics)[j];
+            c0 = c.x, c1 = c.y, c2 = c.z;
+        } else {
+            c0 = conics[(size_t)j * 3], c1 = conics[(size_t)j * 3 + 1], c2 = conics[(size_t)j * 3 + 2];
+        }
         const float a = __fmul_rn(__fmul_rn(c0, X[0]), X[0]);
         const float q = __fmaf_rn(__fmul_rn(c2, X[D - 1]), X[D - 1], a);
         const float m = __fmul_rn(__fmul_rn(c1, X[0]), X[D - 1]);
@@ -560,6 +572,14 @@ __device__ __forceinline__ bool nb_box_reach(const float* blo, const float* bhi,
         sum = fmaf(lb, lb, sum);
     }
     return !(sum > rad * rad * 1.0001f);
+}
+
+template <int D>
+__global__ void __launch_bounds__(256) nb_pack_conics_kernel(int64_t P, const float* __restrict__ conics, float4* __restrict__ cpack)
+{
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    cpack[i] = D == 2 ? make_float4(conics[i * 3], conics[i * 3 + 1], conics[i * 3 + 2], 0.f) : make_float4(conics[i], 0.f, 0.f, 0.f);
 }
 
 // ---- cell-cooperative path: one CTA per grid cell ---------------------------------------------------
@@ -805,7 +825,7 @@ __device__ __forceinline__ void nbc_fill_rows(const NbCellSmem& sm, NbCellShared
                 __syncwarp();
                 const int ii = ring[(done + lane) & 127u];
                 const float mj[2] = {sm.x[ii], sm.y[ii]};
-                total += nb_emit_core<D, !WRAP>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists,
+                total += nb_emit_core<D, !WRAP, true>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists,
                                                 densities);
                 done += 32u;
             }
@@ -814,7 +834,7 @@ __device__ __forceinline__ void nbc_fill_rows(const NbCellSmem& sm, NbCellShared
         if (done + lane < cnt) {
             const int ii = ring[(done + lane) & 127u];
             const float mj[2] = {sm.x[ii], sm.y[ii]};
-            total += nb_emit_core<D, !WRAP>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists, densities);
+            total += nb_emit_core<D, !WRAP, true>(start + done + lane, sm.id[ii], mj, mi, inv_r, conics, indices, dists, densities);
         }
         __syncwarp();
 #pragma unroll
@@ -1280,16 +1300,21 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
     const int cap = nb_cell_cap();
     const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
+    if (D == 2)
+        nb_pack_conics_kernel<2><<<(unsigned)((P + 255) / 256), 256, 0, st>>>(P, conics, w.cpack);
+    else
+        nb_pack_conics_kernel<1><<<(unsigned)((P + 255) / 256), 256, 0, st>>>(P, conics, w.cpack);
+    PIGS_LAUNCH_CHECK();
     if (D == 2) {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_fill_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
-                                                                              cap, w.cell_over, conics, radii, ranges, indices,
-                                                                              dists, densities, inv_total_densities);
+                                                                              cap, w.cell_over, (const float*)w.cpack, radii, ranges,
+                                                                              indices, dists, densities, inv_total_densities);
     } else {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_fill_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
-                                                                              cap, w.cell_over, conics, radii, ranges, indices,
-                                                                              dists, densities, inv_total_densities);
+                                                                              cap, w.cell_over, (const float*)w.cpack, radii, ranges,
+                                                                              indices, dists, densities, inv_total_densities);
     }
     PIGS_LAUNCH_CHECK();
     if (D == 2) {

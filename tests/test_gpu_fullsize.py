@@ -91,3 +91,51 @@ def test_full_size_against_oracle_subset(name):
         rhs = (d["values"].detach().double() * dv.double()).sum().item()
         scale = (o.detach().double().abs() * G.double().abs()).sum().item()
         assert abs(lhs - rhs) <= 1e-5 * scale, (name, "adjoint", fn, lhs, rhs, scale)
+
+
+@pytest.mark.timeout(900)
+def test_neighbor_search_full_size_rows_against_oracle():
+    """C5 part ii: the neighbour search at reference semantics at P = 1M (1.58e9 slots, 31.6 GB of
+    CSR).  The oracle's all-pairs scan is O(P^2), so a random sample of rows is scanned against all P candidates on the
+    CPU and compared with the same rows of the GPU lists: counts and indices bit-exact, dists / densities /
+    inv_total to 1e-5; plus whole-list invariants (row totals, ascending ids, self in every row)."""
+    import torch
+
+    from pigs_b200 import GaussianSampler
+    P = 1_000_000
+    rec = synthetic(P, 1024, seed=0)
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    s = GaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    radii = s.radii.cpu().numpy()   # bit-exact against the oracle in the test above (C3's Gaussians)
+    s.preprocess_aggregate()
+    ranges = s.ranges.cpu().numpy()
+    M = int(ranges[-1])
+    assert s.indices.numel() == M and M > 1_000_000_000
+    rng = np.random.default_rng(11)
+    rows = np.sort(rng.choice(P, 384, replace=False))
+    counts, idx, dists, dens, inv = po.neighbor_rows(rec["means"], rec["conics"], radii, rows)
+    assert counts.max() <= idx.shape[1]
+    starts = np.concatenate([[0], ranges[:-1]])
+    for k, i in enumerate(rows):
+        a, b = int(starts[i]), int(ranges[i])
+        c = int(counts[k])
+        assert b - a == c, (i, b - a, c)
+        np.testing.assert_array_equal(s.indices[a:b].cpu().numpy(), idx[k, :c])
+        assert rel_err(s.dists[a:b].cpu().numpy(), dists[k, :c]) <= TOL
+        assert rel_err(s.densities[a:b].cpu().numpy(), dens[k, :c]) <= TOL
+    assert rel_err(s.inv_total_densities.cpu().numpy()[rows], inv) <= TOL
+    # whole-list invariants, in chunks (the CSR is 12.6 GB of int64 indices)
+    row_of = torch.repeat_interleave(torch.arange(P, device="cuda", dtype=torch.int32),
+                                     torch.from_numpy(np.diff(ranges, prepend=0)).cuda())
+    n_self = 0
+    step = 1 << 28
+    for a in range(0, M, step):
+        b = min(M, a + step + 1)
+        ind = s.indices[a:b]
+        ro = row_of[a:b]
+        same_row = ro[1:] == ro[:-1]
+        asc = (ind[1:] > ind[:-1]) | (ind[1:] < 0) | (ind[:-1] < 0)
+        assert bool((asc | ~same_row).all())
+        n_self += int((ind[: min(step, M - a)] == ro[: min(step, M - a)]).sum())
+    assert n_self == P   # every (valid) Gaussian neighbours itself exactly once

@@ -129,7 +129,7 @@ def main():
         ms = min(times[1:])
         out["neighbour_search_runs_ms"] = [round(t, 3) for t in times]
         Ms = ind.numel()
-        out["rows"].append(row("preprocess_aggregate (grid neighbour search + CSR fill incl. the torch fills of the CSR; best warm run of 2)", ms, 20 * Ms,
+        out["rows"].append(row("preprocess_aggregate (grid neighbour search + CSR write-out; best warm run of 2)", ms, 20 * Ms,
                                "CSR write-out 20 B/slot (idx 8, dist 8, density 4); M=%d slots = %.0f per Gaussian" % (Ms, Ms / P)))
     print(json.dumps(out, indent=1))
 
