@@ -146,11 +146,19 @@ size_t pigs_neighbor_workspace_bytes(int64_t P, int D);
 /* stage A: per-Gaussian neighbour counts (findCollisions semantics) -> counts int64[P] */
 int pigs_neighbors_count(int64_t P, int D, const float *means, const float *radii, int64_t *counts,
                          void *workspace, void *stream);
-/* stage B: caller computes ranges = inclusive cumsum(counts) (int64[P]) and allocates the CSR arrays
- * (indices pre-filled with -1, dists/densities with 0); this fills them (preprocess, :57-127). */
+/* stage B: caller computes ranges = inclusive cumsum(counts) (int64[P]) and allocates the CSR arrays (no pre-fill
+ * needed: every slot is written, skipped neighbours as index -1 / density 0); this fills them (preprocess, :57-127). */
 int pigs_neighbors_fill(int64_t P, int D, const float *means, const float *conics, const float *radii,
                         const int64_t *ranges, int64_t *indices, float *dists, float *densities,
                         float *inv_total_densities, void *workspace, void *stream);
+/* The same two stages for the rows (query Gaussians) [row_lo, row_hi) only — multi-GPU aggregation shards the CSR by
+ * query Gaussian.  Every Gaussian stays a candidate neighbour; rows outside the window get count 0 and
+ * the no-neighbour total 1/(0 + 1e-6), so the aggregation kernels run unchanged on the sharded CSR. */
+int pigs_neighbors_count_rows(int64_t P, int D, const float *means, const float *radii, int64_t row_lo, int64_t row_hi,
+                              int64_t *counts, void *workspace, void *stream);
+int pigs_neighbors_fill_rows(int64_t P, int D, const float *means, const float *conics, const float *radii,
+                             int64_t row_lo, int64_t row_hi, const int64_t *ranges, int64_t *indices, float *dists,
+                             float *densities, float *inv_total_densities, void *workspace, void *stream);
 int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float *features,
                            const float *transform, const float *queries, const float *keys,
                            const float *frequencies, const float *distance_transform,

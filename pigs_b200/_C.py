@@ -235,19 +235,22 @@ def point_lists(num_rendered, binning_buffer, sample_binning_buffer, N):
 
 
 # ---- neighbour aggregation (ext.cpp:29-31) ----------------------------------------------------------
-def preprocess_aggregate(means, conics, radii, debug):
+def preprocess_aggregate(means, conics, radii, debug, rows=None):
     """AggregateNeighborsPreprocessCUDA (aggregate_neighbors.cu:323-367).  Returns
-    (indices i64[M], ranges i64[P], dists f32[M,D], densities f32[M], inv_total_densities f32[P])."""
+    (indices i64[M], ranges i64[P], dists f32[M,D], densities f32[M], inv_total_densities f32[P]).
+    rows = (lo, hi) (extension, multi-GPU): lists of the query Gaussians [lo, hi) only; the others get empty rows."""
     L = _lib.lib()
     means = _f32c(means, "means")
     conics = _f32c(conics, "conics")
     radii = _f32c(radii, "radii")
     P, D = means.size(0), means.size(-1)
+    lo, hi = (0, P) if rows is None else (int(rows[0]), int(rows[1]))
     dev = means.device
     ws = _bytes(max(int(L.pigs_neighbor_workspace_bytes(P, D)), 16), dev)
     counts = torch.zeros(P, dtype=torch.int64, device=dev)
     st = _stream()
-    check(L.pigs_neighbors_count(P, D, _ptr(means), _ptr(radii), _ptr(counts), _ptr(ws), st), "pigs_neighbors_count")
+    check(L.pigs_neighbors_count_rows(P, D, _ptr(means), _ptr(radii), lo, hi, _ptr(counts), _ptr(ws), st),
+          "pigs_neighbors_count_rows")
     ranges = counts.cumsum(0)
     length = int(ranges[-1].item()) if P > 0 else 0
     # every CSR slot is written by the fill kernels (skipped neighbours get index -1 / density 0 there)
@@ -255,8 +258,8 @@ def preprocess_aggregate(means, conics, radii, debug):
     dists = torch.empty((length, D), dtype=torch.float32, device=dev)
     densities = torch.empty((length,), dtype=torch.float32, device=dev)
     inv_total = torch.zeros((P,), dtype=torch.float32, device=dev)
-    check(L.pigs_neighbors_fill(P, D, _ptr(means), _ptr(conics), _ptr(radii), _ptr(ranges), _ptr(indices), _ptr(dists),
-                                _ptr(densities), _ptr(inv_total), _ptr(ws), st), "pigs_neighbors_fill")
+    check(L.pigs_neighbors_fill_rows(P, D, _ptr(means), _ptr(conics), _ptr(radii), lo, hi, _ptr(ranges), _ptr(indices),
+                                     _ptr(dists), _ptr(densities), _ptr(inv_total), _ptr(ws), st), "pigs_neighbors_fill_rows")
     if debug:
         torch.cuda.synchronize()
     return indices, ranges, dists, densities, inv_total

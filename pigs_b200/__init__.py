@@ -126,12 +126,15 @@ def sample_gaussians_third_derivative(debug, *args):
 class _AggregateNeighbors(torch.autograd.Function):
     @staticmethod
     def forward(ctx, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
-                densities, inv_total_densities, debug):
+                densities, inv_total_densities, debug, reduce=None):
         args = (features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
                 inv_total_densities, debug)
         weights, embeddings, factors, neighbor_features = call_debug(_C.aggregate_neighbors, debug, "aggregate", *args)
         ctx.args = args
         ctx.saved = (weights, embeddings, factors)
+        ctx.reduce = reduce  # sharded sampler: sums the row-sharded output and the six gradients over ranks
+        if reduce is not None:
+            neighbor_features = reduce.output(neighbor_features)
         return neighbor_features
 
     @staticmethod
@@ -141,14 +144,16 @@ class _AggregateNeighbors(torch.autograd.Function):
         weights, embeddings, factors = ctx.saved
         grads = call_debug(_C.aggregate_neighbors_backward, debug, "aggregate_bw", features, transform, queries, keys,
                            frequencies, distance_transform, indices, ranges, dists, densities, weights, embeddings,
-                           factors, inv_total_densities, grad_out, debug)
-        return tuple(grads) + (None,) * 6
+                           factors, inv_total_densities, grad_out.contiguous(), debug)
+        if ctx.reduce is not None:
+            grads = ctx.reduce.gradients(grads)
+        return tuple(grads) + (None,) * 7
 
 
 def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
-                        densities, inv_total_densities, debug):
+                        densities, inv_total_densities, debug, reduce=None):
     return _AggregateNeighbors.apply(features, transform, queries, keys, frequencies, distance_transform, indices,
-                                     ranges, dists, densities, inv_total_densities, debug)
+                                     ranges, dists, densities, inv_total_densities, debug, reduce)
 
 
 _BIT_OF = {"u": FN_VALUE, "du": FN_DERIV, "ddu": FN_HESS, "dddu": FN_THIRD}

@@ -65,6 +65,8 @@ SIGNATURES = {
     "pigs_neighbor_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_neighbors_count": (c_int, [c_int64, c_int] + [c_void_p] * 5),
     "pigs_neighbors_fill": (c_int, [c_int64, c_int] + [c_void_p] * 10),
+    "pigs_neighbors_count_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 3),
+    "pigs_neighbors_fill_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 7),
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
     "pigs_set_aggregate_specialised": (None, [c_int]),
     "pigs_set_neighbor_search": (None, [c_int, ctypes.c_float]),

@@ -49,6 +49,13 @@ struct NbGrid {
     int pad[4];
 };
 
+// rows (Gaussian ids) whose lists this call builds: [lo, hi).  Multi-GPU aggregation shards the CSR by query
+// Gaussian; every other row gets count 0 and the no-neighbour total.
+struct NbWindow {
+    uint32_t lo, hi;
+    __host__ __device__ bool has(uint32_t id) const { return id >= lo && id < hi; }
+};
+
 struct NbLayout {
     NbGrid* grid;
     float* reff;          // [P] float(radii * 0.2)
@@ -322,14 +329,15 @@ __global__ void __launch_bounds__(NB_THREADS) nb_count_kernel(int64_t P, const N
                                                               const uint32_t* __restrict__ cell_start,
                                                               const float4* __restrict__ srec, int64_t* __restrict__ counts,
                                                               const uint32_t* __restrict__ row_cell,
-                                                              const uint8_t* __restrict__ cell_over)
+                                                              const uint8_t* __restrict__ cell_over, NbWindow win)
 {
     const int lane = threadIdx.x & 31;
     const int64_t r = (int64_t)blockIdx.x * NB_WARPS + (threadIdx.x >> 5);
+    if (r >= (int64_t)cell_start[gp->ncells]) return;  // invalid rows keep count 0
+    if (!cell_over[row_cell[r]]) return;                // counted by nb_cell_count_kernel
     const NbGrid g = *gp;
-    if (r >= (int64_t)cell_start[g.ncells]) return;  // invalid rows keep count 0
-    if (!cell_over[row_cell[r]]) return;              // counted by nb_cell_count_kernel
     const float4 me = srec[r];
+    if (!win.has(__float_as_uint(me.w))) return;        // row of another shard: count 0
     const float mi[2] = {me.x, me.y};
     uint32_t cnt = 0;
     nb_for_candidates<D>(me, g, cell_start, srec, lane, 32, [&](bool valid, const float4& o) {
@@ -414,20 +422,21 @@ __global__ void __launch_bounds__(NB_THREADS) nb_fill_kernel(int64_t P, NbGrid* 
                                                              float* __restrict__ dists, float* __restrict__ densities,
                                                              float* __restrict__ inv_total, uint32_t* __restrict__ big_list,
                                                              const uint32_t* __restrict__ row_cell,
-                                                             const uint8_t* __restrict__ cell_over)
+                                                             const uint8_t* __restrict__ cell_over, NbWindow win)
 {
     __shared__ uint32_t s_buf[NB_WARPS][NB_WARP_CAP];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int64_t r = (int64_t)blockIdx.x * NB_WARPS + w;
     if (r >= P) return;
+    const bool valid_row = r < (int64_t)cell_start[gp->ncells];
+    if (valid_row && !cell_over[row_cell[r]]) return;  // handled by nb_cell_fill_kernel
     const NbGrid g = *gp;
     const float4 me = srec[r];
     const uint32_t id = __float_as_uint(me.w);
-    if (r >= (int64_t)cell_start[g.ncells]) {  // no neighbours: total density 0 (aggregate_neighbors.cu:124-125)
+    if (!valid_row || !win.has(id)) {  // no neighbours (or another shard's row): total density 0 (aggregate_neighbors.cu:124-125)
         if (lane == 0) inv_total[id] = __double2float_rn(1.0 / (0.0 + 1e-6));
         return;
     }
-    if (!cell_over[row_cell[r]]) return;  // filled by nb_cell_fill_kernel
     const int64_t start = id == 0 ? 0 : ranges[id - 1];
     const int64_t n = ranges[id] - start;
     if (n > NB_WARP_CAP) {
@@ -595,6 +604,14 @@ struct NbCellShared {  // small static part
     uint16_t ring[NBC_WARPS][128];
 };
 
+// block-uniform: does the cell hold a row of this call's window?
+__device__ __forceinline__ bool nbc_any_row_in(NbWindow win, const float4* __restrict__ srec, uint32_t rs, uint32_t re)
+{
+    bool any = false;
+    for (uint32_t p = rs + threadIdx.x; p < re; p += NBC_THREADS) any |= win.has(__float_as_uint(srec[p].w));
+    return __syncthreads_or(any) != 0;
+}
+
 // Builds the candidate superset of cell c in shared memory: every Gaussian of the reachable cells that passes
 // nb_box_reach against the cell's bounding box and largest radius.  SORT = true orders it by ascending id (bitonic
 // sort of the ids, records re-read by id); SORT = false keeps arrival order (enough for counting).
@@ -738,11 +755,12 @@ __device__ __forceinline__ bool nbc_collides(const float* mi, float ri, const fl
 
 template <int D, bool WRAP>
 __device__ __forceinline__ void nbc_count_rows(const NbCellSmem& sm, int n, uint32_t rs, uint32_t re,
-                                               const float4* __restrict__ srec, int64_t* __restrict__ counts)
+                                               const float4* __restrict__ srec, int64_t* __restrict__ counts, NbWindow win)
 {
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
         const float4 me = srec[r];
+        if (!win.has(__float_as_uint(me.w))) continue;
         const float mi[2] = {me.x, me.y};
         uint32_t cnt = 0;
         const int nn = WRAP ? n : ((n + 63) & ~63);  // the padding never collides on the branch-free path
@@ -763,7 +781,8 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_count_kernel(const NbGrid
                                                                     const float4* __restrict__ srec,
                                                                     const float* __restrict__ means,
                                                                     const float* __restrict__ reff, int cap,
-                                                                    uint8_t* __restrict__ cell_over, int64_t* __restrict__ counts)
+                                                                    uint8_t* __restrict__ cell_over, int64_t* __restrict__ counts,
+                                                                    NbWindow win, int windowed)
 {
     extern __shared__ __align__(16) unsigned char nbc_raw[];
     NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
@@ -775,14 +794,18 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_count_kernel(const NbGrid
             if (threadIdx.x == 0) cell_over[c] = 0;
             continue;
         }
+        if (windowed && !nbc_any_row_in(win, srec, rs, re)) {  // no row of this shard in the cell
+            if (threadIdx.x == 0) cell_over[c] = 0;
+            continue;
+        }
         __syncthreads();  // the previous cell's readers are done with shared memory
         const int n = nbc_load_cell<D, false>(g, cell_start, srec, means, reff, cap, sm, sh, rs, re);
         if (threadIdx.x == 0) cell_over[c] = n < 0;
         if (n < 0) continue;
         if (sh.wrap)
-            nbc_count_rows<D, true>(sm, n, rs, re, srec, counts);
+            nbc_count_rows<D, true>(sm, n, rs, re, srec, counts, win);
         else
-            nbc_count_rows<D, false>(sm, n, rs, re, srec, counts);
+            nbc_count_rows<D, false>(sm, n, rs, re, srec, counts, win);
     }
 }
 
@@ -793,7 +816,7 @@ __device__ __forceinline__ void nbc_fill_rows(const NbCellSmem& sm, NbCellShared
                                               const float4* __restrict__ srec, const float* __restrict__ conics,
                                               const float* __restrict__ radii, const int64_t* __restrict__ ranges,
                                               int64_t* __restrict__ indices, float* __restrict__ dists,
-                                              float* __restrict__ densities, float* __restrict__ inv_total)
+                                              float* __restrict__ densities, float* __restrict__ inv_total, NbWindow win)
 {
     const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
     const uint32_t lt = (1u << lane) - 1u;
@@ -801,6 +824,10 @@ __device__ __forceinline__ void nbc_fill_rows(const NbCellSmem& sm, NbCellShared
     for (uint32_t r = rs + wp; r < re; r += NBC_WARPS) {
         const float4 me = srec[r];
         const uint32_t id = __float_as_uint(me.w);
+        if (!win.has(id)) {  // another shard's row: empty list
+            if (lane == 0) inv_total[id] = __double2float_rn(1.0 / (0.0 + 1e-6));
+            continue;
+        }
         const float mi[2] = {me.x, me.y};
         const int64_t start = id == 0 ? 0 : ranges[id - 1];
         const float inv_r = nb_inv_radius(radii[id]);
@@ -854,7 +881,8 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid*
                                                                    const float* __restrict__ radii,
                                                                    const int64_t* __restrict__ ranges,
                                                                    int64_t* __restrict__ indices, float* __restrict__ dists,
-                                                                   float* __restrict__ densities, float* __restrict__ inv_total)
+                                                                   float* __restrict__ densities, float* __restrict__ inv_total,
+                                                                   NbWindow win, int windowed)
 {
     extern __shared__ __align__(16) unsigned char nbc_raw[];
     NbCellSmem& sm = *reinterpret_cast<NbCellSmem*>(nbc_raw);
@@ -863,13 +891,18 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid*
     for (uint32_t c = blockIdx.x; c < (uint32_t)g.ncells; c += gridDim.x) {
         const uint32_t rs = cell_start[c], re = cell_start[c + 1];
         if (rs == re || cell_over[c]) continue;
+        if (windowed && !nbc_any_row_in(win, srec, rs, re)) {
+            for (uint32_t p = rs + threadIdx.x; p < re; p += NBC_THREADS)
+                inv_total[__float_as_uint(srec[p].w)] = __double2float_rn(1.0 / (0.0 + 1e-6));
+            continue;
+        }
         __syncthreads();
         const int n = nbc_load_cell<D, true>(g, cell_start, srec, means, reff, cap, sm, sh, rs, re);
         if (n < 0) continue;  // cannot happen: same inputs as the count pass
         if (sh.wrap)
-            nbc_fill_rows<D, true>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total);
+            nbc_fill_rows<D, true>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total, win);
         else
-            nbc_fill_rows<D, false>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total);
+            nbc_fill_rows<D, false>(sm, sh, n, rs, re, srec, conics, radii, ranges, indices, dists, densities, inv_total, win);
     }
 }
 
@@ -1236,8 +1269,17 @@ size_t pigs_neighbor_workspace_bytes(int64_t P, int D) { return NbLayout(nullptr
 int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radii, int64_t* counts, void* workspace,
                          void* stream)
 {
+    return pigs_neighbors_count_rows(P, D, means, radii, 0, P, counts, workspace, stream);
+}
+
+int pigs_neighbors_count_rows(int64_t P, int D, const float* means, const float* radii, int64_t row_lo, int64_t row_hi,
+                              int64_t* counts, void* workspace, void* stream)
+{
     PIGS_ARG(D == 1 || D == 2);
     PIGS_ARG(P > 0 && P < (1ll << 31) && means && radii && counts && workspace);
+    PIGS_ARG(row_lo >= 0 && row_lo <= row_hi && row_hi <= P);
+    const NbWindow win{(uint32_t)row_lo, (uint32_t)row_hi};
+    const int windowed = row_lo > 0 || row_hi < P;
     cudaStream_t st = (cudaStream_t)stream;
     NbLayout w(workspace, P, D);
     const unsigned nb = (unsigned)((P + 255) / 256);
@@ -1273,18 +1315,18 @@ int pigs_neighbors_count(int64_t P, int D, const float* means, const float* radi
     if (D == 2) {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_count_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
-                                                                               cap, w.cell_over, counts);
+                                                                               cap, w.cell_over, counts, win, windowed);
     } else {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_count_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_count_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
-                                                                               cap, w.cell_over, counts);
+                                                                               cap, w.cell_over, counts, win, windowed);
     }
     PIGS_LAUNCH_CHECK();
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
     if (D == 2)
-        nb_count_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over);
+        nb_count_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over, win);
     else
-        nb_count_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over);
+        nb_count_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, counts, w.keys_b, w.cell_over, win);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
@@ -1293,8 +1335,19 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
                         const int64_t* ranges, int64_t* indices, float* dists, float* densities,
                         float* inv_total_densities, void* workspace, void* stream)
 {
+    return pigs_neighbors_fill_rows(P, D, means, conics, radii, 0, P, ranges, indices, dists, densities, inv_total_densities,
+                                    workspace, stream);
+}
+
+int pigs_neighbors_fill_rows(int64_t P, int D, const float* means, const float* conics, const float* radii, int64_t row_lo,
+                             int64_t row_hi, const int64_t* ranges, int64_t* indices, float* dists, float* densities,
+                             float* inv_total_densities, void* workspace, void* stream)
+{
     PIGS_ARG(D == 1 || D == 2);
     PIGS_ARG(P > 0 && means && conics && radii && ranges && inv_total_densities && workspace);
+    PIGS_ARG(row_lo >= 0 && row_lo <= row_hi && row_hi <= P);
+    const NbWindow win{(uint32_t)row_lo, (uint32_t)row_hi};
+    const int windowed = row_lo > 0 || row_hi < P;
     cudaStream_t st = (cudaStream_t)stream;
     NbLayout w(workspace, P, D);
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
@@ -1309,24 +1362,26 @@ int pigs_neighbors_fill(int64_t P, int D, const float* means, const float* conic
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_fill_kernel<2><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
                                                                               cap, w.cell_over, (const float*)w.cpack, radii, ranges,
-                                                                              indices, dists, densities, inv_total_densities);
+                                                                              indices, dists, densities, inv_total_densities, win,
+                                                                              windowed);
     } else {
         PIGS_CHECK(cudaFuncSetAttribute(nb_cell_fill_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(NbCellSmem)));
         nb_cell_fill_kernel<1><<<ncta, NBC_THREADS, sizeof(NbCellSmem), st>>>(w.grid, w.cell_start, w.srec, means, w.reff,
                                                                               cap, w.cell_over, (const float*)w.cpack, radii, ranges,
-                                                                              indices, dists, densities, inv_total_densities);
+                                                                              indices, dists, densities, inv_total_densities, win,
+                                                                              windowed);
     }
     PIGS_LAUNCH_CHECK();
     if (D == 2) {
         nb_fill_kernel<2><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
-                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over);
+                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over, win);
         PIGS_LAUNCH_CHECK();
         nb_fill_big_kernel<2><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
                                                                       ranges, indices, dists, densities, inv_total_densities,
                                                                       w.big_list, w.bitmaps, w.words);
     } else {
         nb_fill_kernel<1><<<nbw, NB_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii, ranges, indices,
-                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over);
+                                                      dists, densities, inv_total_densities, w.big_list, w.keys_b, w.cell_over, win);
         PIGS_LAUNCH_CHECK();
         nb_fill_big_kernel<1><<<NB_BIG_CTAS, NB_BIG_THREADS, 0, st>>>(P, w.grid, w.cell_start, w.srec, means, conics, radii,
                                                                       ranges, indices, dists, densities, inv_total_densities,

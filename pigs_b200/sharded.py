@@ -10,7 +10,7 @@ torch.distributed host logic (tested on CPU with gloo, world_size 2); the comput
 import torch
 import torch.distributed as dist
 
-from . import GaussianSampler, _C
+from . import GaussianSampler, _C, aggregate_neighbors
 
 
 def shard_range(N, rank, world):
@@ -39,6 +39,44 @@ def allreduce_grads(flat, group=None):
     return flat
 
 
+def pack_grads(grads):
+    """Six aggregation gradients (any may be None) -> one flat fp32 buffer + the recipe to split it again."""
+    live = [(k, g) for k, g in enumerate(grads) if g is not None]
+    flat = torch.cat([g.reshape(-1) for _, g in live]) if live else None
+    return flat, [(k, g.shape) for k, g in live]
+
+
+def unpack_grads(flat, recipe, n):
+    out, at = [None] * n, 0
+    for k, shape in recipe:
+        cnt = 1
+        for d in shape:
+            cnt *= int(d)
+        out[k] = flat[at:at + cnt].view(shape)
+        at += cnt
+    return out
+
+
+class AggregateReduce:
+    """Collectives of the row-sharded aggregation: each rank owns the neighbour lists of a
+    contiguous range of query Gaussians, so its forward output has the other ranks' rows zero (one all-reduce
+    assembles [P, L]) and its backward holds the contributions of its own rows to all six gradients (one all-reduce
+    of the packed buffer)."""
+
+    def __init__(self, group=None):
+        self.group = group
+
+    def output(self, neighbor_features):
+        return allreduce_grads(neighbor_features, self.group)
+
+    def gradients(self, grads):
+        flat, recipe = pack_grads(grads)
+        if flat is None:
+            return grads
+        allreduce_grads(flat, self.group)
+        return unpack_grads(flat, recipe, len(grads))
+
+
 class ShardedGaussianSampler(GaussianSampler):
     """GaussianSampler whose `samples` are this rank's shard.  Same API; preprocess() bins on the global tile
     grid, backward all-reduces the gradients w.r.t. means / values / conics (so every rank ends up with the
@@ -54,3 +92,23 @@ class ShardedGaussianSampler(GaussianSampler):
         mm = _C.sample_bounds(samples, D)
         allreduce_bounds(mm, D, self.group)
         super().preprocess(means, values, covariances, conics, samples, bounds=mm)
+
+    def _rank_world(self):
+        if not dist.is_initialized():
+            return 0, 1
+        return dist.get_rank(self.group), dist.get_world_size(self.group)
+
+    def preprocess_aggregate(self):
+        """Neighbour lists of this rank's contiguous range of query Gaussians (every Gaussian stays a candidate
+        neighbour); the other rows are empty.  1/world of the CSR per GPU."""
+        rank, world = self._rank_world()
+        self.row_range = shard_range(self.means.size(0), rank, world)
+        (self.indices, self.ranges, self.dists, self.densities,
+         self.inv_total_densities) = _C.preprocess_aggregate(self.means, self.conics, self.radii, self.debug,
+                                                             rows=self.row_range)
+
+    def aggregate_neighbors(self, features, transform, queries, keys, frequencies, distance_transform):
+        """Full [P, L] output on every rank; gradients of all six inputs summed over ranks."""
+        return aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, self.indices,
+                                   self.ranges, self.dists, self.densities, self.inv_total_densities, self.debug,
+                                   reduce=AggregateReduce(self.group))

@@ -165,3 +165,47 @@ def test_generic_sizes():
     got.backward(torch.from_numpy(up).cuda())
     for x, wv, key in zip(t, want, AGG_KEYS):
         assert rel_err(x.grad.cpu().numpy(), wv) <= TOL, key
+
+
+@pytest.mark.parametrize("name", ["agg_model", "agg_model_1d", "agg_model_edge"])
+def test_row_sharded_lists_and_aggregation(name, nb_path):
+    """Multi-GPU aggregation without a second GPU: the CSR of each half of the query Gaussians
+    holds exactly the rows of the full CSR, the two row-sharded forward outputs add up to the unsharded output bit for
+    bit (disjoint rows), and the two backward contributions add up to the unsharded gradients."""
+    import torch
+    from pigs_b200 import _C
+    rec = AGG_RECIPES[name]()
+    s, d = _prep(rec)
+    P = rec["means"].shape[0]
+    full = (s.indices, s.ranges, s.dists, s.densities, s.inv_total_densities)
+    a = [d[k] for k in AGG_KEYS]
+    wf, ef, ff, out_full = _C.aggregate_neighbors(*a, *full, False)
+    up = torch.from_numpy(agg_upstream(rec)).cuda()
+    g_full = _C.aggregate_neighbors_backward(*a, s.indices, s.ranges, s.dists, s.densities, wf, ef, ff,
+                                             s.inv_total_densities, up, False)
+    starts_full = torch.cat([torch.zeros(1, dtype=torch.int64, device="cuda"), s.ranges[:-1]])
+    out_sum = torch.zeros_like(out_full)
+    g_sum = [torch.zeros_like(g) for g in g_full]
+    cut = P // 2 + 1
+    for lo, hi in ((0, cut), (cut, P)):
+        idx, rng, dists, dens, inv = _C.preprocess_aggregate(s.means, s.conics, s.radii, False, rows=(lo, hi))
+        cnt = torch.diff(rng, prepend=torch.zeros(1, dtype=torch.int64, device="cuda"))
+        cnt_full = torch.diff(s.ranges, prepend=torch.zeros(1, dtype=torch.int64, device="cuda"))
+        assert int(cnt[:lo].sum()) == 0 and int(cnt[hi:].sum()) == 0
+        assert torch.equal(cnt[lo:hi], cnt_full[lo:hi])
+        a0, b0 = int(starts_full[lo]), int(s.ranges[hi - 1])
+        assert idx.numel() == b0 - a0
+        assert torch.equal(idx, s.indices[a0:b0])          # the rank's rows are the full CSR's rows, bit for bit
+        assert torch.equal(dists, s.dists[a0:b0])
+        assert torch.equal(dens, s.densities[a0:b0])
+        assert torch.equal(inv[lo:hi], s.inv_total_densities[lo:hi])
+        w, e, f, out = _C.aggregate_neighbors(*a, idx, rng, dists, dens, inv, False)
+        assert float(out[:lo].abs().sum()) == 0.0 and float(out[hi:].abs().sum()) == 0.0
+        assert torch.equal(out[lo:hi], out_full[lo:hi])
+        out_sum += out
+        g = _C.aggregate_neighbors_backward(*a, idx, rng, dists, dens, w, e, f, inv, up, False)
+        for acc, part in zip(g_sum, g):
+            acc += part
+    assert torch.equal(out_sum, out_full)
+    for key, got, want in zip(AGG_KEYS, g_sum, g_full):
+        assert rel_err(got.cpu().numpy(), want.cpu().numpy()) <= TOL, key

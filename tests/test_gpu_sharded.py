@@ -84,3 +84,59 @@ def test_two_gpu_sharding_matches_oracle(tmp_path):
             assert rel_err(p[key].reshape(w.shape), w) <= TOL, key
     for key in ("dmeans", "dvalues", "dconics"):  # every rank holds the same all-reduced gradient
         np.testing.assert_array_equal(parts[0][key], parts[1][key])
+
+
+def _agg_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from pigs_b200.sharded import ShardedGaussianSampler
+        from tests.fixtures import AGG_RECIPES
+        from tests.helpers import AGG_KEYS, agg_upstream
+        rec = AGG_RECIPES["agg_model"]()
+        d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+        s = ShardedGaussianSampler(False)
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        s.preprocess_aggregate()
+        t = [d[k].clone().requires_grad_(True) for k in AGG_KEYS]
+        out = s.aggregate_neighbors(*t)
+        out.backward(torch.from_numpy(agg_upstream(rec)).cuda())
+        torch.cuda.synchronize()
+        np.savez(os.path.join(out_dir, "agg_rank%d.npz" % rank), rows=np.array(s.row_range), slots=s.indices.numel(),
+                 out=out.detach().cpu().numpy(), **{"grad_" + k: x.grad.cpu().numpy() for k, x in zip(AGG_KEYS, t)})
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_two_gpu_row_sharded_aggregation_matches_oracle(tmp_path):
+    """C5 on two GPUs: each rank builds the neighbour lists of half of the query Gaussians; the all-reduced output and
+    gradients equal the oracle's unsharded ones on both ranks."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from oracle import pigs_oracle as po
+    from tests.fixtures import AGG_RECIPES
+    from tests.helpers import AGG_KEYS, TOL, agg_upstream, oracle_state, rel_err
+    world = 2
+    mp.spawn(_agg_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    rec = AGG_RECIPES["agg_model"]()
+    st = oracle_state(rec)
+    idx, rng, dists, dens, inv = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    a = [rec[k] for k in AGG_KEYS]
+    w, e, f, out = po.aggregate_forward(*a, idx, rng, dists, dens, inv)
+    want = po.aggregate_backward(*a, idx, rng, dists, dens, w, e, f, inv, agg_upstream(rec))
+    parts = [np.load(os.path.join(str(tmp_path), "agg_rank%d.npz" % r)) for r in range(world)]
+    assert sum(int(p["slots"]) for p in parts) == idx.shape[0]   # the CSR, split by query Gaussian
+    for p in parts:
+        assert rel_err(p["out"], out) <= TOL
+        for key, wv in zip(AGG_KEYS, want):
+            assert rel_err(p["grad_" + key], wv) <= TOL, key
+    for key in ["out"] + ["grad_" + k for k in AGG_KEYS]:
+        np.testing.assert_array_equal(parts[0][key], parts[1][key])

@@ -90,3 +90,76 @@ def test_two_rank_sharding_matches_single_process(tmp_path):
             np.testing.assert_array_equal(p[key], full[k][lo:hi])  # per-sample results do not depend on the shard
         assert rel_err(p["packed"], want) <= TOL
     np.testing.assert_array_equal(parts[0]["packed"], parts[1]["packed"])
+
+
+def _agg_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import pigs_oracle as po
+        from pigs_b200.sharded import AggregateReduce, shard_range
+        from tests.fixtures import AGG_RECIPES
+        from tests.helpers import AGG_KEYS, agg_upstream, oracle_state
+        rec = AGG_RECIPES["agg_model"]()
+        st = oracle_state(rec)
+        idx, rng, dists, dens, inv = po.neighbors(rec["means"], rec["conics"], st["radii"])
+        P = rng.shape[0]
+        lo, hi = shard_range(P, rank, world)
+        # this rank's CSR: the rows [lo, hi) of the full one, every other row empty with the no-neighbour total
+        cnt = np.diff(rng, prepend=0)
+        starts = rng - cnt
+        a0, b0 = int(starts[lo]), int(rng[hi - 1])
+        cnt_r = np.zeros_like(cnt)
+        cnt_r[lo:hi] = cnt[lo:hi]
+        inv_r = np.full_like(inv, np.float32(1.0 / 1e-6))
+        inv_r[lo:hi] = inv[lo:hi]
+        csr = (idx[a0:b0].copy(), np.cumsum(cnt_r).astype(np.int64), dists[a0:b0].copy(), dens[a0:b0].copy(), inv_r)
+        a = [rec[k] for k in AGG_KEYS]
+        w, e, f, out = po.aggregate_forward(*a, *csr)
+        red = AggregateReduce()
+        out_t = red.output(torch.from_numpy(np.ascontiguousarray(out, np.float32)))
+        grads = po.aggregate_backward(*a, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], agg_upstream(rec))
+        gl = [torch.from_numpy(np.ascontiguousarray(g, np.float32)) for g in grads]
+        got = red.gradients(gl)
+        np.savez(os.path.join(out_dir, "agg%d.npz" % rank), out=out_t.numpy(),
+                 **{"grad_" + k: g.numpy() for k, g in zip(AGG_KEYS, got)})
+    finally:
+        dist.destroy_process_group()
+
+
+def test_pack_unpack_grads_roundtrip():
+    from pigs_b200.sharded import pack_grads, unpack_grads
+    gs = [torch.arange(6.0).view(2, 3), None, torch.arange(4.0), torch.ones(1, 2, 2)]
+    flat, recipe = pack_grads(gs)
+    assert flat.numel() == 6 + 4 + 4
+    back = unpack_grads(flat, recipe, len(gs))
+    assert back[1] is None
+    for a, b in zip(gs, back):
+        if a is not None:
+            assert a.shape == b.shape and torch.equal(a, b)
+    assert pack_grads([None, None])[0] is None
+
+
+def test_two_rank_row_sharded_aggregation_matches_single_process(tmp_path):
+    """Host logic of the row-sharded aggregation (AggregateReduce) over gloo: per-rank CSRs of half of the query
+    Gaussians each; the reduced output and gradients equal the unsharded oracle run on both ranks."""
+    from oracle import pigs_oracle as po
+    from tests.fixtures import AGG_RECIPES
+    from tests.helpers import AGG_KEYS, TOL, agg_upstream, oracle_state, rel_err
+    world = 2
+    mp.spawn(_agg_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    rec = AGG_RECIPES["agg_model"]()
+    st = oracle_state(rec)
+    idx, rng, dists, dens, inv = po.neighbors(rec["means"], rec["conics"], st["radii"])
+    a = [rec[k] for k in AGG_KEYS]
+    w, e, f, out = po.aggregate_forward(*a, idx, rng, dists, dens, inv)
+    want = po.aggregate_backward(*a, idx, rng, dists, dens, w, e, f, inv, agg_upstream(rec))
+    parts = [np.load(os.path.join(str(tmp_path), "agg%d.npz" % r)) for r in range(world)]
+    for p in parts:
+        assert rel_err(p["out"], out) <= TOL
+        for key, wv in zip(AGG_KEYS, want):
+            assert rel_err(p["grad_" + key], wv) <= TOL, key
+    for key in ["out"] + ["grad_" + k for k in AGG_KEYS]:
+        np.testing.assert_array_equal(parts[0][key], parts[1][key])
