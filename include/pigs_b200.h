@@ -215,6 +215,25 @@ int pigs_pde_residual_backward(int problem, int64_t N, int D, int C, float nu, f
                                const float *lap, const float *ut, const float *dL_dloss, float *dL_du, float *dL_dux,
                                float *dL_dlap, float *dL_dut, void *stream);
 
+/* NAVIER_STOKES in vorticity form: model_pn.py:629-631 `pde_rhs`, :818 `wt`, :843-845 loss.
+ *   rhs  = nu*(wxx[:,0,0] + wxx[:,1,1]) - (u[:,0]*wx[:,0] + u[:,1]*wx[:,1])
+ *   loss = mean((ux[:,0,0] + ux[:,1,1])^2) + mean((wt - dt*rhs)^2)
+ * u [N,2], ux [N,2,2] = [n,d,c], wx [N,2], wxx [N,2,2], wt [N] (all 16-byte aligned, contiguous).  forward writes the
+ * device scalar `loss` and, if non-NULL, residual [N] = wt - dt*rhs and divergence [N].  backward: every output
+ * pointer may be NULL; dL_dux / dL_dwxx are fully written (off-diagonal entries zero).  Workspace: the
+ * pigs_pde_residual_workspace_bytes query above.
+ * pigs_vorticity_*: model_pn.py:779-781 `w = ux[:,0,1] - ux[:,1,0]`, `wx = uxx[...,0,1] - uxx[...,1,0]`,
+ * `wxx = uxxx[...,0,1] - uxxx[...,1,0]` — over the trailing (spatial axis e, channel c) 2x2 group of the sampler's
+ * C = 2 outputs: out[g] = in[g, 0, 1] - in[g, 1, 0]; `groups` = N, 2N, 4N for ux, uxx, uxxx. */
+int pigs_pde_ns_residual_forward(int64_t N, float nu, float dt, const float *u, const float *ux, const float *wx,
+                                 const float *wxx, const float *wt, float *residual, float *divergence, float *loss,
+                                 void *workspace, void *stream);
+int pigs_pde_ns_residual_backward(int64_t N, float nu, float dt, const float *u, const float *ux, const float *wx,
+                                  const float *wxx, const float *wt, const float *dL_dloss, float *dL_du, float *dL_dux,
+                                  float *dL_dwx, float *dL_dwxx, float *dL_dwt, void *stream);
+int pigs_vorticity_forward(int64_t groups, const float *in, float *out, void *stream);
+int pigs_vorticity_backward(int64_t groups, const float *dL_dout, float *dL_din, void *stream);
+
 /* ---- split / prune as a device-side compaction --------------------------------
  * Replaces the torch chains that change P between steps: model_pn.py:578-610 `Model.split`, :703-716 (prune by
  * keep_indices), test_no_mlp_1d.py:203-247 (keep + displaced clones, Adam moments of the clones zeroed).

@@ -77,6 +77,10 @@ SIGNATURES = {
     "pigs_pde_residual_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_pde_residual_forward": (c_int, [c_int, c_int64, c_int, c_int, ctypes.c_float, ctypes.c_float] + [c_void_p] * 8),
     "pigs_pde_residual_backward": (c_int, [c_int, c_int64, c_int, c_int, ctypes.c_float, ctypes.c_float] + [c_void_p] * 10),
+    "pigs_pde_ns_residual_forward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float] + [c_void_p] * 10),
+    "pigs_pde_ns_residual_backward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float] + [c_void_p] * 12),
+    "pigs_vorticity_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p]),
+    "pigs_vorticity_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p]),
     "pigs_compact_workspace_bytes": (c_size_t, [c_int64]),
     "pigs_compact_count": (c_int, [c_int64, c_void_p, c_void_p, c_void_p, c_void_p]),
     "pigs_compact_fill": (c_int, [c_int64, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_void_p, c_void_p]),

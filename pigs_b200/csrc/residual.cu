@@ -151,6 +151,96 @@ __global__ void __launch_bounds__(RES_THREADS) residual_backward_kernel(ResArgs 
     }
 }
 
+// ---- NAVIER_STOKES (vorticity form), model_pn.py:629-631 pde_rhs and :821,843-845 loss ----------------------
+//   rhs  = nu * (wxx[:,0,0] + wxx[:,1,1]) - (u[:,0] * wx[:,0] + u[:,1] * wx[:,1])
+//   loss = mean((ux[:,0,0] + ux[:,1,1])^2) + mean((wt - dt * rhs)^2)
+// u [N,2] (velocity, C = 2), ux [N,2,2] = [n, d, c], wx [N,2], wxx [N,2,2] (vorticity derivatives, model_pn.py:779-781),
+// wt [N].  52 B read per sample forward; backward re-reads them and writes 52 B.  Whole-row vector loads.
+struct NsArgs {
+    int64_t N;
+    float nu, dt;
+    const float2* u;
+    const float4* ux;
+    const float2* wx;
+    const float4* wxx;
+    const float* wt;
+};
+
+__device__ __forceinline__ void ns_sample(const NsArgs& a, int64_t n, float2& u, float2& wx, float& div, float& r)
+{
+    const float4 ux = a.ux[n], wxx = a.wxx[n];
+    u = a.u[n];
+    wx = a.wx[n];
+    div = __fadd_rn(ux.x, ux.w);  // ux[n,0,0] + ux[n,1,1]
+    const float lap = __fadd_rn(wxx.x, wxx.w);
+    const float adv = __fadd_rn(__fmul_rn(u.x, wx.x), __fmul_rn(u.y, wx.y));
+    const float rhs = __fsub_rn(__fmul_rn(a.nu, lap), adv);
+    r = __fsub_rn(a.wt[n], __fmul_rn(a.dt, rhs));
+}
+
+__global__ void __launch_bounds__(RES_THREADS) ns_residual_forward_kernel(NsArgs a, float* __restrict__ residual,
+                                                                          float* __restrict__ divergence,
+                                                                          double* __restrict__ partial)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    double acc = 0.0;
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < a.N; n += stride) {
+        float2 u, wx;
+        float div, r;
+        ns_sample(a, n, u, wx, div, r);
+        if (residual) residual[n] = r;
+        if (divergence) divergence[n] = div;
+        acc += (double)(div * div) + (double)(r * r);
+    }
+    const double t = block_sum(acc);
+    if (threadIdx.x == 0) partial[blockIdx.x] = t;
+}
+
+__global__ void __launch_bounds__(RES_THREADS) ns_residual_backward_kernel(NsArgs a, const float* __restrict__ g_loss,
+                                                                           float inv_count, float2* __restrict__ d_u,
+                                                                           float4* __restrict__ d_ux, float2* __restrict__ d_wx,
+                                                                           float4* __restrict__ d_wxx, float* __restrict__ d_wt)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const float k = 2.0f * g_loss[0] * inv_count;
+    for (int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; n < a.N; n += stride) {
+        float2 u, wx;
+        float div, r;
+        ns_sample(a, n, u, wx, div, r);
+        const float dr = k * r, drhs = -a.dt * dr, dd = k * div;
+        if (d_wt) d_wt[n] = dr;
+        if (d_ux) d_ux[n] = make_float4(dd, 0.0f, 0.0f, dd);
+        if (d_wxx) d_wxx[n] = make_float4(a.nu * drhs, 0.0f, 0.0f, a.nu * drhs);
+        if (d_u) d_u[n] = make_float2(-wx.x * drhs, -wx.y * drhs);
+        if (d_wx) d_wx[n] = make_float2(-u.x * drhs, -u.y * drhs);
+    }
+}
+
+// ---- vorticity and its derivatives from the sampler's outputs at C = 2, model_pn.py:779-781 ----------------
+//   w = ux[:,0,1] - ux[:,1,0]   wx = uxx[...,0,1] - uxx[...,1,0]   wxx = uxxx[...,0,1] - uxxx[...,1,0]
+// i.e. with the trailing two axes (last spatial axis e, channel c): out[..] = in[.., e=0, c=1] - in[.., e=1, c=0].
+// One float4 {(0,0),(0,1),(1,0),(1,1)} in -> one float out; ux, uxx, uxxx are 1, 2, 4 such groups per sample
+// (112 B read + 28 B written per sample); the backward writes {0, g, -g, 0}.
+__global__ void __launch_bounds__(RES_THREADS) vorticity_forward_kernel(int64_t G, const float4* __restrict__ in,
+                                                                        float* __restrict__ out)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < G; i += stride) {
+        const float4 v = in[i];
+        out[i] = __fsub_rn(v.y, v.z);
+    }
+}
+
+__global__ void __launch_bounds__(RES_THREADS) vorticity_backward_kernel(int64_t G, const float* __restrict__ g,
+                                                                         float4* __restrict__ d_in)
+{
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < G; i += stride) {
+        const float v = g[i];
+        d_in[i] = make_float4(0.0f, v, -v, 0.0f);
+    }
+}
+
 static int res_grid(int64_t work)
 {
     int64_t nb = (work + RES_THREADS - 1) / RES_THREADS;
@@ -213,6 +303,53 @@ int pigs_pde_residual_backward(int problem, int64_t N, int D, int C, float nu, f
     const int64_t work = problem == PIGS_PDE_WAVE ? N : N * C;
     residual_backward_kernel<<<res_grid(work), RES_THREADS, 0, st>>>(a, dL_dloss, (float)(1.0 / (double)work), dL_du,
                                                                      dL_dux, dL_dlap, dL_dut);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_pde_ns_residual_forward(int64_t N, float nu, float dt, const float* u, const float* ux, const float* wx,
+                                 const float* wxx, const float* wt, float* residual, float* divergence, float* loss,
+                                 void* workspace, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(N > 0 && u && ux && wx && wxx && wt && loss && workspace);
+    NsArgs a{N, nu, dt, (const float2*)u, (const float4*)ux, (const float2*)wx, (const float4*)wxx, wt};
+    cudaStream_t st = (cudaStream_t)stream;
+    const int nb = res_grid(N);
+    ns_residual_forward_kernel<<<nb, RES_THREADS, 0, st>>>(a, residual, divergence, (double*)workspace);
+    PIGS_LAUNCH_CHECK();
+    residual_finish_kernel<<<1, RES_THREADS, 0, st>>>(nb, (const double*)workspace, 1.0 / (double)N, loss);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_pde_ns_residual_backward(int64_t N, float nu, float dt, const float* u, const float* ux, const float* wx,
+                                  const float* wxx, const float* wt, const float* dL_dloss, float* dL_du, float* dL_dux,
+                                  float* dL_dwx, float* dL_dwxx, float* dL_dwt, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(N > 0 && u && ux && wx && wxx && wt && dL_dloss);
+    NsArgs a{N, nu, dt, (const float2*)u, (const float4*)ux, (const float2*)wx, (const float4*)wxx, wt};
+    ns_residual_backward_kernel<<<res_grid(N), RES_THREADS, 0, (cudaStream_t)stream>>>(
+        a, dL_dloss, (float)(1.0 / (double)N), (float2*)dL_du, (float4*)dL_dux, (float2*)dL_dwx, (float4*)dL_dwxx, dL_dwt);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_vorticity_forward(int64_t groups, const float* in, float* out, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(groups > 0 && in && out);
+    vorticity_forward_kernel<<<res_grid(groups), RES_THREADS, 0, (cudaStream_t)stream>>>(groups, (const float4*)in, out);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_vorticity_backward(int64_t groups, const float* dL_dout, float* dL_din, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(groups > 0 && dL_dout && dL_din);
+    vorticity_backward_kernel<<<res_grid(groups), RES_THREADS, 0, (cudaStream_t)stream>>>(groups, dL_dout, (float4*)dL_din);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
