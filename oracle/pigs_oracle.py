@@ -408,6 +408,48 @@ def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss):
     return -ux[:, 0] * drhs, d_ux, nu * drhs, dr
 
 
+def vorticity(x):
+    """model_pn.py:779-781: `ux[:,0,1] - ux[:,1,0]`, `uxx[...,0,1] - uxx[...,1,0]`, `uxxx[...,0,1] - uxxx[...,1,0]` — the
+    trailing two axes of a C = 2 sampler output are (last spatial axis, channel)."""
+    x = _f32(x)
+    return (x[..., 0, 1] - x[..., 1, 0]).astype(np.float32)
+
+
+def vorticity_backward(g):
+    g = np.asarray(g, np.float64)
+    d = np.zeros(g.shape + (2, 2))
+    d[..., 0, 1] = g
+    d[..., 1, 0] = -g
+    return d
+
+
+def ns_residual_loss(u, ux, wx, wxx, wt, nu, dt):
+    """NAVIER_STOKES, vorticity form.  model_pn.py:629-631 `nu*(wxx00 + wxx11) - (u0*wx0 + u1*wx1)`, :824 `rhs = dt*...`,
+    :843-845 `mean((ux00 + ux11)**2) + mean((wt - rhs)**2)`; fp32 op by op like the torch expressions.
+    Returns (residual [N] fp32, divergence [N] fp32, loss float64-accumulated)."""
+    f = np.float32
+    u, ux, wx, wxx, wt = (_f32(t) for t in (u, ux, wx, wxx, wt))
+    rhs = (f(nu) * (wxx[:, 0, 0] + wxx[:, 1, 1]) - (u[:, 0] * wx[:, 0] + u[:, 1] * wx[:, 1])).astype(f)
+    r = (wt.reshape(-1) - f(dt) * rhs).astype(f)
+    div = (ux[:, 0, 0] + ux[:, 1, 1]).astype(f)
+    return r, div, (div.astype(np.float64) ** 2).mean() + (r.astype(np.float64) ** 2).mean()
+
+
+def ns_residual_backward(u, ux, wx, wxx, wt, nu, dt, g_loss):
+    """Analytic gradient of ns_residual_loss (checked against torch.autograd through the real model_pn.pde_rhs by
+    tests/golden/pde_golden.npz).  Returns (d_u, d_ux, d_wx, d_wxx, d_wt), float64."""
+    r, div, _ = ns_residual_loss(u, ux, wx, wxx, wt, nu, dt)
+    N = r.shape[0]
+    dr = 2.0 * r.astype(np.float64) / N * g_loss
+    dd = 2.0 * div.astype(np.float64) / N * g_loss
+    drhs = -float(np.float32(dt)) * dr
+    u, wx = np.asarray(u, np.float64).reshape(N, 2), np.asarray(wx, np.float64).reshape(N, 2)
+    d_ux, d_wxx = np.zeros((N, 2, 2)), np.zeros((N, 2, 2))
+    d_ux[:, 0, 0] = d_ux[:, 1, 1] = dd
+    d_wxx[:, 0, 0] = d_wxx[:, 1, 1] = float(np.float32(nu)) * drhs
+    return -wx * drhs[:, None], d_ux, -u * drhs[:, None], d_wxx, dr
+
+
 # ---- split / prune compaction (SURVEY.md 8f rank 4) ---------------------------------------------------
 def compact_plan(P, keep=None, extend=None, m=1):
     """Parent row of every output row: kept rows in order, then m rows per extended row (model_pn.py:598-605 cat order)."""

@@ -413,3 +413,62 @@ def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss, need=(True, T
                                            _ptr(g_loss), _ptr(d_u), _ptr(d_ux), _ptr(d_lap), _ptr(d_ut), _stream()),
               "pigs_pde_residual_backward")
     return d_u, d_ux, d_lap, d_ut
+
+
+# ---- NAVIER_STOKES residual (vorticity form) + vorticity extraction (model_pn.py:629-631, 779-781, 818, 843-845) ----
+def _ns_args(u, ux, wx, wxx, wt):
+    u, ux, wx, wxx, wt = (_f32c(t, n) for t, n in ((u, "u"), (ux, "ux"), (wx, "wx"), (wxx, "wxx"), (wt, "wt")))
+    N = wt.numel()
+    if u.numel() != 2 * N or ux.numel() != 4 * N or wx.numel() != 2 * N or wxx.numel() != 4 * N:
+        raise RuntimeError("NAVIER_STOKES residual: u [N,2], ux [N,2,2], wx [N,2], wxx [N,2,2], wt [N] expected")
+    return N, u, ux, wx, wxx, wt
+
+
+def pde_ns_residual_forward(u, ux, wx, wxx, wt, nu, dt, want_residual=False):
+    """-> (loss: 0-dim device tensor, residual [N] or None, divergence [N] or None)."""
+    L = _lib.lib()
+    N, u, ux, wx, wxx, wt = _ns_args(u, ux, wx, wxx, wt)
+    dev = wt.device
+    loss = torch.zeros((), dtype=torch.float32, device=dev)
+    res = torch.empty(N, dtype=torch.float32, device=dev) if want_residual else None
+    div = torch.empty(N, dtype=torch.float32, device=dev) if want_residual else None
+    if N > 0:
+        ws = _bytes(max(int(L.pigs_pde_residual_workspace_bytes(N, 2)), 16), dev)
+        check(L.pigs_pde_ns_residual_forward(N, float(nu), float(dt), _ptr(u), _ptr(ux), _ptr(wx), _ptr(wxx), _ptr(wt),
+                                             _ptr(res), _ptr(div), _ptr(loss), _ptr(ws), _stream()),
+              "pigs_pde_ns_residual_forward")
+    return loss, res, div
+
+
+def pde_ns_residual_backward(u, ux, wx, wxx, wt, nu, dt, g_loss, need=(True,) * 5):
+    """-> (dL_du, dL_dux, dL_dwx, dL_dwxx, dL_dwt), None where not needed."""
+    L = _lib.lib()
+    N, u, ux, wx, wxx, wt = _ns_args(u, ux, wx, wxx, wt)
+    g_loss = _f32c(g_loss, "dL_dloss").reshape(1)
+    outs = [torch.empty_like(t) if n else None for t, n in zip((u, ux, wx, wxx, wt), need)]
+    if N > 0:
+        check(L.pigs_pde_ns_residual_backward(N, float(nu), float(dt), _ptr(u), _ptr(ux), _ptr(wx), _ptr(wxx), _ptr(wt),
+                                              _ptr(g_loss), *[_ptr(o) for o in outs], _stream()),
+              "pigs_pde_ns_residual_backward")
+    return tuple(outs)
+
+
+def vorticity_forward(x):
+    """x [..., 2, 2] (trailing axes: spatial axis, channel; C = 2) -> x[..., 0, 1] - x[..., 1, 0], shape x.shape[:-2]."""
+    L = _lib.lib()
+    x = _f32c(x, "x")
+    if x.dim() < 2 or x.shape[-1] != 2 or x.shape[-2] != 2:
+        raise RuntimeError("vorticity: trailing axes must be [2 (spatial), 2 (channels)]")
+    out = torch.empty(x.shape[:-2], dtype=torch.float32, device=x.device)
+    if out.numel() > 0:
+        check(L.pigs_vorticity_forward(out.numel(), _ptr(x), _ptr(out), _stream()), "pigs_vorticity_forward")
+    return out
+
+
+def vorticity_backward(g):
+    L = _lib.lib()
+    g = _f32c(g, "dL_dout")
+    d = torch.empty(tuple(g.shape) + (2, 2), dtype=torch.float32, device=g.device)
+    if g.numel() > 0:
+        check(L.pigs_vorticity_backward(g.numel(), _ptr(g), _ptr(d), _stream()), "pigs_vorticity_backward")
+    return d

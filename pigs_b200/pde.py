@@ -7,8 +7,15 @@ uxx[:,1,1]` the reference takes of its [N, D, D, C] Hessian):
 
     loss = pde_residual_loss(Problem.BURGERS, u, ux, lap, ut, dt, nu)     # 0-dim tensor, differentiable
 
+    model_pn.py:629-631  pde_rhs:   NAVIER_STOKES nu*(wxx00 + wxx11) - (u0*wx0 + u1*wx1)   (vorticity form)
+    model_pn.py:843-845  pde_loss += mean((ux[:,0,0] + ux[:,1,1])**2);  pde_loss += mean((wt - rhs)**2)
+    model_pn.py:779-781  w = ux[:,0,1] - ux[:,1,0];  wx = uxx[...,0,1] - uxx[...,1,0];  wxx = uxxx[...,0,1] - uxxx[...,1,0]
+
+    loss = navier_stokes_residual_loss(u, ux, wx, wxx, wt, dt, nu)       # 0-dim tensor, differentiable
+    w, wx, wxx = vorticity(ux), vorticity(uxx), vorticity(uxxx)          # differentiable
+
 A maintainer switches `compute_loss` to it by replacing the two lines above.  POISSON (its
-reference code reads an undefined `t`, model_pn.py:620) and NAVIER_STOKES (third derivatives) are left on torch.
+reference code reads an undefined `t`, model_pn.py:620) is left on torch.
 No CPU path: CUDA fp32 tensors only.
 """
 import enum
@@ -80,3 +87,46 @@ def pde_residual(problem, u, ux, lap, ut, dt, nu=0.0):
     loss, res = _C.pde_residual_forward(code, None if code == _C.PDE_DIFFUSION else u,
                                         ux if code == _C.PDE_BURGERS else None, lap, ut, nu, dt, want_residual=True)
     return res, loss
+
+
+class _NsResidualLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, u, ux, wx, wxx, wt, nu, dt):
+        loss, _, _ = _C.pde_ns_residual_forward(u, ux, wx, wxx, wt, nu, dt)
+        ctx.nu, ctx.dt = nu, dt
+        ctx.save_for_backward(u, ux, wx, wxx, wt)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        saved = ctx.saved_tensors
+        grads = _C.pde_ns_residual_backward(*saved, ctx.nu, ctx.dt, g, tuple(ctx.needs_input_grad[:5]))
+        return tuple(None if d is None else d.reshape(t.shape) for d, t in zip(grads, saved)) + (None, None)
+
+
+def navier_stokes_residual_loss(u, ux, wx, wxx, wt, dt, nu):
+    """mean((ux[:,0,0] + ux[:,1,1])**2) + mean((wt - dt * (nu*(wxx00 + wxx11) - (u0*wx0 + u1*wx1)))**2)
+    (model_pn.py:629-631, 824, 843-845).  u [N,2], ux [N,2,2], wx [N,2], wxx [N,2,2], wt [N]."""
+    return _NsResidualLoss.apply(u, ux, wx, wxx, wt, float(nu), float(dt))
+
+
+def navier_stokes_residual(u, ux, wx, wxx, wt, dt, nu):
+    """(no autograd) -> (residual wt - dt * rhs [N], divergence ux00 + ux11 [N], loss)."""
+    loss, res, div = _C.pde_ns_residual_forward(u, ux, wx, wxx, wt, nu, dt, want_residual=True)
+    return res, div, loss
+
+
+class _Vorticity(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        return _C.vorticity_forward(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return _C.vorticity_backward(g)
+
+
+def vorticity(x):
+    """x[..., 0, 1] - x[..., 1, 0] over the trailing (spatial axis, channel) axes of a C = 2 sampler output
+    (model_pn.py:779-781: ux -> w [N], uxx -> wx [N,2], uxxx -> wxx [N,2,2])."""
+    return _Vorticity.apply(x)

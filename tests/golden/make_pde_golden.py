@@ -46,6 +46,32 @@ def case(problem, seed, N, C, D, nu, dt):
     return {k: (v.detach().numpy().astype(np.float32) if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
 
 
+def ns_case(seed, N, nu, dt):
+    """NAVIER_STOKES the way Model.sample / compute_loss chain it (model_pn.py:772-781, 818, 824, 843-845): the
+    sampler's C = 2 outputs of two time levels -> vorticity terms -> pde_rhs -> the two loss terms."""
+    g = torch.Generator().manual_seed(seed)
+    P = model_pn.Problem
+    mk = lambda *sh: torch.randn(*sh, generator=g).requires_grad_(True)
+    u, ux, uxx, uxxx = mk(N, 2), mk(N, 2, 2), mk(N, 2, 2, 2), mk(N, 2, 2, 2, 2)
+    ux_prev = mk(N, 2, 2)
+    w, w_prev = ux[:, 0, 1] - ux[:, 1, 0], ux_prev[:, 0, 1] - ux_prev[:, 1, 0]      # model_pn.py:779
+    wx = uxx[..., 0, 1] - uxx[..., 1, 0]                                            # :780
+    wxx = uxxx[..., 0, 1] - uxxx[..., 1, 0]                                         # :781
+    for t in (wx, wxx):
+        t.retain_grad()
+    wt = (w - w_prev).detach().requires_grad_(True)                                 # :818 (a leaf here: d_wt is stored)
+    me = types.SimpleNamespace(problem=P.NAVIER_STOKES, nu=nu)
+    rhs = dt * model_pn.Model.pde_rhs(me, None, u, ux, uxx, wx, wxx)                # :824
+    loss = torch.mean((ux[:, 0, 0] + ux[:, 1, 1]) ** 2) + torch.mean((wt - rhs) ** 2)   # :843-845
+    up = torch.randn((), generator=g) + 2.0
+    (loss * up).backward()
+    out = dict(problem=np.int32(P.NAVIER_STOKES.value), nu=np.float32(nu), dt=np.float32(dt), u=u, ux=ux, uxx=uxx,
+               uxxx=uxxx, ux_prev=ux_prev, w=w, w_prev=w_prev, wx=wx, wxx=wxx, wt=wt, residual=(wt - rhs),
+               divergence=ux[:, 0, 0] + ux[:, 1, 1], loss=loss, up=up, d_u=u.grad, d_ux=ux.grad, d_wx=wx.grad,
+               d_wxx=wxx.grad, d_wt=wt.grad, d_uxx=uxx.grad, d_uxxx=uxxx.grad)
+    return {k: (v.detach().numpy().astype(np.float32) if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
+
+
 def main():
     P = model_pn.Problem
     cases = {
@@ -54,6 +80,8 @@ def main():
         "burgers": case(P.BURGERS, 3, 1025, 1, 2, 0.01 / np.pi, 0.01),
         "burgers_c2": case(P.BURGERS, 4, 777, 2, 2, 0.3, 0.25),
         "wave": case(P.WAVE, 5, 1025, 2, 2, 0.0, 0.02),
+        "navier_stokes": ns_case(6, 1025, 0.01, 0.02),
+        "navier_stokes_b": ns_case(7, 333, 0.5, 0.25),
     }
     flat = {}
     for name, d in cases.items():

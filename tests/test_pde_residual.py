@@ -36,6 +36,31 @@ def test_oracle_matches_reference_golden(name):
     assert rel_err(d_ux, c["d_ux"]) <= TOL
 
 
+NS_CASES = ("navier_stokes", "navier_stokes_b")
+
+
+@pytest.mark.parametrize("name", NS_CASES)
+def test_oracle_navier_stokes_matches_reference_golden(name):
+    """Vorticity extraction + NAVIER_STOKES residual / loss / gradients against the real model_pn chain
+    (model_pn.py:779-781 -> pde_rhs :629-631 -> :843-845)."""
+    c = _case(name)
+    nu, dt, up = float(c["nu"]), float(c["dt"]), float(c["up"])
+    np.testing.assert_array_equal(po.vorticity(c["ux"]), c["w"])
+    np.testing.assert_array_equal(po.vorticity(c["uxx"]), c["wx"])
+    np.testing.assert_array_equal(po.vorticity(c["uxxx"]), c["wxx"])
+    np.testing.assert_array_equal(po.vorticity(c["ux"]) - po.vorticity(c["ux_prev"]), c["wt"])
+    r, div, loss = po.ns_residual_loss(c["u"], c["ux"], c["wx"], c["wxx"], c["wt"], nu, dt)
+    assert rel_err(r, c["residual"]) <= TOL
+    assert rel_err(div, c["divergence"]) <= TOL
+    assert abs(loss - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    d_u, d_ux, d_wx, d_wxx, d_wt = po.ns_residual_backward(c["u"], c["ux"], c["wx"], c["wxx"], c["wt"], nu, dt, up)
+    for got, key in ((d_u, "d_u"), (d_ux, "d_ux"), (d_wx, "d_wx"), (d_wxx, "d_wxx"), (d_wt, "d_wt")):
+        assert rel_err(got, c[key]) <= TOL, key
+    # the reference's gradients w.r.t. the sampler outputs are the vorticity adjoint of those w.r.t. wx / wxx
+    assert rel_err(po.vorticity_backward(d_wx), c["d_uxx"]) <= TOL
+    assert rel_err(po.vorticity_backward(d_wxx), c["d_uxxx"]) <= TOL
+
+
 def test_problem_enum_matches_reference_values():
     from pigs_b200._C import PDE_BURGERS, PDE_DIFFUSION, PDE_WAVE  # import of the glue only; no library call
     from pigs_b200.pde import Problem
@@ -159,6 +184,73 @@ def test_residual_cuda_matches_oracle_and_golden(name):
         got = np.zeros(c[k].shape, np.float32) if got is None else got.cpu().numpy()
         assert rel_err(got, w) <= TOL, k
         assert rel_err(got, c["d_" + k]) <= TOL, k
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", NS_CASES)
+def test_navier_stokes_cuda_matches_oracle_and_golden(name):
+    """pigs_b200.pde.vorticity + navier_stokes_residual_loss (C ABI) chained like Model.sample / compute_loss, forward and
+    backward to the sampler's outputs, against the oracle and the goldens of the real model_pn chain."""
+    import torch
+
+    from pigs_b200 import pde
+    c = _case(name)
+    nu, dt, up = float(c["nu"]), float(c["dt"]), float(c["up"])
+    t = {k: torch.from_numpy(c[k]).cuda().requires_grad_(True) for k in ("u", "ux", "uxx", "uxxx", "wt")}
+    w, wx, wxx = pde.vorticity(t["ux"]), pde.vorticity(t["uxx"]), pde.vorticity(t["uxxx"])
+    np.testing.assert_array_equal(w.detach().cpu().numpy(), c["w"])        # one fp32 subtraction: bit-exact
+    np.testing.assert_array_equal(wx.detach().cpu().numpy(), c["wx"])
+    np.testing.assert_array_equal(wxx.detach().cpu().numpy(), c["wxx"])
+    loss = pde.navier_stokes_residual_loss(t["u"], t["ux"], wx, wxx, t["wt"], dt, nu)
+    r_want, div_want, loss_want = po.ns_residual_loss(c["u"], c["ux"], c["wx"], c["wxx"], c["wt"], nu, dt)
+    assert abs(float(loss.detach()) - loss_want) <= TOL * abs(loss_want)
+    assert abs(float(loss.detach()) - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    res, div, loss2 = pde.navier_stokes_residual(t["u"].detach(), t["ux"].detach(), wx.detach(), wxx.detach(),
+                                                 t["wt"].detach(), dt, nu)
+    assert float(loss2) == float(loss.detach())  # deterministic two-stage reduction
+    np.testing.assert_array_equal(res.cpu().numpy(), r_want)   # same fp32 operation order as the torch expressions
+    np.testing.assert_array_equal(div.cpu().numpy(), div_want)
+    assert rel_err(res.cpu().numpy(), c["residual"]) <= TOL
+    (loss * up).backward()
+    for k in ("u", "ux", "uxx", "uxxx", "wt"):
+        assert rel_err(t[k].grad.cpu().numpy(), c["d_" + k]) <= TOL, k
+    want = po.ns_residual_backward(c["u"], c["ux"], c["wx"], c["wxx"], c["wt"], nu, dt, up)
+    assert rel_err(t["u"].grad.cpu().numpy(), want[0]) <= TOL
+    assert rel_err(t["uxx"].grad.cpu().numpy(), po.vorticity_backward(want[2])) <= TOL
+    assert rel_err(t["uxxx"].grad.cpu().numpy(), po.vorticity_backward(want[3])) <= TOL
+
+
+@pytest.mark.gpu
+def test_navier_stokes_chain_through_sampler():
+    """Two-channel Gaussians -> u, grad u, Hessian, third derivative from the sampler -> vorticity terms -> fused
+    NAVIER_STOKES residual loss -> backward to means / values / conics, against the oracle chain."""
+    import torch
+
+    from pigs_b200 import pde
+    rec = synthetic(600, 4000, seed=21, C=2)
+    st = oracle_state(rec)
+    a = (rec["means"], rec["values"], rec["conics"], rec["samples"])
+    N = rec["samples"].shape[0]
+    nu, dt = 0.05, 0.1
+    wt = (0.1 * np.random.default_rng(4).normal(size=N)).astype(np.float32)
+    s, d = _sampler(rec)
+    u, ux, uxx, uxxx = (s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_gaussians_laplacian(),
+                        s.sample_gaussians_third_derivative())
+    loss = pde.navier_stokes_residual_loss(u, ux, pde.vorticity(uxx), pde.vorticity(uxxx), torch.from_numpy(wt).cuda(),
+                                           dt, nu)
+    loss.backward()
+    o = [po.forward(fn, st, *a) for fn in range(4)]
+    wxo, wxxo = po.vorticity(o[2]), po.vorticity(o[3])
+    _, _, loss_want = po.ns_residual_loss(o[0], o[1], wxo, wxxo, wt, nu, dt)
+    assert abs(float(loss.detach()) - loss_want) <= TOL * abs(loss_want)
+    g_u, g_ux, g_wx, g_wxx, _ = po.ns_residual_backward(o[0], o[1], wxo, wxxo, wt, nu, dt, 1.0)
+    ups = (g_u, g_ux, po.vorticity_backward(g_wx), po.vorticity_backward(g_wxx))
+    want = [np.zeros(rec[k].shape, np.float64) for k in ("means", "values", "conics")]
+    for fn, g in enumerate(ups):
+        for acc, p in zip(want, po.backward(fn, st, *a, g.astype(np.float32).reshape(o[fn].shape))):
+            acc += p.reshape(acc.shape)
+    for k, w in zip(("means", "values", "conics"), want):
+        assert rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w) <= 2 * TOL, k
 
 
 @pytest.mark.gpu
