@@ -231,6 +231,33 @@ int pigs_pde_ns_residual_forward(int64_t N, float nu, float dt, const float *u, 
 int pigs_pde_ns_residual_backward(int64_t N, float nu, float dt, const float *u, const float *ux, const float *wx,
                                   const float *wxx, const float *wt, const float *dL_dloss, float *dL_du, float *dL_dux,
                                   float *dL_dwx, float *dL_dwxx, float *dL_dwt, void *stream);
+/* Time integration fused into the residual (model_pn.py:794-811 TRAPEZOID / FORWARD / BACKWARD blends, :818-820 ut):
+ * the two time levels [-1] (suffix 1) and [-2] (suffix 0) of the sampler's outputs go in as they are and the kernels form
+ *   x = ts*x1 + (1 - ts)*x0  per sample (ts [N]; ts == NULL: the constant ts_const, 0 = FORWARD rule, 1 = BACKWARD rule)
+ *   ut = u1 - u0  (NAVIER_STOKES: wt = w1 - w0)
+ * themselves, fp32 operation by operation like the torch lines.  lap1 / lap0 are the traces (PIGS_FN_LAPL) of the two
+ * Hessians (blending commutes with the trace up to rounding).  backward: one gradient per time level and input; any
+ * output pointer may be NULL. */
+int pigs_pde_residual_timelevels_forward(int problem, int64_t N, int D, int C, float nu, float dt, const float *ts,
+                                         float ts_const, const float *u1, const float *u0, const float *ux1,
+                                         const float *ux0, const float *lap1, const float *lap0, float *residual,
+                                         float *loss, void *workspace, void *stream);
+int pigs_pde_residual_timelevels_backward(int problem, int64_t N, int D, int C, float nu, float dt, const float *ts,
+                                          float ts_const, const float *u1, const float *u0, const float *ux1,
+                                          const float *ux0, const float *lap1, const float *lap0, const float *dL_dloss,
+                                          float *dL_du1, float *dL_du0, float *dL_dux1, float *dL_dux0, float *dL_dlap1,
+                                          float *dL_dlap0, void *stream);
+int pigs_pde_ns_residual_timelevels_forward(int64_t N, float nu, float dt, const float *ts, float ts_const, const float *u1,
+                                            const float *u0, const float *ux1, const float *ux0, const float *wx1,
+                                            const float *wx0, const float *wxx1, const float *wxx0, const float *w1,
+                                            const float *w0, float *residual, float *divergence, float *loss,
+                                            void *workspace, void *stream);
+int pigs_pde_ns_residual_timelevels_backward(int64_t N, float nu, float dt, const float *ts, float ts_const, const float *u1,
+                                             const float *u0, const float *ux1, const float *ux0, const float *wx1,
+                                             const float *wx0, const float *wxx1, const float *wxx0, const float *w1,
+                                             const float *w0, const float *dL_dloss, float *dL_du1, float *dL_du0,
+                                             float *dL_dux1, float *dL_dux0, float *dL_dwx1, float *dL_dwx0, float *dL_dwxx1,
+                                             float *dL_dwxx0, float *dL_dw1, float *dL_dw0, void *stream);
 int pigs_vorticity_forward(int64_t groups, const float *in, float *out, void *stream);
 int pigs_vorticity_backward(int64_t groups, const float *dL_dout, float *dL_din, void *stream);
 

@@ -450,6 +450,61 @@ def ns_residual_backward(u, ux, wx, wxx, wt, nu, dt, g_loss):
     return -wx * drhs[:, None], d_ux, -u * drhs[:, None], d_wxx, dr
 
 
+def time_blend(ts, x1, x0):
+    """model_pn.py:795-805 TRAPEZOID `ts.reshape(-1,1,..) * x[-1] + (1 - ts.reshape(-1,1,..)) * x[-2]`, fp32 op by op;
+    a python number stands for the FORWARD (0 -> x[-2]) / BACKWARD (1 -> x[-1]) rules (:806-813)."""
+    x1, x0 = _f32(x1), _f32(x0)
+    if np.isscalar(ts):
+        return x1.copy() if float(ts) == 1.0 else x0.copy()
+    t = _f32(ts).reshape((-1,) + (1,) * (x1.ndim - 1))
+    return (t * x1 + (np.float32(1) - t) * x0).astype(np.float32)
+
+
+def _blend_adjoint(ts, g, ndim):
+    if np.isscalar(ts):
+        return (g, np.zeros_like(g)) if float(ts) == 1.0 else (np.zeros_like(g), g)
+    t = np.asarray(ts, np.float32).astype(np.float64).reshape((-1,) + (1,) * (ndim - 1))
+    return t * g, (np.float32(1) - np.asarray(ts, np.float32)).astype(np.float64).reshape(t.shape) * g
+
+
+def pde_residual_loss_timelevels(problem, ts, u, ux, lap, nu, dt):
+    """compute_loss with two time levels (model_pn.py:794-837): blended u / ux / lap into pde_rhs, ut = u[-1] - u[-2].
+    u, ux, lap: pairs (level [-1], level [-2]).  (The reference blends the Hessians and then takes the trace; blending
+    the traces differs by rounding only.)"""
+    ut = (_f32(u[0]) - _f32(u[1])).astype(np.float32)
+    us = time_blend(ts, *u)
+    uxs = None if ux is None else time_blend(ts, *ux)
+    return pde_residual_loss(problem, us, uxs, time_blend(ts, *lap), ut, nu, dt)
+
+
+def pde_residual_backward_timelevels(problem, ts, u, ux, lap, nu, dt, g_loss):
+    """-> (d_u1, d_u0, d_ux1, d_ux0, d_lap1, d_lap0), float64 (d_ux*: None when ux is None)."""
+    ut = (_f32(u[0]) - _f32(u[1])).astype(np.float32)
+    us = time_blend(ts, *u)
+    uxs = None if ux is None else time_blend(ts, *ux)
+    d_u, d_ux, d_lap, d_ut = pde_residual_backward(problem, us, uxs, time_blend(ts, *lap), ut, nu, dt, g_loss)
+    a, b = _blend_adjoint(ts, d_u, d_u.ndim)
+    la, lb = _blend_adjoint(ts, d_lap, d_lap.ndim)
+    xa, xb = (None, None) if d_ux is None else _blend_adjoint(ts, d_ux, d_ux.ndim)
+    return a + d_ut, b - d_ut, xa, xb, la, lb
+
+
+def ns_residual_loss_timelevels(ts, u, ux, wx, wxx, w, nu, dt):
+    wt = (_f32(w[0]) - _f32(w[1])).astype(np.float32)
+    return ns_residual_loss(time_blend(ts, *u), time_blend(ts, *ux), time_blend(ts, *wx), time_blend(ts, *wxx), wt, nu, dt)
+
+
+def ns_residual_backward_timelevels(ts, u, ux, wx, wxx, w, nu, dt, g_loss):
+    """-> gradients in the order (u1, u0, ux1, ux0, wx1, wx0, wxx1, wxx0, w1, w0), float64."""
+    wt = (_f32(w[0]) - _f32(w[1])).astype(np.float32)
+    gs = ns_residual_backward(time_blend(ts, *u), time_blend(ts, *ux), time_blend(ts, *wx), time_blend(ts, *wxx), wt,
+                              nu, dt, g_loss)
+    out = []
+    for g in gs[:4]:
+        out += list(_blend_adjoint(ts, g, g.ndim))
+    return tuple(out) + (gs[4], -gs[4])
+
+
 # ---- split / prune compaction (SURVEY.md 8f rank 4) ---------------------------------------------------
 def compact_plan(P, keep=None, extend=None, m=1):
     """Parent row of every output row: kept rows in order, then m rows per extended row (model_pn.py:598-605 cat order)."""

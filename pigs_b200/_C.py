@@ -453,6 +453,103 @@ def pde_ns_residual_backward(u, ux, wx, wxx, wt, nu, dt, g_loss, need=(True,) * 
     return tuple(outs)
 
 
+def _ts_args(ts, N):
+    """ts: [N] tensor (TRAPEZOID) or a python number (0 = FORWARD rule, 1 = BACKWARD rule) -> (tensor or None, constant)."""
+    if isinstance(ts, torch.Tensor):
+        ts = _f32c(ts, "time_samples")
+        if ts.numel() != N:
+            raise RuntimeError("time_samples must hold one value per sample")
+        return ts, 0.0
+    return None, float(ts)
+
+
+def _levels(name, cur, prev):
+    cur, prev = _f32c(cur, name + "[-1]"), _f32c(prev, name + "[-2]")
+    if cur.shape != prev.shape:
+        raise RuntimeError("the two time levels of %s must have the same shape" % name)
+    return cur, prev
+
+
+def pde_residual_timelevels_forward(problem, ts, u, ux, lap, nu, dt, want_residual=False):
+    """u, ux, lap: pairs (level [-1], level [-2]); ux may be None unless BURGERS.  -> (loss, residual or None)."""
+    L = _lib.lib()
+    u1, u0 = _levels("u", *u)
+    lap1, lap0 = _levels("lap", *lap)
+    ux1, ux0 = _levels("ux", *ux) if (ux is not None and problem == PDE_BURGERS) else (None, None)
+    N, D, C, _, _, _, _ = _pde_args(problem, u1, ux1, lap1, u0)
+    ts_t, ts_c = _ts_args(ts, N)
+    dev = lap1.device
+    loss = torch.zeros((), dtype=torch.float32, device=dev)
+    res = torch.empty_like(lap1) if want_residual else None
+    if N > 0:
+        ws = _bytes(max(int(L.pigs_pde_residual_workspace_bytes(N, C)), 16), dev)
+        check(L.pigs_pde_residual_timelevels_forward(problem, N, D, C, float(nu), float(dt), _ptr(ts_t), ts_c, _ptr(u1),
+                                                     _ptr(u0), _ptr(ux1), _ptr(ux0), _ptr(lap1), _ptr(lap0), _ptr(res),
+                                                     _ptr(loss), _ptr(ws), _stream()), "pigs_pde_residual_timelevels_forward")
+    return loss, res
+
+
+def pde_residual_timelevels_backward(problem, ts, u, ux, lap, nu, dt, g_loss, need=(True,) * 6):
+    """-> (dL_du1, dL_du0, dL_dux1, dL_dux0, dL_dlap1, dL_dlap0); None where not needed (ux: BURGERS only)."""
+    L = _lib.lib()
+    u1, u0 = _levels("u", *u)
+    lap1, lap0 = _levels("lap", *lap)
+    ux1, ux0 = _levels("ux", *ux) if (ux is not None and problem == PDE_BURGERS) else (None, None)
+    N, D, C, _, _, _, _ = _pde_args(problem, u1, ux1, lap1, u0)
+    ts_t, ts_c = _ts_args(ts, N)
+    g_loss = _f32c(g_loss, "dL_dloss").reshape(1)
+    like = (u1, u0, ux1, ux0, lap1, lap0)
+    outs = [torch.empty_like(t) if (n and t is not None) else None for t, n in zip(like, need)]
+    if N > 0:
+        check(L.pigs_pde_residual_timelevels_backward(problem, N, D, C, float(nu), float(dt), _ptr(ts_t), ts_c, _ptr(u1),
+                                                      _ptr(u0), _ptr(ux1), _ptr(ux0), _ptr(lap1), _ptr(lap0), _ptr(g_loss),
+                                                      *[_ptr(o) for o in outs], _stream()),
+              "pigs_pde_residual_timelevels_backward")
+    return tuple(outs)
+
+
+def _ns_levels(u, ux, wx, wxx, w):
+    cur = _ns_args(u[0], ux[0], wx[0], wxx[0], w[0])
+    prev = _ns_args(u[1], ux[1], wx[1], wxx[1], w[1])
+    if cur[0] != prev[0]:
+        raise RuntimeError("the two time levels must hold the same number of samples")
+    flat = []
+    for a, b in zip(cur[1:], prev[1:]):
+        flat += [a, b]
+    return cur[0], flat  # N, [u1, u0, ux1, ux0, wx1, wx0, wxx1, wxx0, w1, w0]
+
+
+def pde_ns_residual_timelevels_forward(ts, u, ux, wx, wxx, w, nu, dt, want_residual=False):
+    """u, ux, wx, wxx, w: pairs (level [-1], level [-2]).  -> (loss, residual [N] or None, divergence [N] or None)."""
+    L = _lib.lib()
+    N, flat = _ns_levels(u, ux, wx, wxx, w)
+    ts_t, ts_c = _ts_args(ts, N)
+    dev = flat[0].device
+    loss = torch.zeros((), dtype=torch.float32, device=dev)
+    res = torch.empty(N, dtype=torch.float32, device=dev) if want_residual else None
+    div = torch.empty(N, dtype=torch.float32, device=dev) if want_residual else None
+    if N > 0:
+        ws = _bytes(max(int(L.pigs_pde_residual_workspace_bytes(N, 2)), 16), dev)
+        check(L.pigs_pde_ns_residual_timelevels_forward(N, float(nu), float(dt), _ptr(ts_t), ts_c, *[_ptr(t) for t in flat],
+                                                        _ptr(res), _ptr(div), _ptr(loss), _ptr(ws), _stream()),
+              "pigs_pde_ns_residual_timelevels_forward")
+    return loss, res, div
+
+
+def pde_ns_residual_timelevels_backward(ts, u, ux, wx, wxx, w, nu, dt, g_loss, need=(True,) * 10):
+    """-> gradients in the order (u1, u0, ux1, ux0, wx1, wx0, wxx1, wxx0, w1, w0), None where not needed."""
+    L = _lib.lib()
+    N, flat = _ns_levels(u, ux, wx, wxx, w)
+    ts_t, ts_c = _ts_args(ts, N)
+    g_loss = _f32c(g_loss, "dL_dloss").reshape(1)
+    outs = [torch.empty_like(t) if n else None for t, n in zip(flat, need)]
+    if N > 0:
+        check(L.pigs_pde_ns_residual_timelevels_backward(N, float(nu), float(dt), _ptr(ts_t), ts_c, *[_ptr(t) for t in flat],
+                                                         _ptr(g_loss), *[_ptr(o) for o in outs], _stream()),
+              "pigs_pde_ns_residual_timelevels_backward")
+    return tuple(outs)
+
+
 def vorticity_forward(x):
     """x [..., 2, 2] (trailing axes: spatial axis, channel; C = 2) -> x[..., 0, 1] - x[..., 1, 0], shape x.shape[:-2]."""
     L = _lib.lib()

@@ -79,6 +79,14 @@ SIGNATURES = {
     "pigs_pde_residual_backward": (c_int, [c_int, c_int64, c_int, c_int, ctypes.c_float, ctypes.c_float] + [c_void_p] * 10),
     "pigs_pde_ns_residual_forward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float] + [c_void_p] * 10),
     "pigs_pde_ns_residual_backward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float] + [c_void_p] * 12),
+    "pigs_pde_residual_timelevels_forward": (c_int, [c_int, c_int64, c_int, c_int, ctypes.c_float, ctypes.c_float, c_void_p,
+                                                     ctypes.c_float] + [c_void_p] * 10),
+    "pigs_pde_residual_timelevels_backward": (c_int, [c_int, c_int64, c_int, c_int, ctypes.c_float, ctypes.c_float, c_void_p,
+                                                      ctypes.c_float] + [c_void_p] * 14),
+    "pigs_pde_ns_residual_timelevels_forward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float, c_void_p, ctypes.c_float]
+                                                + [c_void_p] * 15),
+    "pigs_pde_ns_residual_timelevels_backward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float, c_void_p, ctypes.c_float]
+                                                 + [c_void_p] * 22),
     "pigs_vorticity_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p]),
     "pigs_vorticity_backward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p]),
     "pigs_compact_workspace_bytes": (c_size_t, [c_int64]),

@@ -14,6 +14,12 @@ uxx[:,1,1]` the reference takes of its [N, D, D, C] Hessian):
     loss = navier_stokes_residual_loss(u, ux, wx, wxx, wt, dt, nu)       # 0-dim tensor, differentiable
     w, wx, wxx = vorticity(ux), vorticity(uxx), vorticity(uxxx)          # differentiable
 
+    model_pn.py:794-811  TRAPEZOID x = ts*x[-1] + (1-ts)*x[-2] | FORWARD x[-2] | BACKWARD x[-1];  :820 ut = u[-1] - u[-2]
+
+    loss = pde_residual_loss_timelevels(problem, time_samples, (u[-1], u[-2]), (ux[-1], ux[-2]), (lap[-1], lap[-2]), dt, nu)
+    loss = navier_stokes_residual_loss_timelevels(time_samples, (u..), (ux..), (wx..), (wxx..), (w[-1], w[-2]), dt, nu)
+    # time_samples: [N] tensor (TRAPEZOID) or 0.0 (FORWARD rule) / 1.0 (BACKWARD rule); the blends happen inside the kernel
+
 A maintainer switches `compute_loss` to it by replacing the two lines above.  POISSON (its
 reference code reads an undefined `t`, model_pn.py:620) is left on torch.
 No CPU path: CUDA fp32 tensors only.
@@ -130,3 +136,58 @@ def vorticity(x):
     """x[..., 0, 1] - x[..., 1, 0] over the trailing (spatial axis, channel) axes of a C = 2 sampler output
     (model_pn.py:779-781: ux -> w [N], uxx -> wx [N,2], uxxx -> wxx [N,2,2])."""
     return _Vorticity.apply(x)
+
+
+class _ResidualLossLevels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, code, ts, nu, dt, u1, u0, ux1, ux0, lap1, lap0):
+        ux = None if ux1 is None else (ux1, ux0)
+        loss, _ = _C.pde_residual_timelevels_forward(code, ts, (u1, u0), ux, (lap1, lap0), nu, dt)
+        ctx.code, ctx.ts, ctx.nu, ctx.dt, ctx.has_ux = code, ts, nu, dt, ux is not None
+        ctx.save_for_backward(*[t for t in (u1, u0, ux1, ux0, lap1, lap0) if t is not None])
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        it = iter(ctx.saved_tensors)
+        u1, u0 = next(it), next(it)
+        ux1, ux0 = (next(it), next(it)) if ctx.has_ux else (None, None)
+        lap1, lap0 = next(it), next(it)
+        ux = (ux1, ux0) if ctx.has_ux else None
+        grads = _C.pde_residual_timelevels_backward(ctx.code, ctx.ts, (u1, u0), ux, (lap1, lap0), ctx.nu, ctx.dt, g,
+                                                    tuple(ctx.needs_input_grad[4:10]))
+        like = (u1, u0, ux1, ux0, lap1, lap0)
+        return (None,) * 4 + tuple(None if d is None else d.reshape(t.shape) for d, t in zip(grads, like))
+
+
+def pde_residual_loss_timelevels(problem, time_samples, u, ux, lap, dt, nu=0.0):
+    """compute_loss's chain with the time integration inside the kernel (model_pn.py:794-837): u, ux, lap are pairs
+    (level [-1], level [-2]) of the sampler's outputs (lap = `sample_laplacian()`), time_samples a [N] tensor
+    (TRAPEZOID) or 0.0 / 1.0 (FORWARD / BACKWARD rule).  ux may be None unless BURGERS.  time_samples gets no gradient."""
+    code = _code(problem)
+    ux1, ux0 = ux if (ux is not None and code == _C.PDE_BURGERS) else (None, None)
+    return _ResidualLossLevels.apply(code, time_samples, float(nu), float(dt), u[0], u[1], ux1, ux0, lap[0], lap[1])
+
+
+class _NsResidualLossLevels(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, ts, nu, dt, *levels):  # levels: u1, u0, ux1, ux0, wx1, wx0, wxx1, wxx0, w1, w0
+        pairs = [levels[i:i + 2] for i in range(0, 10, 2)]
+        loss, _, _ = _C.pde_ns_residual_timelevels_forward(ts, *pairs, nu, dt)
+        ctx.ts, ctx.nu, ctx.dt = ts, nu, dt
+        ctx.save_for_backward(*levels)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        levels = ctx.saved_tensors
+        pairs = [levels[i:i + 2] for i in range(0, 10, 2)]
+        grads = _C.pde_ns_residual_timelevels_backward(ctx.ts, *pairs, ctx.nu, ctx.dt, g, tuple(ctx.needs_input_grad[3:13]))
+        return (None,) * 3 + tuple(None if d is None else d.reshape(t.shape) for d, t in zip(grads, levels))
+
+
+def navier_stokes_residual_loss_timelevels(time_samples, u, ux, wx, wxx, w, dt, nu):
+    """NAVIER_STOKES with the time integration inside the kernel (model_pn.py:794-805, 818, 824, 843-845): every argument
+    a pair (level [-1], level [-2]); w = vorticity(ux) of each level (wt = w[-1] - w[-2] is formed in the kernel)."""
+    return _NsResidualLossLevels.apply(time_samples, float(nu), float(dt), u[0], u[1], ux[0], ux[1], wx[0], wx[1],
+                                       wxx[0], wxx[1], w[0], w[1])

@@ -61,6 +61,45 @@ def test_oracle_navier_stokes_matches_reference_golden(name):
     assert rel_err(po.vorticity_backward(d_wxx), c["d_uxxx"]) <= TOL
 
 
+LEVEL_CASES = ("levels_diffusion", "levels_burgers", "levels_burgers_c2", "levels_burgers_forward",
+               "levels_burgers_backward", "levels_wave")
+LEVEL_KEYS = ("u1", "u0", "ux1", "ux0", "lap1", "lap0")
+
+
+def _ts_of(c):
+    rule = int(c["rule"])  # 2 = TRAPEZOID (per-sample ts), 0 = FORWARD (x[-2]), 1 = BACKWARD (x[-1])
+    return c["ts"] if rule == 2 else float(rule)
+
+
+@pytest.mark.parametrize("name", LEVEL_CASES)
+def test_oracle_timelevels_match_reference_golden(name):
+    """compute_loss's blend -> ut -> dt * pde_rhs -> loss chain (model_pn.py:794-837) with the real pde_rhs + autograd."""
+    c = _case(name)
+    prob, nu, dt, up, ts = int(c["problem"]), float(c["nu"]), float(c["dt"]), float(c["up"]), _ts_of(c)
+    u, ux, lap = (c["u1"], c["u0"]), (c["ux1"], c["ux0"]), (c["lap1"], c["lap0"])
+    r, loss = po.pde_residual_loss_timelevels(prob, ts, u, ux, lap, nu, dt)
+    assert rel_err(r, c["residual"]) <= TOL
+    assert abs(loss - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    grads = po.pde_residual_backward_timelevels(prob, ts, u, ux, lap, nu, dt, up)
+    for got, key in zip(grads, LEVEL_KEYS):
+        assert rel_err(got, c["d_" + key]) <= TOL, key
+
+
+NS_LEVEL_KEYS = ("u1", "u0", "ux1", "ux0", "wx1", "wx0", "wxx1", "wxx0", "w1", "w0")
+
+
+def test_oracle_navier_stokes_timelevels_match_reference_golden():
+    c = _case("levels_navier_stokes")
+    nu, dt, up = float(c["nu"]), float(c["dt"]), float(c["up"])
+    pairs = [(c[NS_LEVEL_KEYS[i]], c[NS_LEVEL_KEYS[i + 1]]) for i in range(0, 10, 2)]
+    r, div, loss = po.ns_residual_loss_timelevels(c["ts"], *pairs, nu, dt)
+    np.testing.assert_array_equal(r, c["residual"])      # same fp32 operation order as the torch lines
+    np.testing.assert_array_equal(div, c["divergence"])
+    assert abs(loss - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    for got, key in zip(po.ns_residual_backward_timelevels(c["ts"], *pairs, nu, dt, up), NS_LEVEL_KEYS):
+        assert rel_err(got, c["d_" + key]) <= TOL, key
+
+
 def test_problem_enum_matches_reference_values():
     from pigs_b200._C import PDE_BURGERS, PDE_DIFFUSION, PDE_WAVE  # import of the glue only; no library call
     from pigs_b200.pde import Problem
@@ -218,6 +257,63 @@ def test_navier_stokes_cuda_matches_oracle_and_golden(name):
     assert rel_err(t["u"].grad.cpu().numpy(), want[0]) <= TOL
     assert rel_err(t["uxx"].grad.cpu().numpy(), po.vorticity_backward(want[2])) <= TOL
     assert rel_err(t["uxxx"].grad.cpu().numpy(), po.vorticity_backward(want[3])) <= TOL
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", LEVEL_CASES)
+def test_timelevels_cuda_matches_oracle_and_golden(name):
+    """Time integration inside the residual kernels (pigs_pde_residual_timelevels_*) against the oracle and the goldens of
+    the real compute_loss chain, all three integration rules."""
+    import torch
+
+    from pigs_b200 import pde
+    c = _case(name)
+    prob, nu, dt, up, ts = int(c["problem"]), float(c["nu"]), float(c["dt"]), float(c["up"]), _ts_of(c)
+    t = {k: torch.from_numpy(c[k]).cuda().requires_grad_(True) for k in LEVEL_KEYS}
+    ts_dev = torch.from_numpy(ts).cuda() if isinstance(ts, np.ndarray) else ts
+    loss = pde.pde_residual_loss_timelevels(pde.Problem(prob), ts_dev, (t["u1"], t["u0"]), (t["ux1"], t["ux0"]),
+                                            (t["lap1"], t["lap0"]), dt, nu)
+    u, ux, lap = (c["u1"], c["u0"]), (c["ux1"], c["ux0"]), (c["lap1"], c["lap0"])
+    _, loss_want = po.pde_residual_loss_timelevels(prob, ts, u, ux, lap, nu, dt)
+    assert abs(float(loss.detach()) - loss_want) <= TOL * abs(loss_want)
+    assert abs(float(loss.detach()) - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    (loss * up).backward()
+    want = po.pde_residual_backward_timelevels(prob, ts, u, ux, lap, nu, dt, up)
+    for k, w in zip(LEVEL_KEYS, want):
+        got = t[k].grad
+        got = np.zeros(c[k].shape, np.float32) if got is None else got.cpu().numpy()
+        assert rel_err(got, w) <= TOL, k
+        assert rel_err(got, c["d_" + k]) <= TOL, k
+    # the [N, C] residual itself
+    from pigs_b200 import _C
+    _, res = _C.pde_residual_timelevels_forward(prob, ts_dev, (t["u1"].detach(), t["u0"].detach()),
+                                                (t["ux1"].detach(), t["ux0"].detach()),
+                                                (t["lap1"].detach(), t["lap0"].detach()), nu, dt, want_residual=True)
+    assert rel_err(res.cpu().numpy(), c["residual"]) <= TOL
+
+
+@pytest.mark.gpu
+def test_navier_stokes_timelevels_cuda_matches_oracle_and_golden():
+    import torch
+
+    from pigs_b200 import _C, pde
+    c = _case("levels_navier_stokes")
+    nu, dt, up = float(c["nu"]), float(c["dt"]), float(c["up"])
+    t = {k: torch.from_numpy(c[k]).cuda().requires_grad_(True) for k in NS_LEVEL_KEYS}
+    ts = torch.from_numpy(c["ts"]).cuda()
+    pairs = [(t[NS_LEVEL_KEYS[i]], t[NS_LEVEL_KEYS[i + 1]]) for i in range(0, 10, 2)]
+    loss = pde.navier_stokes_residual_loss_timelevels(ts, *pairs, dt, nu)
+    assert abs(float(loss.detach()) - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    _, res, div = _C.pde_ns_residual_timelevels_forward(ts, *[(a.detach(), b.detach()) for a, b in pairs], nu, dt,
+                                                        want_residual=True)
+    np.testing.assert_array_equal(res.cpu().numpy(), c["residual"])     # fp32 op order of the torch lines
+    np.testing.assert_array_equal(div.cpu().numpy(), c["divergence"])
+    (loss * up).backward()
+    np_pairs = [(c[NS_LEVEL_KEYS[i]], c[NS_LEVEL_KEYS[i + 1]]) for i in range(0, 10, 2)]
+    want = po.ns_residual_backward_timelevels(c["ts"], *np_pairs, nu, dt, up)
+    for k, w in zip(NS_LEVEL_KEYS, want):
+        assert rel_err(t[k].grad.cpu().numpy(), w) <= TOL, k
+        assert rel_err(t[k].grad.cpu().numpy(), c["d_" + k]) <= TOL, k
 
 
 @pytest.mark.gpu

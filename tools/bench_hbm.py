@@ -89,6 +89,25 @@ def main():
     ms = timed(lambda: _C.build_covariances_backward(sc, tr, gc, gk))
     out["rows"].append(row("cov_backward_kernel", ms, 48 * P, "36 B read + 12 B written per Gaussian"))
 
+    # ---- PDE residual loss kernels at N = 4M samples (model_pn.py:612-631, 822-845) ----
+    g1 = torch.ones((), device="cuda")
+    u1, ux1, lap1, ut1 = (torch.randn(N, 1, device="cuda"), torch.randn(N, 2, 1, device="cuda"),
+                          torch.randn(N, 1, device="cuda"), torch.randn(N, 1, device="cuda"))
+    ms = timed(lambda: _C.pde_residual_forward(_C.PDE_BURGERS, u1, ux1, lap1, ut1, 0.01, 0.01))
+    out["rows"].append(row("residual_forward_kernel + finish (BURGERS, C=1)", ms, 16 * N, "16 B read per sample (u, ux0, lap, ut)"))
+    ms = timed(lambda: _C.pde_residual_backward(_C.PDE_BURGERS, u1, ux1, lap1, ut1, 0.01, 0.01, g1))
+    out["rows"].append(row("residual_backward_kernel (BURGERS, C=1)", ms, 36 * N, "16 B read + 20 B written per sample (d_u, d_ux[2], d_lap, d_ut)"))
+    u2, ux2, wx2, wxx2, wt2 = (torch.randn(N, 2, device="cuda"), torch.randn(N, 2, 2, device="cuda"),
+                               torch.randn(N, 2, device="cuda"), torch.randn(N, 2, 2, device="cuda"), torch.randn(N, device="cuda"))
+    ms = timed(lambda: _C.pde_ns_residual_forward(u2, ux2, wx2, wxx2, wt2, 0.01, 0.01))
+    out["rows"].append(row("ns_residual_forward_kernel + finish (NAVIER_STOKES)", ms, 52 * N, "52 B read per sample (u 8, ux 16, wx 8, wxx 16, wt 4)"))
+    ms = timed(lambda: _C.pde_ns_residual_backward(u2, ux2, wx2, wxx2, wt2, 0.01, 0.01, g1))
+    out["rows"].append(row("ns_residual_backward_kernel (NAVIER_STOKES)", ms, 104 * N, "52 B read + 52 B written per sample"))
+    uxxx2 = torch.randn(N, 2, 2, 2, 2, device="cuda")
+    ms = timed(lambda: _C.vorticity_forward(uxxx2))
+    out["rows"].append(row("vorticity_forward_kernel (uxxx -> wxx)", ms, 80 * N, "4 groups per sample: 16 B read + 4 B written each"))
+    del u1, ux1, lap1, ut1, u2, ux2, wx2, wxx2, wt2, uxxx2
+
     # ---- aggregation on a 16-regular CSR (C5 i): L = K = 16, E = 25, nF = 6 ----
     k = 16
     idx, rng = regular_csr(rec["means"], k)
