@@ -14,6 +14,10 @@
 // DRAM traffic against 2.7 GB algorithmic at P = 1M, 16 neighbours).
 #include "common.cuh"
 
+#ifndef A16_VEC_RED
+#define A16_VEC_RED 1
+#endif
+
 namespace pigs {
 
 constexpr int A16_THREADS = 256;
@@ -214,6 +218,16 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
         for (int a = 0; a < 16; a++) st[a] = __shfl_sync(0xffffffffu, st_l, a, 16);
         const float inv = valid ? inv_total[row] : 0.0f;
         float wz = 0.0f, gq = 0.0f;
+#if A16_VEC_RED
+        // scatter layout of the half-warp: lane = (neighbour t mod 4 -> tq, channel quad cq); one 16-byte vector RED
+        // per (neighbour, quad) instead of four scalar ones (sm_90+: red.global.add.v4.f32)
+        const int cq = gl & 3, tq = gl >> 2;
+        float4 sv, qv;
+        sv.x = __shfl_sync(0xffffffffu, st_l, 4 * cq + 0, 16), sv.y = __shfl_sync(0xffffffffu, st_l, 4 * cq + 1, 16);
+        sv.z = __shfl_sync(0xffffffffu, st_l, 4 * cq + 2, 16), sv.w = __shfl_sync(0xffffffffu, st_l, 4 * cq + 3, 16);
+        qv.x = __shfl_sync(0xffffffffu, q_l, 4 * cq + 0, 16), qv.y = __shfl_sync(0xffffffffu, q_l, 4 * cq + 1, 16);
+        qv.z = __shfl_sync(0xffffffffu, q_l, 4 * cq + 2, 16), qv.w = __shfl_sync(0xffffffffu, q_l, 4 * cq + 3, 16);
+#endif
         for (int c0 = 0; c0 < nmax; c0 += 16) {
             const int64_t s = start + c0 + gl;
             const int64_t j = (c0 + gl < n) ? indices[s] : -1;
@@ -254,20 +268,42 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
                 c_bias[1] += dB;
             }
             const int jl = (int)j;
+#if A16_VEC_RED
+#pragma unroll
+            for (int it = 0; it < 4; it++) {
+                const int t = 4 * it + tq;
+                const int jj = __shfl_sync(0xffffffffu, jl, t, 16);
+                const float t_te = __shfl_sync(0xffffffffu, te, t, 16);
+                const float t_c1 = __shfl_sync(0xffffffffu, c1, t, 16);
+                if (jj >= 0) {
+                    const size_t o = (size_t)jj * 16 + 4 * cq;
+                    atomicAdd(reinterpret_cast<float4*>(g_features + o),
+                              make_float4(t_c1 * sv.x, t_c1 * sv.y, t_c1 * sv.z, t_c1 * sv.w));
+                    atomicAdd(reinterpret_cast<float4*>(g_keys + o),
+                              make_float4(qv.x * t_te, qv.y * t_te, qv.z * t_te, qv.w * t_te));
+                }
+            }
+#endif
 #pragma unroll
             for (int t = 0; t < 16; t++) {
                 const int jj = __shfl_sync(0xffffffffu, jl, t, 16);
                 const float t_te = __shfl_sync(0xffffffffu, te, t, 16);
+#if !A16_VEC_RED
                 const float t_c1 = __shfl_sync(0xffffffffu, c1, t, 16);
+#endif
                 const float t_w = __shfl_sync(0xffffffffu, wgt, t, 16);
                 const float t_dce = __shfl_sync(0xffffffffu, dce, t, 16);
                 const float t_dcf = __shfl_sync(0xffffffffu, dcf, t, 16);
                 if (jj >= 0) {
                     const size_t o = (size_t)jj * 16 + gl;
+#if !A16_VEC_RED
                     atomicAdd(g_features + o, t_c1 * st_l);
+#endif
                     wz = fmaf(t_w, fmaf(t_dcf, features[o], t_dce), wz);
                     gq = fmaf(keys[o], t_te, gq);
+#if !A16_VEC_RED
                     atomicAdd(g_keys + o, q_l * t_te);
+#endif
                 }
             }
         }
