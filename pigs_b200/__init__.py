@@ -266,6 +266,27 @@ class GaussianSampler:
         fused plan (the two share an output slot); asking for both simply runs them unfused."""
         return self._request(FN_LAPL)
 
+    def pair_weights(self):
+        """(extension) per-sample size of the reference pair set: the number of Gaussians binned to the sample's tile,
+        int64 [N] (sums to pair_count()).  Used to cut sample shards of equal WORK (sharded.balanced_ranges)."""
+        ranges, sample_ranges = self._sample_state[3], self._sample_state[4]
+        N = self.samples.shape[0]
+        b = ranges.numel() // 8 - 1
+        w = torch.zeros(N, dtype=torch.int64, device=ranges.device)
+        if b <= 0 or N == 0:
+            return w
+        g = ranges.view(torch.int32)[: 2 * b].view(b, 2).to(torch.int64)
+        sr = sample_ranges.view(torch.int32)[: 2 * b].view(b, 2).to(torch.int64)
+        _, _, sl = _C.point_lists(self.num_rendered, self.binning_buffer, self.sample_binning_buffer, N)
+        # sample_point_list is tile-major: tile t owns positions [sr[t,0], sr[t,1])
+        per_pos = torch.zeros(N, dtype=torch.int64, device=ranges.device)
+        ns = sr[:, 1] - sr[:, 0]
+        starts = sr[:, 0]
+        pos = torch.repeat_interleave(starts - torch.cumsum(ns, 0) + ns, ns) + torch.arange(int(ns.sum()), device=ns.device)
+        per_pos[pos] = torch.repeat_interleave(g[:, 1] - g[:, 0], ns)
+        w[sl.to(torch.int64)] = per_pos
+        return w
+
     def pair_count(self):
         """(extension) size of the reference pair set: sum over tiles of n_samples(tile) * n_gaussians(tile)."""
         ranges, sample_ranges = self._sample_state[3], self._sample_state[4]

@@ -20,6 +20,27 @@ def shard_range(N, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def balanced_ranges(weights, world):
+    """Contiguous split of len(weights) rows into `world` windows of (nearly) equal total weight -> [(lo, hi)] * world.
+    With weights = GaussianSampler.pair_weights() of a pass over ALL samples this equalises the evaluation work per rank
+    where an even split does not (model_pn.py lays its Gaussians out as a grid, so a contiguous range of the means is a
+    band of the domain and the bands differ in pairs per sample).  Deterministic, so every rank computes the same cuts."""
+    w = weights.reshape(-1).to(torch.float64)
+    n, world = w.numel(), int(world)
+    if n == 0:
+        return [(0, 0)] * world
+    cum = torch.cumsum(w, 0)
+    total = float(cum[-1])
+    if total <= 0.0:
+        return [shard_range(n, r, world) for r in range(world)]
+    targets = torch.arange(1, world, dtype=torch.float64, device=w.device) * (total / world)
+    cuts = torch.searchsorted(cum, targets, right=False).clamp_(0, n).tolist() if world > 1 else []
+    edges = [0] + [int(c) for c in cuts] + [n]
+    for i in range(1, len(edges)):  # monotone
+        edges[i] = max(edges[i], edges[i - 1])
+    return [(edges[r], edges[r + 1]) for r in range(world)]
+
+
 def allreduce_bounds(mm, D, group=None):
     """mm = float32[2*D] {min[0..D), max[0..D)} of the local samples -> global bounds, in place, one collective
     (MAX over {-min, max})."""
@@ -98,11 +119,12 @@ class ShardedGaussianSampler(GaussianSampler):
             return 0, 1
         return dist.get_rank(self.group), dist.get_world_size(self.group)
 
-    def preprocess_aggregate(self):
+    def preprocess_aggregate(self, row_range=None):
         """Neighbour lists of this rank's contiguous range of query Gaussians (every Gaussian stays a candidate
-        neighbour); the other rows are empty.  1/world of the CSR per GPU."""
+        neighbour); the other rows are empty.  1/world of the CSR per GPU.  row_range = (lo, hi) overrides the even
+        split, e.g. with this rank's window of balanced_ranges()."""
         rank, world = self._rank_world()
-        self.row_range = shard_range(self.means.size(0), rank, world)
+        self.row_range = shard_range(self.means.size(0), rank, world) if row_range is None else tuple(row_range)
         (self.indices, self.ranges, self.dists, self.densities,
          self.inv_total_densities) = _C.preprocess_aggregate(self.means, self.conics, self.radii, self.debug,
                                                              rows=self.row_range)

@@ -140,3 +140,35 @@ def test_two_gpu_row_sharded_aggregation_matches_oracle(tmp_path):
             assert rel_err(p["grad_" + key], wv) <= TOL, key
     for key in ["out"] + ["grad_" + k for k in AGG_KEYS]:
         np.testing.assert_array_equal(parts[0][key], parts[1][key])
+
+
+@pytest.mark.gpu
+def test_pair_weights_match_oracle_and_balance_bands():
+    """GaussianSampler.pair_weights(): per-sample pair counts equal the oracle's (Gaussians binned to the sample's tile),
+    and windows cut from them carry equal work where an even split of grid-ordered means does not."""
+    import numpy as np
+    import torch
+
+    from oracle import pigs_oracle as po
+    from pigs_b200 import GaussianSampler
+    from pigs_b200.sharded import balanced_ranges, shard_range
+    from tests.fixtures import synthetic
+    rec = synthetic(20000, 16, seed=3)
+    rec["samples"] = rec["means"].copy()                      # model_pn.py:648: the means are the samples
+    st = po.preprocess(rec["means"], rec["covariances"], rec["samples"])
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    s = GaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    w = s.pair_weights()
+    assert int(w.sum()) == s.pair_count()
+    blocks = st["blocks"]
+    ng = (st["ranges"][:blocks, 1].astype(np.int64) - st["ranges"][:blocks, 0].astype(np.int64))
+    want = np.zeros(rec["samples"].shape[0], np.int64)
+    for t in range(blocks):
+        a, b = int(st["sample_ranges"][t, 0]), int(st["sample_ranges"][t, 1])
+        want[st["sample_list"][a:b].astype(np.int64)] = ng[t]
+    np.testing.assert_array_equal(w.cpu().numpy(), want)
+    world = 8
+    bal = [int(w[lo:hi].sum()) for lo, hi in balanced_ranges(w, world)]
+    even = [int(w[slice(*shard_range(w.numel(), r, world))].sum()) for r in range(world)]
+    assert max(bal) <= max(even) and max(bal) - min(bal) <= 2 * int(w.max())

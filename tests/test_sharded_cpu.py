@@ -163,3 +163,25 @@ def test_two_rank_row_sharded_aggregation_matches_single_process(tmp_path):
             assert rel_err(p["grad_" + key], wv) <= TOL, key
     for key in ["out"] + ["grad_" + k for k in AGG_KEYS]:
         np.testing.assert_array_equal(parts[0][key], parts[1][key])
+
+
+def test_balanced_ranges_equalise_weight():
+    """sharded.balanced_ranges: contiguous windows of equal total weight (host logic, torch on CPU)."""
+    import torch
+
+    from pigs_b200.sharded import balanced_ranges, shard_range
+    g = torch.Generator().manual_seed(0)
+    w = torch.cat([torch.full((4000,), 10), torch.full((6000,), 30), torch.randint(5, 50, (5000,), generator=g)])
+    for world in (1, 2, 3, 8):
+        rs = balanced_ranges(w, world)
+        assert rs[0][0] == 0 and rs[-1][1] == w.numel() and len(rs) == world
+        assert all(rs[i][1] == rs[i + 1][0] for i in range(world - 1))
+        sums = [int(w[lo:hi].sum()) for lo, hi in rs]
+        assert max(sums) - min(sums) <= 2 * int(w.max())          # equal up to one row either side
+        even = [int(w[slice(*shard_range(w.numel(), r, world))].sum()) for r in range(world)]
+        assert max(sums) <= max(even)
+    assert balanced_ranges(torch.zeros(10), 4) == [shard_range(10, r, 4) for r in range(4)]   # no weight: even split
+    assert balanced_ranges(torch.zeros(0), 3) == [(0, 0)] * 3
+    heavy = torch.tensor([1.0, 1.0, 100.0, 1.0])
+    rs = balanced_ranges(heavy, 3)
+    assert rs[0][0] == 0 and rs[-1][1] == 4 and all(lo <= hi for lo, hi in rs)
