@@ -261,6 +261,20 @@ int pigs_pde_ns_residual_timelevels_backward(int64_t N, float nu, float dt, cons
 int pigs_vorticity_forward(int64_t groups, const float *in, float *out, void *stream);
 int pigs_vorticity_backward(int64_t groups, const float *dL_dout, float *dL_din, void *stream);
 
+/* ---- dense all-pairs path -----------------------------------------------------
+ * gaussians.py:48-58 `sample_gaussians`, :89-101 `gaussian_derivative`, :103-116 `gaussian_derivative2`: every Gaussian
+ * against every sample, x = sample - mean, FULL conics [n, D, D] (not assumed symmetric), no tile cutoff, no torus
+ * wrap — the pure-PyTorch path of the reference's CPU drivers, without its [N, n, d, ...] broadcast tensors.
+ * fn_mask: PIGS_FN_VALUE | PIGS_FN_DERIV | PIGS_FN_HESS (any subset, one launch).  Outputs u [N,C], ux [N,D,C],
+ * uxx [N,D,D,C]; D in {1,2}, C <= 4.  backward = torch.autograd of those functions: dL_dmeans [n,D], dL_dconics
+ * [n,D,D], dL_dvalues [n,C] (fully written; the dL_d<out> of functions not in fn_mask may be NULL). */
+int pigs_dense_forward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float *means, const float *conics,
+                       const float *values, const float *samples, float *out_u, float *out_ux, float *out_uxx,
+                       void *stream);
+int pigs_dense_backward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float *means, const float *conics,
+                        const float *values, const float *samples, const float *dL_du, const float *dL_dux,
+                        const float *dL_duxx, float *dL_dmeans, float *dL_dconics, float *dL_dvalues, void *stream);
+
 /* ---- split / prune as a device-side compaction --------------------------------
  * Replaces the torch chains that change P between steps: model_pn.py:578-610 `Model.split`, :703-716 (prune by
  * keep_indices), test_no_mlp_1d.py:203-247 (keep + displaced clones, Adam moments of the clones zeroed).

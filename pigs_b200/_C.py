@@ -569,3 +569,45 @@ def vorticity_backward(g):
     if g.numel() > 0:
         check(L.pigs_vorticity_backward(g.numel(), _ptr(g), _ptr(d), _stream()), "pigs_vorticity_backward")
     return d
+
+
+# ---- dense all-pairs path (gaussians.py:48-58, 89-101, 103-116) -------------------
+def _dense_args(means, conics, values, samples):
+    means = _f32c(means, "means")
+    n, D = means.shape
+    conics = _f32c(conics, "conics")
+    values = _f32c(values, "values")
+    samples = _f32c(samples, "samples")
+    if D not in (1, 2) or conics.numel() != n * D * D:
+        raise RuntimeError("dense path: means [n, D] with D in (1, 2) and FULL conics [n, D, D] expected")
+    C = values.numel() // max(n, 1)
+    if values.numel() != n * C or not 1 <= C <= 4:
+        raise RuntimeError("dense path: values [n, C] with C <= 4 expected")
+    N = samples.numel() // D
+    return n, D, C, N, means, conics, values, samples
+
+
+def dense_forward(fn_mask, means, conics, values, samples):
+    """-> (u [N,C] | None, ux [N,D,C] | None, uxx [N,D,D,C] | None) for the bits of fn_mask (FN_VALUE | FN_DERIV | FN_HESS)."""
+    L = _lib.lib()
+    n, D, C, N, means, conics, values, samples = _dense_args(means, conics, values, samples)
+    dev = means.device
+    mk = lambda bit, *sh: torch.zeros(sh, dtype=torch.float32, device=dev) if fn_mask & bit else None
+    u, ux, uxx = mk(1, N, C), mk(2, N, D, C), mk(4, N, D, D, C)
+    if n > 0 and N > 0:
+        check(L.pigs_dense_forward(fn_mask, n, D, C, N, _ptr(means), _ptr(conics), _ptr(values), _ptr(samples), _ptr(u),
+                                   _ptr(ux), _ptr(uxx), _stream()), "pigs_dense_forward")
+    return u, ux, uxx
+
+
+def dense_backward(fn_mask, means, conics, values, samples, g_u, g_ux, g_uxx):
+    """-> (dL_dmeans [n,D], dL_dconics [n,D,D], dL_dvalues [n,C])."""
+    L = _lib.lib()
+    n, D, C, N, means, conics, values, samples = _dense_args(means, conics, values, samples)
+    gs = [None if (g is None or not fn_mask & bit) else _f32c(g, "dL_dout") for g, bit in ((g_u, 1), (g_ux, 2), (g_uxx, 4))]
+    dm, dc, dv = torch.zeros_like(means), torch.zeros((n, D, D), dtype=torch.float32, device=means.device), \
+        torch.zeros((n, C), dtype=torch.float32, device=means.device)
+    if n > 0 and N > 0:
+        check(L.pigs_dense_backward(fn_mask, n, D, C, N, _ptr(means), _ptr(conics), _ptr(values), _ptr(samples),
+                                    *[_ptr(g) for g in gs], _ptr(dm), _ptr(dc), _ptr(dv), _stream()), "pigs_dense_backward")
+    return dm, dc, dv

@@ -1,0 +1,344 @@
+// dense.cu — the reference's dense all-pairs sampling path as CUDA kernels:
+//   gaussians.py:48-58   sample_gaussians      u[N,C]      = sum_g v_g exp(-1/2 x^T K_g x),        x = sample - mean_g
+//   gaussians.py:89-101  gaussian_derivative   ux[N,D,C]   = sum_g -(K_g x) alpha v_g
+//   gaussians.py:103-116 gaussian_derivative2  uxx[N,D,D,C] = sum_g ((K_g x)(K_g x)^T - K_g) alpha v_g
+// with FULL [n, D, D] conics (not assumed symmetric), every Gaussian against every sample: no tile cutoff, no torus wrap,
+// no power > 0 skip — the semantics of the pure-PyTorch path the reference's CPU drivers (test_no_mlp_1d.py,
+// test_derivatives.py:110-143) use, without its O(N n d^2) broadcast tensors.  The backward is what torch.autograd
+// gives those three functions: gradients to means, full conics and values.
+// Forward: one sample per thread, Gaussian records broadcast from shared memory; backward: one Gaussian per thread,
+// sample + upstream-gradient records broadcast from shared memory, sums carried in registers.  The other operand is cut
+// into chunks over blockIdx.y so that small problems still fill the 148 SMs; a chunked launch adds into zeroed outputs
+// with one RED per output element and chunk, an unchunked one stores.
+// FP32-issue bound like the tiled kernels (per pair, D = 2, C = 1, all three outputs: 22 FP32 ops + 1 ex2 forward).
+#include "common.cuh"
+
+namespace pigs {
+
+constexpr int DN_FWD_THREADS = 256, DN_BWD_THREADS = 128, DN_BATCH = 256;
+constexpr float DN_KH = -0.72134752044448170368f;  // -0.5 * log2(e)
+
+__device__ __forceinline__ float dn_ex2(float x)
+{
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+
+template <int D, int C>
+__global__ void __launch_bounds__(DN_FWD_THREADS)
+    dense_fwd_kernel(unsigned mask, int64_t n, int64_t N, int64_t per_chunk, const float* __restrict__ means,
+                     const float* __restrict__ conics, const float* __restrict__ values, const float* __restrict__ samples,
+                     float* __restrict__ out_u, float* __restrict__ out_ux, float* __restrict__ out_uxx)
+{
+    constexpr int REC = D + D * D + C;
+    __shared__ float rec[DN_BATCH * REC];
+    const int64_t s = (int64_t)blockIdx.x * DN_FWD_THREADS + threadIdx.x;
+    const bool live = s < N;
+    float x[D];
+#pragma unroll
+    for (int d = 0; d < D; d++) x[d] = live ? samples[s * D + d] : 0.0f;
+    float au[C], ax[D][C], ah[D][D][C];
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        au[c] = 0.0f;
+#pragma unroll
+        for (int i = 0; i < D; i++) {
+            ax[i][c] = 0.0f;
+#pragma unroll
+            for (int j = 0; j < D; j++) ah[i][j][c] = 0.0f;
+        }
+    }
+    const int64_t g0 = (int64_t)blockIdx.y * per_chunk, g1 = min(n, g0 + per_chunk);
+    for (int64_t b = g0; b < g1; b += DN_BATCH) {
+        const int nb = (int)min((int64_t)DN_BATCH, g1 - b);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nb * D; i += DN_FWD_THREADS) rec[(i / D) * REC + i % D] = means[b * D + i];
+        for (int i = threadIdx.x; i < nb * D * D; i += DN_FWD_THREADS)
+            rec[(i / (D * D)) * REC + D + i % (D * D)] = conics[b * D * D + i];
+        for (int i = threadIdx.x; i < nb * C; i += DN_FWD_THREADS) rec[(i / C) * REC + D + D * D + i % C] = values[b * C + i];
+        __syncthreads();
+        for (int g = 0; g < nb; g++) {
+            const float* r = rec + g * REC;
+            float X[D], a[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) X[d] = x[d] - r[d];
+            float q = 0.0f;
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+                a[i] = 0.0f;
+#pragma unroll
+                for (int j = 0; j < D; j++) a[i] = fmaf(r[D + i * D + j], X[j], a[i]);
+                q = fmaf(X[i], a[i], q);
+            }
+            const float alpha = dn_ex2(DN_KH * q);
+#pragma unroll
+            for (int c = 0; c < C; c++) {
+                const float w = alpha * r[D + D * D + c];
+                au[c] += w;
+#pragma unroll
+                for (int i = 0; i < D; i++) {
+                    ax[i][c] = fmaf(-a[i], w, ax[i][c]);
+#pragma unroll
+                    for (int j = 0; j < D; j++) ah[i][j][c] = fmaf(fmaf(a[i], a[j], -r[D + i * D + j]), w, ah[i][j][c]);
+                }
+            }
+        }
+    }
+    if (!live) return;
+    const bool add = gridDim.y > 1;
+    auto put = [add](float* p, float v) {
+        if (add)
+            atomicAdd(p, v);
+        else
+            *p = v;
+    };
+#pragma unroll
+    for (int c = 0; c < C; c++) {
+        if (mask & PIGS_FN_VALUE) put(out_u + s * C + c, au[c]);
+#pragma unroll
+        for (int i = 0; i < D; i++) {
+            if (mask & PIGS_FN_DERIV) put(out_ux + (s * D + i) * C + c, ax[i][c]);
+#pragma unroll
+            for (int j = 0; j < D; j++)
+                if (mask & PIGS_FN_HESS) put(out_uxx + ((s * D + i) * D + j) * C + c, ah[i][j][c]);
+        }
+    }
+}
+
+// per pair, with S_c = dL/dw_c (w_c = alpha v_c):
+//   S_c   = g_c - sum_i gx_ic a_i + sum_ij gH_ijc (a_i a_j - K_ij)
+//   dv_c += alpha S_c ;  dq = -1/2 alpha sum_c v_c S_c
+//   dA_i  = sum_c w_c (-gx_ic + sum_j (gH_ijc + gH_jic) a_j) + dq X_i          (a = K X, q = X . a)
+//   dK_ij += dA_i X_j - sum_c w_c gH_ijc ;  dX_j = dq a_j + sum_i dA_i K_ij ;  dmean -= dX
+template <int D, int C>
+__global__ void __launch_bounds__(DN_BWD_THREADS)
+    dense_bwd_kernel(unsigned mask, int64_t n, int64_t N, int64_t per_chunk, const float* __restrict__ means,
+                     const float* __restrict__ conics, const float* __restrict__ values, const float* __restrict__ samples,
+                     const float* __restrict__ g_u, const float* __restrict__ g_ux, const float* __restrict__ g_uxx,
+                     float* __restrict__ d_means, float* __restrict__ d_conics, float* __restrict__ d_values)
+{
+    constexpr int REC = D + C + D * C + D * D * C;  // sample, g, gx, gH
+    constexpr int SB = 128;
+    __shared__ float rec[SB * REC];
+    const int64_t g = (int64_t)blockIdx.x * DN_BWD_THREADS + threadIdx.x;
+    const bool live = g < n;
+    float mu[D], K[D][D], v[C];
+#pragma unroll
+    for (int i = 0; i < D; i++) {
+        mu[i] = live ? means[g * D + i] : 0.0f;
+#pragma unroll
+        for (int j = 0; j < D; j++) K[i][j] = live ? conics[(g * D + i) * D + j] : 0.0f;
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) v[c] = live ? values[g * C + c] : 0.0f;
+    float dmu[D], dK[D][D], dv[C];
+#pragma unroll
+    for (int i = 0; i < D; i++) {
+        dmu[i] = 0.0f;
+#pragma unroll
+        for (int j = 0; j < D; j++) dK[i][j] = 0.0f;
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) dv[c] = 0.0f;
+    const int64_t s0 = (int64_t)blockIdx.y * per_chunk, s1 = min(N, s0 + per_chunk);
+    for (int64_t b = s0; b < s1; b += SB) {
+        const int nb = (int)min((int64_t)SB, s1 - b);
+        __syncthreads();
+        for (int i = threadIdx.x; i < nb * D; i += DN_BWD_THREADS) rec[(i / D) * REC + i % D] = samples[b * D + i];
+        for (int i = threadIdx.x; i < nb * C; i += DN_BWD_THREADS)
+            rec[(i / C) * REC + D + i % C] = (mask & PIGS_FN_VALUE) ? g_u[b * C + i] : 0.0f;
+        for (int i = threadIdx.x; i < nb * D * C; i += DN_BWD_THREADS)
+            rec[(i / (D * C)) * REC + D + C + i % (D * C)] = (mask & PIGS_FN_DERIV) ? g_ux[b * D * C + i] : 0.0f;
+        for (int i = threadIdx.x; i < nb * D * D * C; i += DN_BWD_THREADS)
+            rec[(i / (D * D * C)) * REC + D + C + D * C + i % (D * D * C)] =
+                (mask & PIGS_FN_HESS) ? g_uxx[b * D * D * C + i] : 0.0f;
+        __syncthreads();
+        for (int k = 0; k < nb; k++) {
+            const float* r = rec + k * REC;
+            const float* gu = r + D;
+            const float* gx = r + D + C;          // [i][c]
+            const float* gh = r + D + C + D * C;  // [i][j][c]
+            float X[D], a[D];
+#pragma unroll
+            for (int d = 0; d < D; d++) X[d] = r[d] - mu[d];
+            float q = 0.0f;
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+                a[i] = 0.0f;
+#pragma unroll
+                for (int j = 0; j < D; j++) a[i] = fmaf(K[i][j], X[j], a[i]);
+                q = fmaf(X[i], a[i], q);
+            }
+            const float alpha = dn_ex2(DN_KH * q);
+            float dalpha = 0.0f, dA[D], wH[D][D];
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+                dA[i] = 0.0f;
+#pragma unroll
+                for (int j = 0; j < D; j++) wH[i][j] = 0.0f;
+            }
+#pragma unroll
+            for (int c = 0; c < C; c++) {
+                float S = gu[c];
+                const float w = alpha * v[c];
+#pragma unroll
+                for (int i = 0; i < D; i++) {
+                    S = fmaf(-gx[i * C + c], a[i], S);
+                    dA[i] = fmaf(-gx[i * C + c], w, dA[i]);
+#pragma unroll
+                    for (int j = 0; j < D; j++) {
+                        const float h = gh[(i * D + j) * C + c];
+                        S = fmaf(h, fmaf(a[i], a[j], -K[i][j]), S);
+                        wH[i][j] = fmaf(w, h, wH[i][j]);
+                    }
+                }
+                dv[c] = fmaf(alpha, S, dv[c]);
+                dalpha = fmaf(v[c], S, dalpha);
+            }
+            const float dq = -0.5f * alpha * dalpha;
+#pragma unroll
+            for (int i = 0; i < D; i++) {
+#pragma unroll
+                for (int j = 0; j < D; j++) dA[i] = fmaf(wH[i][j] + wH[j][i], a[j], dA[i]);
+                dA[i] = fmaf(dq, X[i], dA[i]);
+            }
+#pragma unroll
+            for (int j = 0; j < D; j++) {
+                float dX = dq * a[j];
+#pragma unroll
+                for (int i = 0; i < D; i++) {
+                    dX = fmaf(dA[i], K[i][j], dX);
+                    dK[i][j] += fmaf(dA[i], X[j], -wH[i][j]);
+                }
+                dmu[j] -= dX;
+            }
+        }
+    }
+    if (!live) return;
+    const bool add = gridDim.y > 1;
+    auto put = [add](float* p, float val) {
+        if (add)
+            atomicAdd(p, val);
+        else
+            *p = val;
+    };
+#pragma unroll
+    for (int i = 0; i < D; i++) {
+        put(d_means + g * D + i, dmu[i]);
+#pragma unroll
+        for (int j = 0; j < D; j++) put(d_conics + (g * D + i) * D + j, dK[i][j]);
+    }
+#pragma unroll
+    for (int c = 0; c < C; c++) put(d_values + g * C + c, dv[c]);
+}
+
+// chunks of the streamed operand so that the grid has ~4 CTAs per SM even for small stationary counts
+static int64_t dn_chunks(int64_t stationary_blocks, int64_t streamed, int batch)
+{
+    const int64_t want = 4 * (int64_t)num_sms();
+    int64_t ny = (want + stationary_blocks - 1) / stationary_blocks;
+    const int64_t most = (streamed + 4 * batch - 1) / (4 * batch);  // at least four batches per chunk
+    if (ny > most) ny = most;
+    if (ny > 65535) ny = 65535;
+    return ny < 1 ? 1 : ny;
+}
+
+template <int D>
+static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means, const float* conics, const float* values,
+                  const float* samples, float* u, float* ux, float* uxx, cudaStream_t st)
+{
+    const int64_t nx = (N + DN_FWD_THREADS - 1) / DN_FWD_THREADS;
+    const int64_t ny = dn_chunks(nx, n, DN_BATCH);
+    const int64_t per = ((n + ny - 1) / ny + DN_BATCH - 1) / DN_BATCH * DN_BATCH;
+    const dim3 grid((unsigned)nx, (unsigned)((n + per - 1) / per));
+    if (grid.y > 1) {  // chunked: the kernel adds into zeroed outputs
+        if ((mask & PIGS_FN_VALUE) && cudaMemsetAsync(u, 0, sizeof(float) * N * C, st) != cudaSuccess) return -2;
+        if ((mask & PIGS_FN_DERIV) && cudaMemsetAsync(ux, 0, sizeof(float) * N * D * C, st) != cudaSuccess) return -2;
+        if ((mask & PIGS_FN_HESS) && cudaMemsetAsync(uxx, 0, sizeof(float) * N * D * D * C, st) != cudaSuccess) return -2;
+    }
+#define DN_F(CC)                                                                                                        \
+    case CC:                                                                                                            \
+        dense_fwd_kernel<D, CC><<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx); \
+        break;
+    switch (C) {
+        DN_F(1) DN_F(2) DN_F(3) DN_F(4)
+    default:
+        return -1;
+    }
+#undef DN_F
+    return 0;
+}
+
+template <int D>
+static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means, const float* conics, const float* values,
+                  const float* samples, const float* gu, const float* gux, const float* guxx, float* dm, float* dc, float* dv,
+                  cudaStream_t st)
+{
+    const int64_t nx = (n + DN_BWD_THREADS - 1) / DN_BWD_THREADS;
+    const int64_t ny = dn_chunks(nx, N, 128);
+    const int64_t per = ((N + ny - 1) / ny + 127) / 128 * 128;
+    const dim3 grid((unsigned)nx, (unsigned)((N + per - 1) / per));
+    if (grid.y > 1) {
+        if (cudaMemsetAsync(dm, 0, sizeof(float) * n * D, st) != cudaSuccess) return -2;
+        if (cudaMemsetAsync(dc, 0, sizeof(float) * n * D * D, st) != cudaSuccess) return -2;
+        if (cudaMemsetAsync(dv, 0, sizeof(float) * n * C, st) != cudaSuccess) return -2;
+    }
+#define DN_B(CC)                                                                                                        \
+    case CC:                                                                                                            \
+        dense_bwd_kernel<D, CC><<<grid, DN_BWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, gu, gux,  \
+                                                                 guxx, dm, dc, dv);                                     \
+        break;
+    switch (C) {
+        DN_B(1) DN_B(2) DN_B(3) DN_B(4)
+    default:
+        return -1;
+    }
+#undef DN_B
+    return 0;
+}
+
+}  // namespace pigs
+
+extern "C" {
+
+int pigs_dense_forward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float* means, const float* conics,
+                       const float* values, const float* samples, float* out_u, float* out_ux, float* out_uxx, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(n > 0 && N > 0 && (D == 1 || D == 2) && C >= 1 && C <= 4);
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~(PIGS_FN_VALUE | PIGS_FN_DERIV | PIGS_FN_HESS)) == 0);
+    PIGS_ARG(means && conics && values && samples);
+    PIGS_ARG(!(fn_mask & PIGS_FN_VALUE) || out_u);
+    PIGS_ARG(!(fn_mask & PIGS_FN_DERIV) || out_ux);
+    PIGS_ARG(!(fn_mask & PIGS_FN_HESS) || out_uxx);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rc = D == 1 ? dn_fwd<1>(C, fn_mask, n, N, means, conics, values, samples, out_u, out_ux, out_uxx, st)
+                          : dn_fwd<2>(C, fn_mask, n, N, means, conics, values, samples, out_u, out_ux, out_uxx, st);
+    PIGS_ARG(rc == 0);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_dense_backward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float* means, const float* conics,
+                        const float* values, const float* samples, const float* dL_du, const float* dL_dux,
+                        const float* dL_duxx, float* dL_dmeans, float* dL_dconics, float* dL_dvalues, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(n > 0 && N > 0 && (D == 1 || D == 2) && C >= 1 && C <= 4);
+    PIGS_ARG(fn_mask != 0 && (fn_mask & ~(PIGS_FN_VALUE | PIGS_FN_DERIV | PIGS_FN_HESS)) == 0);
+    PIGS_ARG(means && conics && values && samples && dL_dmeans && dL_dconics && dL_dvalues);
+    PIGS_ARG(!(fn_mask & PIGS_FN_VALUE) || dL_du);
+    PIGS_ARG(!(fn_mask & PIGS_FN_DERIV) || dL_dux);
+    PIGS_ARG(!(fn_mask & PIGS_FN_HESS) || dL_duxx);
+    cudaStream_t st = (cudaStream_t)stream;
+    const int rc = D == 1 ? dn_bwd<1>(C, fn_mask, n, N, means, conics, values, samples, dL_du, dL_dux, dL_duxx, dL_dmeans,
+                                      dL_dconics, dL_dvalues, st)
+                          : dn_bwd<2>(C, fn_mask, n, N, means, conics, values, samples, dL_du, dL_dux, dL_duxx, dL_dmeans,
+                                      dL_dconics, dL_dvalues, st);
+    PIGS_ARG(rc == 0);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+}  // extern "C"

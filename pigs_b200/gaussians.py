@@ -51,3 +51,49 @@ def flatten_covariances(covariances, conics):
     covariances = covariances.reshape(*covariances.shape[:-2], -1)[..., [0, 1, 3]]
     conics = conics.reshape(*conics.shape[:-2], -1)[..., [0, 1, 3]]
     return covariances, conics
+
+
+# ---- dense all-pairs sampling (gaussians.py:48-58, 89-101, 103-116) ----------------
+class _DenseSample(torch.autograd.Function):
+    """One launch for any subset of (u, grad u, Hessian); backward = what torch.autograd gives the reference's dense
+    functions (gradients to means, FULL conics and values; none to samples)."""
+
+    @staticmethod
+    def forward(ctx, mask, means, conics, values, samples):
+        outs = _C.dense_forward(mask, means, conics, values, samples)
+        ctx.mask = mask
+        ctx.save_for_backward(means, conics, values, samples)
+        ctx.shapes = (conics.shape, values.shape)
+        return tuple(o for o in outs if o is not None)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        means, conics, values, samples = ctx.saved_tensors
+        it = iter(grads)
+        g = [next(it) if ctx.mask & bit else None for bit in (1, 2, 4)]
+        mask = sum(bit for bit, x in zip((1, 2, 4), g) if x is not None)
+        if mask == 0:
+            return None, None, None, None, None
+        dm, dc, dv = _C.dense_backward(mask, means, conics, values, samples, *g)
+        return None, dm.reshape(means.shape), dc.reshape(ctx.shapes[0]), dv.reshape(ctx.shapes[1]), None
+
+
+def dense_sample(mask, means, conics, values, samples):
+    """(extension) any subset of u / grad u / Hessian of the dense path in ONE launch; mask bits 1 | 2 | 4.
+    Returns a tuple in that order."""
+    return _DenseSample.apply(int(mask), means, conics, values, samples)
+
+
+def sample_gaussians(means, conics, values, samples):
+    """gaussians.py:48-58: [N, C]; conics FULL [n, d, d]; samples [N, d] (any shape with N*d elements)."""
+    return dense_sample(1, means, conics, values, samples)[0]
+
+
+def gaussian_derivative(means, conics, values, samples):
+    """gaussians.py:89-101: [N, d, C]."""
+    return dense_sample(2, means, conics, values, samples)[0]
+
+
+def gaussian_derivative2(means, conics, values, samples):
+    """gaussians.py:103-116: [N, d, d, C]."""
+    return dense_sample(4, means, conics, values, samples)[0]
