@@ -268,6 +268,9 @@ int pigs_vorticity_backward(int64_t groups, const float *dL_dout, float *dL_din,
  * fn_mask: PIGS_FN_VALUE | PIGS_FN_DERIV | PIGS_FN_HESS (any subset, one launch).  Outputs u [N,C], ux [N,D,C],
  * uxx [N,D,D,C]; D in {1,2}, C <= 4.  backward = torch.autograd of those functions: dL_dmeans [n,D], dL_dconics
  * [n,D,D], dL_dvalues [n,C] (fully written; the dL_d<out> of functions not in fn_mask may be NULL). */
+/* Test knob: the kernels hold 1-4 samples (forward) / 1-2 Gaussians (backward) per thread, chosen from the problem size;
+ * 1 forces one, > 1 forces the most the channel count allows, 0 (default) restores the choice. */
+void pigs_set_dense_slots(int samples_per_thread, int gaussians_per_thread);
 int pigs_dense_forward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float *means, const float *conics,
                        const float *values, const float *samples, float *out_u, float *out_ux, float *out_uxx,
                        void *stream);

@@ -87,6 +87,7 @@ SIGNATURES = {
                                                 + [c_void_p] * 15),
     "pigs_pde_ns_residual_timelevels_backward": (c_int, [c_int64, ctypes.c_float, ctypes.c_float, c_void_p, ctypes.c_float]
                                                  + [c_void_p] * 22),
+    "pigs_set_dense_slots": (None, [c_int, c_int]),
     "pigs_dense_forward": (c_int, [ctypes.c_uint, c_int64, c_int, c_int, c_int64] + [c_void_p] * 8),
     "pigs_dense_backward": (c_int, [ctypes.c_uint, c_int64, c_int, c_int, c_int64] + [c_void_p] * 11),
     "pigs_vorticity_forward": (c_int, [c_int64, c_void_p, c_void_p, c_void_p]),

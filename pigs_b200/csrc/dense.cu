@@ -6,7 +6,7 @@
 // no power > 0 skip — the semantics of the pure-PyTorch path the reference's CPU drivers (test_no_mlp_1d.py,
 // test_derivatives.py:110-143) use, without its O(N n d^2) broadcast tensors.  The backward is what torch.autograd
 // gives those three functions: gradients to means, full conics and values.
-// Forward: one sample per thread, Gaussian records broadcast from shared memory; backward: one Gaussian per thread,
+// Forward: 1-4 samples per thread, Gaussian records broadcast from shared memory; backward: 1-2 Gaussians per thread,
 // sample + upstream-gradient records broadcast from shared memory, sums carried in registers.  The other operand is cut
 // into chunks over blockIdx.y so that small problems still fill the 148 SMs; a chunked launch adds into zeroed outputs
 // with one RED per output element and chunk, an unchunked one stores.
@@ -25,7 +25,10 @@ __device__ __forceinline__ float dn_ex2(float x)
     return y;
 }
 
-template <int D, int C>
+// KS samples per thread (strided by the block size, so loads and stores stay coalesced): one set of shared-memory reads
+// of a Gaussian's record serves KS pairs (ncu on the one-sample version: 0.83 issue slots busy per cycle with the LSU pipe
+// at 40 % — the record reads, not the FMAs, filled the issue slots).
+template <int D, int C, int KS>
 __global__ void __launch_bounds__(DN_FWD_THREADS)
     dense_fwd_kernel(unsigned mask, int64_t n, int64_t N, int64_t per_chunk, const float* __restrict__ means,
                      const float* __restrict__ conics, const float* __restrict__ values, const float* __restrict__ samples,
@@ -33,20 +36,23 @@ __global__ void __launch_bounds__(DN_FWD_THREADS)
 {
     constexpr int REC = D + D * D + C;
     __shared__ float rec[DN_BATCH * REC];
-    const int64_t s = (int64_t)blockIdx.x * DN_FWD_THREADS + threadIdx.x;
-    const bool live = s < N;
-    float x[D];
+    int64_t sidx[KS];
+    float x[KS][D];
+    float au[KS][C], ax[KS][D][C], ah[KS][D][D][C];
 #pragma unroll
-    for (int d = 0; d < D; d++) x[d] = live ? samples[s * D + d] : 0.0f;
-    float au[C], ax[D][C], ah[D][D][C];
+    for (int k = 0; k < KS; k++) {
+        sidx[k] = ((int64_t)blockIdx.x * KS + k) * DN_FWD_THREADS + threadIdx.x;
 #pragma unroll
-    for (int c = 0; c < C; c++) {
-        au[c] = 0.0f;
+        for (int d = 0; d < D; d++) x[k][d] = sidx[k] < N ? samples[sidx[k] * D + d] : 0.0f;
 #pragma unroll
-        for (int i = 0; i < D; i++) {
-            ax[i][c] = 0.0f;
+        for (int c = 0; c < C; c++) {
+            au[k][c] = 0.0f;
 #pragma unroll
-            for (int j = 0; j < D; j++) ah[i][j][c] = 0.0f;
+            for (int i = 0; i < D; i++) {
+                ax[k][i][c] = 0.0f;
+#pragma unroll
+                for (int j = 0; j < D; j++) ah[k][i][j][c] = 0.0f;
+            }
         }
     }
     const int64_t g0 = (int64_t)blockIdx.y * per_chunk, g1 = min(n, g0 + per_chunk);
@@ -59,33 +65,38 @@ __global__ void __launch_bounds__(DN_FWD_THREADS)
         for (int i = threadIdx.x; i < nb * C; i += DN_FWD_THREADS) rec[(i / C) * REC + D + D * D + i % C] = values[b * C + i];
         __syncthreads();
         for (int g = 0; g < nb; g++) {
-            const float* r = rec + g * REC;
-            float X[D], a[D];
+            float r[REC];
 #pragma unroll
-            for (int d = 0; d < D; d++) X[d] = x[d] - r[d];
-            float q = 0.0f;
+            for (int i = 0; i < REC; i++) r[i] = rec[g * REC + i];
 #pragma unroll
-            for (int i = 0; i < D; i++) {
-                a[i] = 0.0f;
+            for (int k = 0; k < KS; k++) {
+                float X[D], a[D];
 #pragma unroll
-                for (int j = 0; j < D; j++) a[i] = fmaf(r[D + i * D + j], X[j], a[i]);
-                q = fmaf(X[i], a[i], q);
-            }
-            const float alpha = dn_ex2(DN_KH * q);
-#pragma unroll
-            for (int c = 0; c < C; c++) {
-                const float w = alpha * r[D + D * D + c];
-                au[c] += w;
+                for (int d = 0; d < D; d++) X[d] = x[k][d] - r[d];
+                float q = 0.0f;
 #pragma unroll
                 for (int i = 0; i < D; i++) {
-                    ax[i][c] = fmaf(-a[i], w, ax[i][c]);
+                    a[i] = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < D; j++) ah[i][j][c] = fmaf(fmaf(a[i], a[j], -r[D + i * D + j]), w, ah[i][j][c]);
+                    for (int j = 0; j < D; j++) a[i] = fmaf(r[D + i * D + j], X[j], a[i]);
+                    q = fmaf(X[i], a[i], q);
+                }
+                const float alpha = dn_ex2(DN_KH * q);
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    const float w = alpha * r[D + D * D + c];
+                    au[k][c] += w;
+#pragma unroll
+                    for (int i = 0; i < D; i++) {
+                        ax[k][i][c] = fmaf(-a[i], w, ax[k][i][c]);
+#pragma unroll
+                        for (int j = 0; j < D; j++)
+                            ah[k][i][j][c] = fmaf(fmaf(a[i], a[j], -r[D + i * D + j]), w, ah[k][i][j][c]);
+                    }
                 }
             }
         }
     }
-    if (!live) return;
     const bool add = gridDim.y > 1;
     auto put = [add](float* p, float v) {
         if (add)
@@ -94,14 +105,19 @@ __global__ void __launch_bounds__(DN_FWD_THREADS)
             *p = v;
     };
 #pragma unroll
-    for (int c = 0; c < C; c++) {
-        if (mask & PIGS_FN_VALUE) put(out_u + s * C + c, au[c]);
+    for (int k = 0; k < KS; k++) {
+        const int64_t s = sidx[k];
+        if (s >= N) continue;
 #pragma unroll
-        for (int i = 0; i < D; i++) {
-            if (mask & PIGS_FN_DERIV) put(out_ux + (s * D + i) * C + c, ax[i][c]);
+        for (int c = 0; c < C; c++) {
+            if (mask & PIGS_FN_VALUE) put(out_u + s * C + c, au[k][c]);
 #pragma unroll
-            for (int j = 0; j < D; j++)
-                if (mask & PIGS_FN_HESS) put(out_uxx + ((s * D + i) * D + j) * C + c, ah[i][j][c]);
+            for (int i = 0; i < D; i++) {
+                if (mask & PIGS_FN_DERIV) put(out_ux + (s * D + i) * C + c, ax[k][i][c]);
+#pragma unroll
+                for (int j = 0; j < D; j++)
+                    if (mask & PIGS_FN_HESS) put(out_uxx + ((s * D + i) * D + j) * C + c, ah[k][i][j][c]);
+            }
         }
     }
 }
@@ -111,7 +127,7 @@ __global__ void __launch_bounds__(DN_FWD_THREADS)
 //   dv_c += alpha S_c ;  dq = -1/2 alpha sum_c v_c S_c
 //   dA_i  = sum_c w_c (-gx_ic + sum_j (gH_ijc + gH_jic) a_j) + dq X_i          (a = K X, q = X . a)
 //   dK_ij += dA_i X_j - sum_c w_c gH_ijc ;  dX_j = dq a_j + sum_i dA_i K_ij ;  dmean -= dX
-template <int D, int C>
+template <int D, int C, int KG>
 __global__ void __launch_bounds__(DN_BWD_THREADS)
     dense_bwd_kernel(unsigned mask, int64_t n, int64_t N, int64_t per_chunk, const float* __restrict__ means,
                      const float* __restrict__ conics, const float* __restrict__ values, const float* __restrict__ samples,
@@ -121,26 +137,30 @@ __global__ void __launch_bounds__(DN_BWD_THREADS)
     constexpr int REC = D + C + D * C + D * D * C;  // sample, g, gx, gH
     constexpr int SB = 128;
     __shared__ float rec[SB * REC];
-    const int64_t g = (int64_t)blockIdx.x * DN_BWD_THREADS + threadIdx.x;
-    const bool live = g < n;
-    float mu[D], K[D][D], v[C];
+    // KG Gaussians per thread (strided by the block size): one read of a sample record serves KG pairs
+    int64_t gidx[KG];
+    float mu[KG][D], K[KG][D][D], v[KG][C];
+    float dmu[KG][D], dK[KG][D][D], dv[KG][C];
 #pragma unroll
-    for (int i = 0; i < D; i++) {
-        mu[i] = live ? means[g * D + i] : 0.0f;
+    for (int t = 0; t < KG; t++) {
+        gidx[t] = ((int64_t)blockIdx.x * KG + t) * DN_BWD_THREADS + threadIdx.x;
+        const bool live = gidx[t] < n;
 #pragma unroll
-        for (int j = 0; j < D; j++) K[i][j] = live ? conics[(g * D + i) * D + j] : 0.0f;
+        for (int i = 0; i < D; i++) {
+            mu[t][i] = live ? means[gidx[t] * D + i] : 0.0f;
+            dmu[t][i] = 0.0f;
+#pragma unroll
+            for (int j = 0; j < D; j++) {
+                K[t][i][j] = live ? conics[(gidx[t] * D + i) * D + j] : 0.0f;
+                dK[t][i][j] = 0.0f;
+            }
+        }
+#pragma unroll
+        for (int c = 0; c < C; c++) {
+            v[t][c] = live ? values[gidx[t] * C + c] : 0.0f;
+            dv[t][c] = 0.0f;
+        }
     }
-#pragma unroll
-    for (int c = 0; c < C; c++) v[c] = live ? values[g * C + c] : 0.0f;
-    float dmu[D], dK[D][D], dv[C];
-#pragma unroll
-    for (int i = 0; i < D; i++) {
-        dmu[i] = 0.0f;
-#pragma unroll
-        for (int j = 0; j < D; j++) dK[i][j] = 0.0f;
-    }
-#pragma unroll
-    for (int c = 0; c < C; c++) dv[c] = 0.0f;
     const int64_t s0 = (int64_t)blockIdx.y * per_chunk, s1 = min(N, s0 + per_chunk);
     for (int64_t b = s0; b < s1; b += SB) {
         const int nb = (int)min((int64_t)SB, s1 - b);
@@ -155,67 +175,71 @@ __global__ void __launch_bounds__(DN_BWD_THREADS)
                 (mask & PIGS_FN_HESS) ? g_uxx[b * D * D * C + i] : 0.0f;
         __syncthreads();
         for (int k = 0; k < nb; k++) {
-            const float* r = rec + k * REC;
+            float r[REC];
+#pragma unroll
+            for (int i = 0; i < REC; i++) r[i] = rec[k * REC + i];
             const float* gu = r + D;
             const float* gx = r + D + C;          // [i][c]
             const float* gh = r + D + C + D * C;  // [i][j][c]
-            float X[D], a[D];
 #pragma unroll
-            for (int d = 0; d < D; d++) X[d] = r[d] - mu[d];
-            float q = 0.0f;
+            for (int t = 0; t < KG; t++) {
+                float X[D], a[D];
 #pragma unroll
-            for (int i = 0; i < D; i++) {
-                a[i] = 0.0f;
-#pragma unroll
-                for (int j = 0; j < D; j++) a[i] = fmaf(K[i][j], X[j], a[i]);
-                q = fmaf(X[i], a[i], q);
-            }
-            const float alpha = dn_ex2(DN_KH * q);
-            float dalpha = 0.0f, dA[D], wH[D][D];
-#pragma unroll
-            for (int i = 0; i < D; i++) {
-                dA[i] = 0.0f;
-#pragma unroll
-                for (int j = 0; j < D; j++) wH[i][j] = 0.0f;
-            }
-#pragma unroll
-            for (int c = 0; c < C; c++) {
-                float S = gu[c];
-                const float w = alpha * v[c];
+                for (int d = 0; d < D; d++) X[d] = r[d] - mu[t][d];
+                float q = 0.0f;
 #pragma unroll
                 for (int i = 0; i < D; i++) {
-                    S = fmaf(-gx[i * C + c], a[i], S);
-                    dA[i] = fmaf(-gx[i * C + c], w, dA[i]);
+                    a[i] = 0.0f;
 #pragma unroll
-                    for (int j = 0; j < D; j++) {
-                        const float h = gh[(i * D + j) * C + c];
-                        S = fmaf(h, fmaf(a[i], a[j], -K[i][j]), S);
-                        wH[i][j] = fmaf(w, h, wH[i][j]);
+                    for (int j = 0; j < D; j++) a[i] = fmaf(K[t][i][j], X[j], a[i]);
+                    q = fmaf(X[i], a[i], q);
+                }
+                const float alpha = dn_ex2(DN_KH * q);
+                float dalpha = 0.0f, dA[D], wH[D][D];
+#pragma unroll
+                for (int i = 0; i < D; i++) {
+                    dA[i] = 0.0f;
+#pragma unroll
+                    for (int j = 0; j < D; j++) wH[i][j] = 0.0f;
+                }
+#pragma unroll
+                for (int c = 0; c < C; c++) {
+                    float S = gu[c];
+                    const float w = alpha * v[t][c];
+#pragma unroll
+                    for (int i = 0; i < D; i++) {
+                        S = fmaf(-gx[i * C + c], a[i], S);
+                        dA[i] = fmaf(-gx[i * C + c], w, dA[i]);
+#pragma unroll
+                        for (int j = 0; j < D; j++) {
+                            const float h = gh[(i * D + j) * C + c];
+                            S = fmaf(h, fmaf(a[i], a[j], -K[t][i][j]), S);
+                            wH[i][j] = fmaf(w, h, wH[i][j]);
+                        }
                     }
+                    dv[t][c] = fmaf(alpha, S, dv[t][c]);
+                    dalpha = fmaf(v[t][c], S, dalpha);
                 }
-                dv[c] = fmaf(alpha, S, dv[c]);
-                dalpha = fmaf(v[c], S, dalpha);
-            }
-            const float dq = -0.5f * alpha * dalpha;
-#pragma unroll
-            for (int i = 0; i < D; i++) {
-#pragma unroll
-                for (int j = 0; j < D; j++) dA[i] = fmaf(wH[i][j] + wH[j][i], a[j], dA[i]);
-                dA[i] = fmaf(dq, X[i], dA[i]);
-            }
-#pragma unroll
-            for (int j = 0; j < D; j++) {
-                float dX = dq * a[j];
+                const float dq = -0.5f * alpha * dalpha;
 #pragma unroll
                 for (int i = 0; i < D; i++) {
-                    dX = fmaf(dA[i], K[i][j], dX);
-                    dK[i][j] += fmaf(dA[i], X[j], -wH[i][j]);
+#pragma unroll
+                    for (int j = 0; j < D; j++) dA[i] = fmaf(wH[i][j] + wH[j][i], a[j], dA[i]);
+                    dA[i] = fmaf(dq, X[i], dA[i]);
                 }
-                dmu[j] -= dX;
+#pragma unroll
+                for (int j = 0; j < D; j++) {
+                    float dX = dq * a[j];
+#pragma unroll
+                    for (int i = 0; i < D; i++) {
+                        dX = fmaf(dA[i], K[t][i][j], dX);
+                        dK[t][i][j] += fmaf(dA[i], X[j], -wH[i][j]);
+                    }
+                    dmu[t][j] -= dX;
+                }
             }
         }
     }
-    if (!live) return;
     const bool add = gridDim.y > 1;
     auto put = [add](float* p, float val) {
         if (add)
@@ -224,14 +248,21 @@ __global__ void __launch_bounds__(DN_BWD_THREADS)
             *p = val;
     };
 #pragma unroll
-    for (int i = 0; i < D; i++) {
-        put(d_means + g * D + i, dmu[i]);
+    for (int t = 0; t < KG; t++) {
+        const int64_t g = gidx[t];
+        if (g >= n) continue;
 #pragma unroll
-        for (int j = 0; j < D; j++) put(d_conics + (g * D + i) * D + j, dK[i][j]);
+        for (int i = 0; i < D; i++) {
+            put(d_means + g * D + i, dmu[t][i]);
+#pragma unroll
+            for (int j = 0; j < D; j++) put(d_conics + (g * D + i) * D + j, dK[t][i][j]);
+        }
+#pragma unroll
+        for (int c = 0; c < C; c++) put(d_values + g * C + c, dv[t][c]);
     }
-#pragma unroll
-    for (int c = 0; c < C; c++) put(d_values + g * C + c, dv[c]);
 }
+
+static int g_dense_ks = 0, g_dense_kg = 0;  // pigs_set_dense_slots: 0 = chosen from the problem size
 
 // chunks of the streamed operand so that the grid has ~4 CTAs per SM even for small stationary counts
 static int64_t dn_chunks(int64_t stationary_blocks, int64_t streamed, int batch)
@@ -248,7 +279,10 @@ template <int D>
 static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means, const float* conics, const float* values,
                   const float* samples, float* u, float* ux, float* uxx, cudaStream_t st)
 {
-    const int64_t nx = (N + DN_FWD_THREADS - 1) / DN_FWD_THREADS;
+    // samples per thread: 4 for one channel, 2 for two, 1 beyond (register budget); one where N is small anyway
+    int ks = (N < (int64_t)DN_FWD_THREADS * 4 * num_sms()) ? 1 : (C == 1 ? 4 : (C == 2 ? 2 : 1));
+    if (g_dense_ks > 0) ks = g_dense_ks == 1 ? 1 : (C == 1 ? 4 : (C == 2 ? 2 : 1));
+    const int64_t nx = (N + (int64_t)DN_FWD_THREADS * ks - 1) / ((int64_t)DN_FWD_THREADS * ks);
     const int64_t ny = dn_chunks(nx, n, DN_BATCH);
     const int64_t per = ((n + ny - 1) / ny + DN_BATCH - 1) / DN_BATCH * DN_BATCH;
     const dim3 grid((unsigned)nx, (unsigned)((n + per - 1) / per));
@@ -257,15 +291,22 @@ static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
         if ((mask & PIGS_FN_DERIV) && cudaMemsetAsync(ux, 0, sizeof(float) * N * D * C, st) != cudaSuccess) return -2;
         if ((mask & PIGS_FN_HESS) && cudaMemsetAsync(uxx, 0, sizeof(float) * N * D * D * C, st) != cudaSuccess) return -2;
     }
-#define DN_F(CC)                                                                                                        \
-    case CC:                                                                                                            \
-        dense_fwd_kernel<D, CC><<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx); \
-        break;
-    switch (C) {
-        DN_F(1) DN_F(2) DN_F(3) DN_F(4)
-    default:
+#define DN_F(CC, KK)                                                                                                    \
+    dense_fwd_kernel<D, CC, KK><<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx)
+    if (C == 1 && ks == 4)
+        DN_F(1, 4);
+    else if (C == 1)
+        DN_F(1, 1);
+    else if (C == 2 && ks == 2)
+        DN_F(2, 2);
+    else if (C == 2)
+        DN_F(2, 1);
+    else if (C == 3)
+        DN_F(3, 1);
+    else if (C == 4)
+        DN_F(4, 1);
+    else
         return -1;
-    }
 #undef DN_F
     return 0;
 }
@@ -275,7 +316,9 @@ static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
                   const float* samples, const float* gu, const float* gux, const float* guxx, float* dm, float* dc, float* dv,
                   cudaStream_t st)
 {
-    const int64_t nx = (n + DN_BWD_THREADS - 1) / DN_BWD_THREADS;
+    int kg = (C == 1 && n >= (int64_t)DN_BWD_THREADS * 2 * num_sms()) ? 2 : 1;  // Gaussians per thread
+    if (g_dense_kg > 0) kg = (g_dense_kg > 1 && C == 1) ? 2 : 1;
+    const int64_t nx = (n + (int64_t)DN_BWD_THREADS * kg - 1) / ((int64_t)DN_BWD_THREADS * kg);
     const int64_t ny = dn_chunks(nx, N, 128);
     const int64_t per = ((N + ny - 1) / ny + 127) / 128 * 128;
     const dim3 grid((unsigned)nx, (unsigned)((N + per - 1) / per));
@@ -284,16 +327,21 @@ static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
         if (cudaMemsetAsync(dc, 0, sizeof(float) * n * D * D, st) != cudaSuccess) return -2;
         if (cudaMemsetAsync(dv, 0, sizeof(float) * n * C, st) != cudaSuccess) return -2;
     }
-#define DN_B(CC)                                                                                                        \
-    case CC:                                                                                                            \
-        dense_bwd_kernel<D, CC><<<grid, DN_BWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, gu, gux,  \
-                                                                 guxx, dm, dc, dv);                                     \
-        break;
-    switch (C) {
-        DN_B(1) DN_B(2) DN_B(3) DN_B(4)
-    default:
+#define DN_B(CC, KK)                                                                                                    \
+    dense_bwd_kernel<D, CC, KK><<<grid, DN_BWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, gu, gux,  \
+                                                                 guxx, dm, dc, dv)
+    if (C == 1 && kg == 2)
+        DN_B(1, 2);
+    else if (C == 1)
+        DN_B(1, 1);
+    else if (C == 2)
+        DN_B(2, 1);
+    else if (C == 3)
+        DN_B(3, 1);
+    else if (C == 4)
+        DN_B(4, 1);
+    else
         return -1;
-    }
 #undef DN_B
     return 0;
 }
@@ -301,6 +349,12 @@ static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
 }  // namespace pigs
 
 extern "C" {
+
+void pigs_set_dense_slots(int samples_per_thread, int gaussians_per_thread)
+{
+    pigs::g_dense_ks = samples_per_thread;
+    pigs::g_dense_kg = gaussians_per_thread;
+}
 
 int pigs_dense_forward(unsigned fn_mask, int64_t n, int D, int C, int64_t N, const float* means, const float* conics,
                        const float* values, const float* samples, float* out_u, float* out_ux, float* out_uxx, void* stream)

@@ -97,6 +97,31 @@ def test_dense_cuda_chunked_grid_matches_port(D, C, n, N):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("tag", ["f2", "f2asym", "f1", "f1c2"])
+def test_dense_cuda_multi_slot_kernels_match_golden(tag):
+    """The 4-/2-samples-per-thread forward and 2-Gaussians-per-thread backward instantiations (picked by size in
+    production) forced at golden size."""
+    import torch
+
+    from pigs_b200 import _lib
+    from pigs_b200 import gaussians as pg
+    c = _case(tag)
+    L = _lib.lib()
+    L.pigs_set_dense_slots(4, 2)
+    try:
+        m, k, v = (torch.from_numpy(c[x]).cuda().requires_grad_(True) for x in ("means", "conics", "values"))
+        outs = pg.dense_sample(7, m, k, v, torch.from_numpy(c["samples"]).cuda())
+        sum((o * torch.from_numpy(c["g" + key]).cuda()).sum() for o, (key, _) in zip(outs, FNS)).backward()
+        for o, (key, _) in zip(outs, FNS):
+            assert rel_err(o.detach().cpu().numpy(), c[key]) <= TOL, key
+        for t, suffix in ((m, "_dmeans"), (k, "_dconics"), (v, "_dvalues")):
+            want = sum(c[key + suffix].astype(np.float64) for key, _ in FNS)
+            assert rel_err(t.grad.cpu().numpy(), want) <= TOL, suffix
+    finally:
+        L.pigs_set_dense_slots(0, 0)
+
+
+@pytest.mark.gpu
 def test_dense_cuda_rejects_bad_shapes():
     import torch
 
