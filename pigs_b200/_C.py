@@ -580,7 +580,7 @@ def _dense_args(means, conics, values, samples):
     samples = _f32c(samples, "samples")
     if D not in (1, 2) or conics.numel() != n * D * D:
         raise RuntimeError("dense path: means [n, D] with D in (1, 2) and FULL conics [n, D, D] expected")
-    C = values.numel() // max(n, 1)
+    C = values.numel() // n if n > 0 else (values.shape[-1] if values.dim() > 1 else 1)
     if values.numel() != n * C or not 1 <= C <= 4:
         raise RuntimeError("dense path: values [n, C] with C <= 4 expected")
     N = samples.numel() // D

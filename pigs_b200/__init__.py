@@ -279,11 +279,11 @@ class GaussianSampler:
         sr = sample_ranges.view(torch.int32)[: 2 * b].view(b, 2).to(torch.int64)
         _, _, sl = _C.point_lists(self.num_rendered, self.binning_buffer, self.sample_binning_buffer, N)
         # sample_point_list is tile-major: tile t owns positions [sr[t,0], sr[t,1])
-        per_pos = torch.zeros(N, dtype=torch.int64, device=ranges.device)
         ns = sr[:, 1] - sr[:, 0]
-        starts = sr[:, 0]
-        pos = torch.repeat_interleave(starts - torch.cumsum(ns, 0) + ns, ns) + torch.arange(int(ns.sum()), device=ns.device)
-        per_pos[pos] = torch.repeat_interleave(g[:, 1] - g[:, 0], ns)
+        first = torch.cumsum(ns, 0) - ns                       # index of each tile's first entry in the concatenation
+        pos = torch.repeat_interleave(sr[:, 0] - first, ns) + torch.arange(int(ns.sum()), device=ns.device)
+        per_pos = torch.zeros(N, dtype=torch.int64, device=ranges.device)
+        per_pos[pos] = torch.repeat_interleave(g[:, 1] - g[:, 0], ns)   # Gaussians of the tile, once per sample of the tile
         w[sl.to(torch.int64)] = per_pos
         return w
 

@@ -131,3 +131,18 @@ def test_dense_cuda_rejects_bad_shapes():
         pg.sample_gaussians(m, torch.zeros(4, 3).cuda(), v, x)  # flattened conics are not the dense path's input
     with pytest.raises(RuntimeError):
         pg.sample_gaussians(torch.zeros(4, 3).cuda(), torch.zeros(4, 3, 3).cuda(), v, torch.zeros(8, 3).cuda())
+
+
+@pytest.mark.gpu
+def test_dense_cuda_empty_operands():
+    import torch
+
+    from pigs_b200 import gaussians as pg
+    m, k, v = torch.zeros(0, 2).cuda(), torch.zeros(0, 2, 2).cuda(), torch.zeros(0, 1).cuda()
+    u, ux, uxx = pg.dense_sample(7, m, k, v, torch.rand(5, 2).cuda())
+    assert u.shape == (5, 1) and ux.shape == (5, 2, 1) and uxx.shape == (5, 2, 2, 1) and not u.any() and not uxx.any()
+    m, k, v = torch.rand(3, 2).cuda().requires_grad_(True), torch.eye(2).repeat(3, 1, 1).cuda(), torch.ones(3, 1).cuda()
+    (u,) = pg.dense_sample(1, m, k, v, torch.zeros(0, 2).cuda())
+    assert u.shape == (0, 1)
+    u.sum().backward()
+    assert m.grad is not None and not m.grad.any()
