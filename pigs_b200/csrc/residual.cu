@@ -332,6 +332,9 @@ __global__ void __launch_bounds__(RES_THREADS) vorticity_backward_kernel(int64_t
     }
 }
 
+static inline bool al16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static inline bool al8(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 7) == 0; }
+
 static int res_grid(int64_t work)
 {
     int64_t nb = (work + RES_THREADS - 1) / RES_THREADS;
@@ -450,6 +453,7 @@ int pigs_pde_ns_residual_forward(int64_t N, float nu, float dt, const float* u, 
 {
     using namespace pigs;
     PIGS_ARG(N > 0 && u && ux && wx && wxx && wt && loss && workspace);
+    PIGS_ARG(al8(u) && al16(ux) && al8(wx) && al16(wxx));  // whole-row vector loads
     NsArgs a{N, nu, dt, (const float2*)u, (const float4*)ux, (const float2*)wx, (const float4*)wxx, wt};
     cudaStream_t st = (cudaStream_t)stream;
     const int nb = res_grid(N);
@@ -466,6 +470,7 @@ int pigs_pde_ns_residual_backward(int64_t N, float nu, float dt, const float* u,
 {
     using namespace pigs;
     PIGS_ARG(N > 0 && u && ux && wx && wxx && wt && dL_dloss);
+    PIGS_ARG(al8(u) && al16(ux) && al8(wx) && al16(wxx) && al8(dL_du) && al16(dL_dux) && al8(dL_dwx) && al16(dL_dwxx));
     NsArgs a{N, nu, dt, (const float2*)u, (const float4*)ux, (const float2*)wx, (const float4*)wxx, wt};
     NsGrads o{(float2*)dL_du, nullptr, (float4*)dL_dux, nullptr, (float2*)dL_dwx, nullptr, (float4*)dL_dwxx, nullptr, dL_dwt,
               nullptr};
@@ -482,6 +487,7 @@ int pigs_pde_ns_residual_timelevels_forward(int64_t N, float nu, float dt, const
 {
     using namespace pigs;
     PIGS_ARG(N > 0 && u1 && u0 && ux1 && ux0 && wx1 && wx0 && wxx1 && wxx0 && w1 && w0 && loss && workspace);
+    PIGS_ARG(al8(u1) && al8(u0) && al16(ux1) && al16(ux0) && al8(wx1) && al8(wx0) && al16(wxx1) && al16(wxx0));
     NsArgs a{N, nu, dt, (const float2*)u1, (const float4*)ux1, (const float2*)wx1, (const float4*)wxx1, w1};
     a.ts = ts, a.ts_const = ts_const, a.u0 = (const float2*)u0, a.ux0 = (const float4*)ux0, a.wx0 = (const float2*)wx0;
     a.wxx0 = (const float4*)wxx0, a.w0 = w0;
@@ -503,6 +509,8 @@ int pigs_pde_ns_residual_timelevels_backward(int64_t N, float nu, float dt, cons
 {
     using namespace pigs;
     PIGS_ARG(N > 0 && u1 && u0 && ux1 && ux0 && wx1 && wx0 && wxx1 && wxx0 && w1 && w0 && dL_dloss);
+    PIGS_ARG(al8(u1) && al8(u0) && al16(ux1) && al16(ux0) && al8(wx1) && al8(wx0) && al16(wxx1) && al16(wxx0));
+    PIGS_ARG(al8(dL_du1) && al8(dL_du0) && al16(dL_dux1) && al16(dL_dux0) && al8(dL_dwx1) && al8(dL_dwx0) && al16(dL_dwxx1) && al16(dL_dwxx0));
     NsArgs a{N, nu, dt, (const float2*)u1, (const float4*)ux1, (const float2*)wx1, (const float4*)wxx1, w1};
     a.ts = ts, a.ts_const = ts_const, a.u0 = (const float2*)u0, a.ux0 = (const float4*)ux0, a.wx0 = (const float2*)wx0;
     a.wxx0 = (const float4*)wxx0, a.w0 = w0;
@@ -517,6 +525,7 @@ int pigs_vorticity_forward(int64_t groups, const float* in, float* out, void* st
 {
     using namespace pigs;
     PIGS_ARG(groups > 0 && in && out);
+    PIGS_ARG(al16(in));
     vorticity_forward_kernel<<<res_grid(groups), RES_THREADS, 0, (cudaStream_t)stream>>>(groups, (const float4*)in, out);
     PIGS_LAUNCH_CHECK();
     return 0;
@@ -526,6 +535,7 @@ int pigs_vorticity_backward(int64_t groups, const float* dL_dout, float* dL_din,
 {
     using namespace pigs;
     PIGS_ARG(groups > 0 && dL_dout && dL_din);
+    PIGS_ARG(al16(dL_din));
     vorticity_backward_kernel<<<res_grid(groups), RES_THREADS, 0, (cudaStream_t)stream>>>(groups, dL_dout, (float4*)dL_din);
     PIGS_LAUNCH_CHECK();
     return 0;
