@@ -361,6 +361,7 @@ int launch_aggregate16_forward(int64_t P, int D, int L, int K, int E, const floa
                                cudaStream_t st)
 {
     if (L != 16 || K != 16 || E != 25) return 0;
+    if ((reinterpret_cast<uintptr_t>(features) & 15) != 0) return 0;  // 16-byte row loads
     int64_t grid = (P + 15) / 16;  // 16 rows per CTA (8 warps x 2)
     const int64_t cap = (int64_t)num_sms() * 16;
     if (grid > cap) grid = cap;
@@ -384,6 +385,8 @@ int launch_aggregate16_backward(int64_t P, int D, int L, int K, int E, const flo
                                 float* g_freqs, float* g_dt, cudaStream_t st)
 {
     if (L != 16 || K != 16 || E != 25) return 0;
+    // 16-byte row loads and vector REDs: rows of an unaligned view go through the generic kernels
+    if (((reinterpret_cast<uintptr_t>(features) | reinterpret_cast<uintptr_t>(g_features) | reinterpret_cast<uintptr_t>(g_keys)) & 15) != 0) return 0;
     int64_t grid = (P + 15) / 16;
     const int64_t cap = (int64_t)num_sms() * 8;  // few CTAs: every CTA ends with ~360 atomics on the shared parameters
     if (grid > cap) grid = cap;
