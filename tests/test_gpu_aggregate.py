@@ -209,3 +209,26 @@ def test_row_sharded_lists_and_aggregation(name, nb_path):
     assert torch.equal(out_sum, out_full)
     for key, got, want in zip(AGG_KEYS, g_sum, g_full):
         assert rel_err(got.cpu().numpy(), want.cpu().numpy()) <= TOL, key
+
+
+def test_unaligned_feature_rows_take_the_generic_kernels():
+    """A features tensor whose storage starts 4 bytes off a 16-byte boundary (a view into a larger buffer): the specialised
+    kernels' 16-byte row loads / vector REDs do not apply, the call falls back to the generic kernels, same results."""
+    import torch
+    rec = AGG_RECIPES["agg_model"]()
+    s, d = _prep(rec)
+    t = [d[k].clone() for k in AGG_KEYS]
+    want = s.aggregate_neighbors(*t)
+    feat = t[0]
+    buf = torch.empty(feat.numel() + 1, dtype=torch.float32, device="cuda")
+    off = buf[1:].view(feat.shape)
+    off.copy_(feat)
+    assert off.data_ptr() % 16 == 4 and off.is_contiguous()
+    off.requires_grad_(True)
+    ref = feat.clone().requires_grad_(True)
+    got = s.aggregate_neighbors(off, *t[1:])
+    assert rel_err(got.detach().cpu().numpy(), want.cpu().numpy()) <= TOL
+    up = torch.from_numpy(agg_upstream(rec)).cuda()
+    got.backward(up)
+    s.aggregate_neighbors(ref, *t[1:]).backward(up)
+    assert rel_err(off.grad.cpu().numpy(), ref.grad.cpu().numpy()) <= TOL
