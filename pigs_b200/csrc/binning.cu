@@ -24,7 +24,8 @@ __global__ void bounds_init(float* mm, int D)
 }
 
 template <int D>
-__global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ samples, int64_t N, float* __restrict__ mm)
+__global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ samples, int64_t N, float* __restrict__ mm,
+                                                     bool pair_loads)
 {
     float lo[D], hi[D];
 #pragma unroll
@@ -35,7 +36,9 @@ __global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ s
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += stride) {
         if (D == 2) {
-            const float2 p = reinterpret_cast<const float2*>(samples)[i];
+            // 8-byte loads when the caller's tensor is 8-byte aligned (a view at an odd float offset is not)
+            const float2 p = pair_loads ? reinterpret_cast<const float2*>(samples)[i]
+                                        : make_float2(samples[2 * i], samples[2 * i + 1]);
             lo[0] = fminf(lo[0], p.x);
             hi[0] = fmaxf(hi[0], p.x);
             lo[D - 1] = fminf(lo[D - 1], p.y);
@@ -467,9 +470,9 @@ int pigs_sample_bounds(const float* samples, int64_t N, int D, float* d_minmax, 
     const int cap = num_sms() * 8;
     if (nb > cap) nb = cap;
     if (D == 2)
-        bounds_kernel<2><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax);
+        bounds_kernel<2><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, (reinterpret_cast<uintptr_t>(samples) & 7) == 0);
     else
-        bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax);
+        bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, false);
     PIGS_LAUNCH_CHECK();
     return 0;
 }

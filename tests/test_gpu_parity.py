@@ -4,7 +4,7 @@ derivatives and parameter gradients (BASELINE.json north_star)."""
 import numpy as np
 import pytest
 
-from tests.fixtures import RECIPES
+from tests.fixtures import RECIPES, synthetic
 from tests.helpers import TOL, oracle_state, ranges_np, rel_err, to_dev, upstream
 from oracle import pigs_oracle as po
 
@@ -180,3 +180,40 @@ def test_noncontiguous_and_dtype_errors(torch_mod):
     assert torch.equal(a, s.sample_gaussians())
     with pytest.raises(RuntimeError):
         s.preprocess(d["means"].double(), d["values"], d["covariances"], d["conics"], d["samples"])
+
+
+@pytest.mark.gpu
+def test_inputs_at_odd_float_offsets(torch_mod):
+    """Every input a contiguous view that starts 4 bytes off an 8-/16-byte boundary (a slice of a larger buffer): no
+    kernel may assume more alignment of the caller's tensors than a float's.  Same bins, same values, same gradients."""
+    torch = torch_mod
+    from pigs_b200 import GaussianSampler, _C
+    rec = synthetic(1500, 9000, seed=77)
+
+    def off(a):
+        t = torch.from_numpy(a).cuda()
+        buf = torch.empty(t.numel() + 1, dtype=t.dtype, device="cuda")
+        v = buf[1:].view(t.shape)
+        v.copy_(t)
+        assert v.data_ptr() % 8 == 4 and v.is_contiguous()
+        return v
+
+    res = []
+    for make in (lambda a: torch.from_numpy(a).cuda(), off):
+        d = {k: make(v) for k, v in rec.items()}
+        for k in ("means", "values", "conics"):
+            d[k].requires_grad_(True)
+        s = GaussianSampler(False)
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        outs = s.sample_fused(7)
+        sum((o * torch.from_numpy(upstream(rec, fn)).cuda()).sum() for fn, o in enumerate(outs)).backward()
+        pl, _, sl = _C.point_lists(s.num_rendered, s.binning_buffer, s.sample_binning_buffer, rec["samples"].shape[0])
+        res.append(dict(nr=s.num_rendered, pl=pl.cpu().numpy(), sl=sl.cpu().numpy(), radii=s.radii.cpu().numpy(),
+                        outs=[o.detach().cpu().numpy() for o in outs],
+                        grads=[d[k].grad.cpu().numpy() for k in ("means", "values", "conics")]))
+    a, b = res
+    assert a["nr"] == b["nr"]
+    for k in ("pl", "sl", "radii"):
+        np.testing.assert_array_equal(a[k], b[k])
+    for x, y in zip(a["outs"] + a["grads"], b["outs"] + b["grads"]):
+        assert rel_err(y, x) <= TOL
