@@ -416,8 +416,13 @@ def pde_residual_backward(problem, u, ux, lap, ut, nu, dt, g_loss, need=(True, T
 
 
 # ---- NAVIER_STOKES residual (vorticity form) + vorticity extraction (model_pn.py:629-631, 779-781, 818, 843-845) ----
+def _al16(t):
+    """the NAVIER_STOKES / vorticity kernels read whole rows as 8-/16-byte vectors: a view at an odd float offset is copied"""
+    return t if t.data_ptr() % 16 == 0 else t.clone(memory_format=torch.contiguous_format)
+
+
 def _ns_args(u, ux, wx, wxx, wt):
-    u, ux, wx, wxx, wt = (_f32c(t, n) for t, n in ((u, "u"), (ux, "ux"), (wx, "wx"), (wxx, "wxx"), (wt, "wt")))
+    u, ux, wx, wxx, wt = (_al16(_f32c(t, n)) for t, n in ((u, "u"), (ux, "ux"), (wx, "wx"), (wxx, "wxx"), (wt, "wt")))
     N = wt.numel()
     if u.numel() != 2 * N or ux.numel() != 4 * N or wx.numel() != 2 * N or wxx.numel() != 4 * N:
         raise RuntimeError("NAVIER_STOKES residual: u [N,2], ux [N,2,2], wx [N,2], wxx [N,2,2], wt [N] expected")
@@ -553,7 +558,7 @@ def pde_ns_residual_timelevels_backward(ts, u, ux, wx, wxx, w, nu, dt, g_loss, n
 def vorticity_forward(x):
     """x [..., 2, 2] (trailing axes: spatial axis, channel; C = 2) -> x[..., 0, 1] - x[..., 1, 0], shape x.shape[:-2]."""
     L = _lib.lib()
-    x = _f32c(x, "x")
+    x = _al16(_f32c(x, "x"))
     if x.dim() < 2 or x.shape[-1] != 2 or x.shape[-2] != 2:
         raise RuntimeError("vorticity: trailing axes must be [2 (spatial), 2 (channels)]")
     out = torch.empty(x.shape[:-2], dtype=torch.float32, device=x.device)

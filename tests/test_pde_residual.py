@@ -377,3 +377,32 @@ def test_residual_large_and_chain_through_sampler():
             acc += p.reshape(acc.shape)
     for k, w in zip(("means", "values", "conics"), want):
         assert rel_err(d[k].grad.cpu().numpy().reshape(w.shape), w) <= 2 * TOL, k
+
+
+@pytest.mark.gpu
+def test_navier_stokes_inputs_at_odd_float_offsets():
+    """Views that start 4 bytes off a 16-byte boundary are copied by the binding (the kernels read whole rows as vectors;
+    the C ABI itself answers a misaligned pointer with 'bad argument')."""
+    import torch
+
+    from pigs_b200 import _lib, pde
+    c = _case("navier_stokes_b")
+    nu, dt = float(c["nu"]), float(c["dt"])
+
+    def off(a):
+        t = torch.from_numpy(a).cuda()
+        buf = torch.empty(t.numel() + 1, dtype=torch.float32, device="cuda")
+        v = buf[1:].view(t.shape)
+        v.copy_(t)
+        return v
+
+    uxx, uxxx = off(c["uxx"]), off(c["uxxx"])
+    assert uxx.data_ptr() % 16 == 4
+    np.testing.assert_array_equal(pde.vorticity(uxx).cpu().numpy(), c["wx"])
+    loss = pde.navier_stokes_residual_loss(off(c["u"]), off(c["ux"]), pde.vorticity(uxx), pde.vorticity(uxxx), off(c["wt"]), dt, nu)
+    assert abs(float(loss) - float(c["loss"])) <= TOL * abs(float(c["loss"]))
+    L = _lib.lib()
+    out = torch.empty(c["wx"].size, dtype=torch.float32, device="cuda")
+    import ctypes
+    rc = L.pigs_vorticity_forward(out.numel(), ctypes.c_void_p(uxx.data_ptr()), ctypes.c_void_p(out.data_ptr()), None)
+    assert rc != 0 and b"bad argument" in L.pigs_last_error()
