@@ -16,6 +16,8 @@ timeout 600 python bench.py --impl reference > $OUT/bench_reference_arm.json 2> 
 timeout 600 python tools/quick_perf.py --big > $OUT/quick_perf.log 2>&1; echo "quick exit $?"
 cat $OUT/quick_perf.log | tail -12
 timeout 600 python tools/bench_hbm.py > $OUT/hbm_kernels.json 2> $OUT/hbm.err; echo "hbm exit $?"
+timeout 300 python tools/bench_dense.py > $OUT/dense.json 2> $OUT/dense.err; echo "dense exit $?"
+timeout 300 python tools/bench_c5.py > $OUT/c5_stages.json 2> $OUT/c5.err; echo "c5 exit $?"
 # launch list of the same bench command (per-launch times are cold-cache and serialised)
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $OUT/launches_c3.csv \
     python bench.py --steps 2 --warmup 1 --no-cpu-baseline --no-e2e > $OUT/ncu_launch.log 2>&1; echo "ncu launch exit $?"
