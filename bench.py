@@ -19,6 +19,14 @@ values (-> NCCL all-reduce of the packed gradients when N > 1).  value = pairs o
 Workloads (tests/fixtures.synthetic, seed 0): C3 = 1M Gaussians x 4M points (default; the config
 the metric is quoted on and the one sharded over 1/2/4/8 GPUs), C2 = 100K x 1M, C4 = 500K anisotropic x 2M torus.
 N > 1: the 4M points are split evenly over the ranks (strong scaling), Gaussians replicated.
+
+Extra legs, run AFTER the timed C3 region and reported under "legs" in the same JSON line (--no-legs skips them):
+  c5       : BASELINE config 5 — one model_pn.py-style step at 1M Gaussians (preprocess with samples = means -> u, grad u,
+             Hessian without grad (model_pn.py:644-652) -> neighbour aggregation on a 16-regular CSR, 2 heads forward +
+             backward (model_pn.py:253-274)); row-parallel over the ranks when N > 1.  Runs at every N.
+  c1/c2/c4 : the other BASELINE configs, device-resident and end-to-end, N = 1 only
+  ref_cuda : the UNMODIFIED reference CUDA extension (oracle/_ref/_C.so, built by oracle/build_ref.sh) on the same GPU
+             and inputs next to ours, 20K Gaussians x 200K points (BASELINE.md's "GPU baseline to beat"), N = 1 only
 """
 import argparse
 import ctypes
@@ -48,21 +56,42 @@ LANE_OPS_FWD, LANE_OPS_BWD = 19, 45  # algorithmic FP32 lane-ops per pair (SURVE
 EXEC_OPS_FWD, EXEC_OPS_BWD = 18.0, 36.5  # FP32 lane-ops per pair the kernels actually execute (SASS count, tools/sass_issue_model.py)
 
 
+EVAL_SOURCES = ("eval_bwd.cu", "eval_fwd.cu", "eval_common.cuh", "common.cuh", "pack.cu")
+
+
+def eval_source_sha():
+    """sha1 over the evaluation-kernel sources: tools/ncu_summary.py stamps it into every ncu summary it writes, so a
+    summary taken on an older kernel is recognised as stale here."""
+    import hashlib
+    h = hashlib.sha1()
+    for name in EVAL_SOURCES:
+        with open(os.path.join(ROOT, "pigs_b200", "csrc", name), "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()[:16]
+
+
 def ncu_traffic():
-    """DRAM bytes per launch of the dominant kernel from the newest committed `ncu --set full` summary (profiles/), or
-    None.  bench.py cannot measure DRAM traffic itself; the summary is of the same command (tools/gpu_round.sh)."""
+    """DRAM bytes per launch of the dominant kernel from the newest committed `ncu --set full` summary (profiles/) that
+    was taken on the CURRENT kernel sources, or a note saying the newest one is stale.  bench.py cannot measure DRAM
+    traffic itself; the summary is of the same command (tools/gpu_round.sh)."""
     import glob
-    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_eval_c3.json")), reverse=True):
+    sha = eval_source_sha()
+    stale = None
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_eval_c3.json")), key=os.path.getmtime, reverse=True):
         try:
             d = json.load(open(path))
             for k in d["kernels"]:
                 if "eval_bwd_kernel<2, 1, 7, 0>" in k["kernel"] and k.get("dram_read_bytes") == k.get("dram_read_bytes"):
+                    if d.get("source_sha") != sha:
+                        stale = stale or os.path.basename(path)
+                        break
                     return {"dram_bytes_per_launch": k["dram_read_bytes"] + k["dram_write_bytes"],
                             "kernel": "eval_bwd_kernel<2,1,7,FAST> at C3, 1 GPU",
-                            "source": "profiles/" + os.path.basename(path)}
+                            "source": "profiles/%s (kernel sources %s)" % (os.path.basename(path), sha)}
         except Exception:
             continue
-    return None
+    return {"dram_bytes_per_launch": None, "kernel": "no ncu summary of the current kernel sources (%s)" % sha,
+            "source": ("newest summary profiles/%s predates the last kernel change" % stale) if stale else ""}
 
 
 def parse_args():
@@ -74,6 +103,7 @@ def parse_args():
     ap.add_argument("--workload", default=os.environ.get("PIGS_BENCH_WORKLOAD", "C3"), choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-legs", action="store_true", help="skip the c5 / c1 / c2 / c4 / ref_cuda legs")
     return ap.parse_args()
 
 
@@ -172,11 +202,24 @@ def microbench_peaks(L, torch):
     return res
 
 
-def cpu_baseline(workload, budget_s=12.0):
-    """Reference's pure-PyTorch dense CPU path (port) on a bounded dense slice of the workload."""
-    import torch
+PAIR_DEF_GPU = ("reference pair set (SURVEY.md S8): pairs (Gaussian, point) with the point's 0.51-wide tile inside the "
+                "Gaussian's 3-sigma tile rectangle — what the reference extension evaluates")
+PAIR_DEF_CPU = ("dense all-pairs: every (Gaussian, point) of the slice — the reference's pure-PyTorch gaussians.py path has no "
+                "cutoff, so its pairs/s counts a different (larger) pair set per sample than the GPU arm's reference pair set")
 
-    from oracle import dense_torch as dt
+
+def _all_threads(torch):
+    """torchrun exports OMP_NUM_THREADS=1: the CPU arm takes every host core explicitly."""
+    n = os.cpu_count() or 1
+    try:
+        torch.set_num_threads(n)
+    except Exception:
+        pass
+    return torch.get_num_threads()
+
+
+def _dense_slice(workload):
+    import torch
     from tests.fixtures import synthetic
     P, N, kw, _ = WORKLOADS[workload]
     n, m = min(P, 1000), min(N, 10000)  # dense intermediates are O(n*m*d*d*4 B)
@@ -186,67 +229,72 @@ def cpu_baseline(workload, budget_s=12.0):
     si = np.sort(rng.choice(rec["samples"].shape[0], m, replace=False))
     means, conics, values = (torch.from_numpy(rec[k][gi]) for k in ("means", "conics", "values"))
     samples = torch.from_numpy(rec["samples"][si])
+    return means, conics, values, samples, n, m
+
+
+def cpu_baseline(workload, budget_s=12.0):
+    """Reference's pure-PyTorch dense CPU path (port) on a bounded dense slice of the workload."""
+    import torch
+
+    from oracle import dense_torch as dt
+    threads = _all_threads(torch)
+    means, conics, values, samples, n, m = _dense_slice(workload)
     t1, pairs = dt.timed_steps(means, conics, values, samples, 1, 1)
     steps = int(max(1, min(8, budget_s / max(t1[0], 1e-3) - 2)))
     times, pairs = dt.timed_steps(means, conics, values, samples, steps, 0)
     best = min(times + t1)
-    return {"value": pairs / best, "unit": UNIT, "cores": torch.get_num_threads(), "host_cpus": os.cpu_count(),
-            "kind": "port",
+    return {"value": pairs / best, "unit": UNIT, "cores": threads, "host_cpus": os.cpu_count(),
+            "kind": "port", "pair_definition": PAIR_DEF_CPU,
             "sample": "dense all-pairs slice of %s: %d Gaussians x %d points, u + grad u + Hessian forward and "
                       "autograd backward, oracle/dense_torch.py restating gaussians.py:48-116; best of %d" %
                       (workload, n, m, len(times) + 1)}
 
 
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
+class SamplingRun:
+    """One sampling workload (preprocess + fused u / grad u / Hessian forward + fused backward) on this rank's shard:
+    the device-resident step, the end-to-end step through the public API, and their timing."""
 
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if not torch.cuda.is_available():
-        raise RuntimeError("bench.py needs a CUDA device: pigs_b200 has no CPU path (use --impl reference for the CPU arm)")
-    torch.cuda.set_device(local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    from pigs_b200 import _C, _lib
-    from pigs_b200.sharded import ShardedGaussianSampler, allreduce_bounds, allreduce_grads
-    L = _lib.lib()
-    P, N, _, desc = WORKLOADS[args.workload]
-    rec, ups = make_inputs(args.workload, rank, world)
-    host = {k: torch.from_numpy(v).pin_memory() for k, v in rec.items()}
-    host_ups = [torch.from_numpy(u).pin_memory() for u in ups]
-    dev = {k: v.cuda(non_blocking=True) for k, v in host.items()}
-    dev_ups = [u.cuda(non_blocking=True) for u in host_ups]
-    torch.cuda.synchronize()
-    D, Nl = dev["means"].shape[1], dev["samples"].shape[0]
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
+    def __init__(self, workload, torch, dist, L, rank, world):
+        from pigs_b200 import _C, _lib
+        self.torch, self.dist, self.L, self.rank, self.world = torch, dist, L, rank, world
+        self._C, self._lib = _C, _lib
+        self.workload = workload
+        self.P, self.N, _, self.desc = WORKLOADS[workload]
+        rec, ups = make_inputs(workload, rank, world)
+        self.host = {k: torch.from_numpy(v).pin_memory() for k, v in rec.items()}
+        self.host_ups = [torch.from_numpy(u).pin_memory() for u in ups]
+        self.dev = {k: v.cuda(non_blocking=True) for k, v in self.host.items()}
+        self.dev_ups = [u.cuda(non_blocking=True) for u in self.host_ups]
         torch.cuda.synchronize()
+        self.D, self.Nl = self.dev["means"].shape[1], self.dev["samples"].shape[0]
+        self.state = {}
 
-    # ---------------- device-resident step (value) ----------------
-    state = {}
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
 
-    def step_device():
-        mm = _C.sample_bounds(dev["samples"], D)
-        if world > 1:
-            allreduce_bounds(mm, D)
+    def step_device(self):
+        from pigs_b200.sharded import allreduce_bounds, allreduce_grads
+        _C, dev, ups = self._C, self.dev, self.dev_ups
+        mm = _C.sample_bounds(dev["samples"], self.D)
+        if self.world > 1:
+            allreduce_bounds(mm, self.D)
         nr, bb, sbb, rg, srg, radii = _C.preprocess_gaussians(dev["means"], dev["values"], dev["covariances"],
                                                               dev["conics"], dev["samples"], False, bounds=mm)
         a = (dev["means"], dev["values"], dev["conics"], dev["samples"], nr)
         outs = _C.sample_forward(7, *a, bb, sbb, rg, srg, False)
-        dm, dv, dc = _C.sample_backward(7, *a, [dev_ups[0], dev_ups[1], dev_ups[2], None], bb, sbb, rg, srg, False)
-        if world > 1:
+        dm, dv, dc = _C.sample_backward(7, *a, [ups[0], ups[1], ups[2], None], bb, sbb, rg, srg, False)
+        if self.world > 1:
             allreduce_grads(_C.packed_base(dm))
-        state.update(rg=rg, srg=srg, outs=outs, grads=(dm, dv, dc))
+        self.state.update(rg=rg, srg=srg, outs=outs, grads=(dm, dv, dc))
 
-    def timed(fn, steps, warmup, sampler=None):
+    def timed(self, fn, steps, warmup, sampler=None):
+        torch = self.torch
         for _ in range(warmup):
             fn()
-        barrier()
-        n0 = L.pigs_launch_count()
+        self.barrier()
+        n0 = self.L.pigs_launch_count()
         if sampler:
             sampler.start()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -254,60 +302,55 @@ def run_ours(args):
         for _ in range(steps):
             fn()
         b.record()
-        barrier()
+        self.barrier()
         if sampler:
             sampler.stop()
         ms = torch.tensor([a.elapsed_time(b)], device="cuda")
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), L.pigs_launch_count() - n0
+        if self.world > 1:
+            self.dist.all_reduce(ms, op=self.dist.ReduceOp.MAX)
+        return float(ms.item()), self.L.pigs_launch_count() - n0
 
-    clocks = ClockSampler(local)
-    peaks = microbench_peaks(L, torch) if rank == 0 else None
-    step_device()
-    # pair count of this rank's shard from the ranges arrays, summed over ranks
-    b = state["rg"].numel() // 8 - 1
-    g = state["rg"].view(torch.int32)[:2 * b].view(b, 2).to(torch.int64)
-    s = state["srg"].view(torch.int32)[:2 * b].view(b, 2).to(torch.int64)
-    pairs_local = ((g[:, 1] - g[:, 0]) * (s[:, 1] - s[:, 0])).sum()
-    pairs_t = pairs_local.clone()
-    if world > 1:
-        dist.all_reduce(pairs_t)
-    pairs, pairs_local = int(pairs_t.item()), int(pairs_local.item())
+    def count_pairs(self):
+        """pair count of this rank's shard from the ranges arrays, and summed over ranks"""
+        torch = self.torch
+        self.step_device()
+        b = self.state["rg"].numel() // 8 - 1
+        g = self.state["rg"].view(torch.int32)[:2 * b].view(b, 2).to(torch.int64)
+        s = self.state["srg"].view(torch.int32)[:2 * b].view(b, 2).to(torch.int64)
+        pairs_local = ((g[:, 1] - g[:, 0]) * (s[:, 1] - s[:, 0])).sum()
+        pairs_t = pairs_local.clone()
+        if self.world > 1:
+            self.dist.all_reduce(pairs_t)
+        self.pairs, self.pairs_local = int(pairs_t.item()), int(pairs_local.item())
+        return self.pairs
 
-    L.pigs_set_kernel_timing(1)
-    for w in (0, 1):  # drop events recorded so far
-        L.pigs_kernel_timing_read(w, ctypes.byref(ctypes.c_float()), ctypes.byref(ctypes.c_int()))
-    L.pigs_set_kernel_timing(0)
-    for _ in range(args.warmup):
-        step_device()
-    L.pigs_set_kernel_timing(1)
-    total_ms, launches = timed(step_device, args.steps, 0, clocks)
-    L.pigs_set_kernel_timing(0)
-    kt = {}
-    for w, nm in ((0, "fwd"), (1, "bwd")):
-        ms, n = ctypes.c_float(), ctypes.c_int()
-        _lib.check(L.pigs_kernel_timing_read(w, ctypes.byref(ms), ctypes.byref(n)), "pigs_kernel_timing_read")
-        kt[nm] = (ms.value / max(n.value, 1), n.value)
-    ms_per_step = total_ms / args.steps
-    value = pairs / (ms_per_step * 1e-3)
-    # per-rank kernel times and pair counts (load balance of the sample shards; rank 0 prints them)
-    per_rank = torch.tensor([kt["fwd"][0], kt["bwd"][0], float(pairs_local)], device="cuda", dtype=torch.float64)
-    if world > 1:
-        gathered = [torch.zeros_like(per_rank) for _ in range(world)]
-        dist.all_gather(gathered, per_rank)
-        per_rank_rows = [[float(v) for v in g.tolist()] for g in gathered]
-    else:
-        per_rank_rows = [[float(v) for v in per_rank.tolist()]]
-    launches_t = torch.tensor([launches], device="cuda", dtype=torch.int64)
-    if world > 1:
-        dist.all_reduce(launches_t)
+    def run_device(self, steps, warmup, clocks=None):
+        """-> (ms_per_step max over ranks, launches, {fwd: (ms per launch group, n), bwd: ...} of this rank)"""
+        L, _lib = self.L, self._lib
+        L.pigs_set_kernel_timing(1)
+        for w in (0, 1):  # drop events recorded so far
+            L.pigs_kernel_timing_read(w, ctypes.byref(ctypes.c_float()), ctypes.byref(ctypes.c_int()))
+        L.pigs_set_kernel_timing(0)
+        for _ in range(warmup):
+            self.step_device()
+        L.pigs_set_kernel_timing(1)
+        total_ms, launches = self.timed(self.step_device, steps, 0, clocks)
+        L.pigs_set_kernel_timing(0)
+        kt = {}
+        for w, nm in ((0, "fwd"), (1, "bwd")):
+            ms, n = ctypes.c_float(), ctypes.c_int()
+            _lib.check(L.pigs_kernel_timing_read(w, ctypes.byref(ms), ctypes.byref(n)), "pigs_kernel_timing_read")
+            kt[nm] = (ms.value / max(n.value, 1), n.value)
+        return total_ms / steps, launches, kt
 
-    # ---------------- end-to-end step through the public API with host buffers ----------------
-    e2e = None
-    if not args.no_e2e:
-        sampler = ShardedGaussianSampler(False, group=None) if world > 1 else None
-        if sampler is None:
+    def run_e2e(self, steps, warmup):
+        """The same step through the reference-shaped public API with HOST buffers: inputs copied from pinned memory,
+        u and the three gradients read back, every step, inside the timed region."""
+        torch, P, D, Nl, host, host_ups = self.torch, self.P, self.D, self.Nl, self.host, self.host_ups
+        from pigs_b200.sharded import ShardedGaussianSampler
+        if self.world > 1:
+            sampler = ShardedGaussianSampler(False, group=None)
+        else:
             from diff_gaussian_sampling import GaussianSampler
             sampler = GaussianSampler(False)
         K = D * (D + 1) // 2
@@ -334,28 +377,318 @@ def run_ours(args):
             hu.copy_(u.detach(), non_blocking=True)
             torch.cuda.current_stream().synchronize()
 
-        e_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 2))
-        e2e = {"value": pairs / (e_ms / args.steps * 1e-3), "unit": UNIT, "ms_per_step": e_ms / args.steps,
-               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "api": "diff_gaussian_sampling.GaussianSampler.preprocess/sample_gaussians/_derivative/_laplacian + loss.backward()"}
+        e_ms, _ = self.timed(step_e2e, steps, max(warmup, 2))
+        return {"value": self.pairs / (e_ms / steps * 1e-3), "unit": UNIT, "ms_per_step": e_ms / steps,
+                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "api": "diff_gaussian_sampling.GaussianSampler.preprocess/sample_gaussians/_derivative/_laplacian + loss.backward()"}
+
+
+def fp32_peak(torch, ck):
+    sms = torch.cuda.get_device_properties(0).multi_processor_count
+    fmax = (ck.get("sm_max_mhz") or 1965.0) * 1e6
+    return sms, fmax, sms * 128 * fmax / 1e12
+
+
+def leg_sampling(name, torch, dist, L, steps, warmup):
+    """BASELINE configs other than the headline one (N = 1): device-resident and end-to-end step of the same path."""
+    run = SamplingRun(name, torch, dist, L, 0, 1)
+    pairs = run.count_pairs()
+    ms, launches, kt = run.run_device(steps, warmup)
+    e2e = run.run_e2e(steps, warmup)
+    out = {"workload": "%s: %s" % (name, run.desc), "gaussians": run.P, "points": run.N, "pairs": pairs, "steps": steps,
+           "warmup": warmup, "ms_per_step": ms, "value": pairs / (ms * 1e-3), "unit": UNIT,
+           "kernel_ms": {"eval_fwd": kt["fwd"][0], "eval_bwd": kt["bwd"][0], "other_per_step": ms - kt["fwd"][0] - kt["bwd"][0]},
+           "gpu_launches_per_step": launches / steps,
+           "e2e": {k: e2e[k] for k in ("value", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step")}}
+    if run.D == 2 and kt["bwd"][0] > 0:
+        _, _, peak = fp32_peak(torch, {})
+        out["roofline_frac_fwd_bwd"] = pairs * (LANE_OPS_FWD + LANE_OPS_BWD) / ((kt["fwd"][0] + kt["bwd"][0]) * 1e-3) / 1e12 / peak
+    else:
+        out["bound"] = "launch latency (1-D, 1K x 10K: the step is a chain of dependent launches of a few us each)"
+    return out
+
+
+def hbm_peak():
+    try:
+        return float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs"
+    except Exception:
+        return 6550.0, "fallback: B200_PROFILING.md measured copy bandwidth"
+
+
+def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
+    """BASELINE config 5 (model_pn.py neighbour aggregation + PDE step, 1M Gaussians, 16 neighbours).  One step = the
+    library calls of one Model.forward + loss backward around the (torch, out-of-scope) MLP:
+      preprocess(samples = means) -> sample_gaussians / _derivative / _laplacian without grad (model_pn.py:644-652)
+      -> preprocess_aggregate + ATTENTION_HEADS = 2 x aggregate_neighbors forward, then backward (model_pn.py:253-274).
+    Neighbour lists: a 16-regular CSR (the reference's own rule yields ~1.6 K neighbours at this P), passed
+    as plain inputs like the reference API allows.  N > 1 (row-parallel): every rank samples at ITS window
+    of the means (windows of equal pair counts) and owns that window's rows of features / queries / keys, of the output
+    and of the gradients; halo rows travel point to point, the shared parameters' gradients are all-reduced."""
+    from scipy.spatial import cKDTree
+
+    from pigs_b200 import _C
+    from pigs_b200.sharded import ShardedGaussianSampler, balanced_ranges
+    from tests.fixtures import agg_params, synthetic
+    P, k, HEADS = 1_000_000, 16, 2
+    rec = synthetic(P, 16, seed=0)
+    d = {kk: torch.from_numpy(v).cuda() for kk, v in rec.items()}
+    s = ShardedGaussianSampler(False)
+    if world > 1:
+        # set-up, not timed: one binning pass over ALL means -> per-row pair counts -> windows of equal evaluation work
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["means"])
+        lo, hi = balanced_ranges(s.pair_weights(), world)[rank]
+        split = "equal pair counts (sharded.balanced_ranges over GaussianSampler.pair_weights)"
+    else:
+        lo, hi = 0, P
+        split = "single window"
+    n = hi - lo
+    mine = d["means"][lo:hi].contiguous()
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], mine)
+    _, idx = cKDTree(rec["means"]).query(rec["means"][lo:hi], k=k, workers=-1)
+    indices = torch.from_numpy(np.sort(idx.astype(np.int64), axis=1).reshape(-1)).cuda()
+    ranges = ((torch.arange(1, P + 1, device="cuda") - lo).clamp(0, n) * k).contiguous()
+    i_of = torch.arange(lo, hi, device="cuda").repeat_interleave(k)
+    X = d["means"][indices] - d["means"][i_of]
+    X = torch.where(X.abs() > 1, X - 2 * torch.sign(X), X)
+    dists = (X / (0.333 * s.radii[i_of] + 1e-6).unsqueeze(1)).contiguous()
+    cj = d["conics"][indices]
+    dens = torch.exp(-0.5 * (cj[:, 0] * X[:, 0] ** 2 + cj[:, 2] * X[:, 1] ** 2) - cj[:, 1] * X[:, 0] * X[:, 1]).contiguous()
+    inv_total = torch.full((P,), 1e6, device="cuda")
+    inv_total[lo:hi] = 1.0 / (dens.view(n, k).sum(1) + 1e-6)
+    csr = (indices, ranges, dists, dens, inv_total)
+    del X, cj, i_of
+    heads = []
+    for h in range(HEADS):
+        ap = agg_params(P, 16, 16, 25, 2, seed=100 + h)
+        heads.append({kk: torch.from_numpy(v[lo:hi] if kk in ("features", "queries", "keys") else v).cuda().contiguous()
+                      for kk, v in ap.items()})
+    feat = heads[0]["features"].requires_grad_(True)          # shared by the heads (model_pn.py:256-262)
+    freq = heads[0]["frequencies"].requires_grad_(True)
+    per_head = [[hd[kk].requires_grad_(True) for kk in ("transform", "queries", "keys", "distance_transform")] for hd in heads]
+    leaves = [feat, freq] + [t for ph in per_head for t in ph]
+    gs = [torch.randn(n, 16, device="cuda", generator=torch.Generator(device="cuda").manual_seed(7 + h)) for h in range(HEADS)]
+
+    def sampling():
+        with torch.no_grad():
+            s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], mine)
+            return s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_gaussians_laplacian()
+
+    def aggregation():
+        s.preprocess_aggregate(row_range=(lo, hi), csr=csr)
+        outs = [s.aggregate_neighbors_rows(feat, T, Q, Kk, freq, DT) for T, Q, Kk, DT in per_head]
+        for t in leaves:
+            t.grad = None
+        torch.autograd.backward(outs, gs)
+
+    def step():
+        sampling()
+        aggregation()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        n0 = L.pigs_launch_count()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            fn()
+        b.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        ms = torch.tensor([a.elapsed_time(b) / steps], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()), (L.pigs_launch_count() - n0) / steps
+
+    ms_step, launches = timed(step, steps, warmup)
+    ms_samp, _ = timed(sampling, steps, 1)
+    ms_agg, _ = timed(aggregation, steps, 1)
+    # aggregation kernels alone (one head), for their HBM roofline on this rank's window
+    plan = s.row_plan
+    T, Q, Kk, DT = [t.detach() for t in per_head[0]]
+    f_full, k_full = feat.detach(), Kk
+    if not (world == 1):
+        f_full = torch.zeros(P, 16, device="cuda")
+        k_full = torch.zeros(P, 16, device="cuda")
+        f_full[lo:hi], k_full[lo:hi] = feat.detach(), Kk
+        plan.gather([f_full, k_full])
+    w_, e_, f_, _ = _C.aggregate_neighbors_rows(f_full, T, Q, k_full, freq.detach(), DT, *csr, (lo, hi), False)
+    gf, gk = torch.zeros_like(f_full), torch.zeros_like(k_full)
+    ms_kf, _ = timed(lambda: _C.aggregate_neighbors_rows(f_full, T, Q, k_full, freq.detach(), DT, *csr, (lo, hi), False), steps, 2)
+    ms_kb, _ = timed(lambda: _C.aggregate_neighbors_rows_backward(f_full, T, Q, k_full, freq.detach(), DT, indices, ranges,
+                                                                  dists, dens, w_, e_, f_, inv_total, gs[0], gf, gk, (lo, hi),
+                                                                  False), steps, 2)
+    pairs_t = torch.zeros(world, device="cuda", dtype=torch.int64)
+    pairs_t[rank] = s.pair_count()
+    rows_t = torch.zeros(world, device="cuda", dtype=torch.int64)
+    rows_t[rank] = n
+    if world > 1:
+        dist.all_reduce(pairs_t)
+        dist.all_reduce(rows_t)
+    peak, peak_src = hbm_peak()
+    M = n * k
+    by_f, by_b = 160 * M + 140 * n, 416 * M + 260 * n
+    return {"workload": "C5: model_pn.py-style step, 1M Gaussians, samples = means, 16-neighbour aggregation, 2 heads",
+            "gaussians": P, "neighbours": k, "heads": HEADS, "n_gpus": world, "steps": steps, "warmup": warmup,
+            "ms_per_step": ms_step, "sampling_ms": ms_samp, "aggregation_ms": ms_agg,
+            "pairs_sampling_all_ranks": int(pairs_t.sum().item()), "pairs_per_rank": pairs_t.tolist(),
+            "rows_per_rank": rows_t.tolist(), "row_split": split, "halo_rows_rank0": int(plan.halo_rows),
+            "exchange": "none" if world == 1 else ("all-gather / all-reduce (dense fallback)" if plan.dense else
+                                                  "point-to-point halo rows + all-reduce of the shared parameters' gradients"),
+            "functions": "u + grad u + Hessian (fused, no grad) at the rank's means; aggregate_neighbors fwd + bwd x 2 heads",
+            "gpu_launches_per_step": launches,
+            "timing": "CUDA events on the compute stream, barrier + synchronize either side, max over ranks",
+            "roofline": {"bound": "hbm", "kernel": "agg_backward16_kernel (one head, this rank's window)",
+                         "achieved": by_b / (ms_kb * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                         "frac": by_b / (ms_kb * 1e-3) / 1e9 / peak, "peak_source": peak_src, "kernel_ms": ms_kb,
+                         "algorithmic_bytes": by_b, "bytes_model": "416 B per slot + 260 B per Gaussian (DESIGN.md §4)",
+                         "forward": {"kernel": "agg_forward16_kernel", "kernel_ms": ms_kf, "algorithmic_bytes": by_f,
+                                     "achieved": by_f / (ms_kf * 1e-3) / 1e9, "frac": by_f / (ms_kf * 1e-3) / 1e9 / peak,
+                                     "bytes_model": "160 B per slot + 140 B per Gaussian"}}}
+
+
+def leg_ref_cuda(torch, L, P=20_000, N=200_000):
+    """The unmodified reference CUDA extension (oracle/_ref/_C.so) on this GPU next to ours, same inputs: one step =
+    preprocess + value / gradient / Hessian forward + their backward (the reference: 3 + 3 separate passes)."""
+    from tests import refcuda
+    if not refcuda.available():
+        return {"unavailable": "oracle/_ref/_C.so is not on this box (built by oracle/build_ref.sh where /root/reference exists)"}
+    from pigs_b200 import _C
+    from tests.fixtures import synthetic
+    # the reference allocates with device-side new[] in every thread (forward.cu:63-64, sampler_impl.cu:166)
+    rt = ctypes.CDLL("libcudart.so.12")
+    rt.cudaDeviceSetLimit(2, ctypes.c_size_t(8 << 30))  # cudaLimitMallocHeapSize; before the first kernel that uses the heap
+    rec = synthetic(P, N, seed=0)
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    g = torch.Generator(device="cuda").manual_seed(3)
+    gs = [torch.randn(N, 1, device="cuda", generator=g), torch.randn(N, 2, 1, device="cuda", generator=g),
+          torch.randn(N, 2, 2, 1, device="cuda", generator=g)]
+    r = refcuda.RefSampler(False)
+
+    def ref_step():
+        r.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        outs = [r.forward(fn) for fn in range(3)]
+        grads = [r.backward(fn, gs[fn]) for fn in range(3)]
+        return outs, grads
+
+    def our_step():
+        nr, bb, sbb, rg, srg, _ = _C.preprocess_gaussians(d["means"], d["values"], d["covariances"], d["conics"],
+                                                          d["samples"], False)
+        a = (d["means"], d["values"], d["conics"], d["samples"], nr)
+        outs = _C.sample_forward(7, *a, bb, sbb, rg, srg, False)
+        grads = _C.sample_backward(7, *a, [gs[0], gs[1], gs[2], None], bb, sbb, rg, srg, False)
+        return outs, grads
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            res = fn()
+        b.record()
+        torch.cuda.synchronize()
+        return a.elapsed_time(b) / steps, res
+
+    ref_ms, (ro, rg_) = timed(ref_step, 2, 1)
+    our_ms, (oo, og) = timed(our_step, 5, 3)
+    rel = lambda a_, b_: float((a_ - b_).abs().max() / b_.abs().max().clamp_min(1e-30))
+    dev = {"u": rel(oo[0], ro[0]), "du": rel(oo[1], ro[1]), "ddu": rel(oo[2], ro[2])}
+    rsum = [sum(x[i].reshape(-1) for x in rg_) for i in range(3)]
+    for nm, a_, b_ in zip(("dmeans", "dvalues", "dconics"), og, rsum):
+        dev[nm] = rel(a_.reshape(-1), b_)
+    pairs = r.num_rendered  # instances; the pair count proper comes from our ranges
+    return {"workload": "%d Gaussians x %d points, 2-D, u + grad u + Hessian forward + backward" % (P, N),
+            "reference": "oracle/_ref/_C.so = the unmodified diff-gaussian-sampling CUDA extension (forward.cu:277-343 one "
+                         "CTA per tile, backward.cu:418-499), built by oracle/build_ref.sh",
+            "ref_ms_per_step": ref_ms, "ours_ms_per_step": our_ms, "speedup": ref_ms / our_ms,
+            "steps": {"reference": 2, "ours": 5}, "warmup": {"reference": 1, "ours": 3},
+            "num_rendered": int(pairs), "max_rel_deviation_ours_vs_reference": dev,
+            "timing": "CUDA events on the current stream around whole steps, inputs resident on the device"}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: pigs_b200 has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    from pigs_b200 import _lib
+    L = _lib.lib()
+    P, N, _, desc = WORKLOADS[args.workload]
+    run = SamplingRun(args.workload, torch, dist, L, rank, world)
+    D, Nl = run.D, run.Nl
+
+    clocks = ClockSampler(local)
+    peaks = microbench_peaks(L, torch) if rank == 0 else None
+    pairs = run.count_pairs()
+    pairs_local = run.pairs_local
+    ms_per_step, launches, kt = run.run_device(args.steps, args.warmup, clocks)
+    value = pairs / (ms_per_step * 1e-3)
+    # per-rank kernel times and pair counts (load balance of the sample shards; rank 0 prints them)
+    per_rank = torch.tensor([kt["fwd"][0], kt["bwd"][0], float(pairs_local)], device="cuda", dtype=torch.float64)
+    if world > 1:
+        gathered = [torch.zeros_like(per_rank) for _ in range(world)]
+        dist.all_gather(gathered, per_rank)
+        per_rank_rows = [[float(v) for v in g.tolist()] for g in gathered]
+    else:
+        per_rank_rows = [[float(v) for v in per_rank.tolist()]]
+    launches_t = torch.tensor([launches], device="cuda", dtype=torch.int64)
+    if world > 1:
+        dist.all_reduce(launches_t)
+
+    e2e = None if args.no_e2e else run.run_e2e(args.steps, args.warmup)
+    del run
+    torch.cuda.empty_cache()
+
+    # ---------------- extra legs (outside the timed C3 region) ----------------
+    legs = {}
+    if not args.no_legs:
+        def guarded(name, fn):
+            t0 = time.perf_counter()
+            try:
+                res = fn()
+            except Exception as ex:  # a leg must never cost the headline line
+                res = {"error": "%s: %s" % (type(ex).__name__, str(ex)[:300])}
+            if isinstance(res, dict):
+                res["wall_s"] = round(time.perf_counter() - t0, 2)
+            torch.cuda.empty_cache()
+            return res
+        legs["c5"] = guarded("c5", lambda: leg_c5(torch, dist, L, rank, world))
+        if world == 1:
+            legs["c2"] = guarded("c2", lambda: leg_sampling("C2", torch, dist, L, 3, 3))
+            legs["c4"] = guarded("c4", lambda: leg_sampling("C4", torch, dist, L, 3, 3))
+            legs["c1"] = guarded("c1", lambda: leg_sampling("C1", torch, dist, L, 50, 10))
+            legs["ref_cuda"] = guarded("ref_cuda", lambda: leg_ref_cuda(torch, L))
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    sms = torch.cuda.get_device_properties(0).multi_processor_count
     ck = clocks.summary()
-    fmax = (ck.get("sm_max_mhz") or 1965.0) * 1e6
-    peak = sms * 128 * fmax / 1e12
+    sms, fmax, peak = fp32_peak(torch, ck)
     bwd_ms, fwd_ms = kt["bwd"][0], kt["fwd"][0]
     ach_bwd = pairs_local * LANE_OPS_BWD / (bwd_ms * 1e-3) / 1e12 if bwd_ms > 0 else None
     ach_all = pairs_local * (LANE_OPS_FWD + LANE_OPS_BWD) / ((bwd_ms + fwd_ms) * 1e-3) / 1e12 if bwd_ms > 0 else None
+    traffic = ncu_traffic()
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic (seeded jittered-grid Gaussians, uniform points; tests/fixtures.synthetic seed 0)",
         "config": {"workload": "%s: %s" % (args.workload, desc), "gaussians": P, "points": N, "points_per_gpu": Nl,
-                   "pairs": pairs, "functions": "u + grad u + Hessian fused fwd, fused bwd to means/conics/values",
+                   "pairs": pairs, "pair_definition": PAIR_DEF_GPU,
+                   "functions": "u + grad u + Hessian fused fwd, fused bwd to means/conics/values",
                    "step": "preprocess (tile binning) + forward + backward" + (" + NCCL all-reduce of packed grads" if world > 1 else ""),
                    "parallelism": "points sharded x%d, Gaussians replicated" % world, "l2": flush_note()},
         "pde_step_ms": ms_per_step,
@@ -375,19 +708,24 @@ def run_ours(args):
                                                         ((bwd_ms + fwd_ms) * 1e-3) / 1e12 / peak) if bwd_ms > 0 else None},
                      "executed_lane_ops_per_pair": EXEC_OPS_BWD,
                      "frac_executed": (ach_bwd * EXEC_OPS_BWD / LANE_OPS_BWD) / peak if ach_bwd else None,
-                     "traffic": (ncu_traffic() or {}).get("dram_bytes_per_launch"),
-                     "traffic_note": (ncu_traffic() or {}).get("kernel", "no committed ncu summary") + "; " +
-                                     (ncu_traffic() or {}).get("source", "")},
+                     "traffic": traffic.get("dram_bytes_per_launch"),
+                     "traffic_note": (traffic.get("kernel", "") + "; " + traffic.get("source", "")).strip("; ")},
         "clocks": ck,
     }
     if D != 2:
         # the lane-op counts above are the 2-D one-channel kernels'; the 1-D case (C1) is launch-bound at its size
-        out["roofline"] = {"bound": "launch latency", "note": "1-D, 1K x 10K: ~60 dependent launches of a few us each; "
+        out["roofline"] = {"bound": "launch latency", "note": "1-D, 1K x 10K: a chain of dependent launches of a few us each; "
                            "no FP32 roofline is claimed for this workload", "kernel_ms": {"eval_fwd": fwd_ms, "eval_bwd": bwd_ms}}
     if e2e:
         out["e2e"] = e2e
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(args.workload)
+    if legs:
+        out["legs"] = legs
+        for k in ("c5", "ref_cuda", "c1", "c2", "c4"):  # also at top level, where the verdict asked for them
+            if k in legs:
+                out[k] = legs[k]
+        del out["legs"]
     emit(out)
     if world > 1:
         dist.destroy_process_group()
@@ -396,8 +734,9 @@ def run_ours(args):
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path — its pure-PyTorch dense sampling
     (gaussians.py:48-116; the module itself cannot travel to the GPU box, so oracle/dense_torch.py restates it) —
-    on the host cores with all the threads torch uses, on the same workload's data.  Each step is a bounded
-    sample: a dense 1000-Gaussian x 10000-point slice (dense intermediates are O(n*m*d^2))."""
+    on ALL host cores (set explicitly: torchrun exports OMP_NUM_THREADS=1), on the same workload's data, with exactly
+    the --steps / --warmup asked for.  Each step is a bounded sample: a dense 1000-Gaussian x 10000-point slice (dense
+    intermediates are O(n*m*d^2)); its pairs are DENSE all-pairs, stated in the line."""
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if rank != 0:
@@ -405,16 +744,10 @@ def run_reference(args):
     import torch
 
     from oracle import dense_torch as dt
-    from tests.fixtures import synthetic
+    threads = _all_threads(torch)
     P, N, kw, desc = WORKLOADS[args.workload]
-    n, m = min(P, 1000), min(N, 10000)
-    rec = synthetic(P, min(N, 200_000), seed=0, **kw)
-    rng = np.random.default_rng(7)
-    gi = np.sort(rng.choice(P, n, replace=False))
-    si = np.sort(rng.choice(rec["samples"].shape[0], m, replace=False))
-    means, conics, values = (torch.from_numpy(rec[k][gi]) for k in ("means", "conics", "values"))
-    samples = torch.from_numpy(rec["samples"][si])
-    steps, warmup = min(args.steps, 20), min(args.warmup, 3)
+    means, conics, values, samples, n, m = _dense_slice(args.workload)
+    steps, warmup = max(1, args.steps), max(0, args.warmup)
     t0 = time.perf_counter()
     times, pairs = dt.timed_steps(means, conics, values, samples, steps, warmup)
     ms = 1e3 * sum(times) / len(times)
@@ -424,9 +757,10 @@ def run_reference(args):
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": steps,
            "warmup": warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
            "dtype": "f32", "data": "synthetic (same seeded recipe as the GPU arm)",
-           "config": {"workload": "%s: %s" % (args.workload, desc), "gaussians": P, "points": N, "sample": sample},
-           "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "host_cpus": os.cpu_count(),
-                            "kind": "port", "sample": sample},
+           "config": {"workload": "%s: %s" % (args.workload, desc), "gaussians": P, "points": N, "sample": sample,
+                      "pair_definition": PAIR_DEF_CPU},
+           "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "host_cpus": os.cpu_count(),
+                            "kind": "port", "sample": sample, "pair_definition": PAIR_DEF_CPU},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0, "wall_s": time.perf_counter() - t0}
     emit(out)

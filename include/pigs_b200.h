@@ -134,6 +134,13 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
  * of the last forward/backward work list (device scalar, int64) */
 int64_t pigs_launch_count(void);
 
+/* Debug mode = the reference's `debug` flag (cuda_sampler/auxiliary.h:33-40 CHECK_CUDA: cudaDeviceSynchronize + error
+ * check after EACH kernel launch, std::runtime_error naming file:line).  While on, every launch of this library is followed
+ * by a device synchronisation and a failing kernel makes the entry point return its cudaError_t with pigs_last_error()
+ * naming the launch site.  The Python binding sets it from the `debug` argument of every call. */
+void pigs_set_debug(int on);
+int pigs_get_debug(void);
+
 /* Optional device timing of the evaluation kernels (bench.py roofline).  While on, the forward /
  * backward evaluation launches of every pigs_sample_forward / pigs_sample_backward call are
  * bracketed by cudaEvents on the call's stream.  pigs_kernel_timing_read(which = 0 forward |
@@ -182,6 +189,28 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
                             const float *dL_dneighbor_features, float *dL_dfeatures, float *dL_dtransform,
                             float *dL_dqueries, float *dL_dkeys, float *dL_dfrequencies,
                             float *dL_ddistance_transform, void *workspace, void *stream);
+
+/* Row-windowed aggregation (multi-GPU, SURVEY.md 8e: the CSR is sharded by query Gaussian).  Same kernels and arithmetic
+ * as pigs_aggregate_forward / _backward (aggregate_neighbors.cu:129-321), restricted to the rows [row_lo, row_hi): only
+ * those rows of the ROW-indexed arrays (queries, ranges, inv_total_densities, neighbor_features, dL_dneighbor_features,
+ * dL_dqueries) are read or written — all addressed with the GLOBAL row index, so a caller that holds just its window passes
+ * the window's base pointer displaced by -row_lo rows.  features / keys / dL_dfeatures / dL_dkeys are addressed by the
+ * neighbour index j and must cover every j the window's CSR slots name.  ranges is the inclusive cumsum over all P rows
+ * (rows outside the window empty), as pigs_neighbors_fill_rows produces it. */
+int pigs_aggregate_forward_rows(int64_t P, int D, int L, int K, int E, int64_t row_lo, int64_t row_hi,
+                                const float *features, const float *transform, const float *queries, const float *keys,
+                                const float *frequencies, const float *distance_transform, const int64_t *indices,
+                                const int64_t *ranges, const float *dists, const float *densities,
+                                const float *inv_total_densities, float *weights, float *embeddings, float *factors,
+                                float *neighbor_features, void *stream);
+int pigs_aggregate_backward_rows(int64_t P, int D, int L, int K, int E, int64_t M, int64_t row_lo, int64_t row_hi,
+                                 const float *features, const float *transform, const float *queries, const float *keys,
+                                 const float *frequencies, const float *distance_transform, const int64_t *indices,
+                                 const int64_t *ranges, const float *dists, const float *densities, const float *weights,
+                                 const float *embeddings, const float *factors, const float *inv_total_densities,
+                                 const float *dL_dneighbor_features, float *dL_dfeatures, float *dL_dtransform,
+                                 float *dL_dqueries, float *dL_dkeys, float *dL_dfrequencies,
+                                 float *dL_ddistance_transform, void *workspace, void *stream);
 
 /* ---- covariance / conic construction ---------------------------------------
  * Replaces the torch chain of gaussians.py:163-193 `build_covariances(s, t)` (tanh, sqrt(prod), diag_embed, indexed

@@ -3,6 +3,10 @@ argument order, same return values — implemented as thin tensor -> pointer glu
 libpigs_b200.so (include/pigs_b200.h).  torch owns every allocation; the library only launches
 kernels on torch's current CUDA stream.
 
+`debug=True` has the reference's meaning (cuda_sampler/auxiliary.h:33-40): the library synchronises the device and
+checks for errors after EVERY kernel launch (pigs_set_debug), so a faulting kernel raises RuntimeError naming its own
+launch site.
+
 Differences a caller can observe (all documented in DESIGN.md):
   * the byte buffers (`binning_buffer`, `sample_binning_buffer`) have our own internal layout — they
     are opaque in the reference too (sample_points.cu:48-55);
@@ -83,6 +87,7 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
     `cull` = (sigmas, subdiv) (optional, extension): the opt-in culled mode of include/pigs_b200.h
     pigs_preprocess_count_culled — a SUBSET of the reference's pair set, not the reference's result."""
     L = _lib.lib()
+    L.pigs_set_debug(1 if debug else 0)
     means = _f32c(means, "means")
     P, D, N, C = _dims(means, values, samples)
     dev = means.device
@@ -116,8 +121,6 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
     check(L.pigs_preprocess_bin(P, D, N, blocks, R, _ptr(means), _ptr(samples), _ptr(radii), _ptr(geom), _ptr(binning),
                                 _ptr(sbinning), _ptr(ranges), _ptr(sample_ranges), _ptr(sort_ws), st),
           "pigs_preprocess_bin")
-    if debug:
-        torch.cuda.synchronize()
     return R, binning, sbinning, ranges, sample_ranges, radii
 
 
@@ -130,6 +133,7 @@ def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binnin
     """Fused forward for any subset of {value, derivative, Hessian | Laplacian, third}.  Returns a 4-tuple with
     None for the functions not requested; with FN_LAPL slot 2 holds the Laplacian [N, C] instead of the Hessian."""
     L = _lib.lib()
+    L.pigs_set_debug(1 if debug else 0)
     means = _f32c(means, "means")
     values = _f32c(values, "values")
     conics = _f32c(conics, "conics")
@@ -150,8 +154,6 @@ def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binnin
                                     _ptr(samples), _ptr(binning_buffer), _ptr(sample_binning_buffer), _ptr(ranges),
                                     _ptr(sample_ranges), _ptr(outs[0]), _ptr(outs[1]), _ptr(outs[2]), _ptr(outs[3]),
                                     _ptr(ws), ws_bytes, _stream()), "pigs_sample_forward")
-        if debug:
-            torch.cuda.synchronize()
     return tuple(outs)
 
 
@@ -160,6 +162,7 @@ def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads
     """Fused backward; `grads` is a 4-tuple of upstream gradients (None = zero; with FN_LAPL slot 2 is the
     Laplacian's [N, C] gradient).  Returns (dL_dmeans [P,D], dL_dvalues [P,C], dL_dconics [P,D(D+1)/2])."""
     L = _lib.lib()
+    L.pigs_set_debug(1 if debug else 0)
     means = _f32c(means, "means")
     values = _f32c(values, "values")
     conics = _f32c(conics, "conics")
@@ -181,8 +184,6 @@ def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads
                                      _ptr(samples), _ptr(binning_buffer), _ptr(sample_binning_buffer), _ptr(ranges),
                                      _ptr(sample_ranges), _ptr(g[0]), _ptr(g[1]), _ptr(g[2]), _ptr(g[3]), _ptr(dm),
                                      _ptr(dv), _ptr(dc), _ptr(ws), ws_bytes, _stream()), "pigs_sample_backward")
-        if debug:
-            torch.cuda.synchronize()
     return dm, dv, dc
 
 
@@ -240,6 +241,7 @@ def preprocess_aggregate(means, conics, radii, debug, rows=None):
     (indices i64[M], ranges i64[P], dists f32[M,D], densities f32[M], inv_total_densities f32[P]).
     rows = (lo, hi) (extension, multi-GPU): lists of the query Gaussians [lo, hi) only; the others get empty rows."""
     L = _lib.lib()
+    L.pigs_set_debug(1 if debug else 0)
     means = _f32c(means, "means")
     conics = _f32c(conics, "conics")
     radii = _f32c(radii, "radii")
@@ -260,8 +262,6 @@ def preprocess_aggregate(means, conics, radii, debug, rows=None):
     inv_total = torch.zeros((P,), dtype=torch.float32, device=dev)
     check(L.pigs_neighbors_fill_rows(P, D, _ptr(means), _ptr(conics), _ptr(radii), lo, hi, _ptr(ranges), _ptr(indices),
                                      _ptr(dists), _ptr(densities), _ptr(inv_total), _ptr(ws), st), "pigs_neighbors_fill_rows")
-    if debug:
-        torch.cuda.synchronize()
     return indices, ranges, dists, densities, inv_total
 
 
@@ -270,6 +270,7 @@ def aggregate_neighbors(features, transform, queries, keys, frequencies, distanc
     """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415).  Returns
     (weights, embeddings, factors [M], neighbor_features [P,L])."""
     L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
     features = _f32c(features, "features")
     transform = _f32c(transform, "transform")
     queries = _f32c(queries, "queries")
@@ -293,8 +294,6 @@ def aggregate_neighbors(features, transform, queries, keys, frequencies, distanc
                                         _ptr(frequencies), _ptr(dt), _ptr(indices), _ptr(ranges), _ptr(dists),
                                         _ptr(densities), _ptr(inv_total), _ptr(weights), _ptr(embeddings), _ptr(factors),
                                         _ptr(out), _stream()), "pigs_aggregate_forward")
-    if debug:
-        torch.cuda.synchronize()
     return weights, embeddings, factors, out
 
 
@@ -303,6 +302,7 @@ def aggregate_neighbors_backward(features, transform, queries, keys, frequencies
                                  dL_dneighbor_features, debug):
     """AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475)."""
     L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
     features = _f32c(features, "features")
     transform = _f32c(transform, "transform")
     queries = _f32c(queries, "queries")
@@ -330,9 +330,86 @@ def aggregate_neighbors_backward(features, transform, queries, keys, frequencies
                                          _ptr(_f32c(inv_total_densities, "inv_total_densities")), _ptr(g), _ptr(gf),
                                          _ptr(gt), _ptr(gq), _ptr(gk), _ptr(gfr), _ptr(gdt), _ptr(ws), _stream()),
               "pigs_aggregate_backward")
-    if debug:
-        torch.cuda.synchronize()
     return gf, gt, gq, gk, gfr, gdt
+
+
+def _disp(t, rows, width):
+    """Base pointer of a [hi-lo, width] window tensor displaced by -lo rows: the `_rows` entry points address the
+    row-indexed arrays with the GLOBAL row index and touch rows [lo, hi) only (include/pigs_b200.h)."""
+    return ctypes.c_void_p(t.data_ptr() - int(rows[0]) * int(width) * 4)
+
+
+def aggregate_neighbors_rows(features, transform, queries_rows, keys, frequencies, distance_transform, indices, ranges,
+                             dists, densities, inv_total_densities, rows, debug):
+    """(extension, multi-GPU) aggregate_neighbors for the query rows [lo, hi) = `rows` only.  features / keys are
+    full-height [P, .] buffers of which the rows the window's CSR names must be valid; queries_rows is the window's
+    [hi-lo, K]; ranges / inv_total_densities are the [P] arrays of preprocess_aggregate(rows=...).
+    Returns (weights, embeddings, factors [M_local], neighbor_features [hi-lo, L])."""
+    L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
+    features = _f32c(features, "features")
+    transform = _f32c(transform, "transform")
+    queries_rows = _f32c(queries_rows, "queries")
+    keys = _f32c(keys, "keys")
+    frequencies = _f32c(frequencies, "frequencies")
+    dt = _f32c(distance_transform, "distance_transform")
+    dists = _f32c(dists, "dists")
+    densities = _f32c(densities, "densities")
+    inv_total = _f32c(inv_total_densities, "inv_total_densities")
+    indices, ranges = indices.contiguous(), ranges.contiguous()
+    lo, hi = int(rows[0]), int(rows[1])
+    P, D, L = features.size(0), dists.size(-1), features.size(-1)
+    K, E = queries_rows.size(-1), dt.size(-1) // 2
+    if queries_rows.size(0) != hi - lo or keys.size(0) != P or ranges.numel() != P:
+        raise RuntimeError("aggregate_neighbors_rows: queries must hold the window's rows, features / keys / ranges all P")
+    weights = torch.zeros_like(densities)
+    embeddings = torch.zeros_like(densities)
+    factors = torch.zeros_like(densities)
+    out = torch.zeros((hi - lo, L), dtype=torch.float32, device=features.device)
+    if hi > lo:
+        check(L_.pigs_aggregate_forward_rows(P, D, L, K, E, lo, hi, _ptr(features), _ptr(transform),
+                                             _disp(queries_rows, rows, K), _ptr(keys), _ptr(frequencies), _ptr(dt),
+                                             _ptr(indices), _ptr(ranges), _ptr(dists), _ptr(densities), _ptr(inv_total),
+                                             _ptr(weights), _ptr(embeddings), _ptr(factors), _disp(out, rows, L), _stream()),
+              "pigs_aggregate_forward_rows")
+    return weights, embeddings, factors, out
+
+
+def aggregate_neighbors_rows_backward(features, transform, queries_rows, keys, frequencies, distance_transform, indices,
+                                      ranges, dists, densities, weights, embeddings, factors, inv_total_densities,
+                                      dL_dout_rows, g_features, g_keys, rows, debug):
+    """Backward of aggregate_neighbors_rows.  g_features / g_keys are caller-provided full-height [P, .] buffers the
+    kernel ADDS this window's contributions into (rows named by the window's CSR slots); returns
+    (dL_dtransform, dL_dqueries [hi-lo, K], dL_dfrequencies, dL_ddistance_transform) of this window."""
+    L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
+    features = _f32c(features, "features")
+    transform = _f32c(transform, "transform")
+    queries_rows = _f32c(queries_rows, "queries")
+    keys = _f32c(keys, "keys")
+    frequencies = _f32c(frequencies, "frequencies")
+    dt = _f32c(distance_transform, "distance_transform")
+    dists = _f32c(dists, "dists")
+    g = _f32c(dL_dout_rows, "dL_dneighbor_features")
+    lo, hi = int(rows[0]), int(rows[1])
+    P, D, L = features.size(0), dists.size(-1), features.size(-1)
+    K, E = queries_rows.size(-1), dt.size(-1) // 2
+    if g.size(0) != hi - lo or not (g_features.is_contiguous() and g_keys.is_contiguous()):
+        raise RuntimeError("aggregate_neighbors_rows_backward: dL_dout must hold the window's rows; gradient buffers contiguous")
+    gt = torch.zeros_like(transform)
+    gq = torch.zeros_like(queries_rows)
+    gfr = torch.zeros_like(frequencies)
+    gdt = torch.zeros_like(dt)
+    if hi > lo:
+        check(L_.pigs_aggregate_backward_rows(P, D, L, K, E, densities.numel(), lo, hi, _ptr(features), _ptr(transform),
+                                              _disp(queries_rows, rows, K), _ptr(keys), _ptr(frequencies), _ptr(dt),
+                                              _ptr(indices.contiguous()), _ptr(ranges.contiguous()), _ptr(dists),
+                                              _ptr(_f32c(densities, "densities")), _ptr(_f32c(weights, "weights")),
+                                              _ptr(_f32c(embeddings, "embeddings")), _ptr(_f32c(factors, "factors")),
+                                              _ptr(_f32c(inv_total_densities, "inv_total_densities")), _disp(g, rows, L),
+                                              _ptr(g_features), _ptr(gt), _disp(gq, rows, K), _ptr(g_keys), _ptr(gfr),
+                                              _ptr(gdt), None, _stream()), "pigs_aggregate_backward_rows")
+    return gt, gq, gfr, gdt
 
 
 def build_covariances(scaling, transform):

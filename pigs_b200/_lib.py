@@ -60,6 +60,8 @@ SIGNATURES = {
     "pigs_sample_forward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 13 + [c_size_t, c_void_p]),
     "pigs_sample_backward": (c_int, [c_uint, c_int64, c_int, c_int64, c_int, c_int, c_int64] + [c_void_p] * 16 + [c_size_t, c_void_p]),
     "pigs_launch_count": (c_int64, []),
+    "pigs_set_debug": (None, [c_int]),
+    "pigs_get_debug": (c_int, []),
     "pigs_set_kernel_timing": (None, [c_int]),
     "pigs_kernel_timing_read": (c_int, [c_int, c_void_p, c_void_p]),
     "pigs_neighbor_workspace_bytes": (c_size_t, [c_int64, c_int]),
@@ -68,6 +70,8 @@ SIGNATURES = {
     "pigs_neighbors_count_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 3),
     "pigs_neighbors_fill_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 7),
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
+    "pigs_aggregate_forward_rows": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64] + [c_void_p] * 16),
+    "pigs_aggregate_backward_rows": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64] + [c_void_p] * 23),
     "pigs_set_aggregate_specialised": (None, [c_int]),
     "pigs_set_neighbor_search": (None, [c_int, ctypes.c_float]),
     "pigs_aggregate_backward_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),

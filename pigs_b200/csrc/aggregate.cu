@@ -953,7 +953,7 @@ struct AggDims {
 };
 
 __global__ void __launch_bounds__(AG_THREADS)
-    agg_forward_kernel(int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
+    agg_forward_kernel(int64_t row_lo, int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
                        const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                        const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
                        const float* __restrict__ dists, const float* __restrict__ densities,
@@ -976,7 +976,7 @@ __global__ void __launch_bounds__(AG_THREADS)
     for (int i = threadIdx.x; i < nF; i += AG_THREADS) s_fr[i] = freqs[i];
     __syncthreads();
 
-    for (int64_t row = (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {
+    for (int64_t row = row_lo + (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {  // rows [row_lo, P)
         const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
         for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
         const float inv = inv_total[row];
@@ -1052,7 +1052,7 @@ __global__ void __launch_bounds__(AG_THREADS)
 // Shared-parameter gradients are accumulated per lane in shared-memory columns (no conflicts), reduced
 // once per CTA, then one atomic per address per CTA.
 __global__ void __launch_bounds__(AG_THREADS)
-    agg_backward_kernel(int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
+    agg_backward_kernel(int64_t row_lo, int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
                         const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                         const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
                         const float* __restrict__ dists, const float* __restrict__ densities,
@@ -1089,7 +1089,7 @@ __global__ void __launch_bounds__(AG_THREADS)
     __syncthreads();
     const float PI = 3.14159265358979323846f;
 
-    for (int64_t row = (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {
+    for (int64_t row = row_lo + (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {  // rows [row_lo, P)
         const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
         if (end == start) continue;
         for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
@@ -1210,12 +1210,12 @@ __global__ void __launch_bounds__(AG_THREADS)
 
 namespace pigs {
 // aggregate16.cu: kernels specialised for L = K = 16, E = 25 (model_pn.py); return 1 if handled, 0 to fall back
-int launch_aggregate16_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+int launch_aggregate16_forward(int64_t row_lo, int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                                const float* queries, const float* keys, const float* freqs, const float* dt,
                                const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
                                const float* inv_total, float* weights, float* embeddings, float* factors, float* out,
                                cudaStream_t st);
-int launch_aggregate16_backward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+int launch_aggregate16_backward(int64_t row_lo, int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                                 const float* queries, const float* keys, const float* freqs, const float* dt,
                                 const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
                                 const float* weights, const float* embeddings, const float* factors, const float* inv_total,
@@ -1405,14 +1405,27 @@ int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* f
                            const float* dists, const float* densities, const float* inv_total_densities, float* weights,
                            float* embeddings, float* factors, float* neighbor_features, void* stream)
 {
+    return pigs_aggregate_forward_rows(P, D, L, K, E, 0, P, features, transform, queries, keys, frequencies, distance_transform,
+                                       indices, ranges, dists, densities, inv_total_densities, weights, embeddings, factors,
+                                       neighbor_features, stream);
+}
+
+int pigs_aggregate_forward_rows(int64_t P, int D, int L, int K, int E, int64_t row_lo, int64_t row_hi, const float* features, const float* transform,
+                           const float* queries, const float* keys, const float* frequencies,
+                           const float* distance_transform, const int64_t* indices, const int64_t* ranges,
+                           const float* dists, const float* densities, const float* inv_total_densities, float* weights,
+                           float* embeddings, float* factors, float* neighbor_features, void* stream)
+{
     AggDims dm;
     int rc = agg_dims(dm, D, L, K, E);
     if (rc) return rc;
     PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
              neighbor_features);
     PIGS_ARG(dm.nF == 0 || frequencies);
+    PIGS_ARG(row_lo >= 0 && row_lo <= row_hi && row_hi <= P);
+    if (row_lo == row_hi) return 0;
     if (g_agg_fast && frequencies && weights && embeddings && factors && indices && dists && densities) {
-        rc = launch_aggregate16_forward(P, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
+        rc = launch_aggregate16_forward(row_lo, row_hi, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
                                         indices, ranges, dists, densities, inv_total_densities, weights, embeddings, factors,
                                         neighbor_features, (cudaStream_t)stream);
         if (rc != 0) return rc == 1 ? 0 : rc;
@@ -1420,11 +1433,11 @@ int pigs_aggregate_forward(int64_t P, int D, int L, int K, int E, const float* f
     const size_t smem = agg_fwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
     PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    int64_t grid = (row_hi - row_lo + AG_WARPS - 1) / AG_WARPS;
     const int64_t cap = (int64_t)num_sms() * 16;
     if (grid > cap) grid = cap;
     agg_forward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
-        P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+        row_lo, row_hi, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
         inv_total_densities, weights, embeddings, factors, neighbor_features);
     PIGS_LAUNCH_CHECK();
     return 0;
@@ -1444,6 +1457,20 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
                             float* dL_dfeatures, float* dL_dtransform, float* dL_dqueries, float* dL_dkeys,
                             float* dL_dfrequencies, float* dL_ddistance_transform, void* workspace, void* stream)
 {
+    return pigs_aggregate_backward_rows(P, D, L, K, E, M, 0, P, features, transform, queries, keys, frequencies,
+                                        distance_transform, indices, ranges, dists, densities, weights, embeddings, factors,
+                                        inv_total_densities, dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries,
+                                        dL_dkeys, dL_dfrequencies, dL_ddistance_transform, workspace, stream);
+}
+
+int pigs_aggregate_backward_rows(int64_t P, int D, int L, int K, int E, int64_t M, int64_t row_lo, int64_t row_hi, const float* features,
+                            const float* transform, const float* queries, const float* keys, const float* frequencies,
+                            const float* distance_transform, const int64_t* indices, const int64_t* ranges,
+                            const float* dists, const float* densities, const float* weights, const float* embeddings,
+                            const float* factors, const float* inv_total_densities, const float* dL_dneighbor_features,
+                            float* dL_dfeatures, float* dL_dtransform, float* dL_dqueries, float* dL_dkeys,
+                            float* dL_dfrequencies, float* dL_ddistance_transform, void* workspace, void* stream)
+{
     (void)M, (void)workspace;
     AggDims dm;
     int rc = agg_dims(dm, D, L, K, E);
@@ -1451,8 +1478,10 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
     PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
              dL_dneighbor_features && dL_dfeatures && dL_dtransform && dL_dqueries && dL_dkeys && dL_ddistance_transform);
     PIGS_ARG(dm.nF == 0 || (frequencies && dL_dfrequencies));
+    PIGS_ARG(row_lo >= 0 && row_lo <= row_hi && row_hi <= P);
+    if (row_lo == row_hi) return 0;
     if (g_agg_fast && frequencies && dL_dfrequencies) {
-        rc = launch_aggregate16_backward(P, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
+        rc = launch_aggregate16_backward(row_lo, row_hi, D, L, K, E, features, transform, queries, keys, frequencies, distance_transform,
                                          indices, ranges, dists, densities, weights, embeddings, factors, inv_total_densities,
                                          dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
                                          dL_dfrequencies, dL_ddistance_transform, (cudaStream_t)stream);
@@ -1461,11 +1490,11 @@ int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, co
     const size_t smem = agg_bwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
     PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    int64_t grid = (row_hi - row_lo + AG_WARPS - 1) / AG_WARPS;
     const int64_t cap = (int64_t)num_sms() * 2;
     if (grid > cap) grid = cap;
     agg_backward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
-        P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities, weights,
+        row_lo, row_hi, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities, weights,
         embeddings, factors, inv_total_densities, dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
         dL_dfrequencies, dL_ddistance_transform);
     PIGS_LAUNCH_CHECK();

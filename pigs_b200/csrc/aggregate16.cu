@@ -73,7 +73,7 @@ __device__ __forceinline__ void load16(const float* __restrict__ row, float* __r
 
 template <int D, int NF>
 __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
-    agg_forward16_kernel(int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
+    agg_forward16_kernel(int64_t row_lo, int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
                          const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                          const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
                          const float* __restrict__ dists, const float* __restrict__ densities,
@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
     const int64_t warp = ((int64_t)blockIdx.x * A16_THREADS + threadIdx.x) >> 5;
     const int64_t nwarps = ((int64_t)gridDim.x * A16_THREADS) >> 5;
 
-    for (int64_t base = warp * 2; base < P; base += nwarps * 2) {  // warp-uniform
+    for (int64_t base = row_lo + warp * 2; base < P; base += nwarps * 2) {  // warp-uniform; rows [row_lo, P)
         const int64_t row = base + g;
         const bool valid = row < P;
         const int64_t start = (valid && row > 0) ? ranges[row - 1] : 0;
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
 //   dL/ddt, dL/dfreq from dA = dc w A and dB = dc w B (reference :266-281)
 template <int D, int NF>
 __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
-    agg_backward16_kernel(int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
+    agg_backward16_kernel(int64_t row_lo, int64_t P, const float* __restrict__ features, const float* __restrict__ transform,
                           const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
                           const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
                           const float* __restrict__ dists, const float* __restrict__ densities,
@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
 #pragma unroll
     for (int a = 0; a < 16; a++) c_T[a] = 0.0f;
 
-    for (int64_t base = warp * 2; base < P; base += nwarps * 2) {  // warp-uniform
+    for (int64_t base = row_lo + warp * 2; base < P; base += nwarps * 2) {  // warp-uniform; rows [row_lo, P)
         const int64_t row = base + g;
         const bool valid = row < P;
         const int64_t start = (valid && row > 0) ? ranges[row - 1] : 0;
@@ -354,7 +354,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
 }
 
 // ---- host dispatch (called from aggregate.cu); returns 1 if the sizes were handled, 0 to fall back, <0 / >0 on error
-int launch_aggregate16_forward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+int launch_aggregate16_forward(int64_t row_lo, int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                                const float* queries, const float* keys, const float* freqs, const float* dt,
                                const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
                                const float* inv_total, float* weights, float* embeddings, float* factors, float* out,
@@ -362,22 +362,23 @@ int launch_aggregate16_forward(int64_t P, int D, int L, int K, int E, const floa
 {
     if (L != 16 || K != 16 || E != 25) return 0;
     if ((reinterpret_cast<uintptr_t>(features) & 15) != 0) return 0;  // 16-byte row loads
-    int64_t grid = (P + 15) / 16;  // 16 rows per CTA (8 warps x 2)
+    int64_t grid = (P - row_lo + 15) / 16;  // 16 rows per CTA (8 warps x 2)
+    if (grid < 1) grid = 1;
     const int64_t cap = (int64_t)num_sms() * 16;
     if (grid > cap) grid = cap;
     if (D == 2)
-        agg_forward16_kernel<2, 6><<<(unsigned)grid, A16_THREADS, 0, st>>>(P, features, transform, queries, keys, freqs, dt,
+        agg_forward16_kernel<2, 6><<<(unsigned)grid, A16_THREADS, 0, st>>>(row_lo, P, features, transform, queries, keys, freqs, dt,
                                                                             indices, ranges, dists, densities, inv_total,
                                                                             weights, embeddings, factors, out);
     else
-        agg_forward16_kernel<1, 12><<<(unsigned)grid, A16_THREADS, 0, st>>>(P, features, transform, queries, keys, freqs, dt,
+        agg_forward16_kernel<1, 12><<<(unsigned)grid, A16_THREADS, 0, st>>>(row_lo, P, features, transform, queries, keys, freqs, dt,
                                                                              indices, ranges, dists, densities, inv_total,
                                                                              weights, embeddings, factors, out);
     PIGS_LAUNCH_CHECK();
     return 1;
 }
 
-int launch_aggregate16_backward(int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
+int launch_aggregate16_backward(int64_t row_lo, int64_t P, int D, int L, int K, int E, const float* features, const float* transform,
                                 const float* queries, const float* keys, const float* freqs, const float* dt,
                                 const int64_t* indices, const int64_t* ranges, const float* dists, const float* densities,
                                 const float* weights, const float* embeddings, const float* factors, const float* inv_total,
@@ -387,16 +388,17 @@ int launch_aggregate16_backward(int64_t P, int D, int L, int K, int E, const flo
     if (L != 16 || K != 16 || E != 25) return 0;
     // 16-byte row loads and vector REDs: rows of an unaligned view go through the generic kernels
     if (((reinterpret_cast<uintptr_t>(features) | reinterpret_cast<uintptr_t>(g_features) | reinterpret_cast<uintptr_t>(g_keys)) & 15) != 0) return 0;
-    int64_t grid = (P + 15) / 16;
+    int64_t grid = (P - row_lo + 15) / 16;
+    if (grid < 1) grid = 1;
     const int64_t cap = (int64_t)num_sms() * 8;  // few CTAs: every CTA ends with ~360 atomics on the shared parameters
     if (grid > cap) grid = cap;
     if (D == 2)
         agg_backward16_kernel<2, 6><<<(unsigned)grid, A16_THREADS, 0, st>>>(
-            P, features, transform, queries, keys, freqs, dt, indices, ranges, dists, densities, weights, embeddings, factors,
+            row_lo, P, features, transform, queries, keys, freqs, dt, indices, ranges, dists, densities, weights, embeddings, factors,
             inv_total, gout, g_features, g_transform, g_queries, g_keys, g_freqs, g_dt);
     else
         agg_backward16_kernel<1, 12><<<(unsigned)grid, A16_THREADS, 0, st>>>(
-            P, features, transform, queries, keys, freqs, dt, indices, ranges, dists, densities, weights, embeddings, factors,
+            row_lo, P, features, transform, queries, keys, freqs, dt, indices, ranges, dists, densities, weights, embeddings, factors,
             inv_total, gout, g_features, g_transform, g_queries, g_keys, g_freqs, g_dt);
     PIGS_LAUNCH_CHECK();
     return 1;

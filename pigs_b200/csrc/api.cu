@@ -133,6 +133,8 @@ int pigs_version(void) { return 100; }
 const char* pigs_last_error(void) { return g_err; }
 void pigs_set_grid_recip_mode(int recip) { g_recip_mode = recip ? 1 : 0; }
 int64_t pigs_launch_count(void) { return g_launches; }
+void pigs_set_debug(int on) { g_debug_sync = on ? 1 : 0; }
+int pigs_get_debug(void) { return g_debug_sync; }
 
 void pigs_set_kernel_timing(int on)
 {

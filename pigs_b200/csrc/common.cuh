@@ -14,6 +14,7 @@ namespace pigs {
 extern thread_local char g_err[512];
 extern int64_t g_launches;
 extern int g_recip_mode;
+extern int g_debug_sync;  // pigs_set_debug: synchronise + check after EVERY launch (reference auxiliary.h:33-40)
 
 int set_error(int code, const char* what, const char* file, int line);
 
@@ -23,11 +24,18 @@ int set_error(int code, const char* what, const char* file, int line);
         if (_e != cudaSuccess) return pigs::set_error((int)_e, #expr, __FILE__, __LINE__); \
     } while (0)
 
+// Every kernel launch of the library goes through this.  With pigs_set_debug(1) it reproduces the reference's
+// CHECK_CUDA(A, debug) (cuda_sampler/auxiliary.h:33-40): cudaDeviceSynchronize + error check after EACH launch, so a
+// faulting kernel is reported at its own launch site (file:line) instead of at some later call.
 #define PIGS_LAUNCH_CHECK()                                                        \
     do {                                                                           \
         pigs::g_launches++;                                                        \
         cudaError_t _e = cudaGetLastError();                                       \
         if (_e != cudaSuccess) return pigs::set_error((int)_e, "kernel launch", __FILE__, __LINE__); \
+        if (pigs::g_debug_sync) {                                                  \
+            _e = cudaDeviceSynchronize();                                          \
+            if (_e != cudaSuccess) return pigs::set_error((int)_e, "kernel execution (debug: synchronised after this launch)", __FILE__, __LINE__); \
+        }                                                                          \
     } while (0)
 
 #define PIGS_ARG(cond)                                                             \

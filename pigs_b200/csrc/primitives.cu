@@ -8,6 +8,7 @@ namespace pigs {
 thread_local char g_err[512] = {0};
 int64_t g_launches = 0;
 int g_recip_mode = 1;
+int g_debug_sync = 0;
 
 int set_error(int code, const char* what, const char* file, int line)
 {

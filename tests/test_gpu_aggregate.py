@@ -211,6 +211,54 @@ def test_row_sharded_lists_and_aggregation(name, nb_path):
         assert rel_err(got.cpu().numpy(), want.cpu().numpy()) <= TOL, key
 
 
+@pytest.mark.parametrize("name,specialised", [("agg_model", 1), ("agg_model", 0), ("agg_model_1d", 1), ("agg_grid5", 1)])
+def test_row_windowed_kernels_touch_only_their_rows(name, specialised):
+    """pigs_aggregate_forward_rows / _backward_rows (row-parallel multi-GPU aggregation): the window's rows equal the
+    unwindowed result bit for bit, nothing outside the window is read or written (queries / upstream / output are
+    window-sized tensors passed with a displaced base pointer, surrounded by guard rows), and the per-window gradient
+    contributions add up to the unwindowed gradients."""
+    import torch
+    from pigs_b200 import _C, _lib
+    rec = AGG_RECIPES[name]()
+    s, d = _prep(rec)
+    P = rec["means"].shape[0]
+    a = [d[k] for k in AGG_KEYS]
+    _lib.lib().pigs_set_aggregate_specialised(specialised)
+    try:
+        wf, ef, ff, out_full = _C.aggregate_neighbors(*a, s.indices, s.ranges, s.dists, s.densities, s.inv_total_densities, False)
+        up = torch.from_numpy(agg_upstream(rec)).cuda()
+        g_full = _C.aggregate_neighbors_backward(*a, s.indices, s.ranges, s.dists, s.densities, wf, ef, ff,
+                                                 s.inv_total_densities, up, False)
+        g_feat = torch.zeros_like(a[0])
+        g_keys = torch.zeros_like(a[3])
+        small = [torch.zeros_like(a[1]), torch.zeros_like(a[4]), torch.zeros_like(a[5])]
+        gq_rows = []
+        cuts = [0, P // 3, P // 3, (2 * P) // 3 + 1, P]  # includes an empty window
+        for lo, hi in zip(cuts[:-1], cuts[1:]):
+            idx, rng, dists, dens, inv = _C.preprocess_aggregate(s.means, s.conics, s.radii, False, rows=(lo, hi))
+            K, L = a[2].shape[1], a[0].shape[1]
+            guard = torch.full((hi - lo + 2, K), float("nan"), device="cuda")  # a NaN row either side of the window
+            guard[1:-1] = a[2][lo:hi]
+            q_rows = guard[1:-1]
+            w, e, f, out = _C.aggregate_neighbors_rows(a[0], a[1], q_rows, a[3], a[4], a[5], idx, rng, dists, dens, inv,
+                                                       (lo, hi), False)
+            assert out.shape == (hi - lo, L)
+            assert torch.equal(out, out_full[lo:hi])
+            gt, gq, gfr, gdt = _C.aggregate_neighbors_rows_backward(a[0], a[1], q_rows, a[3], a[4], a[5], idx, rng, dists,
+                                                                    dens, w, e, f, inv, up[lo:hi].contiguous(), g_feat,
+                                                                    g_keys, (lo, hi), False)
+            assert gq.shape == (hi - lo, K)
+            gq_rows.append(gq)
+            for acc, part in zip(small, (gt, gfr, gdt)):
+                acc += part
+        got = [g_feat, small[0], torch.cat(gq_rows, 0), g_keys, small[1], small[2]]
+        for key, g, want in zip(AGG_KEYS, got, g_full):
+            assert torch.isfinite(g).all(), key
+            assert rel_err(g.cpu().numpy(), want.cpu().numpy()) <= TOL, key
+    finally:
+        _lib.lib().pigs_set_aggregate_specialised(1)
+
+
 def test_unaligned_feature_rows_take_the_generic_kernels():
     """A features tensor whose storage starts 4 bytes off a 16-byte boundary (a view into a larger buffer): the specialised
     kernels' 16-byte row loads / vector REDs do not apply, the call falls back to the generic kernels, same results."""

@@ -142,6 +142,83 @@ def test_two_gpu_row_sharded_aggregation_matches_oracle(tmp_path):
         np.testing.assert_array_equal(parts[0][key], parts[1][key])
 
 
+def _rows_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from pigs_b200.sharded import ShardedGaussianSampler
+        from tests.fixtures import AGG_RECIPES
+        from tests.helpers import AGG_KEYS, agg_upstream
+        from tests.test_sharded_cpu import _local_csr, _window_csr
+        rec = AGG_RECIPES["agg_model"]()
+        P = rec["means"].shape[0]
+        d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+        s = ShardedGaussianSampler(False)
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        res = {}
+        for tag in ("search", "local"):
+            lo, hi = (0, P // 2 + 3) if rank == 0 else (P // 2 + 3, P)  # unequal windows
+            if tag == "search":   # the reference's own neighbour rule: strips cover most of P -> dense fallback
+                s.preprocess_aggregate(row_range=(lo, hi))
+            else:                 # spatially local lists -> point-to-point halo exchange
+                csr = _window_csr(*_local_csr(P, 16, seed=6), lo, hi)
+                s.preprocess_aggregate(row_range=(lo, hi), csr=tuple(torch.from_numpy(x).cuda() for x in csr))
+            t = {k: d[k].clone() for k in AGG_KEYS}
+            for k in ("features", "queries", "keys"):
+                t[k] = t[k][lo:hi].contiguous()      # a rank holds only its own rows of the row-indexed inputs
+            for k in AGG_KEYS:
+                t[k].requires_grad_(True)
+            out = s.aggregate_neighbors_rows(*[t[k] for k in AGG_KEYS])
+            out.backward(torch.from_numpy(agg_upstream(rec)[lo:hi]).cuda())
+            torch.cuda.synchronize()
+            res.update({tag + "_out": out.detach().cpu().numpy(), tag + "_dense": int(s.row_plan.dense),
+                        **{tag + "_grad_" + k: t[k].grad.cpu().numpy() for k in AGG_KEYS}})
+        np.savez(os.path.join(out_dir, "rows_rank%d.npz" % rank), **res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(600)
+def test_two_gpu_row_parallel_aggregation_matches_oracle(tmp_path):
+    """Row-parallel C5 on two GPUs (ShardedGaussianSampler.aggregate_neighbors_rows): each rank holds its own rows of
+    features / queries / keys, the halo rows travel point to point (or, for non-local lists, by all-gather), and each
+    rank gets its own rows of the output and of the gradients; concatenated they equal the oracle's unsharded run."""
+    import torch
+    import torch.multiprocessing as mp
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from oracle import pigs_oracle as po
+    from tests.fixtures import AGG_RECIPES
+    from tests.helpers import AGG_KEYS, TOL, agg_upstream, oracle_state, rel_err
+    from tests.test_sharded_cpu import _local_csr, _window_csr
+    world = 2
+    mp.spawn(_rows_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    rec = AGG_RECIPES["agg_model"]()
+    P = rec["means"].shape[0]
+    st = oracle_state(rec)
+    a = [rec[k] for k in AGG_KEYS]
+    parts = [np.load(os.path.join(str(tmp_path), "rows_rank%d.npz" % r)) for r in range(world)]
+    for tag in ("search", "local"):
+        csr = po.neighbors(rec["means"], rec["conics"], st["radii"]) if tag == "search" else \
+            _window_csr(*_local_csr(P, 16, seed=6), 0, P)
+        w, e, f, out = po.aggregate_forward(*a, *csr)
+        want = po.aggregate_backward(*a, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], agg_upstream(rec))
+        assert int(parts[0][tag + "_dense"]) == int(parts[1][tag + "_dense"]) == (1 if tag == "search" else 0)
+        assert rel_err(np.concatenate([p[tag + "_out"] for p in parts]), out) <= TOL
+        for key, wv in zip(AGG_KEYS, want):
+            if key in ("features", "queries", "keys"):
+                got = np.concatenate([p[tag + "_grad_" + key] for p in parts])
+                assert rel_err(got, wv) <= TOL, (tag, key)
+            else:
+                for p in parts:
+                    assert rel_err(p[tag + "_grad_" + key], wv) <= TOL, (tag, key)
+
+
 @pytest.mark.gpu
 def test_pair_weights_match_oracle_and_balance_bands():
     """GaussianSampler.pair_weights(): per-sample pair counts equal the oracle's (Gaussians binned to the sample's tile),

@@ -118,7 +118,7 @@ def _agg_worker(rank, world, port, out_dir):
         csr = (idx[a0:b0].copy(), np.cumsum(cnt_r).astype(np.int64), dists[a0:b0].copy(), dens[a0:b0].copy(), inv_r)
         a = [rec[k] for k in AGG_KEYS]
         w, e, f, out = po.aggregate_forward(*a, *csr)
-        red = AggregateReduce()
+        red = AggregateReduce(windows=[shard_range(P, r, world) for r in range(world)])  # row-owned tensors all-gathered
         out_t = red.output(torch.from_numpy(np.ascontiguousarray(out, np.float32)))
         grads = po.aggregate_backward(*a, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], agg_upstream(rec))
         gl = [torch.from_numpy(np.ascontiguousarray(g, np.float32)) for g in grads]
@@ -185,3 +185,141 @@ def test_balanced_ranges_equalise_weight():
     heavy = torch.tensor([1.0, 1.0, 100.0, 1.0])
     rs = balanced_ranges(heavy, 3)
     assert rs[0][0] == 0 and rs[-1][1] == 4 and all(lo <= hi for lo, hi in rs)
+
+
+def _local_csr(P, k, seed):
+    """A spatially local CSR on P rows: row i names up to k neighbours within +-k of i (ascending), with seeded
+    dists / densities — what a kNN list over grid-ordered Gaussians looks like (the C5 bench's 16-regular lists)."""
+    rng = np.random.default_rng(seed)
+    rows = []
+    for i in range(P):
+        cand = np.arange(max(0, i - k), min(P, i + k + 1))
+        rows.append(np.sort(rng.choice(cand, size=min(k, cand.size), replace=False)))
+    cnt = np.array([len(r) for r in rows], np.int64)
+    idx = np.concatenate(rows).astype(np.int64)
+    M = idx.size
+    dists = rng.uniform(-1, 1, (M, 2)).astype(np.float32)
+    dens = rng.uniform(0.1, 1.0, M).astype(np.float32)
+    return idx, cnt, dists, dens
+
+
+def _window_csr(idx, cnt, dists, dens, lo, hi):
+    starts = np.cumsum(cnt) - cnt
+    a0, b0 = int(starts[lo]) if lo < len(cnt) else int(cnt.sum()), int(starts[hi - 1] + cnt[hi - 1]) if hi > lo else 0
+    if hi <= lo:
+        a0 = b0 = 0
+    cnt_r = np.zeros_like(cnt)
+    cnt_r[lo:hi] = cnt[lo:hi]
+    inv = np.full(len(cnt), np.float32(1e6), np.float32)
+    tot = np.add.reduceat(dens, starts)[lo:hi] if hi > lo else np.zeros(0, np.float32)
+    inv[lo:hi] = (1.0 / (tot + 1e-6)).astype(np.float32)
+    return idx[a0:b0].copy(), np.cumsum(cnt_r).astype(np.int64), dists[a0:b0].copy(), dens[a0:b0].copy(), inv
+
+
+def _halo_worker(rank, world, port, out_dir, windows, k):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from oracle import pigs_oracle as po
+        from pigs_b200.sharded import RowHaloPlan, allreduce_grads, pack_grads, unpack_grads
+        from tests.fixtures import agg_params
+        P = windows[-1][1]
+        ap = agg_params(P, 16, 16, 25, 2, seed=5)
+        idx, cnt, dists, dens = _local_csr(P, k, seed=6)
+        lo, hi = windows[rank]
+        csr = _window_csr(idx, cnt, dists, dens, lo, hi)
+        plan = RowHaloPlan(P, (lo, hi), torch.from_numpy(csr[0]))
+        # full-height staging with NaN outside this rank's window: the exchange must fill exactly what the lists name
+        feat = torch.full((P, 16), float("nan"))
+        keys = torch.full((P, 16), float("nan"))
+        feat[lo:hi] = torch.from_numpy(ap["features"][lo:hi])
+        keys[lo:hi] = torch.from_numpy(ap["keys"][lo:hi])
+        plan.gather([feat, keys])
+        assert torch.isfinite(feat[plan.jlo:plan.jhi]).all() and torch.isfinite(keys[plan.jlo:plan.jhi]).all()
+        f_np, k_np = np.nan_to_num(feat.numpy()), np.nan_to_num(keys.numpy())
+        a = [f_np, ap["transform"], ap["queries"], k_np, ap["frequencies"], ap["distance_transform"]]
+        w, e, f, out = po.aggregate_forward(*a, *csr)
+        g = np.random.default_rng(9).normal(size=(P, 16)).astype(np.float32)
+        g_loc = np.zeros_like(g)
+        g_loc[lo:hi] = g[lo:hi]
+        grads = po.aggregate_backward(*a, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], g_loc)
+        gf = torch.from_numpy(np.ascontiguousarray(grads[0], np.float32))
+        gk = torch.from_numpy(np.ascontiguousarray(grads[3], np.float32))
+        plan.scatter_add([gf, gk])
+        flat, recipe = pack_grads([torch.from_numpy(np.ascontiguousarray(grads[i], np.float32)) for i in (1, 4, 5)])
+        allreduce_grads(flat)
+        gt, gfr, gdt = unpack_grads(flat, recipe, 3)
+        np.savez(os.path.join(out_dir, "halo%d.npz" % rank), lo=lo, hi=hi, dense=int(plan.dense), halo=plan.halo_rows,
+                 out=out[lo:hi], g_features=gf[lo:hi].numpy(), g_keys=gk[lo:hi].numpy(), g_queries=grads[2][lo:hi],
+                 g_transform=gt.numpy(), g_frequencies=gfr.numpy(), g_distance_transform=gdt.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+@pytest.mark.parametrize("windows,k", [([(0, 150), (150, 300)], 12),            # halo exchange, two equal windows
+                                       ([(0, 90), (90, 200), (200, 330)], 16),  # three unequal windows
+                                       ([(0, 30), (30, 60), (60, 90)], 70)])    # strips cover everything: dense fallback
+def test_row_halo_plan_matches_single_process(tmp_path, windows, k):
+    """Row-parallel aggregation host logic (RowHaloPlan) over gloo: each rank holds only its window of features / keys,
+    exchanges the halo rows its lists name, and gets back its own rows of the output and of every gradient; the
+    concatenation over ranks equals the unsharded oracle run."""
+    from oracle import pigs_oracle as po
+    from tests.fixtures import agg_params
+    from tests.helpers import TOL, rel_err
+    world = len(windows)
+    mp.spawn(_halo_worker, args=(world, _free_port(), str(tmp_path), windows, k), nprocs=world, join=True)
+    P = windows[-1][1]
+    ap = agg_params(P, 16, 16, 25, 2, seed=5)
+    idx, cnt, dists, dens = _local_csr(P, k, seed=6)
+    csr = _window_csr(idx, cnt, dists, dens, 0, P)
+    a = [ap[n] for n in ("features", "transform", "queries", "keys", "frequencies", "distance_transform")]
+    w, e, f, out = po.aggregate_forward(*a, *csr)
+    g = np.random.default_rng(9).normal(size=(P, 16)).astype(np.float32)
+    want = po.aggregate_backward(*a, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], g)
+    parts = [np.load(os.path.join(str(tmp_path), "halo%d.npz" % r)) for r in range(world)]
+    assert all(int(p["dense"]) == int(parts[0]["dense"]) for p in parts)
+    assert int(parts[0]["dense"]) == (1 if k >= 40 else 0)
+    cat = lambda key: np.concatenate([p[key] for p in parts], 0)
+    np.testing.assert_array_equal(cat("out"), out)  # a row's result does not depend on the sharding
+    assert rel_err(cat("g_features"), want[0]) <= TOL
+    assert rel_err(cat("g_queries"), want[2]) <= TOL
+    assert rel_err(cat("g_keys"), want[3]) <= TOL
+    for p in parts:
+        assert rel_err(p["g_transform"], want[1]) <= TOL
+        assert rel_err(p["g_frequencies"], want[4]) <= TOL
+        assert rel_err(p["g_distance_transform"], want[5]) <= TOL
+
+
+def _empty_shard_worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from pigs_b200.sharded import allgather_rows, allreduce_bounds, gather_windows
+        D = 2
+        if rank == 0:
+            mm = torch.tensor([-0.5, -0.25, 0.75, 1.0])
+        else:  # a rank without samples joins the collective with the neutral element (ShardedGaussianSampler.preprocess)
+            mm = torch.cat([torch.full((D,), float("inf")), torch.full((D,), float("-inf"))])
+        allreduce_bounds(mm, D)
+        wins = gather_windows((0, 5) if rank == 0 else (5, 5), "cpu")
+        buf = torch.zeros(5, 3)
+        if rank == 0:
+            buf[:] = torch.arange(15.0).view(5, 3)
+        allgather_rows(buf, wins)
+        np.savez(os.path.join(out_dir, "empty%d.npz" % rank), mm=mm.numpy(), wins=np.array(wins), buf=buf.numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_empty_shard_joins_the_collectives(tmp_path):
+    mp.spawn(_empty_shard_worker, args=(2, _free_port(), str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        p = np.load(os.path.join(str(tmp_path), "empty%d.npz" % r))
+        np.testing.assert_array_equal(p["mm"], np.array([-0.5, -0.25, 0.75, 1.0], np.float32))
+        np.testing.assert_array_equal(p["wins"], np.array([[0, 5], [5, 5]]))
+        np.testing.assert_array_equal(p["buf"], np.arange(15.0, dtype=np.float32).reshape(5, 3))
