@@ -98,12 +98,16 @@ int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float *means
                                  float cull_sigmas, void *stream);
 
 /* ---- preprocess stage B: key emission, stable sort by tile, ranges; sample binning ---------------
- * (sampler_impl.cu:54-189, 259-327).  Sizes are functions of the header values read back by the host. */
+ * (sampler_impl.cu:54-189, 259-327).  Sizes are functions of the header values read back by the host.
+ * Also builds, once per preprocess, the evaluation staging that depends on the binning only and is reused by every
+ * forward / backward call of the cycle (kept inside the opaque binning_buffer): the class of every (tile, Gaussian)
+ * instance (no torus wrap possible / constant wrap / general — decided from `conics`, the ones PreprocessCUDA receives,
+ * sample_points.cu:41, and the tile's sample bounding box), its scan, and the kernels' device-side work lists. */
 size_t pigs_binning_bytes(int64_t num_rendered, int blocks);
 size_t pigs_sample_binning_bytes(int64_t N, int blocks, int D);
 size_t pigs_sort_workspace_bytes(int64_t num_rendered, int64_t N);
 int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_rendered, const float *means,
-                        const float *samples, const float *radii, const void *geom_ws,
+                        const float *conics, const float *samples, const float *radii, const void *geom_ws,
                         void *binning_buffer, void *sample_binning_buffer,
                         void *ranges /* uint2[blocks+1] out */, void *sample_ranges /* uint2[blocks+1] out */,
                         void *sort_ws, void *stream);
@@ -141,6 +145,22 @@ int64_t pigs_launch_count(void);
 void pigs_set_debug(int on);
 int pigs_get_debug(void);
 
+/* Deterministic forward (default off; read by pigs_preprocess_bin).  The reference forward gives every sample to one
+ * thread and adds its Gaussians in ascending id (forward.cu:100-166), so its outputs are bitwise reproducible; the default
+ * mode here splits a tile's Gaussians over several work items and classes that each add their partial sum with one
+ * RED.ADD, so u / grad u / Hessian vary at the 1e-6 level from run to run.  With the option on, every instance takes the
+ * GENERAL class (exact per-pair wrap and skip; a tile's list stays in ascending id) and the forward's Gaussians are not
+ * split: each output element is written by exactly one work item, in the reference's order -> run-to-run bit equality
+ * of pigs_sample_forward, at the GENERAL loop's pace.  The backward was never deterministic in the reference either
+ * (atomics per pair, backward.cu:131-147) and is not made so here. */
+void pigs_set_deterministic(int on);
+int pigs_get_deterministic(void);
+
+/* Library-level option (default 1): the FAST / SHIFT / GENERAL kernels of one forward / backward call run concurrently on
+ * three streams forked from and joined back into the caller's stream (one launch tail instead of three).  0 launches them
+ * in order on the caller's stream.  Results are the same up to the order of the RED.ADDs. */
+void pigs_set_class_concurrency(int on);
+
 /* Optional device timing of the evaluation kernels (bench.py roofline).  While on, the forward /
  * backward evaluation launches of every pigs_sample_forward / pigs_sample_backward call are
  * bracketed by cudaEvents on the call's stream.  pigs_kernel_timing_read(which = 0 forward |
@@ -158,6 +178,12 @@ int pigs_neighbors_count(int64_t P, int D, const float *means, const float *radi
 int pigs_neighbors_fill(int64_t P, int D, const float *means, const float *conics, const float *radii,
                         const int64_t *ranges, int64_t *indices, float *dists, float *densities,
                         float *inv_total_densities, void *workspace, void *stream);
+/* between the stages: ranges = inclusive prefix sum of counts (the library's single-pass scan; the reference uses
+ * cub::DeviceScan / torch.cumsum, aggregate_neighbors.cu:343-350) and *total (device int64) = the CSR length M, which
+ * the host reads back once to size the arrays.  workspace: pigs_neighbors_scan_workspace_bytes(P). */
+size_t pigs_neighbors_scan_workspace_bytes(int64_t P);
+int pigs_neighbors_ranges(int64_t P, const int64_t *counts, int64_t *ranges, int64_t *total, void *workspace,
+                          void *stream);
 /* The same two stages for the rows (query Gaussians) [row_lo, row_hi) only — multi-GPU aggregation shards the CSR by
  * query Gaussian.  Every Gaussian stays a candidate neighbour; rows outside the window get count 0 and
  * the no-neighbour total 1/(0 + 1e-6), so the aggregation kernels run unchanged on the sharded CSR. */

@@ -79,6 +79,18 @@ def read_header(buf):
     return PigsHeader.from_buffer_copy(host.numpy().tobytes())
 
 
+def _read_i64(dev_scalar):
+    """One device int64 -> host through pinned memory on the current stream (the only sync of the call)."""
+    key = ("i64", dev_scalar.device.index, torch.cuda.current_stream().cuda_stream)
+    host = _pinned.get(key)
+    if host is None:
+        host = torch.empty(1, dtype=torch.int64).pin_memory()
+        _pinned[key] = host
+    host.copy_(dev_scalar, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return int(host.item())
+
+
 def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, cull=None):
     """PreprocessCUDA (sample_points.cu:37-98).  Returns
     (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii).
@@ -99,7 +111,7 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
         raise RuntimeError(f"pigs_b200 supports 1-D and 2-D mixtures (got D={D}), like the reference kernels")
     cov = _f32c(covariances, "covariances")
     samples = _f32c(samples, "samples")
-    _f32c(values, "values"), _f32c(conics, "conics")
+    _f32c(values, "values")
     if cov.numel() != P * D * (D + 1) // 2:
         raise RuntimeError("covariances must hold P*D*(D+1)/2 elements")
     st = _stream()
@@ -115,10 +127,11 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
     blocks, R = int(h.blocks), int(h.num_rendered)
     binning = _bytes(L.pigs_binning_bytes(R, blocks), dev)
     sbinning = _bytes(L.pigs_sample_binning_bytes(N, blocks, D), dev)
-    ranges = torch.zeros(blocks * 8 + 8, dtype=torch.uint8, device=dev)
-    sample_ranges = torch.zeros(blocks * 8 + 8, dtype=torch.uint8, device=dev)
+    ranges = torch.empty(blocks * 8 + 8, dtype=torch.uint8, device=dev)  # written (or zeroed) by the library
+    sample_ranges = torch.empty(blocks * 8 + 8, dtype=torch.uint8, device=dev)
     sort_ws = _bytes(L.pigs_sort_workspace_bytes(R, N), dev)
-    check(L.pigs_preprocess_bin(P, D, N, blocks, R, _ptr(means), _ptr(samples), _ptr(radii), _ptr(geom), _ptr(binning),
+    conics = _f32c(conics, "conics")
+    check(L.pigs_preprocess_bin(P, D, N, blocks, R, _ptr(means), _ptr(conics), _ptr(samples), _ptr(radii), _ptr(geom), _ptr(binning),
                                 _ptr(sbinning), _ptr(ranges), _ptr(sample_ranges), _ptr(sort_ws), st),
           "pigs_preprocess_bin")
     return R, binning, sbinning, ranges, sample_ranges, radii
@@ -253,8 +266,14 @@ def preprocess_aggregate(means, conics, radii, debug, rows=None):
     st = _stream()
     check(L.pigs_neighbors_count_rows(P, D, _ptr(means), _ptr(radii), lo, hi, _ptr(counts), _ptr(ws), st),
           "pigs_neighbors_count_rows")
-    ranges = counts.cumsum(0)
-    length = int(ranges[-1].item()) if P > 0 else 0
+    # CSR ranges = inclusive scan of the counts (library scan), total read back once through pinned memory
+    ranges = torch.empty_like(counts)
+    total = torch.zeros(1, dtype=torch.int64, device=dev)
+    length = 0
+    if P > 0:
+        sws = _bytes(max(int(L.pigs_neighbors_scan_workspace_bytes(P)), 16), dev)
+        check(L.pigs_neighbors_ranges(P, _ptr(counts), _ptr(ranges), _ptr(total), _ptr(sws), st), "pigs_neighbors_ranges")
+        length = _read_i64(total)
     # every CSR slot is written by the fill kernels (skipped neighbours get index -1 / density 0 there)
     indices = torch.empty((length,), dtype=torch.int64, device=dev)
     dists = torch.empty((length, D), dtype=torch.float32, device=dev)

@@ -22,8 +22,21 @@ from ._C import FN_DERIV, FN_HESS, FN_LAPL, FN_THIRD, FN_VALUE
 __all__ = [
     "GaussianSampler", "sample_gaussians", "sample_gaussians_derivative", "sample_gaussians_laplacian",
     "sample_gaussians_third_derivative", "aggregate_neighbors", "preprocess_gaussians", "preprocess_aggregate",
-    "FN_VALUE", "FN_DERIV", "FN_HESS", "FN_THIRD", "FN_LAPL",
+    "FN_VALUE", "FN_DERIV", "FN_HESS", "FN_THIRD", "FN_LAPL", "set_deterministic", "get_deterministic",
 ]
+
+
+def set_deterministic(on):
+    """(extension) Deterministic forward: bitwise run-to-run reproducible u / grad u / Hessian, like the reference's
+    forward (include/pigs_b200.h pigs_set_deterministic).  Takes effect at the next preprocess().  Also switched on by
+    the environment variable PIGS_DETERMINISTIC=1 when the library is loaded."""
+    from . import _lib
+    _lib.lib().pigs_set_deterministic(1 if on else 0)
+
+
+def get_deterministic():
+    from . import _lib
+    return bool(_lib.lib().pigs_get_deterministic())
 
 
 def cpu_deep_copy_tuple(input_tuple):

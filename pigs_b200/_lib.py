@@ -52,7 +52,7 @@ SIGNATURES = {
     "pigs_binning_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_sample_binning_bytes": (c_size_t, [c_int64, c_int, c_int]),
     "pigs_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),
-    "pigs_preprocess_bin": (c_int, [c_int64, c_int, c_int64, c_int, c_int64] + [c_void_p] * 10),
+    "pigs_preprocess_bin": (c_int, [c_int64, c_int, c_int64, c_int, c_int64] + [c_void_p] * 11),
     "pigs_point_list": (c_void_p, [c_void_p]),
     "pigs_point_tiles": (c_void_p, [c_void_p, c_int64]),
     "pigs_sample_list": (c_void_p, [c_void_p]),
@@ -62,11 +62,16 @@ SIGNATURES = {
     "pigs_launch_count": (c_int64, []),
     "pigs_set_debug": (None, [c_int]),
     "pigs_get_debug": (c_int, []),
+    "pigs_set_deterministic": (None, [c_int]),
+    "pigs_get_deterministic": (c_int, []),
+    "pigs_set_class_concurrency": (None, [c_int]),
     "pigs_set_kernel_timing": (None, [c_int]),
     "pigs_kernel_timing_read": (c_int, [c_int, c_void_p, c_void_p]),
     "pigs_neighbor_workspace_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_neighbors_count": (c_int, [c_int64, c_int] + [c_void_p] * 5),
     "pigs_neighbors_fill": (c_int, [c_int64, c_int] + [c_void_p] * 10),
+    "pigs_neighbors_scan_workspace_bytes": (c_size_t, [c_int64]),
+    "pigs_neighbors_ranges": (c_int, [c_int64] + [c_void_p] * 5),
     "pigs_neighbors_count_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 3),
     "pigs_neighbors_fill_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 7),
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
@@ -128,6 +133,8 @@ def lib():
             fn = getattr(L, name)  # AttributeError if the .so does not export a declared symbol
             fn.restype = res
             fn.argtypes = args
+        if os.environ.get("PIGS_DETERMINISTIC", "0") not in ("", "0"):
+            L.pigs_set_deterministic(1)  # bitwise reproducible forward (include/pigs_b200.h)
         _lib = L
     return _lib
 

@@ -1391,6 +1391,14 @@ int pigs_neighbors_fill_rows(int64_t P, int D, const float* means, const float* 
     return 0;
 }
 
+size_t pigs_neighbors_scan_workspace_bytes(int64_t P) { return scan_ws_bytes(P); }
+
+int pigs_neighbors_ranges(int64_t P, const int64_t* counts, int64_t* ranges, int64_t* total, void* workspace, void* stream)
+{
+    PIGS_ARG(P > 0 && counts && ranges && total && workspace);
+    return inclusive_scan_i64(counts, ranges, P, workspace, (cudaStream_t)stream, (long long*)total);
+}
+
 void pigs_set_aggregate_specialised(int on) { g_agg_fast = on != 0; }
 
 void pigs_set_neighbor_search(int cell_cap, float cell_div)

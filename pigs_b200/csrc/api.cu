@@ -3,7 +3,6 @@
 // compiled (mask, channel-group) kernels, stage, launch.  No host synchronisation anywhere.
 #include "layouts.cuh"
 
-#include <stdlib.h>
 #include <vector>
 
 using namespace pigs;
@@ -90,39 +89,19 @@ int resolve(EvalCall& c, int64_t P, int D, int64_t N, int C, int blocks, int64_t
     c.values = values;
     c.conics = conics;
     c.samples = samples;
-    BinLayout b(const_cast<void*>(binning_buffer), R);
+    BinLayout b(const_cast<void*>(binning_buffer), R, blocks);
     SampleBinLayout s(const_cast<void*>(sample_binning_buffer), N, blocks, D);
     c.list = b.list;
     c.tiles = b.tiles;
+    c.cls = b.cls;
+    c.scode = b.scode;
+    c.segs = b.segs;
+    c.wt = b.wt;
     c.slist = s.list;
     c.bbox = s.bbox;
     c.ranges = (const uint2*)ranges;
     c.sample_ranges = (const uint2*)sample_ranges;
     return 0;
-}
-
-// Work items per SM the list aims for.  The tail of a persistent launch is about one item long, and the backward's
-// items (1024 Gaussians x a slice of the tile's samples) are the heavier ones: measured on B200 at C3 the backward goes
-// 696.5 -> 649 ms from 48 to 768 items per SM, the forward is flat to slightly worse (profiles/r01n_split_target.log).
-int split_target_per_sm(bool backward)
-{
-    static int v[2] = {0, 0};
-    if (v[backward] == 0) {
-        const char* e = getenv(backward ? "PIGS_SPLIT_TARGET_BWD" : "PIGS_SPLIT_TARGET_FWD");  // tuning hook
-        v[backward] = e ? atoi(e) : (backward ? 768 : 48);
-        if (v[backward] < 1) v[backward] = 48;
-    }
-    return v[backward];
-}
-
-uint32_t split_hint(int64_t stationary, uint32_t chunk, int blocks, bool backward)
-{
-    const int64_t target = (int64_t)num_sms() * split_target_per_sm(backward);
-    const int64_t base = stationary / chunk + blocks;
-    int64_t s = (target + base - 1) / base;
-    if (s < 1) s = 1;
-    if (s > 4096) s = 4096;
-    return (uint32_t)s;
 }
 
 }  // namespace
@@ -134,6 +113,9 @@ const char* pigs_last_error(void) { return g_err; }
 void pigs_set_grid_recip_mode(int recip) { g_recip_mode = recip ? 1 : 0; }
 int64_t pigs_launch_count(void) { return g_launches; }
 void pigs_set_debug(int on) { g_debug_sync = on ? 1 : 0; }
+void pigs_set_deterministic(int on) { g_deterministic = on ? 1 : 0; }
+int pigs_get_deterministic(void) { return g_deterministic; }
+void pigs_set_class_concurrency(int on) { g_class_concurrency = on ? 1 : 0; }
 int pigs_get_debug(void) { return g_debug_sync; }
 
 void pigs_set_kernel_timing(int on)
@@ -199,16 +181,14 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
 
     for (int ch0 = 0; ch0 < C; ch0 += 2) {
         const int cw = (C - ch0) >= 2 ? 2 : 1;
-        rc = stage_gaussians(c, cw, ch0, true, ws, st);
-        if (rc) return rc;
         // Laplacian: 2-D one-channel groups run the trace-only kernels (mask 16 / 19); other shapes run the Hessian
         // kernels and form the trace in the epilogue
         const bool lap_native = lap && D == 2 && cw == 1;
         unsigned todo[2] = {native_low_mask(lap_native ? ((fn_mask & 3u) | PIGS_FN_LAPL) : fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
             if (!m) continue;
-            const uint32_t chunk = EV_THREADS * fwd_ks(D, cw, m);
-            rc = stage_worklist(c, ws, chunk, split_hint(N, chunk, blocks, false), 256, true, st);
+            const int wl = fwd_ks(D, cw, m) == 8 ? WL_FWD8 : WL_FWD4;
+            rc = stage_gaussians(c, cw, ch0, true, wl, ws, st);  // packed records + this launch's work header
             if (rc) return rc;
             FwdOut o;
             o.u = (fn_mask & PIGS_FN_VALUE) ? out_u : nullptr;
@@ -218,10 +198,8 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
             o.lap = (lap && !lap_native) ? 1 : 0;
             {
                 ScopedKernelTimer tm(0, st);
-                for (int mode = 0; mode < EV_NSEG; mode++) {
-                    rc = launch_forward(c, cw, m, mode, ch0, ws, o, st);
-                    if (rc) return rc;
-                }
+                rc = launch_forward(c, cw, m, wl, ch0, ws, o, st);
+                if (rc) return rc;
             }
         }
     }
@@ -258,26 +236,21 @@ int pigs_sample_backward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, i
 
     for (int ch0 = 0; ch0 < C; ch0 += 2) {
         const int cw = (C - ch0) >= 2 ? 2 : 1;
-        rc = stage_gaussians(c, cw, ch0, false, ws, st);
-        if (rc) return rc;
         const bool lap_native = lap && D == 2 && cw == 1;
         unsigned todo[2] = {native_low_mask(lap_native ? ((fn_mask & 3u) | PIGS_FN_LAPL) : fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
             if (!m) continue;
+            rc = stage_gaussians(c, cw, ch0, false, WL_BWD, ws, st);
+            if (rc) return rc;
             rc = stage_samples(c, cw, m, ch0, (fn_mask & PIGS_FN_VALUE) ? dL_du : nullptr,
                                (fn_mask & PIGS_FN_DERIV) ? dL_ddu : nullptr, (fn_mask & PIGS_FN_HESS) ? dL_dddu : nullptr,
                                (fn_mask & PIGS_FN_THIRD) ? dL_ddddu : nullptr, lap && !lap_native, ws, st);
             if (rc) return rc;
-            const uint32_t chunk = EV_THREADS * bwd_kg(D, cw, m);
-            rc = stage_worklist(c, ws, chunk, split_hint(num_rendered, chunk, blocks, true), 128, false, st);
-            if (rc) return rc;
             BwdOut o{dL_dmeans, dL_dvalues, dL_dconics};
             {
                 ScopedKernelTimer tm(1, st);
-                for (int mode = 0; mode < EV_NSEG; mode++) {
-                    rc = launch_backward(c, cw, m, mode, ch0, ws, o, st);
-                    if (rc) return rc;
-                }
+                rc = launch_backward(c, cw, m, ch0, ws, o, st);
+                if (rc) return rc;
             }
         }
     }

@@ -25,7 +25,7 @@ __global__ void bounds_init(float* mm, int D)
 
 template <int D>
 __global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ samples, int64_t N, float* __restrict__ mm,
-                                                     bool pair_loads)
+                                                     bool pair_loads, bool direct)
 {
     float lo[D], hi[D];
 #pragma unroll
@@ -73,19 +73,22 @@ __global__ void __launch_bounds__(256) bounds_kernel(const float* __restrict__ s
             l = fminf(l, slo[i][d]);
             h = fmaxf(h, shi[i][d]);
         }
-        atomic_min_float(mm + d, l + 0.0f);
-        atomic_max_float(mm + D + d, h + 0.0f);
+        if (direct) {  // single-CTA launch (small N): no initialisation launch needed
+            mm[d] = l + 0.0f;
+            mm[D + d] = h + 0.0f;
+        } else {
+            atomic_min_float(mm + d, l + 0.0f);
+            atomic_max_float(mm + D + d, h + 0.0f);
+        }
     }
 }
 
 // ---------------------------------------------------------------------------------------------
 // header / tile grid (sample_points.cu:73-74)
 // ---------------------------------------------------------------------------------------------
-__global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int64_t N, int recip, int subdiv, float cull,
-                            pigs_header* hdr)
+__device__ __forceinline__ void make_header(const float* __restrict__ mm, int D, int64_t P, int64_t N, int recip, int subdiv,
+                                            float cull, pigs_header& h)
 {
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    pigs_header h;
     memset(&h, 0, sizeof(h));
     h.magic = PIGS_MAGIC;
     h.D = D;
@@ -112,7 +115,6 @@ __global__ void grid_kernel(const float* __restrict__ mm, int D, int64_t P, int6
     h.tile_width = subdiv > 1 ? __fdiv_rn(PIGS_TILE_WIDTH, (float)subdiv) : PIGS_TILE_WIDTH;
     h.blocks = blocks;
     h.nslots = blocks + h.grid[0] + 2;
-    *hdr = h;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -212,12 +214,22 @@ struct CullDim {
     }
 };
 
+// S1 (tile grid, sample_points.cu:73-74) + S2/S3 in ONE launch: every CTA derives the header from the sample bounds
+// in shared memory (a dozen flops); block 0 publishes it for the host readback and the later kernels.
 template <int D>
-__global__ void __launch_bounds__(256) count_kernel(int64_t P, const float* __restrict__ means,
-                                                    const float* __restrict__ cov, const pigs_header* __restrict__ hdr,
+__global__ void __launch_bounds__(256) count_kernel(int64_t P, int64_t N, const float* __restrict__ means,
+                                                    const float* __restrict__ cov, const float* __restrict__ mm, int recip,
+                                                    int subdiv, float cull, pigs_header* __restrict__ hdr_out,
                                                     float* __restrict__ radii, uint32_t* __restrict__ touched,
                                                     float* __restrict__ cull_r)
 {
+    __shared__ pigs_header s_hdr;
+    if (threadIdx.x == 0) {
+        make_header(mm, D, P, N, recip, subdiv, cull, s_hdr);
+        if (blockIdx.x == 0) *hdr_out = s_hdr;
+    }
+    __syncthreads();
+    const pigs_header* hdr = &s_hdr;
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= P) return;
     constexpr int K = D * (D + 1) / 2;
@@ -248,12 +260,6 @@ __global__ void __launch_bounds__(256) count_kernel(int64_t P, const float* __re
         }
     }
     touched[g] = n;
-}
-
-// total -> header.num_rendered
-__global__ void store_total(const uint32_t* __restrict__ offsets, int64_t P, pigs_header* hdr)
-{
-    if (threadIdx.x == 0 && blockIdx.x == 0) hdr->num_rendered = (int64_t)offsets[P];
 }
 
 // culled mode: one (fine tile, id) pair per kept fine tile, id-major
@@ -304,8 +310,20 @@ __global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __res
                                                    const float* __restrict__ radii, const float* __restrict__ cull_r,
                                                    const uint32_t* __restrict__ offsets,
                                                    const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
-                                                   uint32_t* __restrict__ vals)
+                                                   uint32_t* __restrict__ vals, float* __restrict__ bbox, int nbox,
+                                                   pigs_header* __restrict__ hdr_b, pigs_header* __restrict__ hdr_s)
 {
+    if (blockIdx.x == 0) {
+        // side jobs of the first CTA (they used to be a launch and two copies): empty sample boxes for
+        // sample_key_kernel, and the header at the front of the two opaque buffers
+        for (int k = threadIdx.x; k < nbox * 2 * D; k += blockDim.x)
+            bbox[k] = (k % (2 * D)) < D ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
+        if (threadIdx.x < (int)(sizeof(pigs_header) / 4)) {
+            const uint32_t w = reinterpret_cast<const uint32_t*>(hdr)[threadIdx.x];
+            reinterpret_cast<uint32_t*>(hdr_b)[threadIdx.x] = w;
+            reinterpret_cast<uint32_t*>(hdr_s)[threadIdx.x] = w;
+        }
+    }
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (g >= P) return;
     const float r = radii[g];
@@ -344,13 +362,17 @@ __global__ void __launch_bounds__(256) emit_kernel(int64_t P, const float* __res
 // SMEM = true (few tile slots, the usual 4x4 grid): the boxes are reduced in shared memory by a grid-stride CTA and
 // merged with one global atomic per slot component per CTA — with uniformly scattered samples every lane of a warp
 // hits a different tile, so per-sample global atomics on a few dozen addresses serialise (6.8 ms at 4M samples).
+// Each CTA walks whole sort tiles (SORT_TILE_ELEMS consecutive samples) and leaves the per-tile digit histogram of the
+// sort's first pass behind (ghist[digit * ntiles + tile]), so the sort starts at its scan.
 template <int D, bool SMEM>
 __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float* __restrict__ samples,
                                                          const pigs_header* __restrict__ hdr, uint32_t* __restrict__ keys,
                                                          uint32_t* __restrict__ vals, float* __restrict__ bbox /* [nslots][2*D] */,
-                                                         int nslots)
+                                                         int nslots, uint32_t* __restrict__ ghist, int64_t ntiles,
+                                                         uint32_t digit_mask)
 {
     extern __shared__ float s_box[];  // [nslots][2*D]
+    __shared__ uint32_t s_hist[256];
     if constexpr (SMEM) {
         for (int k = threadIdx.x; k < nslots * 2 * D; k += blockDim.x)
             s_box[k] = (k % (2 * D)) < D ? __int_as_float(0x7f800000) : __int_as_float(0xff800000);
@@ -367,41 +389,51 @@ __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float*
         mn[d] = hdr->min_b[d];
         gr[d] = hdr->ref_grid[d];
     }
-    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < N; i += (int64_t)gridDim.x * blockDim.x) {
-        float x[D];
-        int t[D];
+    for (int64_t st = blockIdx.x; st < ntiles; st += gridDim.x) {
+        s_hist[threadIdx.x] = 0;
+        __syncthreads();
+        for (int r = 0; r < SORT_TILE_ELEMS / 256; r++) {
+            const int64_t i = st * SORT_TILE_ELEMS + r * 256 + threadIdx.x;
+            if (i >= N) break;
+            float x[D];
+            int t[D];
 #pragma unroll
-        for (int d = 0; d < D; d++) {
-            x[d] = samples[i * D + d];
-            const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
-            t[d] = min(gr[d], max(0, q));
-        }
-        uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
-        if (k > 1) {
-            // culled mode: the reference tile (alias quirk included) cut k x k; not a real tile -> dump slot
-            const uint32_t rt = tile;
-            tile = (uint32_t)hdr->blocks;
-            if ((int)rt < rblocks) {
-                const int par[2] = {(int)(rt % (uint32_t)g0), (int)(rt / (uint32_t)g0)};
-                int f[D];
+            for (int d = 0; d < D; d++) {
+                x[d] = samples[i * D + d];
+                const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
+                t[d] = min(gr[d], max(0, q));
+            }
+            uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+            if (k > 1) {
+                // culled mode: the reference tile (alias quirk included) cut k x k; not a real tile -> dump slot
+                const uint32_t rt = tile;
+                tile = (uint32_t)hdr->blocks;
+                if ((int)rt < rblocks) {
+                    const int par[2] = {(int)(rt % (uint32_t)g0), (int)(rt / (uint32_t)g0)};
+                    int f[D];
 #pragma unroll
-                for (int d = 0; d < D; d++) {
-                    const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), h) - k * par[d];
-                    f[d] = k * par[d] + min(k - 1, max(0, q));
+                    for (int d = 0; d < D; d++) {
+                        const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), h) - k * par[d];
+                        f[d] = k * par[d] + min(k - 1, max(0, q));
+                    }
+                    tile = D == 2 ? (uint32_t)f[D - 1] * (uint32_t)hdr->grid[0] + (uint32_t)f[0] : (uint32_t)f[0];
                 }
-                tile = D == 2 ? (uint32_t)f[D - 1] * (uint32_t)hdr->grid[0] + (uint32_t)f[0] : (uint32_t)f[0];
+            }
+            keys[i] = tile;
+            vals[i] = (uint32_t)i;
+            atomicAdd(&s_hist[tile & digit_mask], 1u);
+            float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
+#pragma unroll
+            for (int d = 0; d < D; d++) {
+                const float v = x[d] + 0.0f;  // -0 -> +0 so the integer-ordered atomics below are consistent
+                // the boxes only ever grow, so a stale read can at worst let a redundant atomic through
+                if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
+                if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
             }
         }
-        keys[i] = tile;
-        vals[i] = (uint32_t)i;
-        float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
-#pragma unroll
-        for (int d = 0; d < D; d++) {
-            const float v = x[d] + 0.0f;  // -0 -> +0 so the integer-ordered atomics below are consistent
-            // the boxes only ever grow, so a stale read can at worst let a redundant atomic through
-            if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
-            if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
-        }
+        __syncthreads();
+        ghist[(int64_t)threadIdx.x * ntiles + st] = s_hist[threadIdx.x];
+        __syncthreads();
     }
     if constexpr (SMEM) {
         __syncthreads();
@@ -464,15 +496,20 @@ int pigs_sample_bounds(const float* samples, int64_t N, int D, float* d_minmax, 
     PIGS_ARG(D == 1 || D == 2);
     PIGS_ARG(N > 0 && samples && d_minmax);
     cudaStream_t st = (cudaStream_t)stream;
-    bounds_init<<<1, 32, 0, st>>>(d_minmax, D);
-    PIGS_LAUNCH_CHECK();
     int64_t nb = (N + 255) / 256;
     const int cap = num_sms() * 8;
     if (nb > cap) nb = cap;
+    const bool direct = N <= 64 * 1024;  // one CTA writes the result itself: one launch instead of two
+    if (direct) {
+        nb = 1;
+    } else {
+        bounds_init<<<1, 32, 0, st>>>(d_minmax, D);
+        PIGS_LAUNCH_CHECK();
+    }
     if (D == 2)
-        bounds_kernel<2><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, (reinterpret_cast<uintptr_t>(samples) & 7) == 0);
+        bounds_kernel<2><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, (reinterpret_cast<uintptr_t>(samples) & 7) == 0, direct);
     else
-        bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, false);
+        bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, false, direct);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
@@ -494,26 +531,19 @@ int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float* means
     PIGS_ARG(subdiv >= 1 && subdiv <= 64 && (subdiv == 1 || cull_sigmas > 0.0f));
     cudaStream_t st = (cudaStream_t)stream;
     GeomLayout g(geom_ws, P);
-    grid_kernel<<<1, 32, 0, st>>>(d_minmax, D, P, N, g_recip_mode, subdiv, cull_sigmas, g.hdr);
-    PIGS_LAUNCH_CHECK();
     const unsigned nb = (unsigned)((P + 255) / 256);
     if (D == 2)
-        count_kernel<2><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched, g.cull_r);
+        count_kernel<2><<<nb, 256, 0, st>>>(P, N, means, covariances, d_minmax, g_recip_mode, subdiv, cull_sigmas, g.hdr, radii,
+                                            g.touched, g.cull_r);
     else
-        count_kernel<1><<<nb, 256, 0, st>>>(P, means, covariances, g.hdr, radii, g.touched, g.cull_r);
+        count_kernel<1><<<nb, 256, 0, st>>>(P, N, means, covariances, d_minmax, g_recip_mode, subdiv, cull_sigmas, g.hdr, radii,
+                                            g.touched, g.cull_r);
     PIGS_LAUNCH_CHECK();
-    int rc = exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st);
-    if (rc) return rc;
-    store_total<<<1, 32, 0, st>>>(g.touched, P, g.hdr);
-    PIGS_LAUNCH_CHECK();
-    return 0;
+    // offsets + the total straight into header.num_rendered (the word the host reads back)
+    return exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st, (long long*)&g.hdr->num_rendered);
 }
 
-size_t pigs_binning_bytes(int64_t num_rendered, int blocks)
-{
-    (void)blocks;
-    return BinLayout(nullptr, num_rendered).bytes;
-}
+size_t pigs_binning_bytes(int64_t num_rendered, int blocks) { return BinLayout(nullptr, num_rendered, blocks).bytes; }
 size_t pigs_sample_binning_bytes(int64_t N, int blocks, int D) { return SampleBinLayout(nullptr, N, blocks, D).bytes; }
 size_t pigs_sort_workspace_bytes(int64_t num_rendered, int64_t N)
 {
@@ -522,16 +552,17 @@ size_t pigs_sort_workspace_bytes(int64_t num_rendered, int64_t N)
 }
 
 int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_rendered, const float* means,
-                        const float* samples, const float* radii, const void* geom_ws, void* binning_buffer,
-                        void* sample_binning_buffer, void* ranges, void* sample_ranges, void* sort_ws, void* stream)
+                        const float* conics, const float* samples, const float* radii, const void* geom_ws,
+                        void* binning_buffer, void* sample_binning_buffer, void* ranges, void* sample_ranges, void* sort_ws,
+                        void* stream)
 {
     PIGS_ARG(D == 1 || D == 2);
     PIGS_ARG(P > 0 && N > 0 && blocks > 0 && num_rendered >= 0);
-    PIGS_ARG(means && samples && radii && geom_ws && binning_buffer && sample_binning_buffer && ranges && sample_ranges &&
-             sort_ws);
+    PIGS_ARG(means && conics && samples && radii && geom_ws && binning_buffer && sample_binning_buffer && ranges &&
+             sample_ranges && sort_ws);
     cudaStream_t st = (cudaStream_t)stream;
     GeomLayout g(const_cast<void*>(geom_ws), P);
-    BinLayout b(binning_buffer, num_rendered);
+    BinLayout b(binning_buffer, num_rendered, blocks);
     SampleBinLayout s(sample_binning_buffer, N, blocks, D);
     const int64_t nmax = num_rendered > N ? num_rendered : N;
     Carver c(sort_ws);
@@ -540,45 +571,71 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
     char* sws = c.take<char>(sort_ws_bytes(nmax));
     // tile ids are <= blocks + grid[0] (alias slots) <= 2*blocks
     const int bits = bit_length((uint32_t)(2 * blocks + 1));
-
-    PIGS_CHECK(cudaMemcpyAsync(b.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
-    PIGS_CHECK(cudaMemcpyAsync(s.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
-    PIGS_CHECK(cudaMemsetAsync(ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
-    PIGS_CHECK(cudaMemsetAsync(sample_ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+    const int64_t nslots = 2 * (int64_t)blocks + 4;
 
     if (num_rendered > 0) {
         const unsigned nb = (unsigned)((P + 255) / 256);
         if (D == 2)
-            emit_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u);
+            emit_kernel<2><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u, s.bbox, (int)nslots,
+                                               b.hdr, s.hdr);
         else
-            emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u);
+            emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u, s.bbox, (int)nslots,
+                                               b.hdr, s.hdr);
         PIGS_LAUNCH_CHECK();
-        int rc = stable_sort_pairs_u32(keys_u, vals_u, b.tiles, b.list, num_rendered, bits, sws, st);
+        bool done = false;
+        SortExtras ex;
+        ex.ranges = (uint2*)ranges;
+        ex.max_slot = blocks;
+        ex.ranges_written = &done;
+        int rc = stable_sort_pairs_u32(keys_u, vals_u, b.tiles, b.list, num_rendered, bits, sws, st, &ex);
         if (rc) return rc;
-        ranges_kernel<<<(unsigned)((num_rendered + 255) / 256), 256, 0, st>>>(num_rendered, b.tiles, (uint2*)ranges, blocks);
+        if (!done) {
+            PIGS_CHECK(cudaMemsetAsync(ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+            ranges_kernel<<<(unsigned)((num_rendered + 255) / 256), 256, 0, st>>>(num_rendered, b.tiles, (uint2*)ranges, blocks);
+            PIGS_LAUNCH_CHECK();
+        }
+    } else {
+        PIGS_CHECK(cudaMemcpyAsync(b.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
+        PIGS_CHECK(cudaMemcpyAsync(s.hdr, g.hdr, sizeof(pigs_header), cudaMemcpyDeviceToDevice, st));
+        PIGS_CHECK(cudaMemsetAsync(ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+        bbox_init<<<(unsigned)((nslots * 2 * D + 255) / 256), 256, 0, st>>>(s.bbox, nslots, D);
         PIGS_LAUNCH_CHECK();
     }
     {
-        const int64_t nslots = 2 * (int64_t)blocks + 4;
-        bbox_init<<<(unsigned)((nslots * 2 * D + 255) / 256), 256, 0, st>>>(s.bbox, nslots, D);
-        PIGS_LAUNCH_CHECK();
-        const int64_t nb_all = (N + 255) / 256;
+        const int64_t ntiles = sort_tiles(N);
         const size_t box_bytes = (size_t)nslots * 2 * D * sizeof(float);
         const bool smem = box_bytes <= 32 * 1024;
-        const unsigned nb = (unsigned)(smem ? (nb_all < (int64_t)num_sms() * 8 ? nb_all : (int64_t)num_sms() * 8) : nb_all);
+        const unsigned nb = (unsigned)(ntiles < (int64_t)num_sms() * 8 ? ntiles : (int64_t)num_sms() * 8);
+        const uint32_t dmask = (1u << (bits >= 8 ? 8 : bits)) - 1u;
+        uint32_t* gh = sort_ghist(sws);
         if (D == 2 && smem)
-            sample_key_kernel<2, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+            sample_key_kernel<2, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots, gh, ntiles, dmask);
         else if (D == 2)
-            sample_key_kernel<2, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+            sample_key_kernel<2, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots, gh, ntiles, dmask);
         else if (smem)
-            sample_key_kernel<1, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+            sample_key_kernel<1, true><<<nb, 256, box_bytes, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots, gh, ntiles, dmask);
         else
-            sample_key_kernel<1, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots);
+            sample_key_kernel<1, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots, gh, ntiles, dmask);
         PIGS_LAUNCH_CHECK();
-        int rc = stable_sort_pairs_u32(keys_u, vals_u, s.tiles, s.list, N, bits, sws, st);
+        bool done = false;
+        SortExtras ex;
+        ex.hist_done = true;
+        ex.ranges = (uint2*)sample_ranges;
+        ex.max_slot = blocks;
+        ex.ranges_written = &done;
+        int rc = stable_sort_pairs_u32(keys_u, vals_u, s.tiles, s.list, N, bits, sws, st, &ex);
         if (rc) return rc;
-        ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, s.tiles, (uint2*)sample_ranges, blocks);
-        PIGS_LAUNCH_CHECK();
+        if (!done) {
+            PIGS_CHECK(cudaMemsetAsync(sample_ranges, 0, (size_t)(blocks + 1) * sizeof(uint2), st));
+            ranges_kernel<<<(unsigned)((N + 255) / 256), 256, 0, st>>>(N, s.tiles, (uint2*)sample_ranges, blocks);
+            PIGS_LAUNCH_CHECK();
+        }
+    }
+    // evaluation staging that depends on the binning only: instance classes, their scan, the three work lists
+    if (num_rendered > 0) {
+        int rc = stage_classes(D, blocks, num_rendered, N, means, conics, s.bbox, (const uint2*)ranges,
+                               (const uint2*)sample_ranges, b, st);
+        if (rc) return rc;
     }
     return 0;
 }

@@ -14,6 +14,7 @@ namespace pigs {
 extern thread_local char g_err[512];
 extern int64_t g_launches;
 extern int g_recip_mode;
+extern int g_deterministic;  // pigs_set_deterministic (pack.cu)
 extern int g_debug_sync;  // pigs_set_debug: synchronise + check after EVERY launch (reference auxiliary.h:33-40)
 
 int set_error(int code, const char* what, const char* file, int line);
@@ -65,17 +66,36 @@ struct Carver {
 int num_sms();
 
 // ---------------------------------------------------------------------------------------------
-// exclusive scan of u32 (three small kernels; n up to 2^31).  out may alias in.  out[n] = total if
-// write_total.  ws: scan_ws_bytes(n).
+// exclusive scan of u32: ONE launch for any n (single-pass, decoupled look-back; one CTA for small n).  out may alias
+// in.  out[n] = total if write_total; *total_out (device int64, optional) = total.  ws: scan_ws_bytes(n).
 size_t scan_ws_bytes(int64_t n);
-int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_total, void* ws, cudaStream_t st);
+int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_total, void* ws, cudaStream_t st,
+                       long long* total_out = nullptr);
+// exclusive scan of u64 words (two packed 31-bit class counters, pack.cu), same kernel
+int exclusive_scan_u64(const unsigned long long* in, unsigned long long* out, int64_t n, bool write_total, void* ws,
+                       cudaStream_t st);
+// inclusive scan of int64 (neighbour counts -> CSR ranges), same kernel
+int inclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n, void* ws, cudaStream_t st, long long* total_out = nullptr);
 
 // stable LSD radix sort of (key u32, value u32) pairs on the low `bits` bits of the key.
 // keys_in/vals_in are clobbered when more than one pass is needed (ping-pong); result lands in
 // keys_out/vals_out.  ws: sort_ws_bytes(n).
 size_t sort_ws_bytes(int64_t n);
+// hist_done: the caller's key-producing kernel already wrote the first pass's per-tile digit histogram
+//   sort_ghist(ws)[digit * sort_tiles(n) + tile] (tiles of SORT_TILE_ELEMS consecutive keys, digit = key & 0xff)
+// ranges / max_slot: when ONE pass sorts the whole key (bits <= 8) the scatter kernel also writes the tile ranges
+//   [first, last + 1) of the keys 0..max_slot from the scanned histogram (*ranges_written tells whether it did).
+struct SortExtras {
+    bool hist_done = false;
+    uint2* ranges = nullptr;
+    int max_slot = 0;
+    bool* ranges_written = nullptr;
+};
+constexpr int SORT_TILE_ELEMS = 4096;
+uint32_t* sort_ghist(void* ws);
+int64_t sort_tiles(int64_t n);
 int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, int64_t n,
-                          int bits, void* ws, cudaStream_t st);
+                          int bits, void* ws, cudaStream_t st, const SortExtras* ex = nullptr);
 
 // ---------------------------------------------------------------------------------------------
 #ifdef __CUDACC__

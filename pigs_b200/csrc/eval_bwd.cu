@@ -555,30 +555,33 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
 }
 
 template <int D, int C, unsigned MASK, int MODE>
-static void launch_bwd_m(const EvalCall& c, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
+static void launch_bwd_m(const EvalCall& c, const TileSeg* segs, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
 {
-    eval_bwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, ws.rec_id, ws.srecs,
+    eval_bwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, segs, ws.wh, ws.recs, ws.rec_id, ws.srecs,
                                                                            c.C, ch0, o.dmeans, o.dvalues, o.dconics);
 }
 
+// the three class kernels run concurrently on forked streams (see eval_fwd.cu launch_fwd_t)
 template <int D, int C, unsigned MASK>
-static int launch_bwd_t(const EvalCall& c, int mode, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
+static int launch_bwd_t(const EvalCall& c, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
 {
-    if (mode == EV_FAST)
-        launch_bwd_m<D, C, MASK, EV_FAST>(c, ch0, ws, o, st);
-    else if (mode == EV_SHIFT)
-        launch_bwd_m<D, C, MASK, EV_SHIFT>(c, ch0, ws, o, st);
-    else
-        launch_bwd_m<D, C, MASK, EV_GENERAL>(c, ch0, ws, o, st);
+    const TileSeg* segs = c.segs + (size_t)WL_BWD * EV_NSEG * c.blocks;
+    ClassFork fk;
+    int rc = fk.fork(st);
+    if (rc) return rc;
+    launch_bwd_m<D, C, MASK, EV_FAST>(c, segs, ch0, ws, o, fk.stream(0));
     PIGS_LAUNCH_CHECK();
-    return 0;
+    launch_bwd_m<D, C, MASK, EV_SHIFT>(c, segs, ch0, ws, o, fk.stream(1));
+    PIGS_LAUNCH_CHECK();
+    launch_bwd_m<D, C, MASK, EV_GENERAL>(c, segs, ch0, ws, o, fk.stream(2));
+    PIGS_LAUNCH_CHECK();
+    return fk.join();
 }
 
-int launch_backward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, BwdOut out,
-                    cudaStream_t st)
+int launch_backward(const EvalCall& c, int C, unsigned mask, int ch0, const EvalWs& ws, BwdOut out, cudaStream_t st)
 {
 #define BW(D_, C_, M_) \
-    if (c.D == D_ && C == C_ && mask == M_) return launch_bwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
+    if (c.D == D_ && C == C_ && mask == M_) return launch_bwd_t<D_, C_, M_>(c, ch0, ws, out, st);
 #define BW_ALL(D_, C_) BW(D_, C_, 1u) BW(D_, C_, 2u) BW(D_, C_, 4u) BW(D_, C_, 7u) BW(D_, C_, 8u)
     BW_ALL(2, 1) BW_ALL(2, 2) BW_ALL(1, 1) BW_ALL(1, 2)
     BW(2, 1, 16u) BW(2, 1, 19u)  // trace-only Laplacian kernels

@@ -72,12 +72,13 @@ struct TileSeg {
 };
 
 struct WorkHeader {
-    uint32_t counter[4];  // dynamic work counters per seg
-    uint32_t items[4];    // total items per seg
+    uint32_t counter[4];  // dynamic work counters per class
+    uint32_t items[4];    // total items per class
     unsigned long long pairs;
     uint32_t neg_zero;  // bit pattern of -0.0f: a run-time addend ptxas cannot fold (pk2_once)
     uint32_t pad[5];
 };
+static_assert(sizeof(WorkHeader) == 64, "WorkHeader is one 64-byte line");
 
 struct WorkItem {
     uint32_t g_begin, g_count, s_begin, s_count;

@@ -320,30 +320,36 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
 }
 
 template <int D, int C, unsigned MASK, int MODE>
-static void launch_fwd_m(const EvalCall& c, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
+static void launch_fwd_m(const EvalCall& c, const TileSeg* segs, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
 {
-    eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, ws.segs, ws.wh, ws.recs, c.slist, c.samples,
+    eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, segs, ws.wh, ws.recs, c.slist, c.samples,
                                                                            c.C, ch0, o.u, o.du, o.ddu, o.dddu, o.lap);
 }
 
+// The three class kernels of one call are independent (own work counters, outputs combined with RED.ADD), so they are
+// launched on three streams forked from / joined back into the caller's: the persistent CTAs of the SHIFT and GENERAL
+// kernels move in as the FAST kernel's CTAs run out of items, and the call has ONE tail instead of three back-to-back
+// ones — what a small shard (N = 8: a few ms of forward per rank) loses most on.  Deterministic mode keeps them in order.
 template <int D, int C, unsigned MASK>
-static int launch_fwd_t(const EvalCall& c, int mode, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
+static int launch_fwd_t(const EvalCall& c, int wl, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
 {
-    if (mode == EV_FAST)
-        launch_fwd_m<D, C, MASK, EV_FAST>(c, ch0, ws, o, st);
-    else if (mode == EV_SHIFT)
-        launch_fwd_m<D, C, MASK, EV_SHIFT>(c, ch0, ws, o, st);
-    else
-        launch_fwd_m<D, C, MASK, EV_GENERAL>(c, ch0, ws, o, st);
+    const TileSeg* segs = c.segs + (size_t)wl * EV_NSEG * c.blocks;
+    ClassFork fk;
+    int rc = fk.fork(st);
+    if (rc) return rc;
+    launch_fwd_m<D, C, MASK, EV_FAST>(c, segs, ch0, ws, o, fk.stream(0));
     PIGS_LAUNCH_CHECK();
-    return 0;
+    launch_fwd_m<D, C, MASK, EV_SHIFT>(c, segs, ch0, ws, o, fk.stream(1));
+    PIGS_LAUNCH_CHECK();
+    launch_fwd_m<D, C, MASK, EV_GENERAL>(c, segs, ch0, ws, o, fk.stream(2));
+    PIGS_LAUNCH_CHECK();
+    return fk.join();
 }
 
-int launch_forward(const EvalCall& c, int C, unsigned mask, int mode, int ch0, const EvalWs& ws, FwdOut out,
-                   cudaStream_t st)
+int launch_forward(const EvalCall& c, int C, unsigned mask, int wl, int ch0, const EvalWs& ws, FwdOut out, cudaStream_t st)
 {
 #define FW(D_, C_, M_) \
-    if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, mode, ch0, ws, out, st);
+    if (c.D == D_ && C == C_ && mask == M_) return launch_fwd_t<D_, C_, M_>(c, wl, ch0, ws, out, st);
 #define FW_ALL(D_, C_) FW(D_, C_, 1u) FW(D_, C_, 2u) FW(D_, C_, 4u) FW(D_, C_, 7u) FW(D_, C_, 8u)
     FW_ALL(2, 1) FW_ALL(2, 2) FW_ALL(1, 1) FW_ALL(1, 2)
     FW(2, 1, 16u) FW(2, 1, 19u)  // trace-only Laplacian kernels (PIGS_FN_LAPL as a kernel mask bit)

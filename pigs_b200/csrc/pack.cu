@@ -1,12 +1,16 @@
-// pack.cu — per-call staging for the evaluation kernels:
-//   * classify every (tile, Gaussian) list entry as FAST or GENERAL,
-//   * stable-partition each tile's list into [fast | general] and write the Gaussian parameters as
-//     packed float4 records in that order (what the evaluation kernels stream through shared memory),
-//   * gather the sorted samples' coordinates and upstream gradients into float4 records (backward),
-//   * build the device-side work lists.
+// pack.cu — staging for the evaluation kernels.
+// Once per preprocess (stage_classes; depends on the binning only, reused by every forward / backward of the cycle):
+//   * classify every (tile, Gaussian) list entry as FAST, SHIFT or GENERAL and scan the class flags (one 64-bit scan),
+//   * build the device-side work lists (forward with 8 / 4 samples per thread, backward).
+// Per call:
+//   * stable-partition each tile's list into [fast | shift | general] and write the Gaussian parameters as packed
+//     float4 records in that order (what the evaluation kernels stream through shared memory),
+//   * gather the sorted samples' coordinates and upstream gradients into float4 records (backward).
 // All HBM-bound, a few bytes per list entry; no host synchronisation.
 #include "eval_common.cuh"
 #include "layouts.cuh"
+
+#include <stdlib.h>
 
 namespace pigs {
 
@@ -21,7 +25,7 @@ template <int D>
 __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __restrict__ list,
                                                    const uint32_t* __restrict__ tiles, const float* __restrict__ means,
                                                    const float* __restrict__ conics, const float* __restrict__ bbox,
-                                                   uint32_t* __restrict__ flags_general, uint32_t* __restrict__ flags_shift,
+                                                   int all_general, unsigned long long* __restrict__ cls,
                                                    uint32_t* __restrict__ scode)
 {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -35,7 +39,7 @@ __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __
         const float cc = c0 * c2;
         pd = (c0 > 0.0f) && (c2 > 0.0f) && (cc - c1 * c1 >= 1e-4f * cc) && (cc < 3.0e38f);
     }
-    bool ok = pd;
+    bool ok = pd && !all_general;
     uint32_t code = 0;
 #pragma unroll
     for (int d = 0; d < D; d++) {
@@ -53,44 +57,48 @@ __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __
         code |= (k & 3u) << (2 * d);
     }
     const bool general = !ok;
-    flags_general[e] = general ? 1u : 0u;
-    flags_shift[e] = (!general && code != 0u) ? 1u : 0u;
+    cls[e] = general ? CLS_GENERAL : (code != 0u ? CLS_SHIFT : 0ull);
     scode[e] = general ? 0u : code;
 }
 
-// gen_prefix / shift_prefix = exclusive scans of the two flag arrays (with totals at [R]).  Writes the
-// records in partitioned order [fast | shift | general] within each tile (stable within each class).
+// cls = exclusive scan of the packed class flags (with the total at [R]).  Writes the records in partitioned order
+// [fast | shift | general] within each tile (stable within each class); block 0 also turns the work-list template into
+// this call's WorkHeader (dynamic counter at zero).
 template <int D, int C, bool FWD>
 __global__ void __launch_bounds__(256) pack_gauss_kernel(int64_t R, const uint32_t* __restrict__ list,
                                                          const uint32_t* __restrict__ tiles,
-                                                         const uint32_t* __restrict__ gen_prefix,
-                                                         const uint32_t* __restrict__ shift_prefix,
+                                                         const unsigned long long* __restrict__ cls,
                                                          const uint32_t* __restrict__ scode,
                                                          const uint2* __restrict__ ranges, int blocks,
                                                          const float* __restrict__ means, const float* __restrict__ values,
                                                          const float* __restrict__ conics, int Ctot, int ch0,
                                                          float4* __restrict__ recs, uint32_t* __restrict__ rec_id,
-                                                         uint32_t* __restrict__ nfast)
+                                                         const WorkTemplate* __restrict__ wt, WorkHeader* __restrict__ wh)
 {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+        for (int k = 0; k < 4; k++) {
+            wh->counter[k] = 0;
+            wh->items[k] = wt->items[k];
+        }
+        wh->pairs = wt->pairs;
+        wh->neg_zero = 0x80000000u;
+    }
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= R) return;
     const uint32_t id = list[e], t = tiles[e];
     if ((int)t >= blocks) return;  // alias slots are never evaluated (the reference launches `blocks` CTAs)
     const uint2 r = ranges[t];
-    const uint32_t gen_before = gen_prefix[e] - gen_prefix[r.x];
-    const uint32_t gen_total = gen_prefix[r.y] - gen_prefix[r.x];
-    const uint32_t sh_before = shift_prefix[e] - shift_prefix[r.x];
-    const uint32_t sh_total = shift_prefix[r.y] - shift_prefix[r.x];
+    const unsigned long long ce = cls[e], c0 = cls[r.x], c1 = cls[r.y], cn = cls[e + 1];
+    const uint32_t gen_before = (uint32_t)((ce & CLS_MASK) - (c0 & CLS_MASK));
+    const uint32_t gen_total = (uint32_t)((c1 & CLS_MASK) - (c0 & CLS_MASK));
+    const uint32_t sh_before = (uint32_t)((ce >> 31) - (c0 >> 31));
+    const uint32_t sh_total = (uint32_t)((c1 >> 31) - (c0 >> 31));
     const uint32_t nf = (r.y - r.x) - gen_total - sh_total;
-    const bool general = gen_prefix[e + 1] != gen_prefix[e];
-    const bool shift = shift_prefix[e + 1] != shift_prefix[e];
+    const bool general = (cn & CLS_MASK) != (ce & CLS_MASK);
+    const bool shift = (cn >> 31) != (ce >> 31);
     const uint32_t before = (uint32_t)(e - r.x);
     const uint32_t pos = general ? r.x + nf + sh_total + gen_before
                                  : (shift ? r.x + nf + sh_before : r.x + before - gen_before - sh_before);
-    if (e == r.x) {
-        nfast[t] = nf;
-        nfast[blocks + 1 + t] = sh_total;
-    }
     constexpr int NV = FWD ? frec_v4(D, C) : grec_v4(D, C);
     constexpr int NC = nconic(D);
     float f[NV * 4];
@@ -187,16 +195,25 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
     for (int k = 0; k < SV; k++) srecs[(size_t)i * SV + k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
 }
 
-// One CTA.  For every tile: the FAST / SHIFT / GENERAL segments and how many work items each yields.
+// One CTA per work list (blockIdx.x = WL_FWD8 | WL_FWD4 | WL_BWD).  For every tile: the FAST / SHIFT / GENERAL segments
+// and how many work items each yields.
 //   forward : stationary = samples in chunks of `chunk`, streamed = Gaussians split `split_hint` ways
 //   backward: stationary = Gaussians in chunks of `chunk`, streamed = samples split `split_hint` ways
+struct WorkListCfg {
+    uint32_t chunk[WL_COUNT], split_hint[WL_COUNT], min_stream[WL_COUNT];
+    int stream_is_gauss[WL_COUNT];
+};
+
 __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* __restrict__ ranges,
                                                        const uint2* __restrict__ sample_ranges,
-                                                       const uint32_t* __restrict__ nfast, uint32_t chunk,
-                                                       uint32_t split_hint, uint32_t min_stream, int stream_is_gauss,
-                                                       TileSeg* __restrict__ segs /* [EV_NSEG][blocks] */,
-                                                       WorkHeader* __restrict__ wh)
+                                                       const unsigned long long* __restrict__ cls, WorkListCfg cfg,
+                                                       TileSeg* __restrict__ segs_all /* [WL_COUNT][EV_NSEG][blocks] */,
+                                                       WorkTemplate* __restrict__ wt_all)
 {
+    const int wl = blockIdx.x;
+    const uint32_t chunk = cfg.chunk[wl], split_hint = cfg.split_hint[wl], min_stream = cfg.min_stream[wl];
+    const int stream_is_gauss = cfg.stream_is_gauss[wl];
+    TileSeg* segs = segs_all + (size_t)wl * EV_NSEG * blocks;
     __shared__ uint32_t s_scan[256];
     __shared__ uint32_t s_carry[EV_NSEG];
     __shared__ unsigned long long s_pairs;
@@ -215,11 +232,16 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
         if (t < blocks) {
             const uint2 gr = ranges[t], sr = sample_ranges[t];
             const uint32_t G = gr.y - gr.x, S = sr.y - sr.x;
-            const uint32_t nf = (G > 0) ? nfast[t] : 0;
-            const uint32_t ns = (G > 0) ? nfast[blocks + 1 + t] : 0;
+            uint32_t ng = 0, ns = 0;
+            if (G > 0) {
+                const unsigned long long c0 = cls[gr.x], c1 = cls[gr.y];
+                ng = (uint32_t)((c1 & CLS_MASK) - (c0 & CLS_MASK));
+                ns = (uint32_t)((c1 >> 31) - (c0 >> 31));
+            }
+            const uint32_t nf = G - ng - ns;
             my_pairs += (unsigned long long)G * S;
             const uint32_t begin[EV_NSEG] = {gr.x, gr.x + nf, gr.x + nf + ns};
-            const uint32_t count[EV_NSEG] = {nf, ns, G - nf - ns};
+            const uint32_t count[EV_NSEG] = {nf, ns, ng};
 #pragma unroll
             for (int k = 0; k < EV_NSEG; k++) {
                 sg[k].g_begin = begin[k];
@@ -262,35 +284,132 @@ __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* 
     atomicAdd(&s_pairs, my_pairs);
     __syncthreads();
     if (threadIdx.x == 0) {
-        for (int k = 0; k < EV_NSEG; k++) {
-            wh->counter[k] = 0;
-            wh->items[k] = s_carry[k];
-        }
-        wh->pairs = s_pairs;
-        wh->neg_zero = 0x80000000u;
+        WorkTemplate w;
+        for (int k = 0; k < EV_NSEG; k++) w.items[k] = s_carry[k];
+        w.items[3] = 0;
+        w.pairs = s_pairs;
+        w.pad[0] = w.pad[1] = 0;
+        wt_all[wl] = w;
     }
 }
 
+// Work items per SM the lists aim for.  The tail of a persistent launch is about one item long, and the backward's
+// items (1024 Gaussians x a slice of the tile's samples) are the heavier ones: measured on B200 at C3 the backward goes
+// 696.5 -> 649 ms from 48 to 768 items per SM, the forward is flat to slightly worse (profiles/r01n_split_target.log).
+static int split_target_per_sm(bool backward)
+{
+    static int v[2] = {0, 0};
+    if (v[backward] == 0) {
+        const char* e = getenv(backward ? "PIGS_SPLIT_TARGET_BWD" : "PIGS_SPLIT_TARGET_FWD");  // tuning hook
+        v[backward] = e ? atoi(e) : (backward ? 768 : 48);
+        if (v[backward] < 1) v[backward] = 48;
+    }
+    return v[backward];
+}
+
+static uint32_t split_hint(int64_t stationary, uint32_t chunk, int blocks, bool backward)
+{
+    const int64_t target = (int64_t)num_sms() * split_target_per_sm(backward);
+    const int64_t base = stationary / chunk + blocks;
+    int64_t s = (target + base - 1) / base;
+    if (s < 1) s = 1;
+    if (s > 4096) s = 4096;
+    return (uint32_t)s;
+}
+
+int g_deterministic = 0;
+int g_class_concurrency = 1;
+
+namespace {
+struct ForkState {
+    bool ready = false;
+    cudaStream_t side[2];
+    cudaEvent_t forked, joined[2];
+};
+ForkState g_fork[64];  // per device
+}  // namespace
+
+int ClassFork::fork(cudaStream_t st)
+{
+    main = st;
+    forked = false;
+    if (!g_class_concurrency || g_deterministic || g_debug_sync) return 0;
+    int dev = 0;
+    PIGS_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return 0;
+    ForkState& f = g_fork[dev];
+    if (!f.ready) {
+        for (int k = 0; k < 2; k++) {
+            PIGS_CHECK(cudaStreamCreateWithFlags(&f.side[k], cudaStreamNonBlocking));
+            PIGS_CHECK(cudaEventCreateWithFlags(&f.joined[k], cudaEventDisableTiming));
+        }
+        PIGS_CHECK(cudaEventCreateWithFlags(&f.forked, cudaEventDisableTiming));
+        f.ready = true;
+    }
+    PIGS_CHECK(cudaEventRecord(f.forked, st));
+    for (int k = 0; k < 2; k++) PIGS_CHECK(cudaStreamWaitEvent(f.side[k], f.forked, 0));
+    forked = true;
+    return 0;
+}
+
+cudaStream_t ClassFork::stream(int k) const
+{
+    if (!forked || k == 0) return main;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return g_fork[dev].side[k - 1];
+}
+
+int ClassFork::join()
+{
+    if (!forked) return 0;
+    int dev = 0;
+    PIGS_CHECK(cudaGetDevice(&dev));
+    ForkState& f = g_fork[dev];
+    for (int k = 0; k < 2; k++) {
+        PIGS_CHECK(cudaEventRecord(f.joined[k], f.side[k]));
+        PIGS_CHECK(cudaStreamWaitEvent(main, f.joined[k], 0));
+    }
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
-// host-side staging entry points (called from api.cu)
+// host-side staging entry points
 // ---------------------------------------------------------------------------------------------
-int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, const EvalWs& ws, cudaStream_t st)
+int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, const float* conics, const float* bbox,
+                  const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st)
+{
+    const unsigned nb = (unsigned)((R + 255) / 256);
+    // deterministic mode: every instance GENERAL (exact wrap + skip per pair), so a tile's list stays in ascending
+    // Gaussian id and — with the forward's Gaussians unsplit — every output element is written by exactly one item
+    if (D == 2)
+        flag_kernel<2><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic, b.cls, b.scode);
+    else
+        flag_kernel<1><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic, b.cls, b.scode);
+    PIGS_LAUNCH_CHECK();
+    int rc = exclusive_scan_u64(b.cls, b.cls, R, true, b.scan_ws, st);
+    if (rc) return rc;
+    WorkListCfg cfg;
+    const uint32_t chunks[WL_COUNT] = {EV_THREADS * 8u, EV_THREADS * 4u, EV_THREADS * (uint32_t)bwd_kg(2, 1, 7u)};
+    for (int wl = 0; wl < WL_COUNT; wl++) {
+        const bool bwd = wl == WL_BWD;
+        cfg.chunk[wl] = chunks[wl];
+        cfg.split_hint[wl] = (g_deterministic && !bwd) ? 1u : split_hint(bwd ? R : N, chunks[wl], blocks, bwd);
+        cfg.min_stream[wl] = bwd ? 128u : 256u;
+        cfg.stream_is_gauss[wl] = bwd ? 0 : 1;
+    }
+    worklist_kernel<<<WL_COUNT, 256, 0, st>>>(blocks, ranges, sample_ranges, b.cls, cfg, b.segs, b.wt);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, int wl, const EvalWs& ws, cudaStream_t st)
 {
     const int64_t R = c.R;
     const unsigned nb = (unsigned)((R + 255) / 256);
-    if (c.D == 2)
-        flag_kernel<2><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags, ws.flags1, ws.scode);
-    else
-        flag_kernel<1><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.means, c.conics, c.bbox, ws.flags, ws.flags1, ws.scode);
-    PIGS_LAUNCH_CHECK();
-    int rc = exclusive_scan_u32(ws.flags, ws.flags, R, true, ws.scan_ws, st);
-    if (rc) return rc;
-    rc = exclusive_scan_u32(ws.flags1, ws.flags1, R, true, ws.scan_ws, st);
-    if (rc) return rc;
-    PIGS_CHECK(cudaMemsetAsync(ws.nfast, 0, (size_t)2 * (c.blocks + 1) * sizeof(uint32_t), st));
-#define PACK1(D_, C_, F_)                                                                                               \
-    pack_gauss_kernel<D_, C_, F_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, ws.flags, ws.flags1, ws.scode, c.ranges, c.blocks, \
-                                                      c.means, c.values, c.conics, c.C, ch0, ws.recs, ws.rec_id, ws.nfast)
+#define PACK1(D_, C_, F_)                                                                                            \
+    pack_gauss_kernel<D_, C_, F_><<<nb, 256, 0, st>>>(R, c.list, c.tiles, c.cls, c.scode, c.ranges, c.blocks, c.means, \
+                                                      c.values, c.conics, c.C, ch0, ws.recs, ws.rec_id, c.wt + wl, ws.wh)
 #define PACK(D_, C_)       \
     do {                   \
         if (fwd_layout)    \
@@ -308,15 +427,6 @@ int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, const Ev
         PACK(1, 2);
 #undef PACK
 #undef PACK1
-    PIGS_LAUNCH_CHECK();
-    return 0;
-}
-
-int stage_worklist(const EvalCall& c, const EvalWs& ws, uint32_t chunk, uint32_t split_hint, uint32_t min_stream,
-                   bool stream_is_gauss, cudaStream_t st)
-{
-    worklist_kernel<<<1, 256, 0, st>>>(c.blocks, c.ranges, c.sample_ranges, ws.nfast, chunk, split_hint, min_stream,
-                                       stream_is_gauss ? 1 : 0, ws.segs, ws.wh);
     PIGS_LAUNCH_CHECK();
     return 0;
 }

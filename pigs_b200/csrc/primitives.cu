@@ -1,4 +1,4 @@
-// primitives.cu — hand-written exclusive scan and stable LSD radix sort (u32 key/value pairs).
+// primitives.cu — hand-written single-pass scan (decoupled look-back) and stable LSD radix sort (u32 key/value pairs).
 // Replaces cub::DeviceScan::InclusiveSum and cub::DeviceRadixSort::SortPairs used by the reference
 // (cuda_sampler/sampler_impl.cu:253,279,316).  HBM-bound; sized for 148 SMs.
 #include "common.cuh"
@@ -69,64 +69,113 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* total)
     return r;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums(const uint32_t* __restrict__ in, uint32_t* __restrict__ bsum,
-                                                                int64_t n)
+// ---- single-pass scan with decoupled look-back -------------------------------------------------------------------
+// One launch for any n (replaces cub::DeviceScan::InclusiveSum, sampler_impl.cu:253, and this file's former
+// three-kernel reduce / scan-of-sums / apply chain): every CTA takes the next tile from an atomic ticket (so a tile only
+// ever waits for tiles whose CTAs are already running), scans it, publishes its aggregate, and warp 0 walks the
+// predecessors' descriptors backwards until it meets an inclusive prefix.  A descriptor is ONE 64-bit word
+// (status << 62 | value), written and read atomically, so no fence is needed between status and value.
+// ws = [ticket u64][desc u64 x tiles], zeroed by one cudaMemsetAsync before the launch.
+constexpr unsigned long long SCAN_AGG = 1ull << 62, SCAN_INC = 2ull << 62, SCAN_VAL = (1ull << 62) - 1ull;
+
+__device__ __forceinline__ unsigned long long ld_desc(const unsigned long long* p)
 {
-    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE;
-    uint32_t s = 0;
-#pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
-        int64_t idx = base + i * SCAN_THREADS + threadIdx.x;
-        if (idx < n) s += in[idx];
-    }
-    uint32_t tot;
-    block_excl_scan(s, &tot);
-    if (threadIdx.x == 0) bsum[blockIdx.x] = tot;
+    unsigned long long v;
+    asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long long v)
+{
+    asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// single block: exclusive scan of bsum[nb] in place; bsum[nb] = grand total
-__global__ void __launch_bounds__(SCAN_THREADS) scan_of_sums(uint32_t* bsum, int64_t nb)
+// T = uint32_t (tile-touch counts, flags, histograms) or int64_t (neighbour counts).  INCLUSIVE: out[i] = sum in[0..i];
+// else out[i] = sum in[0..i) and, with write_total, out[n] = grand total.  total_out (optional): the grand total as
+// int64 (device), e.g. the word of a header the host reads back.  out may alias in.
+template <typename T, bool INCLUSIVE>
+__global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const T* in, T* out, int64_t n,
+                                                                     int write_total, unsigned long long* __restrict__ ws,
+                                                                     long long* __restrict__ total_out)
 {
-    uint32_t carry = 0;
-    for (int64_t base = 0; base < nb; base += SCAN_THREADS) {
-        int64_t idx = base + threadIdx.x;
-        uint32_t v = idx < nb ? bsum[idx] : 0;
-        uint32_t tot;
-        uint32_t ex = block_excl_scan(v, &tot);
-        if (idx < nb) bsum[idx] = ex + carry;
-        carry += tot;
-    }
-    if (threadIdx.x == 0) bsum[nb] = carry;
-}
-
-__global__ void __launch_bounds__(SCAN_THREADS) scan_apply(const uint32_t* __restrict__ in, uint32_t* __restrict__ out,
-                                                           const uint32_t* __restrict__ bsum, int64_t n, int64_t nb,
-                                                           int write_total)
-{
-    // each thread owns SCAN_ITEMS consecutive elements so the order is preserved
-    const int64_t base = (int64_t)blockIdx.x * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
-    uint32_t v[SCAN_ITEMS];
-    uint32_t s = 0;
+    __shared__ unsigned long long s_wsum[SCAN_THREADS / 32];
+    __shared__ unsigned long long s_prefix;
+    __shared__ unsigned int s_tile;
+    unsigned long long* desc = ws + 1;
+    if (threadIdx.x == 0) s_tile = (unsigned int)atomicAdd(ws, 1ull);
+    __syncthreads();
+    const int64_t tile = s_tile;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int64_t base = tile * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
+    T v[SCAN_ITEMS];
+    unsigned long long s = 0;
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
-        v[i] = (base + i < n) ? in[base + i] : 0;
-        s += v[i];
+        v[i] = (base + i < n) ? in[base + i] : T(0);
+        s += (unsigned long long)v[i];
     }
-    uint32_t tot;
-    uint32_t ex = block_excl_scan(s, &tot) + bsum[blockIdx.x];
+    // block scan of the per-thread sums (64-bit)
+    unsigned long long inc = s;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned long long t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) s_wsum[w] = inc;
+    __syncthreads();
+    unsigned long long woff = 0, agg = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_THREADS / 32; k++) {
+        const unsigned long long t = s_wsum[k];
+        if (k < w) woff += t;
+        agg += t;
+    }
+    if (w == 0) {
+        unsigned long long excl = 0;
+        if (tile == 0) {
+            if (lane == 0) st_desc(desc, SCAN_INC | agg);
+        } else {
+            if (lane == 0) st_desc(desc + tile, SCAN_AGG | agg);
+            int64_t jb = tile - 1;
+            for (;;) {
+                const int64_t j = jb - lane;
+                unsigned long long d = j >= 0 ? ld_desc(desc + j) : SCAN_INC;  // before tile 0: inclusive prefix 0
+                while (__any_sync(0xffffffffu, (d >> 62) == 0ull)) {
+                    if ((d >> 62) == 0ull) d = ld_desc(desc + j);
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, (d >> 62) == 2ull);
+                const int first = m ? (__ffs(m) - 1) : 31;  // nearest predecessor holding an inclusive prefix
+                unsigned long long c = lane <= first ? (d & SCAN_VAL) : 0ull;
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+                excl += c;
+                if (m) break;
+                jb -= 32;
+            }
+            if (lane == 0) st_desc(desc + tile, SCAN_INC | (excl + agg));
+        }
+        if (lane == 0) s_prefix = excl;
+    }
+    __syncthreads();
+    unsigned long long run = s_prefix + woff + (inc - s);
 #pragma unroll
     for (int i = 0; i < SCAN_ITEMS; i++) {
-        if (base + i < n) out[base + i] = ex;
-        ex += v[i];
+        if (INCLUSIVE) run += (unsigned long long)v[i];
+        if (base + i < n) out[base + i] = (T)run;
+        if (!INCLUSIVE) run += (unsigned long long)v[i];
     }
-    if (write_total && blockIdx.x == 0 && threadIdx.x == 0) out[n] = bsum[nb];
+    const int64_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    if (tile == ntiles - 1 && threadIdx.x == 0) {
+        const unsigned long long tot = s_prefix + agg;
+        if (write_total) out[n] = (T)tot;
+        if (total_out) *total_out = (long long)tot;
+    }
 }
 
 // small inputs (the reference's own drivers run 1K-40K Gaussians): ONE CTA walks the tiles with a running carry —
 // one launch instead of three; out may alias in (a tile is read into registers before it is written)
 constexpr int64_t SCAN_SMALL_MAX = 16 * SCAN_TILE;
 __global__ void __launch_bounds__(SCAN_THREADS) scan_small(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int64_t n,
-                                                           int write_total)
+                                                           int write_total, long long* __restrict__ total_out)
 {
     uint32_t carry = 0;
     for (int64_t tile = 0; tile < n; tile += SCAN_TILE) {
@@ -148,34 +197,60 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_small(const uint32_t* __res
         carry += tot;
     }
     if (write_total && threadIdx.x == 0) out[n] = carry;
+    if (total_out && threadIdx.x == 0) *total_out = (long long)carry;
 }
 
 size_t scan_ws_bytes(int64_t n)
 {
     int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
-    return align_up((size_t)(nb + 2) * sizeof(uint32_t));
+    return align_up((size_t)(nb + 2) * sizeof(unsigned long long));
 }
 
-int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_total, void* ws, cudaStream_t st)
+int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_total, void* ws, cudaStream_t st,
+                       long long* total_out)
 {
-    uint32_t* bsum = (uint32_t*)ws;
     if (n <= 0) {
         if (write_total) PIGS_CHECK(cudaMemsetAsync(out, 0, sizeof(uint32_t), st));
+        if (total_out) PIGS_CHECK(cudaMemsetAsync(total_out, 0, sizeof(long long), st));
         return 0;
     }
     if (n <= SCAN_SMALL_MAX) {
-        scan_small<<<1, SCAN_THREADS, 0, st>>>(in, out, n, write_total ? 1 : 0);
+        scan_small<<<1, SCAN_THREADS, 0, st>>>(in, out, n, write_total ? 1 : 0, total_out);
         PIGS_LAUNCH_CHECK();
         return 0;
     }
     const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
-    // NB: scan_block_sums reads the tile strided, scan_apply reads it blocked — both sum the same
-    // SCAN_TILE elements, so the per-block totals agree.
-    scan_block_sums<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, bsum, n);
+    PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
+    scan_lookback_kernel<uint32_t, false><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, write_total ? 1 : 0,
+                                                                                 (unsigned long long*)ws, total_out);
     PIGS_LAUNCH_CHECK();
-    scan_of_sums<<<1, SCAN_THREADS, 0, st>>>(bsum, nb);
+    return 0;
+}
+
+int exclusive_scan_u64(const unsigned long long* in, unsigned long long* out, int64_t n, bool write_total, void* ws,
+                       cudaStream_t st)
+{
+    if (n <= 0) {
+        if (write_total) PIGS_CHECK(cudaMemsetAsync(out, 0, sizeof(unsigned long long), st));
+        return 0;
+    }
+    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
+    scan_lookback_kernel<unsigned long long, false><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(
+        in, out, n, write_total ? 1 : 0, (unsigned long long*)ws, nullptr);
     PIGS_LAUNCH_CHECK();
-    scan_apply<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, bsum, n, nb, write_total ? 1 : 0);
+    return 0;
+}
+
+int inclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n, void* ws, cudaStream_t st, long long* total_out)
+{
+    if (n <= 0) {
+        if (total_out) PIGS_CHECK(cudaMemsetAsync(total_out, 0, sizeof(long long), st));
+        return 0;
+    }
+    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
+    scan_lookback_kernel<int64_t, true><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, 0, (unsigned long long*)ws, total_out);
     PIGS_LAUNCH_CHECK();
     return 0;
 }
@@ -192,6 +267,7 @@ constexpr int SORT_WARPS = SORT_THREADS / 32;
 constexpr int SORT_ROUNDS = 16;                                // 32-element groups per warp
 constexpr int SORT_WARP_ITEMS = 32 * SORT_ROUNDS;              // 512
 constexpr int SORT_TILE = SORT_WARP_ITEMS * SORT_WARPS;        // 4096
+static_assert(SORT_TILE == SORT_TILE_ELEMS, "key-producing kernels histogram whole sort tiles");
 constexpr int RADIX = 256;
 
 __global__ void __launch_bounds__(SORT_THREADS) radix_hist(const uint32_t* __restrict__ keys, int64_t n, int shift,
@@ -214,10 +290,20 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
                                                               const uint32_t* __restrict__ vals, int64_t n, int shift,
                                                               uint32_t mask, const uint32_t* __restrict__ gbase,
                                                               int64_t nb, uint32_t* __restrict__ keys_out,
-                                                              uint32_t* __restrict__ vals_out)
+                                                              uint32_t* __restrict__ vals_out, uint2* __restrict__ ranges,
+                                                              int max_slot)
 {
     __shared__ uint32_t wcount[SORT_WARPS][RADIX];  // per-warp digit counts, then per-warp running offsets
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    if (ranges && blockIdx.x == 0) {
+        // single-pass sort whose digit IS the tile key: the scanned histogram holds every tile's range
+        // (identifyTileRanges, sampler_impl.cu:134-151: [first, last + 1) of present tiles, (0, 0) otherwise)
+        for (int t = threadIdx.x; t <= max_slot; t += SORT_THREADS) {
+            const uint32_t b0 = gbase[(int64_t)t * nb];
+            const uint32_t b1 = t + 1 < RADIX ? gbase[(int64_t)(t + 1) * nb] : (uint32_t)n;
+            ranges[t] = b1 > b0 ? make_uint2(b0, b1) : make_uint2(0u, 0u);
+        }
+    }
     for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&wcount[0][0])[i] = 0;
     __syncthreads();
 
@@ -274,18 +360,22 @@ size_t sort_ws_bytes(int64_t n)
     return hist + scan_ws_bytes(RADIX * nb) + 2 * align_up((size_t)(n > 0 ? n : 1) * sizeof(uint32_t));
 }
 
+uint32_t* sort_ghist(void* ws) { return (uint32_t*)ws; }
+int64_t sort_tiles(int64_t n) { return (n + SORT_TILE - 1) / SORT_TILE; }
+
 int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_out, uint32_t* vals_out, int64_t n,
-                          int bits, void* ws, cudaStream_t st)
+                          int bits, void* ws, cudaStream_t st, const SortExtras* ex)
 {
     if (n <= 0) return 0;
     const int64_t nb = (n + SORT_TILE - 1) / SORT_TILE;
     Carver c(ws);
-    uint32_t* ghist = c.take<uint32_t>(RADIX * nb + 1);
+    uint32_t* ghist = c.take<uint32_t>(RADIX * nb + 1);  // sort_ghist(ws)
     char* scan_ws = c.take<char>(scan_ws_bytes(RADIX * nb));
     uint32_t* tmp_k = c.take<uint32_t>(n);
     uint32_t* tmp_v = c.take<uint32_t>(n);
     int passes = (bits + 7) / 8;
     if (passes < 1) passes = 1;
+    if (ex && ex->ranges_written) *ex->ranges_written = false;
     // choose ping-pong so the final pass writes keys_out/vals_out
     uint32_t *src_k = keys_in, *src_v = vals_in;
     for (int p = 0; p < passes; p++) {
@@ -296,11 +386,20 @@ int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_o
         const int shift = p * 8;
         const int pb = bits - shift >= 8 ? 8 : (bits - shift > 0 ? bits - shift : 8);
         const uint32_t mask = (1u << pb) - 1u;
-        radix_hist<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, n, shift, mask, ghist, nb);
-        PIGS_LAUNCH_CHECK();
+        if (!(p == 0 && ex && ex->hist_done)) {  // the key-producing kernel may have left the first histogram behind
+            radix_hist<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, n, shift, mask, ghist, nb);
+            PIGS_LAUNCH_CHECK();
+        }
         int rc = exclusive_scan_u32(ghist, ghist, RADIX * nb, false, scan_ws, st);
         if (rc) return rc;
-        radix_scatter<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, src_v, n, shift, mask, ghist, nb, dst_k, dst_v);
+        uint2* rg = nullptr;
+        int max_slot = 0;
+        if (passes == 1 && ex && ex->ranges && ex->max_slot < RADIX) {
+            rg = ex->ranges;
+            max_slot = ex->max_slot;
+            if (ex->ranges_written) *ex->ranges_written = true;
+        }
+        radix_scatter<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, src_v, n, shift, mask, ghist, nb, dst_k, dst_v, rg, max_slot);
         PIGS_LAUNCH_CHECK();
         src_k = dst_k;
         src_v = dst_v;

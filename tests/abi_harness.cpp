@@ -102,7 +102,7 @@ int main(int argc, char** argv)
     uint32_t* ranges = dev<uint32_t>(2 * (blocks + 1));
     uint32_t* sranges = dev<uint32_t>(2 * (blocks + 1));
     void* sort_ws = dev<uint8_t>(pigs_sort_workspace_bytes(R, N));
-    CK(pigs_preprocess_bin(P, D, N, blocks, R, means, samples, radii, geom, binning, sbinning, ranges, sranges, sort_ws, st));
+    CK(pigs_preprocess_bin(P, D, N, blocks, R, means, conics, samples, radii, geom, binning, sbinning, ranges, sranges, sort_ws, st));
 
     // ---- fused forward + backward (sample_points.cu:100-372 as one call each way); outputs zero-initialised
     const unsigned mask = PIGS_FN_VALUE | PIGS_FN_DERIV | PIGS_FN_HESS;
