@@ -480,9 +480,17 @@ def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
             t.grad = None
         torch.autograd.backward(outs, gs)
 
+    mids, ends = [], []
+
     def step():
         sampling()
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        mids.append(e)
         aggregation()
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        ends.append(e)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -491,6 +499,7 @@ def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
             dist.barrier()
         torch.cuda.synchronize()
         n0 = L.pigs_launch_count()
+        del mids[:], ends[:]
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for _ in range(steps):
@@ -502,11 +511,14 @@ def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
         ms = torch.tensor([a.elapsed_time(b) / steps], device="cuda")
         if world > 1:
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item()), (L.pigs_launch_count() - n0) / steps
+        return float(ms.item()), (L.pigs_launch_count() - n0) / steps, a
 
-    ms_step, launches = timed(step, steps, warmup)
-    ms_samp, _ = timed(sampling, steps, 1)
-    ms_agg, _ = timed(aggregation, steps, 1)
+    ms_step, launches, ev0 = timed(step, steps, warmup)
+    # split of the SAME timed steps at the events between / behind the two halves (this rank's stream; the step time is
+    # the max over ranks)
+    starts = [ev0] + ends[:-1]
+    ms_samp = float(np.mean([a_.elapsed_time(m_) for a_, m_ in zip(starts, mids)]))
+    ms_agg = float(np.mean([m_.elapsed_time(e_) for m_, e_ in zip(mids, ends)]))
     # aggregation kernels alone (one head), for their HBM roofline on this rank's window
     plan = s.row_plan
     T, Q, Kk, DT = [t.detach() for t in per_head[0]]
@@ -518,10 +530,10 @@ def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
         plan.gather([f_full, k_full])
     w_, e_, f_, _ = _C.aggregate_neighbors_rows(f_full, T, Q, k_full, freq.detach(), DT, *csr, (lo, hi), False)
     gf, gk = torch.zeros_like(f_full), torch.zeros_like(k_full)
-    ms_kf, _ = timed(lambda: _C.aggregate_neighbors_rows(f_full, T, Q, k_full, freq.detach(), DT, *csr, (lo, hi), False), steps, 2)
-    ms_kb, _ = timed(lambda: _C.aggregate_neighbors_rows_backward(f_full, T, Q, k_full, freq.detach(), DT, indices, ranges,
-                                                                  dists, dens, w_, e_, f_, inv_total, gs[0], gf, gk, (lo, hi),
-                                                                  False), steps, 2)
+    ms_kf, _, _ = timed(lambda: _C.aggregate_neighbors_rows(f_full, T, Q, k_full, freq.detach(), DT, *csr, (lo, hi), False), steps, 2)
+    ms_kb, _, _ = timed(lambda: _C.aggregate_neighbors_rows_backward(f_full, T, Q, k_full, freq.detach(), DT, indices, ranges,
+                                                                     dists, dens, w_, e_, f_, inv_total, gs[0], gf, gk, (lo, hi),
+                                                                     False), steps, 2)
     pairs_t = torch.zeros(world, device="cuda", dtype=torch.int64)
     pairs_t[rank] = s.pair_count()
     rows_t = torch.zeros(world, device="cuda", dtype=torch.int64)

@@ -35,12 +35,24 @@ constexpr int A16_THREADS = 256;
 
 // sin(pi t), cos(pi t) for t = f * X formed exactly as p + e, reduced modulo 2 exactly (reference: double sin/cos of
 // frequencies[e] * M_PI * X[d], aggregate_neighbors.cu:181-182)
+#ifndef A16_MUFU_SINCOS
+#define A16_MUFU_SINCOS 1
+#endif
 __device__ __forceinline__ void sincospi_fx(float f, float X, float& s, float& c)
 {
     const float p = __fmul_rn(f, X);
     const float e = __fmaf_rn(f, X, -p);
     const float r = __fmaf_rn(-2.0f, rintf(0.5f * p), p);  // exact: p - 2 rint(p / 2) in [-1, 1]
     const float t = __fadd_rn(r, e);
+#if A16_MUFU_SINCOS
+    // the argument is reduced EXACTLY to [-pi, pi] above, where MUFU.SIN / MUFU.COS are good to 2^-21 absolute
+    // (3.6e-7; the 24 terms of an embedding average it down to ~5e-7 of its magnitude, tolerance 1e-5): 9 instructions
+    // per sin / cos pair instead of 22 for the polynomial form — 12 pairs per neighbour slot were a third of the kernels'
+    // instructions (ncu: both kernels are issue-bound, not HBM-bound)
+    const float ang = t * 3.14159265358979323846f;
+    s = __sinf(ang);
+    c = __cosf(ang);
+#else
     const float q = rintf(t + t);                          // nearest half-integer quadrant, -2 .. 2
     const float u = __fmaf_rn(q, -0.5f, t);                // exact, |u| <= 1/4
     const float u2 = u * u;
@@ -57,6 +69,7 @@ __device__ __forceinline__ void sincospi_fx(float f, float X, float& s, float& c
     // quadrant 1: (c, -s); 2: (-s, -c); 3: (-c, s)
     s = __uint_as_float(__float_as_uint(s0) ^ (((unsigned)qi & 2u) << 30));
     c = __uint_as_float(__float_as_uint(c0) ^ (((unsigned)(qi + 1) & 2u) << 30));
+#endif
 }
 
 __device__ __forceinline__ void load16(const float* __restrict__ row, float* __restrict__ v)
@@ -140,12 +153,17 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
                 dwe = dw * emb;
             }
             const int jl = (int)j;
+            // z[lane] += sum_t (dwe_t + dwf_t feat_t[lane]): the first sum does not depend on the channel — one
+            // half-warp butterfly instead of a broadcast per slot
+            float se = dwe;
+#pragma unroll
+            for (int o = 8; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o, 16);
+            z += se;
 #pragma unroll
             for (int t = 0; t < 16; t++) {
                 const int jj = __shfl_sync(0xffffffffu, jl, t, 16);
-                const float a0 = __shfl_sync(0xffffffffu, dwe, t, 16);
                 const float a1 = __shfl_sync(0xffffffffu, dwf, t, 16);
-                if (jj >= 0) z += fmaf(a1, features[(size_t)jj * 16 + gl], a0);
+                if (jj >= 0) z = fmaf(a1, features[(size_t)jj * 16 + gl], z);
             }
         }
         // out_i = z . T  (the reference applies T inside the neighbour loop, aggregate_neighbors.cu:201-206)

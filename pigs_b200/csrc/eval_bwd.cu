@@ -312,6 +312,191 @@ __device__ __forceinline__ void bwd_sample_2d_packed(GaussPairs<KP>& G, const fl
     }
 }
 
+// ---- generalised packed path: 2-D, one or TWO channels, any subset of value / gradient / Hessian / third derivative ----
+// (NAVIER_STOKES' shape: model_pn.py:654,778 samples C = 2 with the third derivative; backward.cu:300-416.)
+// Same formulation as bwd_sample_2d_packed — S, p = dS/da, E = explicit dS/dConic, then dL/dmu ~ alpha (p - S X),
+// dL/dConic ~ alpha (sym(e X^T) + E) — with
+//   * the polynomial factors shared by the channels (h = a a^T - C and the four third-derivative factors, written in
+//     terms of h: f_xxx = a0 (2 c0 - h00), f_xxy = 2 c1 a0 - a1 h00, f_xyy = 2 c1 a1 - a0 h11, f_yyy = a1 (2 c2 - h11)),
+//   * per channel only S_c (for dL/dv_c = alpha S_c),
+//   * p and E formed from the VALUE-WEIGHTED upstream weights W = sum_c v_c G_c (one FFMA2 + FMUL2 per weight for two
+//     channels; for one channel W is the sample's scalar itself and v is applied once per Gaussian in the epilogue).
+template <int KP, int C>
+struct GaussPairsG {
+    f32x2 m0[KP], m1[KP], c0[KP], c1[KP], c2[KP], sh0[KP], sh1[KP], v[C][KP];
+    f32x2 t0[KP], t1[KP], t2[KP];  // 2 c (third-derivative factors)
+    f32x2 dv[C][KP], dm0[KP], dm1[KP], dc0[KP], dc1[KP], dc2[KP];
+};
+
+template <unsigned MASK, int MODE, int KP, int C>
+__device__ __forceinline__ void bwd_sample_2d_packed_gen(GaussPairsG<KP, C>& G, const float* __restrict__ r)
+{
+    constexpr bool HV = (MASK & PIGS_FN_VALUE) != 0, HD = (MASK & PIGS_FN_DERIV) != 0, HH = (MASK & PIGS_FN_HESS) != 0;
+    constexpr bool HT = (MASK & PIGS_FN_THIRD) != 0;
+    static_assert((MASK & PIGS_FN_LAPL) == 0 && C >= 1 && C <= 2, "value / gradient / Hessian / third, one or two channels");
+    constexpr int NA = nacc(2, MASK);
+    constexpr int OD = HV ? 1 : 0, OH = OD + (HD ? 2 : 0), OT = OH + (HH ? 3 : 0);
+    const float x0 = r[0], x1 = r[1];
+    f32x2 X0[KP], X1[KP], a0[KP], a1[KP], al[KP];
+#pragma unroll
+    for (int k = 0; k < KP; k++) X0[k] = add2(G.m0[k], bc2(-x0));
+#pragma unroll
+    for (int k = 0; k < KP; k++) X1[k] = add2(G.m1[k], bc2(-x1));
+    if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) X0[k] = add2(X0[k], G.sh0[k]);
+#pragma unroll
+        for (int k = 0; k < KP; k++) X1[k] = add2(X1[k], G.sh1[k]);
+    }
+    if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) {
+            float lo, hi;
+            upk2(X0[k], lo, hi);
+            X0[k] = pk2(torus_wrap(lo), torus_wrap(hi));
+            upk2(X1[k], lo, hi);
+            X1[k] = pk2(torus_wrap(lo), torus_wrap(hi));
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < KP; k++) a0[k] = mul2(G.c0[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a1[k] = mul2(G.c1[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a0[k] = fma2(G.c1[k], X1[k], a0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) a1[k] = fma2(G.c2[k], X1[k], a1[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) al[k] = mul2(a0[k], X0[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) al[k] = fma2(a1[k], X1[k], al[k]);
+#pragma unroll
+    for (int k = 0; k < KP; k++) {
+        float qlo, qhi;
+        upk2(al[k], qlo, qhi);
+        float alo = ex2_approx(qlo * KH), ahi = ex2_approx(qhi * KH);
+        if constexpr (MODE == EV_GENERAL) {
+            if (qlo < 0.0f) alo = 0.0f;  // power > 0: the reference skips the pair (backward.cu:81)
+            if (qhi < 0.0f) ahi = 0.0f;
+        }
+        al[k] = pk2(alo, ahi);
+    }
+    // factors shared by the channels
+    f32x2 h00[KP], h01[KP], h11[KP], f3[4][KP];
+    if constexpr (HH || HT) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) h00[k] = fma2(a0[k], a0[k], neg2(G.c0[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) h01[k] = fma2(a0[k], a1[k], neg2(G.c1[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) h11[k] = fma2(a1[k], a1[k], neg2(G.c2[k]));
+    }
+    if constexpr (HT) {
+#pragma unroll
+        for (int k = 0; k < KP; k++) f3[0][k] = mul2(a0[k], add2(G.t0[k], neg2(h00[k])));
+#pragma unroll
+        for (int k = 0; k < KP; k++) f3[1][k] = fma2(neg2(a1[k]), h00[k], mul2(G.t1[k], a0[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) f3[2][k] = fma2(neg2(a0[k]), h11[k], mul2(G.t1[k], a1[k]));
+#pragma unroll
+        for (int k = 0; k < KP; k++) f3[3][k] = mul2(a1[k], add2(G.t2[k], neg2(h11[k])));
+    }
+    // per channel: S_c = sum_w G_w f_w, dL/dv_c += alpha S_c
+    f32x2 Sc[C][KP];
+#pragma unroll
+    for (int ch = 0; ch < C; ch++) {
+        const float* __restrict__ g = r + 2 + ch * NA;
+#pragma unroll
+        for (int k = 0; k < KP; k++) {
+            f32x2 S = HV ? bc2(g[0]) : bc2(0.0f);
+            if constexpr (HD) {
+                S = fma2(bc2(g[OD]), a0[k], S);
+                S = fma2(bc2(g[OD + 1]), a1[k], S);
+            }
+            if constexpr (HH) {
+                S = fma2(bc2(g[OH]), h00[k], S);
+                S = fma2(bc2(g[OH + 1]), h01[k], S);
+                S = fma2(bc2(g[OH + 2]), h11[k], S);
+            }
+            if constexpr (HT) {
+#pragma unroll
+                for (int i = 0; i < 4; i++) S = fma2(bc2(g[OT + i]), f3[i][k], S);
+            }
+            Sc[ch][k] = S;
+            G.dv[ch][k] = fma2(al[k], S, G.dv[ch][k]);
+        }
+    }
+    // value-weighted upstream weight q of the pair block k (C == 1: the sample's scalar, `scale` folded in on the scalar side)
+    auto W = [&](int q, int k, float scale) -> f32x2 {
+        if constexpr (C == 1) {
+            return bc2(scale == 1.0f ? r[2 + q] : scale * r[2 + q]);
+        } else {
+            const f32x2 w = fma2(G.v[1][k], bc2(r[2 + NA + q]), mul2(G.v[0][k], bc2(r[2 + q])));
+            return scale == 1.0f ? w : (scale == 2.0f ? add2(w, w) : mul2(w, bc2(scale)));
+        }
+    };
+#pragma unroll
+    for (int k = 0; k < KP; k++) {
+        f32x2 S;
+        if constexpr (C == 1)
+            S = Sc[0][k];
+        else
+            S = fma2(G.v[1][k], Sc[1][k], mul2(G.v[0][k], Sc[0][k]));
+        f32x2 p0 = HD ? W(OD, k, 1.0f) : bc2(0.0f), p1 = HD ? W(OD + 1, k, 1.0f) : bc2(0.0f);
+        f32x2 E00 = bc2(0.0f), E01 = bc2(0.0f), E11 = bc2(0.0f);
+        if constexpr (HH) {
+            const f32x2 W00 = W(OH, k, 1.0f), W01 = W(OH + 1, k, 1.0f), W11 = W(OH + 2, k, 1.0f);
+            const f32x2 a0x2 = add2(a0[k], a0[k]), a1x2 = add2(a1[k], a1[k]);
+            p0 = fma2(W00, a0x2, p0);
+            p1 = fma2(W11, a1x2, p1);
+            p0 = fma2(W01, a1[k], p0);
+            p1 = fma2(W01, a0[k], p1);
+            E00 = neg2(W00);
+            E01 = neg2(W01);
+            E11 = neg2(W11);
+        }
+        if constexpr (HT) {
+            // dS/da and explicit dS/dC of the third-derivative factors (eval_common.cuh upstream_spe), h = a a^T - C
+            const f32x2 T0x3 = W(OT, k, 3.0f), T1 = W(OT + 1, k, 1.0f), T2 = W(OT + 2, k, 1.0f), T3x3 = W(OT + 3, k, 3.0f);
+            const f32x2 T1x2 = add2(T1, T1), T2x2 = add2(T2, T2);
+            p0 = fma2(neg2(T0x3), h00[k], p0);
+            p1 = fma2(neg2(T1), h00[k], p1);
+            p0 = fma2(neg2(T1x2), h01[k], p0);
+            p1 = fma2(neg2(T2x2), h01[k], p1);
+            p0 = fma2(neg2(T2), h11[k], p0);
+            p1 = fma2(neg2(T3x3), h11[k], p1);
+            E00 = fma2(T0x3, a0[k], E00);
+            E01 = fma2(T1x2, a0[k], E01);
+            E11 = fma2(T2, a0[k], E11);
+            E00 = fma2(T1, a1[k], E00);
+            E01 = fma2(T2x2, a1[k], E01);
+            E11 = fma2(T3x3, a1[k], E11);
+        }
+        const f32x2 hS = mul2(S, bc2(-0.5f));
+        f32x2 r0, r1, e1, e2;
+        if constexpr (HD || HH || HT) {
+            r0 = fma2(neg2(S), X0[k], p0);
+            e1 = fma2(hS, X0[k], p0);
+            r1 = fma2(neg2(S), X1[k], p1);
+            e2 = fma2(hS, X1[k], p1);
+        } else {
+            r0 = mul2(neg2(S), X0[k]);
+            e1 = mul2(hS, X0[k]);
+            r1 = mul2(neg2(S), X1[k]);
+            e2 = mul2(hS, X1[k]);
+        }
+        const f32x2 T0 = fma2(e1, X0[k], E00);
+        const f32x2 T1 = fma2(e1, X1[k], fma2(e2, X0[k], E01));
+        const f32x2 T2 = fma2(e2, X1[k], E11);
+        const f32x2 w = al[k];
+        G.dm0[k] = fma2(w, r0, G.dm0[k]);
+        G.dm1[k] = fma2(w, r1, G.dm1[k]);
+        G.dc0[k] = fma2(w, T0, G.dc0[k]);
+        G.dc1[k] = fma2(w, T1, G.dc1[k]);
+        G.dc2[k] = fma2(w, T2, G.dc2[k]);
+    }
+}
+
 template <int D, int C, unsigned MASK, int MODE>
 __global__ void __launch_bounds__(EV_THREADS, 2)
     eval_bwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
@@ -390,6 +575,36 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             }
         }
 
+        // generalised packed view (2-D; two channels and / or the third derivative)
+        constexpr bool PACKED_GEN = PIGS_BWD_PACKED && !PACKED && D == 2 && C <= 2 && (KG % 2) == 0 &&
+                                    (MASK & PIGS_FN_LAPL) == 0 && (C == 2 || (MASK & PIGS_FN_THIRD) != 0);
+        GaussPairsG<PACKED_GEN ? KG / 2 : 1, PACKED_GEN ? C : 1> GG;
+        if constexpr (PACKED_GEN) {
+            const float nz = __uint_as_float(wh->neg_zero);
+#pragma unroll
+            for (int k = 0; k < KG / 2; k++) {
+                const GaussReg<D, C>&ga = g[2 * k], &gb = g[2 * k + 1];
+                GG.m0[k] = pk2_once(ga.m[0], gb.m[0], nz);
+                GG.m1[k] = pk2_once(ga.m[D - 1], gb.m[D - 1], nz);
+                GG.c0[k] = pk2_once(ga.c[0], gb.c[0], nz);
+                GG.c1[k] = pk2_once(ga.c[NC > 1 ? 1 : 0], gb.c[NC > 1 ? 1 : 0], nz);
+                GG.c2[k] = pk2_once(ga.c[NC - 1], gb.c[NC - 1], nz);
+                GG.sh0[k] = pk2_once(ga.sh[0], gb.sh[0], nz);
+                GG.sh1[k] = pk2_once(ga.sh[D - 1], gb.sh[D - 1], nz);
+#pragma unroll
+                for (int ch = 0; ch < C; ch++) {
+                    GG.v[ch][k] = pk2_once(ga.v[ch], gb.v[ch], nz);
+                    GG.dv[ch][k] = bc2(0.0f);
+                }
+                if constexpr ((MASK & PIGS_FN_THIRD) != 0) {
+                    GG.t0[k] = pk2_once(2.0f * ga.c[0], 2.0f * gb.c[0], nz);
+                    GG.t1[k] = pk2_once(2.0f * ga.c[NC > 1 ? 1 : 0], 2.0f * gb.c[NC > 1 ? 1 : 0], nz);
+                    GG.t2[k] = pk2_once(2.0f * ga.c[NC - 1], 2.0f * gb.c[NC - 1], nz);
+                }
+                GG.dm0[k] = GG.dm1[k] = GG.dc0[k] = GG.dc1[k] = GG.dc2[k] = bc2(0.0f);
+            }
+        }
+
         // ---- streamed operand: sample records through shared memory ----
         const float4* __restrict__ src = srecs + (size_t)it.s_begin * SV;
         const uint32_t total_v4 = it.s_count * SV;
@@ -425,6 +640,10 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 load_v4<SV>(batch + s * SV, r);
                 if constexpr (PACKED) {
                     bwd_sample_2d_packed<MASK, MODE, KG / 2>(GP, r);
+                    continue;
+                }
+                if constexpr (PACKED_GEN) {
+                    bwd_sample_2d_packed_gen<MASK, MODE, KG / 2, C>(GG, r);
                     continue;
                 }
                 if constexpr (PIGS_BWD_OPMAJOR && D == 2 && C == 1 && (MASK & PIGS_FN_THIRD) == 0) {
@@ -524,6 +743,21 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 upk2(GP.c1[k], ec[2 * k][NC > 1 ? 1 : 0], ec[2 * k + 1][NC > 1 ? 1 : 0]);
                 upk2(GP.c2[k], ec[2 * k][NC - 1], ec[2 * k + 1][NC - 1]);
                 upk2(GP.v[k], ev[2 * k], ev[2 * k + 1]);
+            }
+        } else if constexpr (PACKED_GEN) {
+#pragma unroll
+            for (int k = 0; k < KG / 2; k++) {
+#pragma unroll
+                for (int ch = 0; ch < C; ch++) upk2(GG.dv[ch][k], dv[2 * k][ch], dv[2 * k + 1][ch]);
+                upk2(GG.dm0[k], dm[2 * k][0], dm[2 * k + 1][0]);
+                upk2(GG.dm1[k], dm[2 * k][D - 1], dm[2 * k + 1][D - 1]);
+                upk2(GG.dc0[k], dc[2 * k][0], dc[2 * k + 1][0]);
+                upk2(GG.dc1[k], dc[2 * k][NC > 1 ? 1 : 0], dc[2 * k + 1][NC > 1 ? 1 : 0]);
+                upk2(GG.dc2[k], dc[2 * k][NC - 1], dc[2 * k + 1][NC - 1]);
+                upk2(GG.c0[k], ec[2 * k][0], ec[2 * k + 1][0]);
+                upk2(GG.c1[k], ec[2 * k][NC > 1 ? 1 : 0], ec[2 * k + 1][NC > 1 ? 1 : 0]);
+                upk2(GG.c2[k], ec[2 * k][NC - 1], ec[2 * k + 1][NC - 1]);
+                upk2(GG.v[0][k], ev[2 * k], ev[2 * k + 1]);
             }
         } else {
 #pragma unroll

@@ -29,6 +29,16 @@ def ev_time(fn, warm=2, it=5):
     return float(np.median(ts))
 
 
+# FP32 lane-ops per pair the kernels EXECUTE in their inner loops, counted in the SASS (tools/sass_issue_model.py; FFMA2 /
+# FMUL2 / FADD2 = 2): (D, C, mask) -> (forward, backward).  Used as the (conservative) algorithmic count of each variant:
+# the roofline fraction below is FP32-pipe utilisation.  DESIGN.md §4 lists them.
+EXEC_LANE_OPS = {
+    (2, 1, 7): (18.0, 36.5), (2, 1, 19): (16.0, 31.5), (2, 1, 8): (25.1, 52.5), (2, 2, 7): (25.0, 56.0), (2, 2, 8): (30.25, 70.0),
+    (2, 1, 1): (10.0, None), (1, 1, 7): (8.0, None),
+}
+PEAK_T = 148 * 128 * 1.965e9 / 1e12  # T lane-op/s at the maximum SM clock
+
+
 def case(name, P, N, masks, **kw):
     rec = synthetic(P, N, seed=0, **kw)
     d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
@@ -45,7 +55,14 @@ def case(name, P, N, masks, **kw):
         g = [torch.randn(shape(k), device="cuda") if (mask & (1 << k) or (k == 2 and mask & 16)) else None for k in range(4)]
         tf = ev_time(lambda: _C.sample_forward(mask, *a, bb, sbb, rg, srg, False))
         tb = ev_time(lambda: _C.sample_backward(mask, *a, g, bb, sbb, rg, srg, False))
-        rows.append(dict(mask=mask, fwd_ms=tf, bwd_ms=tb, fwd_Gpairs_s=pairs / tf / 1e6, bwd_Gpairs_s=pairs / tb / 1e6))
+        row = dict(mask=mask, fwd_ms=tf, bwd_ms=tb, fwd_Gpairs_s=pairs / tf / 1e6, bwd_Gpairs_s=pairs / tb / 1e6)
+        ops = EXEC_LANE_OPS.get((D, min(C, 2), mask))
+        if ops and C <= 2:
+            if ops[0]:
+                row["fwd_lane_ops_per_pair"], row["fwd_frac_fp32_roofline"] = ops[0], pairs / (tf * 1e-3) * ops[0] / 1e12 / PEAK_T
+            if ops[1]:
+                row["bwd_lane_ops_per_pair"], row["bwd_frac_fp32_roofline"] = ops[1], pairs / (tb * 1e-3) * ops[1] / 1e12 / PEAK_T
+        rows.append(row)
     return dict(case=name, P=P, N=N, D=D, C=C, pairs=pairs, rows=rows)
 
 
