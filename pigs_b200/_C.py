@@ -712,3 +712,83 @@ def dense_backward(fn_mask, means, conics, values, samples, g_u, g_ux, g_uxx):
         check(L.pigs_dense_backward(fn_mask, n, D, C, N, _ptr(means), _ptr(conics), _ptr(values), _ptr(samples),
                                     *[_ptr(g) for g in gs], _ptr(dm), _ptr(dc), _ptr(dv), _stream()), "pigs_dense_backward")
     return dm, dc, dv
+
+
+# ---- compiled binding ------------------------------------------------------------------------------------------------
+# pigs_b200/_Cext.so (csrc/torch_ext.cpp) implements the entry points above in C++ (the reference's own binding is a
+# pybind module too, ext.cpp:19-32).  When it is built it takes over the hot entry points; the ctypes functions above stay
+# importable as `<name>_ctypes` (torch-free-build alternative, and the cross-check in tests/test_compiled_binding.py).
+# PIGS_B200_BINDING=ctypes keeps the ctypes path.
+_HOT = ("preprocess_gaussians", "sample_forward", "sample_backward", "preprocess_aggregate", "aggregate_neighbors",
+        "aggregate_neighbors_backward", "sample_gaussians", "sample_gaussians_backward", "sample_gaussians_derivative",
+        "sample_gaussians_derivative_backward", "sample_gaussians_laplacian", "sample_gaussians_laplacian_backward",
+        "sample_gaussians_third_derivative", "sample_gaussians_third_derivative_backward")
+BINDING = "ctypes"
+_ext = None
+
+
+def _load_compiled():
+    import importlib.util
+    import os
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_Cext.so")
+    if os.environ.get("PIGS_B200_BINDING", "compiled") == "ctypes" or not os.path.exists(path):
+        return None
+    _lib.lib()  # the one libpigs_b200.so instance both bindings share
+    spec = importlib.util.spec_from_file_location("pigs_b200._Cext", path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def use_binding(name):
+    """Select "compiled" or "ctypes" for the hot entry points (tests compare the two)."""
+    global BINDING, _ext
+    g = globals()
+    if name == "compiled":
+        if _ext is None:
+            _ext = _load_compiled()
+        if _ext is None:
+            raise RuntimeError("pigs_b200/_Cext.so is not built (python -c 'import __graft_entry__ as g; g.build()')")
+        for n in _HOT:
+            g[n] = _wrap_compiled(n)
+    elif name == "ctypes":
+        for n in _HOT:
+            g[n] = g[n + "_ctypes"]
+    else:
+        raise ValueError(name)
+    BINDING = name
+
+
+def _wrap_compiled(n):
+    f = getattr(_ext, n)
+    if n == "sample_forward":
+        return lambda *a: tuple(f(*a))
+    if n == "sample_backward":
+        def bw(fn_mask, means, values, conics, samples, num_rendered, grads, *rest):
+            return f(fn_mask, means, values, conics, samples, num_rendered, list(grads), *rest)
+        return bw
+    if n == "preprocess_gaussians":
+        def pre(means, values, covariances, conics, samples, debug, bounds=None, cull=None):
+            if cull is not None:
+                cull = (float(cull[0]), int(cull[1]))
+            return f(means, values, covariances, conics, samples, bool(debug), bounds, cull)
+        return pre
+    if n == "preprocess_aggregate":
+        def pa(means, conics, radii, debug, rows=None):
+            if rows is not None:
+                rows = (int(rows[0]), int(rows[1]))
+            return f(means, conics, radii, bool(debug), rows)
+        return pa
+    return f
+
+
+for _n in _HOT:
+    globals()[_n + "_ctypes"] = globals()[_n]
+try:
+    _ext = _load_compiled()
+    if _ext is not None:
+        use_binding("compiled")
+except Exception as _ex:  # a stale or unloadable _Cext.so must not take the package down: the ctypes binding is complete
+    import warnings
+    warnings.warn("pigs_b200: compiled binding not usable (%s); using the ctypes binding" % (_ex,))
+    _ext = None

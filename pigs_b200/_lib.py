@@ -120,6 +120,12 @@ def build(verbose=False):
     subprocess.run(cmd, check=True)
 
 
+def build_ext(verbose=False):
+    """Compile the torch binding pigs_b200/_Cext.so (csrc/torch_ext.cpp, host compiler only) over the library."""
+    subprocess.run(["bash", os.path.join(_HERE, "csrc", "build_ext.sh")], check=True,
+                   stdout=None if verbose else subprocess.DEVNULL)
+
+
 def lib():
     """The loaded library; raises RuntimeError when it has not been built."""
     global _lib
