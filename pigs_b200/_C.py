@@ -45,6 +45,21 @@ def _f32c(t, name):
     return t.contiguous()
 
 
+def _on_device(fn):
+    """Run a binding function with the device of its first tensor argument current (the library launches on the current
+    device's stream); the compiled binding does the same with a CUDAGuard."""
+    import functools
+
+    @functools.wraps(fn)
+    def wrapped(*a, **k):
+        t = next((x for x in a if isinstance(x, torch.Tensor) and x.is_cuda), None)
+        if t is None or t.device.index == torch.cuda.current_device():
+            return fn(*a, **k)
+        with torch.cuda.device(t.device):
+            return fn(*a, **k)
+    return wrapped
+
+
 def _bytes(n, device):
     return torch.empty(int(n), dtype=torch.uint8, device=device)
 
@@ -57,6 +72,7 @@ def _dims(means, values, samples):
     return P, D, N, C
 
 
+@_on_device
 def sample_bounds(samples, D):
     """float32[2*D] on the device: per-dimension min then max of the samples (sample_points.cu:70-71)."""
     L = _lib.lib()
@@ -91,6 +107,7 @@ def _read_i64(dev_scalar):
     return int(host.item())
 
 
+@_on_device
 def preprocess_gaussians(means, values, covariances, conics, samples, debug, bounds=None, cull=None):
     """PreprocessCUDA (sample_points.cu:37-98).  Returns
     (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges, radii).
@@ -141,6 +158,7 @@ def _blocks_of(ranges):
     return ranges.numel() // 8 - 1
 
 
+@_on_device
 def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binning_buffer, sample_binning_buffer, ranges,
                    sample_ranges, debug):
     """Fused forward for any subset of {value, derivative, Hessian | Laplacian, third}.  Returns a 4-tuple with
@@ -170,6 +188,7 @@ def sample_forward(fn_mask, means, values, conics, samples, num_rendered, binnin
     return tuple(outs)
 
 
+@_on_device
 def sample_backward(fn_mask, means, values, conics, samples, num_rendered, grads, binning_buffer, sample_binning_buffer,
                     ranges, sample_ranges, debug):
     """Fused backward; `grads` is a 4-tuple of upstream gradients (None = zero; with FN_LAPL slot 2 is the
@@ -249,6 +268,7 @@ def point_lists(num_rendered, binning_buffer, sample_binning_buffer, N):
 
 
 # ---- neighbour aggregation (ext.cpp:29-31) ----------------------------------------------------------
+@_on_device
 def preprocess_aggregate(means, conics, radii, debug, rows=None):
     """AggregateNeighborsPreprocessCUDA (aggregate_neighbors.cu:323-367).  Returns
     (indices i64[M], ranges i64[P], dists f32[M,D], densities f32[M], inv_total_densities f32[P]).
@@ -284,6 +304,7 @@ def preprocess_aggregate(means, conics, radii, debug, rows=None):
     return indices, ranges, dists, densities, inv_total
 
 
+@_on_device
 def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
                         densities, inv_total_densities, debug):
     """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415).  Returns
@@ -316,6 +337,7 @@ def aggregate_neighbors(features, transform, queries, keys, frequencies, distanc
     return weights, embeddings, factors, out
 
 
+@_on_device
 def aggregate_neighbors_backward(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
                                  dists, densities, weights, embeddings, factors, inv_total_densities,
                                  dL_dneighbor_features, debug):
@@ -358,6 +380,7 @@ def _disp(t, rows, width):
     return ctypes.c_void_p(t.data_ptr() - int(rows[0]) * int(width) * 4)
 
 
+@_on_device
 def aggregate_neighbors_rows(features, transform, queries_rows, keys, frequencies, distance_transform, indices, ranges,
                              dists, densities, inv_total_densities, rows, debug):
     """(extension, multi-GPU) aggregate_neighbors for the query rows [lo, hi) = `rows` only.  features / keys are
@@ -394,6 +417,7 @@ def aggregate_neighbors_rows(features, transform, queries_rows, keys, frequencie
     return weights, embeddings, factors, out
 
 
+@_on_device
 def aggregate_neighbors_rows_backward(features, transform, queries_rows, keys, frequencies, distance_transform, indices,
                                       ranges, dists, densities, weights, embeddings, factors, inv_total_densities,
                                       dL_dout_rows, g_features, g_keys, rows, debug):

@@ -80,12 +80,16 @@ class _SampleFused(torch.autograd.Function):
         outs = call_debug(lambda *a: _C.sample_forward(mask, *a), debug, "fw%d" % mask, *args)
         ctx.mask = mask
         ctx.args = args
+        ctx.versions = _versions(args)
         ctx.reduce = reduce  # sharded sampler: callable applied to the packed gradient buffer (NCCL all-reduce)
+        # outputs nobody back-propagates through arrive as None instead of materialised zeros and drop out of the backward
+        ctx.set_materialize_grads(False)
         return tuple(o for o in outs if o is not None)
 
     @staticmethod
     def backward(ctx, *grad_outs):
         mask = ctx.mask
+        _check_versions(ctx.args, ctx.versions)
         means, values, conics, samples, num_rendered, bb, sbb, ranges, sample_ranges, debug = ctx.args
         grads, it = [None] * 4, iter(grad_outs)
         live = 0
@@ -103,6 +107,20 @@ class _SampleFused(torch.autograd.Function):
         if ctx.reduce is not None:
             ctx.reduce(_C.packed_base(dm))  # dm, dv, dc are views of one flat buffer: one collective
         return (None, dm, dv, dc, None, None, None, None, None, None, None, None)
+
+
+def _versions(args):
+    return tuple(a._version if isinstance(a, torch.Tensor) else None for a in args)
+
+
+def _check_versions(args, versions):
+    """The inputs are kept on ctx (not save_for_backward) so that each output can be back-propagated in its own
+    backward() call like the reference's separate nodes; autograd's in-place check is re-created here."""
+    for a, v in zip(args, versions):
+        if isinstance(a, torch.Tensor) and a._version != v:
+            raise RuntimeError("one of the variables needed for gradient computation has been modified by an inplace "
+                               "operation (pigs_b200: an input of the sampling / aggregation call changed between its "
+                               "forward and its backward)")
 
 
 def _slot_bit(mask, k):
@@ -144,6 +162,7 @@ class _AggregateNeighbors(torch.autograd.Function):
                 inv_total_densities, debug)
         weights, embeddings, factors, neighbor_features = call_debug(_C.aggregate_neighbors, debug, "aggregate", *args)
         ctx.args = args
+        ctx.versions = _versions(args)
         ctx.saved = (weights, embeddings, factors)
         ctx.reduce = reduce  # sharded sampler: sums the row-sharded output and the six gradients over ranks
         if reduce is not None:
@@ -152,6 +171,7 @@ class _AggregateNeighbors(torch.autograd.Function):
 
     @staticmethod
     def backward(ctx, grad_out):
+        _check_versions(ctx.args, ctx.versions)
         (features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
          inv_total_densities, debug) = ctx.args
         weights, embeddings, factors = ctx.saved
@@ -177,9 +197,10 @@ class GaussianSampler:
 
     fused (extension): True / False / "auto" (default, env PIGS_B200_FUSE=0 disables).  The reference's
     callers ask for u, grad u and the Hessian in three calls after one preprocess(); with fusion on, the
-    sampler remembers which outputs were requested during the previous preprocess() cycle and, on the
-    first request of the next cycle, evaluates that whole set in ONE kernel (and back-propagates it in
-    one), handing out the cached pieces.  Results are identical to the unfused calls."""
+    sampler remembers which outputs were requested during the last preprocess() cycle WITH THE SAME NUMBER OF SAMPLES
+    (the call site: interior / boundary / means cycles alternate on one sampler in model_pn.py) and, on the first
+    request of the next such cycle, evaluates that whole set in ONE kernel (and back-propagates it in one), handing
+    out the cached pieces.  Results are identical to the unfused calls."""
 
     def __init__(self, debug, fused="auto", cull=None):
         self.debug = debug
@@ -191,9 +212,15 @@ class GaussianSampler:
         if fused == "auto":
             fused = os.environ.get("PIGS_B200_FUSE", "1") != "0"
         self.fused = bool(fused)
-        self._plan = 0      # mask requested during the previous cycle
+        # The plan is keyed by the call site, identified by the number of samples: the reference driver alternates
+        # cycles on ONE sampler (model_pn.py:768-786: interior samples -> u, ux, uxx; boundary samples -> u only;
+        # Model.forward: samples = means -> u, ux, uxx), and each kind of cycle keeps asking for its own set.
+        self._plans = {}    # samples per cycle -> mask requested during the last cycle with that many samples
+        self._key = None
+        self._plan = 0      # mask the current cycle is expected to ask for
         self._seen = 0      # mask requested so far in this cycle
         self._cache = {}    # bit -> tensor produced by a fused call in this cycle
+        self._cache_grad = None  # torch.is_grad_enabled() when the cache was filled
 
     def preprocess(self, means, values, covariances, conics, samples, bounds=None):
         debug = self.debug
@@ -215,7 +242,10 @@ class GaussianSampler:
         self.sample_ranges = sample_ranges
         self.radii = radii
         self._sample_state = (num_rendered, binning_buffer, sample_binning_buffer, ranges, sample_ranges)
-        self._plan, self._seen, self._cache = self._seen, 0, {}
+        if self._key is not None and self._seen:
+            self._plans[self._key] = self._seen
+        self._key = int(samples.shape[0])
+        self._plan, self._seen, self._cache = self._plans.get(self._key, 0), 0, {}
         if (self._plan & FN_HESS) and (self._plan & FN_LAPL):
             self._plan &= ~FN_LAPL  # shared output slot: the Laplacian request then runs on its own
 
@@ -249,8 +279,12 @@ class GaussianSampler:
     def _request(self, bit):
         self._seen |= bit
         if bit in self._cache:
-            return self._cache.pop(bit)
+            out = self._cache.pop(bit)
+            if self._cache_grad == torch.is_grad_enabled():
+                return out
+            return self.sample_fused(bit)[0]  # fused under another grad mode: its pieces carry the wrong (or no) graph
         if self.fused and (self._plan & bit) and self._plan != bit and not self._cache:
+            self._cache_grad = torch.is_grad_enabled()
             outs = iter(self.sample_fused(self._plan))
             for k in range(4):
                 b = _slot_bit(self._plan, k)

@@ -324,19 +324,20 @@ class ShardedGaussianSampler(GaussianSampler):
     def _rank_world(self):
         return _rank_world(self.group)
 
-    def preprocess_aggregate(self, row_range=None, csr=None):
+    def preprocess_aggregate(self, row_range=None, csr=None, dense_fraction=0.5):
         """Neighbour lists of this rank's contiguous range of query Gaussians (every Gaussian stays a candidate
         neighbour); the other rows are empty.  1/world of the CSR per GPU.  row_range = (lo, hi) overrides the even
         split, e.g. with this rank's window of balanced_ranges().  csr = (indices, ranges, dists, densities,
         inv_total_densities) installs caller-built lists for the window instead of searching (the reference API takes the
-        CSR as plain inputs too, aggregate_neighbors.h:17-29)."""
+        CSR as plain inputs too, aggregate_neighbors.h:17-29).  dense_fraction: halo size (as a fraction of P) above
+        which the row-parallel form exchanges whole windows with collectives instead of halo rows point to point."""
         rank, world = self._rank_world()
         P = self.means.size(0)
         self.row_range = shard_range(P, rank, world) if row_range is None else tuple(int(v) for v in row_range)
         if csr is None:
             csr = _C.preprocess_aggregate(self.means, self.conics, self.radii, self.debug, rows=self.row_range)
         self.indices, self.ranges, self.dists, self.densities, self.inv_total_densities = csr
-        self.row_plan = RowHaloPlan(P, self.row_range, self.indices, self.group)
+        self.row_plan = RowHaloPlan(P, self.row_range, self.indices, self.group, dense_fraction=dense_fraction)
         self.row_windows = self.row_plan.windows
 
     def aggregate_neighbors(self, features, transform, queries, keys, frequencies, distance_transform):

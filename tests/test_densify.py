@@ -106,3 +106,48 @@ def test_cuda_prune_only_and_1d():
     np.testing.assert_array_equal(src.cpu().numpy(), wsrc)
     assert rel_err(m.cpu().numpy(), wm) <= TOL  # 1-D: v = +1 on both sides, the order is defined
     np.testing.assert_array_equal(uu.cpu().numpy(), wu)
+
+
+@pytest.mark.gpu
+def test_split_is_differentiable_like_the_reference_chain():
+    """Model.split (model_pn.py:578-605) indexes, halves and concatenates NON-LEAF tensors (the dynamics network's outputs),
+    so autograd must flow through it: gradients of pigs_b200.densify.split equal those of the torch formulation
+    (x[~idx], x[idx].repeat_interleave(2) (/ 2), cat; displacement constant) for every input."""
+    import torch
+    from pigs_b200 import densify
+    g = torch.Generator().manual_seed(3)
+    P = 257
+    base = {"means": torch.rand(P, 2, generator=g) * 2 - 1, "scaling": torch.rand(P, 2, generator=g) * 0.01 + 0.001,
+            "transforms": torch.randn(P, 1, generator=g) * 0.3, "u": torch.rand(P, 2, generator=g) * 2 - 1}
+    idx = (torch.arange(P) % 5 == 0).cuda()
+    s0, s1, t = base["scaling"][:, 0], base["scaling"][:, 1], torch.tanh(base["transforms"][:, 0]) * torch.sqrt(base["scaling"][:, 0] * base["scaling"][:, 1])
+    cov = torch.stack([s0, t, s1], -1).cuda()
+    # two graphs over the same non-leaf inputs (x = leaf * 1.5, as the network's `means + dmeans * mask` would be)
+    leaves_a = {k: v.clone().cuda().requires_grad_(True) for k, v in base.items()}
+    leaves_b = {k: v.clone().cuda().requires_grad_(True) for k, v in base.items()}
+    xa = {k: v * 1.5 for k, v in leaves_a.items()}
+    xb = {k: v * 1.5 for k, v in leaves_b.items()}
+    om, os_, ot, ou, src = densify.split(xa["means"], xa["scaling"], xa["transforms"], xa["u"], cov, idx)
+    assert all(o.grad_fn is not None for o in (om, os_, ot, ou))
+    n_keep = int((~idx).sum())
+    # torch formulation; the (constant) displacement is taken from our forward so both sides place the children alike
+    disp = (om[n_keep:] - xa["means"].detach()[src[n_keep:]]).detach()
+    rm = torch.cat((xb["means"][~idx], xb["means"][idx].repeat_interleave(2, 0) + disp), 0)
+    rs = torch.cat((xb["scaling"][~idx], xb["scaling"][idx].repeat_interleave(2, 0)), 0)
+    rt = torch.cat((xb["transforms"][~idx], xb["transforms"][idx].repeat_interleave(2, 0)), 0)
+    ru = torch.cat((xb["u"][~idx], xb["u"][idx].repeat_interleave(2, 0) / 2.0), 0)
+    for a, b in ((om, rm), (os_, rs), (ot, rt), (ou, ru)):
+        assert torch.equal(a.detach(), b.detach())
+    w = [torch.randn(o.shape, generator=torch.Generator().manual_seed(9 + i)).cuda() for i, o in enumerate((om, os_, ot, ou))]
+    sum((o * wi).sum() for o, wi in zip((om, os_, ot, ou), w)).backward()
+    sum((o * wi).sum() for o, wi in zip((rm, rs, rt, ru), w)).backward()
+    for k in base:
+        assert leaves_a[k].grad is not None
+        assert rel_err(leaves_a[k].grad.cpu().numpy(), leaves_b[k].grad.cpu().numpy()) <= 1e-6, k
+    # masks and integer rows: torch indexing, appended rows set like model_pn.py:602-605
+    mask = (torch.arange(P) % 3 == 0).cuda().reshape(P, 1)
+    mo = densify.gather_rows(mask, src, n_keep, appended_value=True)
+    assert mo.dtype == torch.bool and mo.shape == (src.numel(), 1) and bool(mo[n_keep:].all())
+    assert torch.equal(mo[:n_keep], mask[~idx])
+    bo = densify.gather_rows(torch.ones(P, 1).cuda(), src, n_keep, appended_value=0.0)
+    assert float(bo[n_keep:].abs().sum()) == 0.0 and float(bo[:n_keep].sum()) == n_keep

@@ -217,3 +217,47 @@ def test_inputs_at_odd_float_offsets(torch_mod):
         np.testing.assert_array_equal(a[k], b[k])
     for x, y in zip(a["outs"] + a["grads"], b["outs"] + b["grads"]):
         assert rel_err(y, x) <= TOL
+
+
+def test_fusion_plan_is_per_call_site_and_grad_mode_aware(torch_mod):
+    """model_pn.py alternates cycles on ONE sampler (model_pn.py:768-786: interior samples -> u, ux, uxx; boundary samples ->
+    u only; Model.forward: no_grad).  Each kind of cycle keeps its own fusion plan (keyed by the number of samples), pieces
+    fused under no_grad are not handed out to a grad-enabled request, and an in-place edit of an input between forward
+    and backward raises like autograd's own check."""
+    torch = torch_mod
+    from pigs_b200 import GaussianSampler, _lib
+    rec = RECIPES["synth2d"]()
+    d = to_dev(rec)
+    bc = d["samples"][:777].contiguous()
+    for k in ("means", "values", "conics"):
+        d[k].requires_grad_(True)
+    s = GaussianSampler(False, fused=True)
+    L = _lib.lib()
+    counts = {"int": [], "bc": []}
+    for cycle in range(3):
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+        n0 = L.pigs_launch_count()
+        u, du, ddu = s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_gaussians_laplacian()
+        counts["int"].append(L.pigs_launch_count() - n0)
+        s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], bc)
+        n0 = L.pigs_launch_count()
+        ub = s.sample_gaussians()
+        counts["bc"].append(L.pigs_launch_count() - n0)
+        assert ub.shape == (777, 1)
+    assert counts["int"][1] < counts["int"][0] and counts["int"][2] == counts["int"][1]  # interior cycles fuse from the 2nd on
+    assert counts["bc"][0] == counts["bc"][1] == counts["bc"][2]                         # the value-only cycle never inherits plan 7
+    (u.sum() + du.sum()).backward()  # ddu unused: its gradient is not materialised, the backward runs mask 3
+    assert d["means"].grad is not None
+    # a fused evaluation started under no_grad does not serve a grad-enabled request
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    with torch.no_grad():
+        u0 = s.sample_gaussians()
+    du1 = s.sample_gaussians_derivative()
+    assert u0.grad_fn is None and du1.grad_fn is not None
+    # in-place edit between forward and backward
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    u2 = s.sample_gaussians()
+    with torch.no_grad():
+        d["values"].mul_(1.0)
+    with pytest.raises(RuntimeError, match="inplace"):
+        u2.sum().backward()
