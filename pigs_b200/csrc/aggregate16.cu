@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
     for (int i = threadIdx.x; i < 256; i += A16_THREADS) s_T[i] = transform[i];
     __syncthreads();
     const int lane = threadIdx.x & 31, g = lane >> 4, gl = lane & 15;
-    const int64_t warp = ((int64_t)blockIdx.x * A16_THREADS + threadIdx.x) >> 5;
+    // warp index through a broadcast so the compiler knows it (and every loop bound derived from it) is warp-uniform:
+    // otherwise each __shfl_sync below is wrapped in WARPSYNC / ENDCOLLECTIVE re-convergence code
+    const int64_t warp = ((int64_t)blockIdx.x * A16_THREADS >> 5) + __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
     const int64_t nwarps = ((int64_t)gridDim.x * A16_THREADS) >> 5;
 
     for (int64_t base = row_lo + warp * 2; base < P; base += nwarps * 2) {  // warp-uniform; rows [row_lo, P)
@@ -117,7 +119,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
         }
         const float inv = valid ? inv_total[row] : 0.0f;
         float z = 0.0f;
-        const int nmax = max(n, __shfl_xor_sync(0xffffffffu, n, 16));
+        const int nmax = __reduce_max_sync(0xffffffffu, n);  // over both rows of the warp; lands in a uniform register
         for (int c0 = 0; c0 < nmax; c0 += 16) {
             const int64_t s = start + c0 + gl;
             const int64_t j = (c0 + gl < n) ? indices[s] : -1;
@@ -201,7 +203,9 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
     for (int i = threadIdx.x; i < NCOL + 256; i += A16_THREADS) s_red[i] = 0.0f;
     __syncthreads();
     const int lane = threadIdx.x & 31, g = lane >> 4, gl = lane & 15;
-    const int64_t warp = ((int64_t)blockIdx.x * A16_THREADS + threadIdx.x) >> 5;
+    // warp index through a broadcast so the compiler knows it (and every loop bound derived from it) is warp-uniform:
+    // otherwise each __shfl_sync below is wrapped in WARPSYNC / ENDCOLLECTIVE re-convergence code
+    const int64_t warp = ((int64_t)blockIdx.x * A16_THREADS >> 5) + __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
     const int64_t nwarps = ((int64_t)gridDim.x * A16_THREADS) >> 5;
     const float PI = 3.14159265358979323846f;
     // per-thread partial sums, kept in registers over every row this thread touches
@@ -220,7 +224,7 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
         const bool valid = row < P;
         const int64_t start = (valid && row > 0) ? ranges[row - 1] : 0;
         const int n = valid ? (int)(ranges[row] - start) : 0;
-        const int nmax = max(n, __shfl_xor_sync(0xffffffffu, n, 16));
+        const int nmax = __reduce_max_sync(0xffffffffu, n);  // over both rows of the warp; lands in a uniform register
         if (nmax == 0) continue;
         const float q_l = valid ? queries[row * 16 + gl] : 0.0f;  // lane = channel views
         const float g_l = valid ? gout[row * 16 + gl] : 0.0f;
