@@ -325,10 +325,11 @@ def aggregate_neighbors(features, transform, queries, keys, frequencies, distanc
     P, D, L = features.size(0), dists.size(-1), features.size(-1)
     K, E = queries.size(-1), dt.size(-1) // 2
     dev = features.device
-    weights = torch.zeros_like(densities)
-    embeddings = torch.zeros_like(densities)
-    factors = torch.zeros_like(densities)
-    out = torch.zeros((P, L), dtype=torch.float32, device=dev)
+    # no zero fills: the kernels write every slot of every row (skipped neighbours as zeros) and every output row
+    weights = torch.empty_like(densities)
+    embeddings = torch.empty_like(densities)
+    factors = torch.empty_like(densities)
+    out = torch.empty((P, L), dtype=torch.float32, device=dev)
     if P > 0:
         check(L_.pigs_aggregate_forward(P, D, L, K, E, _ptr(features), _ptr(transform), _ptr(queries), _ptr(keys),
                                         _ptr(frequencies), _ptr(dt), _ptr(indices), _ptr(ranges), _ptr(dists),
@@ -404,10 +405,10 @@ def aggregate_neighbors_rows(features, transform, queries_rows, keys, frequencie
     K, E = queries_rows.size(-1), dt.size(-1) // 2
     if queries_rows.size(0) != hi - lo or keys.size(0) != P or ranges.numel() != P:
         raise RuntimeError("aggregate_neighbors_rows: queries must hold the window's rows, features / keys / ranges all P")
-    weights = torch.zeros_like(densities)
-    embeddings = torch.zeros_like(densities)
-    factors = torch.zeros_like(densities)
-    out = torch.zeros((hi - lo, L), dtype=torch.float32, device=features.device)
+    weights = torch.empty_like(densities)
+    embeddings = torch.empty_like(densities)
+    factors = torch.empty_like(densities)
+    out = torch.empty((hi - lo, L), dtype=torch.float32, device=features.device)
     if hi > lo:
         check(L_.pigs_aggregate_forward_rows(P, D, L, K, E, lo, hi, _ptr(features), _ptr(transform),
                                              _disp(queries_rows, rows, K), _ptr(keys), _ptr(frequencies), _ptr(dt),

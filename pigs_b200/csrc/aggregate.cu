@@ -1013,6 +1013,11 @@ __global__ void __launch_bounds__(AG_THREADS)
                 const float dw = inv * densities[s] * wgt;
                 dwf = dw * fac;
                 dwe = dw * emb;
+            } else if (s < end) {
+                // skipped neighbour: every slot of the row is written, so the caller's outputs need no zero fill
+                weights[s] = 0.0f;
+                embeddings[s] = 0.0f;
+                factors[s] = 0.0f;
             }
             s_dwe[lane] = dwe;
             s_dwf[lane] = dwf;

@@ -153,6 +153,11 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
                 const float dw = inv * densities[s] * wgt;
                 dwf = dw * fac;
                 dwe = dw * emb;
+            } else if (c0 + gl < n) {
+                // skipped neighbour: every slot of the row is written, so the caller's outputs need no zero fill
+                weights[s] = 0.0f;
+                embeddings[s] = 0.0f;
+                factors[s] = 0.0f;
             }
             const int jl = (int)j;
             // z[lane] += sum_t (dwe_t + dwf_t feat_t[lane]): the first sum does not depend on the channel — one
@@ -225,7 +230,10 @@ __global__ void __launch_bounds__(A16_THREADS, A16_BWD_MINB)
         const int64_t start = (valid && row > 0) ? ranges[row - 1] : 0;
         const int n = valid ? (int)(ranges[row] - start) : 0;
         const int nmax = __reduce_max_sync(0xffffffffu, n);  // over both rows of the warp; lands in a uniform register
-        if (nmax == 0) continue;
+        if (nmax == 0) {
+            if (valid) g_queries[row * 16 + gl] = 0.0f;  // every row of the window is written: no zero fill needed
+            continue;
+        }
         const float q_l = valid ? queries[row * 16 + gl] : 0.0f;  // lane = channel views
         const float g_l = valid ? gout[row * 16 + gl] : 0.0f;
         // st[a] = sum_b T[a][b] g[b]  (lane a), A = sum_a st[a]

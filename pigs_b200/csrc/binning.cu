@@ -394,41 +394,49 @@ __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float*
         __syncthreads();
         for (int r = 0; r < SORT_TILE_ELEMS / 256; r++) {
             const int64_t i = st * SORT_TILE_ELEMS + r * 256 + threadIdx.x;
-            if (i >= N) break;
+            const bool ok = i < N;
+            uint32_t tile = 0xffffffffu;
             float x[D];
-            int t[D];
+            if (ok) {
+                int t[D];
 #pragma unroll
-            for (int d = 0; d < D; d++) {
-                x[d] = samples[i * D + d];
-                const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
-                t[d] = min(gr[d], max(0, q));
-            }
-            uint32_t tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
-            if (k > 1) {
-                // culled mode: the reference tile (alias quirk included) cut k x k; not a real tile -> dump slot
-                const uint32_t rt = tile;
-                tile = (uint32_t)hdr->blocks;
-                if ((int)rt < rblocks) {
-                    const int par[2] = {(int)(rt % (uint32_t)g0), (int)(rt / (uint32_t)g0)};
-                    int f[D];
-#pragma unroll
-                    for (int d = 0; d < D; d++) {
-                        const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), h) - k * par[d];
-                        f[d] = k * par[d] + min(k - 1, max(0, q));
-                    }
-                    tile = D == 2 ? (uint32_t)f[D - 1] * (uint32_t)hdr->grid[0] + (uint32_t)f[0] : (uint32_t)f[0];
+                for (int d = 0; d < D; d++) {
+                    x[d] = samples[i * D + d];
+                    const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), PIGS_TILE_WIDTH);
+                    t[d] = min(gr[d], max(0, q));
                 }
-            }
-            keys[i] = tile;
-            vals[i] = (uint32_t)i;
-            atomicAdd(&s_hist[tile & digit_mask], 1u);
-            float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
+                tile = D == 2 ? (uint32_t)t[D - 1] * (uint32_t)g0 + (uint32_t)t[0] : (uint32_t)t[0];
+                if (k > 1) {
+                    // culled mode: the reference tile (alias quirk included) cut k x k; not a real tile -> dump slot
+                    const uint32_t rt = tile;
+                    tile = (uint32_t)hdr->blocks;
+                    if ((int)rt < rblocks) {
+                        const int par[2] = {(int)(rt % (uint32_t)g0), (int)(rt / (uint32_t)g0)};
+                        int f[D];
 #pragma unroll
-            for (int d = 0; d < D; d++) {
-                const float v = x[d] + 0.0f;  // -0 -> +0 so the integer-ordered atomics below are consistent
-                // the boxes only ever grow, so a stale read can at worst let a redundant atomic through
-                if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
-                if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
+                        for (int d = 0; d < D; d++) {
+                            const int q = (int)__fdiv_rn(__fsub_rn(x[d], mn[d]), h) - k * par[d];
+                            f[d] = k * par[d] + min(k - 1, max(0, q));
+                        }
+                        tile = D == 2 ? (uint32_t)f[D - 1] * (uint32_t)hdr->grid[0] + (uint32_t)f[0] : (uint32_t)f[0];
+                    }
+                }
+                keys[i] = tile;
+                vals[i] = (uint32_t)i;
+            }
+            // one histogram atomic per distinct tile per warp (a 4x4 grid has 16); every lane takes part in the match
+            const uint32_t dg = ok ? (tile & digit_mask) : 0xffffffffu;
+            const uint32_t peers = __match_any_sync(0xffffffffu, dg);
+            if (ok && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&s_hist[dg], (uint32_t)__popc(peers));
+            if (ok) {
+                float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    const float v = x[d] + 0.0f;  // -0 -> +0 so the integer-ordered atomics below are consistent
+                    // the boxes only ever grow, so a stale read can at worst let a redundant atomic through
+                    if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
+                    if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
+                }
             }
         }
         __syncthreads();

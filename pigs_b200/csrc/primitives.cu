@@ -92,6 +92,11 @@ __device__ __forceinline__ void st_desc(unsigned long long* p, unsigned long lon
 // T = uint32_t (tile-touch counts, flags, histograms) or int64_t (neighbour counts).  INCLUSIVE: out[i] = sum in[0..i];
 // else out[i] = sum in[0..i) and, with write_total, out[n] = grand total.  total_out (optional): the grand total as
 // int64 (device), e.g. the word of a header the host reads back.  out may alias in.
+// look-back tiles are twice the size of the small-scan tiles: the chain of predecessors a tile may have to walk (32 per
+// step, one L2 round trip each) is what a mid-sized scan waits on (15 us for 1M elements with 2048-element tiles)
+constexpr int LB_ITEMS = 16;
+constexpr int LB_TILE = SCAN_THREADS * LB_ITEMS;  // 4096
+
 template <typename T, bool INCLUSIVE>
 __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const T* in, T* out, int64_t n,
                                                                      int write_total, unsigned long long* __restrict__ ws,
@@ -105,11 +110,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const T* in
     __syncthreads();
     const int64_t tile = s_tile;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int64_t base = tile * SCAN_TILE + (int64_t)threadIdx.x * SCAN_ITEMS;
-    T v[SCAN_ITEMS];
+    const int64_t base = tile * LB_TILE + (int64_t)threadIdx.x * LB_ITEMS;
+    T v[LB_ITEMS];
     unsigned long long s = 0;
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
+    for (int i = 0; i < LB_ITEMS; i++) {
         v[i] = (base + i < n) ? in[base + i] : T(0);
         s += (unsigned long long)v[i];
     }
@@ -158,12 +163,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_lookback_kernel(const T* in
     __syncthreads();
     unsigned long long run = s_prefix + woff + (inc - s);
 #pragma unroll
-    for (int i = 0; i < SCAN_ITEMS; i++) {
+    for (int i = 0; i < LB_ITEMS; i++) {
         if (INCLUSIVE) run += (unsigned long long)v[i];
         if (base + i < n) out[base + i] = (T)run;
         if (!INCLUSIVE) run += (unsigned long long)v[i];
     }
-    const int64_t ntiles = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const int64_t ntiles = (n + LB_TILE - 1) / LB_TILE;
     if (tile == ntiles - 1 && threadIdx.x == 0) {
         const unsigned long long tot = s_prefix + agg;
         if (write_total) out[n] = (T)tot;
@@ -202,7 +207,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) scan_small(const uint32_t* __res
 
 size_t scan_ws_bytes(int64_t n)
 {
-    int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    int64_t nb = (n + LB_TILE - 1) / LB_TILE;
     return align_up((size_t)(nb + 2) * sizeof(unsigned long long));
 }
 
@@ -219,7 +224,7 @@ int exclusive_scan_u32(const uint32_t* in, uint32_t* out, int64_t n, bool write_
         PIGS_LAUNCH_CHECK();
         return 0;
     }
-    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const int64_t nb = (n + LB_TILE - 1) / LB_TILE;
     PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
     scan_lookback_kernel<uint32_t, false><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, write_total ? 1 : 0,
                                                                                  (unsigned long long*)ws, total_out);
@@ -234,7 +239,7 @@ int exclusive_scan_u64(const unsigned long long* in, unsigned long long* out, in
         if (write_total) PIGS_CHECK(cudaMemsetAsync(out, 0, sizeof(unsigned long long), st));
         return 0;
     }
-    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const int64_t nb = (n + LB_TILE - 1) / LB_TILE;
     PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
     scan_lookback_kernel<unsigned long long, false><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(
         in, out, n, write_total ? 1 : 0, (unsigned long long*)ws, nullptr);
@@ -248,7 +253,7 @@ int inclusive_scan_i64(const int64_t* in, int64_t* out, int64_t n, void* ws, cud
         if (total_out) PIGS_CHECK(cudaMemsetAsync(total_out, 0, sizeof(long long), st));
         return 0;
     }
-    const int64_t nb = (n + SCAN_TILE - 1) / SCAN_TILE;
+    const int64_t nb = (n + LB_TILE - 1) / LB_TILE;
     PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
     scan_lookback_kernel<int64_t, true><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, 0, (unsigned long long*)ws, total_out);
     PIGS_LAUNCH_CHECK();
@@ -268,6 +273,7 @@ constexpr int SORT_ROUNDS = 16;                                // 32-element gro
 constexpr int SORT_WARP_ITEMS = 32 * SORT_ROUNDS;              // 512
 constexpr int SORT_TILE = SORT_WARP_ITEMS * SORT_WARPS;        // 4096
 static_assert(SORT_TILE == SORT_TILE_ELEMS, "key-producing kernels histogram whole sort tiles");
+static_assert(SORT_THREADS == 256, "radix_scatter phase 2: one thread per digit (RADIX below is 256)");
 constexpr int RADIX = 256;
 
 __global__ void __launch_bounds__(SORT_THREADS) radix_hist(const uint32_t* __restrict__ keys, int64_t n, int shift,
@@ -277,10 +283,16 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_hist(const uint32_t* __res
     for (int i = threadIdx.x; i < RADIX; i += SORT_THREADS) hist[i] = 0;
     __syncthreads();
     const int64_t base = (int64_t)blockIdx.x * SORT_TILE;
+    // tile keys have a handful of distinct digits: one shared-memory atomic per distinct digit per warp (match_any)
+    // instead of 32 colliding ones
+    const int lane = threadIdx.x & 31;
 #pragma unroll 4
     for (int i = 0; i < SORT_TILE / SORT_THREADS; i++) {
         int64_t idx = base + i * SORT_THREADS + threadIdx.x;
-        if (idx < n) atomicAdd(&hist[(keys[idx] >> shift) & mask], 1u);
+        const bool ok = idx < n;
+        const uint32_t d = ok ? ((keys[idx] >> shift) & mask) : RADIX;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        if (ok && lane == (__ffs(peers) - 1)) atomicAdd(&hist[d], (uint32_t)__popc(peers));
     }
     __syncthreads();
     for (int i = threadIdx.x; i < RADIX; i += SORT_THREADS) ghist[(int64_t)i * nb + blockIdx.x] = hist[i];
@@ -293,7 +305,14 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
                                                               uint32_t* __restrict__ vals_out, uint2* __restrict__ ranges,
                                                               int max_slot)
 {
-    __shared__ uint32_t wcount[SORT_WARPS][RADIX];  // per-warp digit counts, then per-warp running offsets
+    // Ranked scatter THROUGH shared memory: the tile's pairs are first placed in digit order (stable) in shared memory,
+    // then copied out so that consecutive threads write consecutive addresses of the same digit's output run.  With the
+    // few distinct digits of a tile key (16 tiles) a direct scatter writes 8 useful bytes per 32-byte sector and the L2
+    // store path, not HBM, sets the pace (43 us for 4M pairs).
+    __shared__ uint32_t wcount[SORT_WARPS][RADIX];  // per-warp digit counts, then per-warp running LOCAL offsets
+    __shared__ uint32_t dstart[RADIX + 1];          // local start of every digit's run inside the tile
+    __shared__ uint32_t dglob[RADIX];               // global base of (digit, this CTA)
+    __shared__ uint32_t s_k[SORT_TILE], s_v[SORT_TILE];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     if (ranges && blockIdx.x == 0) {
         // single-pass sort whose digit IS the tile key: the scanned histogram holds every tile's range
@@ -307,7 +326,9 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
     for (int i = threadIdx.x; i < SORT_WARPS * RADIX; i += SORT_THREADS) (&wcount[0][0])[i] = 0;
     __syncthreads();
 
-    const int64_t wbase = (int64_t)blockIdx.x * SORT_TILE + (int64_t)w * SORT_WARP_ITEMS;
+    const int64_t tbase = (int64_t)blockIdx.x * SORT_TILE;
+    const int64_t wbase = tbase + (int64_t)w * SORT_WARP_ITEMS;
+    const int cnt = (int)((n - tbase) < (int64_t)SORT_TILE ? (n - tbase) : (int64_t)SORT_TILE);
     uint32_t k[SORT_ROUNDS], v[SORT_ROUNDS];
     // phase 1: load + per-warp digit counts
 #pragma unroll
@@ -322,18 +343,40 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
         __syncwarp();
     }
     __syncthreads();
-    // phase 2: per digit, exclusive scan over warps, plus the global base of (digit, this CTA)
-    for (int d = threadIdx.x; d < RADIX; d += SORT_THREADS) {
-        uint32_t run = gbase[(int64_t)d * nb + blockIdx.x];
+    // phase 2: digit totals -> local digit starts; per digit an exclusive scan over the warps
+    {
+        const int d = threadIdx.x;  // SORT_THREADS == RADIX
+        uint32_t tot = 0;
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ww++) tot += wcount[ww][d];
+        // exclusive scan of tot over the 256 digits (warp scan + warp totals)
+        uint32_t inc = tot;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+            if (lane >= o) inc += t;
+        }
+        if (lane == 31) dstart[RADIX - SORT_WARPS + w] = inc;  // scratch: warp totals parked in the tail (rewritten below)
+        __syncthreads();
+        uint32_t woff = 0;
+#pragma unroll
+        for (int ww = 0; ww < SORT_WARPS; ww++)
+            if (ww < w) woff += dstart[RADIX - SORT_WARPS + ww];
+        __syncthreads();
+        const uint32_t start = woff + inc - tot;
+        dstart[d] = start;
+        if (d == RADIX - 1) dstart[RADIX] = start + tot;
+        dglob[d] = gbase[(int64_t)d * nb + blockIdx.x];
+        uint32_t run = start;
 #pragma unroll
         for (int ww = 0; ww < SORT_WARPS; ww++) {
-            uint32_t c = wcount[ww][d];
+            const uint32_t c = wcount[ww][d];
             wcount[ww][d] = run;
             run += c;
         }
     }
     __syncthreads();
-    // phase 3: in-order walk, stable scatter
+    // phase 3: in-order walk, stable placement in shared memory
 #pragma unroll
     for (int r = 0; r < SORT_ROUNDS; r++) {
         const int64_t idx = wbase + r * 32 + lane;
@@ -343,12 +386,21 @@ __global__ void __launch_bounds__(SORT_THREADS) radix_scatter(const uint32_t* __
         if (ok) {
             const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
             const uint32_t pos = wcount[w][d] + rank;
-            keys_out[pos] = k[r];
-            vals_out[pos] = v[r];
+            s_k[pos] = k[r];
+            s_v[pos] = v[r];
         }
         __syncwarp();
         if (ok && lane == (__ffs(peers) - 1)) wcount[w][d] += __popc(peers);
         __syncwarp();
+    }
+    __syncthreads();
+    // phase 4: coalesced copy-out — slot i of the tile belongs to digit d = its key's digit, at offset i - dstart[d]
+    for (int i = threadIdx.x; i < cnt; i += SORT_THREADS) {
+        const uint32_t kk = s_k[i];
+        const uint32_t d = (kk >> shift) & mask;
+        const uint32_t pos = dglob[d] + ((uint32_t)i - dstart[d]);
+        keys_out[pos] = kk;
+        vals_out[pos] = s_v[i];
     }
 }
 

@@ -288,8 +288,9 @@ std::tuple<Tensor, Tensor, Tensor, Tensor> aggregate_neighbors(const Tensor& fea
     Tensor indices = indices_.contiguous(), ranges = ranges_.contiguous();
     const int64_t P = features.size(0);
     const int D = (int)dists.size(-1), L = (int)features.size(-1), K = (int)queries.size(-1), E = (int)(dt.size(-1) / 2);
-    Tensor weights = torch::zeros_like(densities), embeddings = torch::zeros_like(densities), factors = torch::zeros_like(densities);
-    Tensor out = torch::zeros({P, (int64_t)L}, features.options());
+    // no zero fills: the kernels write every slot of every row (skipped neighbours as zeros) and every output row
+    Tensor weights = torch::empty_like(densities), embeddings = torch::empty_like(densities), factors = torch::empty_like(densities);
+    Tensor out = torch::empty({P, (int64_t)L}, features.options());
     if (P > 0)
         check(pigs_aggregate_forward(P, D, L, K, E, fp(features), fp(transform), fp(queries), fp(keys), fp(freqs), fp(dt),
                                      indices.data_ptr<int64_t>(), ranges.data_ptr<int64_t>(), fp(dists), fp(densities), fp(inv_total),

@@ -79,7 +79,10 @@ def guarded(monkeypatch):
     from pigs_b200 import _C
     g = _Guarded(torch)
     monkeypatch.setattr(_C, "torch", g)
-    return g
+    _C.use_binding("ctypes")  # the binding whose allocations go through the guarded proxy
+    yield g
+    if _C._ext is not None:
+        _C.use_binding("compiled")
 
 
 @pytest.mark.parametrize("name", ["synth2d", "torus", "wide", "edge_aniso", "synth1d", "synth2d_c2", "line1d"])

@@ -27,6 +27,12 @@ KEYS = {
     "sm__throughput.avg.pct_of_peak_sustained_elapsed": "sm_throughput_pct",
     "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed": "dram_throughput_pct",
     "smsp__cycles_active.avg": "smsp_cycles_active",
+    "l1tex__t_sector_hit_rate.pct": "l1_hit_rate_pct",
+    "lts__t_sector_hit_rate.pct": "l2_hit_rate_pct",
+    "lts__t_sectors.sum": "l2_sectors",
+    "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum": "l1_global_load_sectors",
+    "launch__occupancy_limit_registers": "occupancy_limit_registers",
+    "smsp__inst_executed_per_warp.ratio": "inst_per_warp",
 }
 STALLS = "smsp__pcsamp_warps_issue_stalled_"
 
@@ -67,7 +73,14 @@ def main():
         tot = sum(st.values()) or 1
         k["warp_state_samples_pct"] = {a: round(100.0 * b / tot, 1) for a, b in sorted(st.items(), key=lambda x: -x[1])[:8]}
         res.append(k)
-    json.dump({"report": rep, "note": "ncu --set full --clock-control none; per-launch values; durations under the "
+    import hashlib
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    hh = hashlib.sha1()
+    for name in ("eval_bwd.cu", "eval_fwd.cu", "eval_common.cuh", "common.cuh", "pack.cu"):  # = bench.py EVAL_SOURCES
+        with open(os.path.join(root, "pigs_b200", "csrc", name), "rb") as f:
+            hh.update(f.read())
+    json.dump({"report": rep, "source_sha": hh.hexdigest()[:16], "note": "ncu --set full --clock-control none; per-launch values; durations under the "
                "profiler are serialised replays, not bench numbers", "kernels": res}, open(out, "w"), indent=1)
     for k in res:
         print(k["kernel"][:60], k.get("duration"), k.get("duration_unit"), "issue", k.get("issue_slots_busy_per_cycle"),
