@@ -67,8 +67,10 @@ def regular_csr(means, k):
 def main():
     torch.cuda.set_device(0)
     out = {"gpu": torch.cuda.get_device_name(0), "peak_GBs": peak_gbs()[0], "peak_source": peak_gbs()[1], "rows": []}
+    only = [a.split("=", 1)[1] for a in sys.argv if a.startswith("--only=")]
+    only = only[0] if only else None  # --only=agg | --only=binning: just those rows (variant sweeps)
     P, N = 1_000_000, 4_000_000
-    rec = synthetic(P, N, seed=0)
+    rec = synthetic(P, N if only != "agg" else 16, seed=0)
     d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
     s = GaussianSampler(False)
 
@@ -76,10 +78,20 @@ def main():
     ms = timed(lambda: s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"]))
     R = s.num_rendered
     nbytes = 28 * P + (8 + 16) * R + 4 * R + (8 + 8) * N + (4 + 16) * N + 4 * N
-    out["rows"].append(row("preprocess (tile binning, ~30 launches, one D2H header readback)", ms, nbytes,
+    out["rows"].append(row("preprocess (tile binning + per-preprocess class staging, 14 launches, one D2H header readback)", ms, nbytes,
                            "28 B/Gaussian + 28 B/instance (emit 8, hist 4, scatter 16) + 40 B/sample (key 16, hist 4, scatter 16, ranges 4); "
                            "P=%d R=%d N=%d" % (P, R, N)))
 
+    if only == "binning":
+        print(json.dumps(out, indent=1))
+        return
+    if only != "agg":
+        rows_other(out, P, N)
+    rows_agg(out, rec, d, s, P)
+    print(json.dumps(out, indent=1))
+
+
+def rows_other(out, P, N):
     # ---- covariance construction ----
     sc = torch.rand(P, 2, device="cuda") * 1e-3 + 1e-4
     tr = torch.randn(P, 1, device="cuda") * 0.3
@@ -108,6 +120,9 @@ def main():
     out["rows"].append(row("vorticity_forward_kernel (uxxx -> wxx)", ms, 80 * N, "4 groups per sample: 16 B read + 4 B written each"))
     del u1, ux1, lap1, ut1, u2, ux2, wx2, wxx2, wt2, uxxx2
 
+
+
+def rows_agg(out, rec, d, s, P):
     # ---- aggregation on a 16-regular CSR (C5 i): L = K = 16, E = 25, nF = 6 ----
     k = 16
     idx, rng = regular_csr(rec["means"], k)
@@ -125,7 +140,7 @@ def main():
     ap = {kk: torch.from_numpy(v).cuda() for kk, v in agg_params(P, 16, 16, 25, 2, seed=100).items()}
     a = (ap["features"], ap["transform"], ap["queries"], ap["keys"], ap["frequencies"], ap["distance_transform"])
     ms = timed(lambda: _C.aggregate_neighbors(*a, indices, ranges, dists, dens, inv_total, False))
-    out["rows"].append(row("agg_forward_kernel (+ zero fills of its 4 outputs)", ms, 160 * M + 140 * P,
+    out["rows"].append(row("agg_forward_kernel (outputs allocated, not filled)", ms, 160 * M + 140 * P,
                            "160 B/slot (idx 8, dist 8, density 4, feature row 64, key row 64, 3 saved 12) + 140 B/Gaussian; M=%d" % M))
     w, e, f, o = _C.aggregate_neighbors(*a, indices, ranges, dists, dens, inv_total, False)
     g = torch.randn_like(o)
@@ -150,7 +165,6 @@ def main():
         Ms = ind.numel()
         out["rows"].append(row("preprocess_aggregate (grid neighbour search + CSR write-out; best warm run of 2)", ms, 20 * Ms,
                                "CSR write-out 20 B/slot (idx 8, dist 8, density 4); M=%d slots = %.0f per Gaussian" % (Ms, Ms / P)))
-    print(json.dumps(out, indent=1))
 
 
 if __name__ == "__main__":
