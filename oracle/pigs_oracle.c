@@ -8,12 +8,16 @@
  * cpu_baseline / --impl reference legs may load this file.  The product path
  * never links, imports or calls it.
  *
- * Parity status: pinned against (i) the dense pure-PyTorch reference
- * (gaussians.py:48-116) on fixtures where the tiled pair set equals the dense
- * one (tests/golden/ fixtures, generated by tests/golden/make_golden.py from
- * /root/reference), and (ii) the unmodified reference CUDA extension compiled
- * by oracle/build_ref.sh and run on the B200 box (tests/test_ref_cuda.py,
- * golden dumps under tests/golden/refcuda_*.npz).
+ * Parity status: PINNED.  (i) Golden dumps of the unmodified reference CUDA
+ * extension (compiled by oracle/build_ref.sh, run on a B200 box by
+ * tests/golden/make_refcuda_golden.py and make_refcuda_agg_golden.py ->
+ * tests/golden/refcuda_*.npz, 18 recipes) are held in tests/test_oracle_cpu.py:
+ * bins and neighbour lists bit for bit, values / gradients to 1e-5.  (ii) The
+ * caller-side pieces are pinned to vectors produced by importing the real
+ * gaussians.py / model_pn.py on the CPU (tests/golden/make_dense_golden.py,
+ * make_covariance_golden.py, make_pde_golden.py, make_densify_golden.py).
+ * (iii) On the GPU box the same extension is compared LIVE with the product
+ * in tests/test_gpu_vs_reference.py.
  *
  * Every function cites the reference file:line it follows
  * (paths relative to /root/reference/diff-gaussian-sampling unless noted).

@@ -14,6 +14,8 @@
 // DRAM traffic against 2.7 GB algorithmic at P = 1M, 16 neighbours).
 #include "common.cuh"
 
+#include <stdlib.h>
+
 #ifndef A16_VEC_RED
 #define A16_VEC_RED 1
 #endif
@@ -28,6 +30,9 @@ constexpr int A16_THREADS = 256;
 // 1.82 ms at 2 (128 registers + 112 B), slower again at 3
 #ifndef A16_FWD_MINB
 #define A16_FWD_MINB 6
+#endif
+#ifndef A16_HOIST
+#define A16_HOIST 0
 #endif
 #ifndef A16_BWD_MINB
 #define A16_BWD_MINB 2
@@ -124,6 +129,19 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
             const int64_t s = start + c0 + gl;
             const int64_t j = (c0 + gl < n) ? indices[s] : -1;
             float dwe = 0.0f, dwf = 0.0f;
+#if A16_HOIST
+            // the 16 feature-row gathers of the second phase depend on the indices only: issue them BEFORE the ~250
+            // instructions of the per-slot phase, whose arithmetic then covers their latency
+            float fv[16];
+            {
+                const int jl0 = (int)j;
+#pragma unroll
+                for (int t = 0; t < 16; t++) {
+                    const int jj = __shfl_sync(0xffffffffu, jl0, t, 16);
+                    fv[t] = jj >= 0 ? features[(size_t)jj * 16 + gl] : 0.0f;
+                }
+            }
+#endif
             if (j >= 0) {
                 float key[16];
                 load16(keys + j * 16, key);
@@ -166,12 +184,18 @@ __global__ void __launch_bounds__(A16_THREADS, A16_FWD_MINB)
 #pragma unroll
             for (int o = 8; o > 0; o >>= 1) se += __shfl_xor_sync(0xffffffffu, se, o, 16);
             z += se;
+#if A16_HOIST
+            (void)jl;
+#pragma unroll
+            for (int t = 0; t < 16; t++) z = fmaf(__shfl_sync(0xffffffffu, dwf, t, 16), fv[t], z);  // skipped slots: dwf = fv = 0
+#else
 #pragma unroll
             for (int t = 0; t < 16; t++) {
                 const int jj = __shfl_sync(0xffffffffu, jl, t, 16);
                 const float a1 = __shfl_sync(0xffffffffu, dwf, t, 16);
                 if (jj >= 0) z = fmaf(a1, features[(size_t)jj * 16 + gl], z);
             }
+#endif
         }
         // out_i = z . T  (the reference applies T inside the neighbour loop, aggregate_neighbors.cu:201-206)
         float acc = 0.0f;
@@ -394,7 +418,15 @@ int launch_aggregate16_forward(int64_t row_lo, int64_t P, int D, int L, int K, i
     if ((reinterpret_cast<uintptr_t>(features) & 15) != 0) return 0;  // 16-byte row loads
     int64_t grid = (P - row_lo + 15) / 16;  // 16 rows per CTA (8 warps x 2)
     if (grid < 1) grid = 1;
-    const int64_t cap = (int64_t)num_sms() * 16;
+    // whole waves of resident CTAs (A16_FWD_MINB per SM), so the grid-stride loop ends everywhere at once: 16 CTAs per SM
+    // were 2.67 waves, the last one two-thirds full
+    static int waves = 0;
+    if (!waves) {
+        const char* e = getenv("PIGS_A16_FWD_WAVES");  // tuning hook
+        waves = e ? atoi(e) : 1;
+        if (waves < 1) waves = 1;
+    }
+    const int64_t cap = (int64_t)num_sms() * A16_FWD_MINB * waves;
     if (grid > cap) grid = cap;
     if (D == 2)
         agg_forward16_kernel<2, 6><<<(unsigned)grid, A16_THREADS, 0, st>>>(row_lo, P, features, transform, queries, keys, freqs, dt,

@@ -90,3 +90,49 @@ def test_tile_grid_arithmetic_matches_torch_cuda():
         cov = torch.tensor([[1e-4]], device="cuda")
         s.preprocess(means, torch.ones(1, 1, device="cuda"), cov, 1.0 / cov, samples)
         assert s.ranges.numel() // 8 - 1 == want, span
+
+
+@pytest.mark.slow
+@pytest.mark.timeout(900)
+def test_reference_extension_at_c2_size():
+    """BASELINE config C2 (100K Gaussians x 1M points) against the LIVE reference extension itself — bins bit for bit over
+    the whole input, the three forward functions and one backward to 1e-5.  The reference needs ~35 s for these passes
+    (one CTA per tile), so the test only runs with PIGS_RUN_SLOW=1 (log: profiles/r03*_ref_c2_parity.log)."""
+    import ctypes
+    import os
+    import torch
+    from pigs_b200 import GaussianSampler, _C
+    from tests.fixtures import synthetic
+    if os.environ.get("PIGS_RUN_SLOW", "0") in ("", "0"):
+        pytest.skip("set PIGS_RUN_SLOW=1 (the reference extension takes ~35 s at this size)")
+    if not refcuda.available():
+        pytest.skip("oracle/_ref/_C.so not built")
+    # the reference allocates with device-side new[] in every thread (forward.cu:63-64, sampler_impl.cu:166)
+    ctypes.CDLL("libcudart.so.12").cudaDeviceSetLimit(2, ctypes.c_size_t(8 << 30))
+    P, N = 100_000, 1_000_000
+    rec = synthetic(P, N, seed=0)
+    d = to_dev(rec)
+    ref = refcuda.RefSampler(False)
+    ref.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    ours = GaussianSampler(False, fused=False)
+    ours.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    assert ours.num_rendered == ref.num_rendered
+    assert torch.equal(ours.radii.view(torch.int32), ref.radii.view(torch.int32))
+    assert torch.equal(ours.ranges, ref.ranges) and torch.equal(ours.sample_ranges, ref.sample_ranges)
+    pl, pt, sl = _C.point_lists(ours.num_rendered, ours.binning_buffer, ours.sample_binning_buffer, N)
+    assert torch.equal(pl, ref.point_list()) and torch.equal(sl, ref.sample_point_list())
+    outs = ours.sample_fused(7)
+    for fn in range(3):
+        want = ref.forward(fn)
+        e = float((outs[fn] - want).abs().max() / want.abs().max())
+        print("C2 forward fn=%d max|a-b|/max|b| = %.3g" % (fn, e))
+        assert e <= TOL, (fn, e)
+    g = torch.randn(N, 2, 2, 1, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5))
+    wm, wv, wc = ref.backward(2, g)
+    nr, bb, sbb, rg, srg = ours._sample_state
+    gm, gv, gc = _C.sample_backward(4, d["means"], d["values"], d["conics"], d["samples"], nr, [None, None, g, None], bb, sbb,
+                                    rg, srg, False)
+    for a, b, nm in ((gm, wm, "means"), (gv, wv, "values"), (gc, wc, "conics")):
+        e = float((a.reshape(-1) - b.reshape(-1)).abs().max() / b.abs().max())
+        print("C2 backward fn=2 d%s max|a-b|/max|b| = %.3g" % (nm, e))
+        assert e <= TOL, (nm, e)
