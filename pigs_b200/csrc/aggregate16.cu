@@ -418,15 +418,16 @@ int launch_aggregate16_forward(int64_t row_lo, int64_t P, int D, int L, int K, i
     if ((reinterpret_cast<uintptr_t>(features) & 15) != 0) return 0;  // 16-byte row loads
     int64_t grid = (P - row_lo + 15) / 16;  // 16 rows per CTA (8 warps x 2)
     if (grid < 1) grid = 1;
-    // whole waves of resident CTAs (A16_FWD_MINB per SM), so the grid-stride loop ends everywhere at once: 16 CTAs per SM
-    // were 2.67 waves, the last one two-thirds full
-    static int waves = 0;
-    if (!waves) {
-        const char* e = getenv("PIGS_A16_FWD_WAVES");  // tuning hook
-        waves = e ? atoi(e) : 1;
-        if (waves < 1) waves = 1;
+    // CTAs per SM the grid-stride loop is cut into.  Measured on B200 at P = 1M x 16 neighbours (profiles/r03h_*): MORE,
+    // smaller CTAs are faster (one resident wave of 6 per SM 0.597 ms, 12: 0.575, 16: 0.558, 32: 0.555, 64: 0.551, 128: 0.562, one per 16 rows: 0.618) — the hardware's
+    // CTA scheduler balances the SMs better than equal shares of rows do
+    static int per_sm = 0;
+    if (!per_sm) {
+        const char* e = getenv("PIGS_A16_FWD_CTAS_PER_SM");  // tuning hook
+        per_sm = e ? atoi(e) : 64;
+        if (per_sm < 1) per_sm = 64;
     }
-    const int64_t cap = (int64_t)num_sms() * A16_FWD_MINB * waves;
+    const int64_t cap = (int64_t)num_sms() * per_sm;
     if (grid > cap) grid = cap;
     if (D == 2)
         agg_forward16_kernel<2, 6><<<(unsigned)grid, A16_THREADS, 0, st>>>(row_lo, P, features, transform, queries, keys, freqs, dt,

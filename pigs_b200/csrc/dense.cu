@@ -122,6 +122,132 @@ __global__ void __launch_bounds__(DN_FWD_THREADS)
     }
 }
 
+// ---- 2-D, one channel, large N: the tiled forward kernel's recipe (eval_fwd.cu) on the dense pair set ----------------
+// EIGHT samples per thread as four register pairs; every Gaussian is staged ONCE per CTA as three float4
+// {mu, Ks = kappa K (4 entries, not assumed symmetric), Ms = kappa^2 K, v} with kappa = -1/2 log2 e folded in, so that
+// log2(alpha) = X . (Ks X) needs no scaling multiply and the record costs 3 broadcast LDS.128 per 8 pairs (the scalar
+// kernel above: 7 LDS.32 per 4 pairs, LSU pipe at 40 % next to the FMAs); geometry written op-major in packed FP32x2
+// over sample pairs with the Gaussian's parameters as scalar-broadcast operands, accumulation sample-major with the
+// pair's weight in one operand slot.  19 FP32 lane-ops + 1 ex2 per pair for u + grad u + the four Hessian entries
+// (H10 is carried as H01 plus the sum of w (Ms01 - Ms10), which vanishes for symmetric conics).
+constexpr int DN2_KS = 8, DN2_REC4 = 3;
+static_assert(DN_BATCH == DN_FWD_THREADS, "dense_fwd2_kernel stages one Gaussian per thread");
+static int g_dense_ks = 0, g_dense_kg = 0;  // pigs_set_dense_slots: 0 = chosen from the problem size
+
+__global__ void __launch_bounds__(DN_FWD_THREADS, 2)
+    dense_fwd2_kernel(unsigned mask, int64_t n, int64_t N, int64_t per_chunk, const float* __restrict__ means,
+                      const float* __restrict__ conics, const float* __restrict__ values, const float* __restrict__ samples,
+                      float* __restrict__ out_u, float* __restrict__ out_ux, float* __restrict__ out_uxx)
+{
+    constexpr int KS = DN2_KS, HP = KS / 2;
+    __shared__ float4 rec[DN_BATCH * DN2_REC4];
+    int64_t sidx[KS];
+    f32x2 xp0[HP], xp1[HP];
+    float acc[KS][7];
+    {
+        float x0[KS], x1[KS];
+#pragma unroll
+        for (int k = 0; k < KS; k++) {
+            sidx[k] = ((int64_t)blockIdx.x * KS + k) * DN_FWD_THREADS + threadIdx.x;
+            x0[k] = sidx[k] < N ? samples[sidx[k] * 2] : 0.0f;
+            x1[k] = sidx[k] < N ? samples[sidx[k] * 2 + 1] : 0.0f;
+#pragma unroll
+            for (int a = 0; a < 7; a++) acc[k][a] = 0.0f;
+        }
+#pragma unroll
+        for (int p = 0; p < HP; p++) {
+            xp0[p] = pk2(x0[2 * p], x0[2 * p + 1]);
+            xp1[p] = pk2(x1[2 * p], x1[2 * p + 1]);
+        }
+    }
+    const int64_t g0 = (int64_t)blockIdx.y * per_chunk, g1 = min(n, g0 + per_chunk);
+    for (int64_t b = g0; b < g1; b += DN_BATCH) {
+        const int nb = (int)min((int64_t)DN_BATCH, g1 - b);
+        __syncthreads();
+        if ((int)threadIdx.x < nb) {  // DN_BATCH == DN_FWD_THREADS: one Gaussian per thread
+            const int64_t g = b + threadIdx.x;
+            const float k00 = conics[g * 4], k01 = conics[g * 4 + 1], k10 = conics[g * 4 + 2], k11 = conics[g * 4 + 3];
+            const float s00 = __fmul_rn(DN_KH, k00), s01 = __fmul_rn(DN_KH, k01), s10 = __fmul_rn(DN_KH, k10),
+                        s11 = __fmul_rn(DN_KH, k11);
+            rec[threadIdx.x * DN2_REC4] = make_float4(means[g * 2], means[g * 2 + 1], s00, s01);
+            rec[threadIdx.x * DN2_REC4 + 1] = make_float4(s10, s11, __fmul_rn(DN_KH, s00), __fmul_rn(DN_KH, s01));
+            // third slot: Ms01 - Ms10 (zero for symmetric conics): H10 = H01 + sum w (Ms01 - Ms10) saves a factor per pair
+            const float m01 = __fmul_rn(DN_KH, s01), m10 = __fmul_rn(DN_KH, s10);
+            rec[threadIdx.x * DN2_REC4 + 2] = make_float4(__fsub_rn(m01, m10), __fmul_rn(DN_KH, s11), values[g], 0.0f);
+        }
+        __syncthreads();
+#pragma unroll 1
+        for (int g = 0; g < nb; g++) {
+            const float4 r0 = rec[g * DN2_REC4], r1 = rec[g * DN2_REC4 + 1], r2 = rec[g * DN2_REC4 + 2];
+            // x = sample - mean (gaussians.py:50), a' = Ks x, e = x . a' = log2(alpha)
+            f32x2 X0[HP], X1[HP], A0[HP], A1[HP], E[HP];
+#pragma unroll
+            for (int p = 0; p < HP; p++) X0[p] = add2(xp0[p], bc2(-r0.x));
+#pragma unroll
+            for (int p = 0; p < HP; p++) X1[p] = add2(xp1[p], bc2(-r0.y));
+#pragma unroll
+            for (int p = 0; p < HP; p++) A0[p] = mul2(bc2(r0.z), X0[p]);
+#pragma unroll
+            for (int p = 0; p < HP; p++) A1[p] = mul2(bc2(r1.x), X0[p]);
+#pragma unroll
+            for (int p = 0; p < HP; p++) A0[p] = fma2(bc2(r0.w), X1[p], A0[p]);
+#pragma unroll
+            for (int p = 0; p < HP; p++) A1[p] = fma2(bc2(r1.y), X1[p], A1[p]);
+#pragma unroll
+            for (int p = 0; p < HP; p++) E[p] = mul2(A0[p], X0[p]);
+#pragma unroll
+            for (int p = 0; p < HP; p++) E[p] = fma2(A1[p], X1[p], E[p]);
+            float a0[KS], a1[KS], al[KS];
+#pragma unroll
+            for (int p = 0; p < HP; p++) {
+                upk2(A0[p], a0[2 * p], a0[2 * p + 1]);
+                upk2(A1[p], a1[2 * p], a1[2 * p + 1]);
+                upk2(E[p], al[2 * p], al[2 * p + 1]);
+            }
+#pragma unroll
+            for (int k = 0; k < KS; k++) al[k] = dn_ex2(al[k]);
+#pragma unroll
+            for (int k = 0; k < KS; k++) {
+                const float w = r2.z * al[k];
+                const float f00 = fmaf(a0[k], a0[k], -r1.z), f01 = fmaf(a0[k], a1[k], -r1.w);
+                const float f11 = fmaf(a1[k], a1[k], -r2.y);
+                acc[k][0] += w;
+                acc[k][1] = fmaf(w, a0[k], acc[k][1]);
+                acc[k][2] = fmaf(w, a1[k], acc[k][2]);
+                acc[k][3] = fmaf(w, f00, acc[k][3]);
+                acc[k][4] = fmaf(w, f01, acc[k][4]);
+                acc[k][5] = fmaf(w, r2.x, acc[k][5]);  // sum w (Ms01 - Ms10)
+                acc[k][6] = fmaf(w, f11, acc[k][6]);
+            }
+        }
+    }
+    const bool add = gridDim.y > 1;
+    auto put = [add](float* p, float v) {
+        if (add)
+            atomicAdd(p, v);
+        else
+            *p = v;
+    };
+    // undo the kappa scaling: grad u = -(1/kappa) sum w a', Hessian = (1/kappa^2) sum w (a' a'^T - Ms)
+    constexpr float IK1 = -1.0f / DN_KH, IK2 = 1.0f / (DN_KH * DN_KH);
+#pragma unroll
+    for (int k = 0; k < KS; k++) {
+        const int64_t s = sidx[k];
+        if (s >= N) continue;
+        if (mask & PIGS_FN_VALUE) put(out_u + s, acc[k][0]);
+        if (mask & PIGS_FN_DERIV) {
+            put(out_ux + s * 2, IK1 * acc[k][1]);
+            put(out_ux + s * 2 + 1, IK1 * acc[k][2]);
+        }
+        if (mask & PIGS_FN_HESS) {
+            put(out_uxx + s * 4, IK2 * acc[k][3]);
+            put(out_uxx + s * 4 + 1, IK2 * acc[k][4]);
+            put(out_uxx + s * 4 + 2, IK2 * (acc[k][4] + acc[k][5]));
+            put(out_uxx + s * 4 + 3, IK2 * acc[k][6]);
+        }
+    }
+}
+
 // per pair, with S_c = dL/dw_c (w_c = alpha v_c):
 //   S_c   = g_c - sum_i gx_ic a_i + sum_ij gH_ijc (a_i a_j - K_ij)
 //   dv_c += alpha S_c ;  dq = -1/2 alpha sum_c v_c S_c
@@ -262,7 +388,6 @@ __global__ void __launch_bounds__(DN_BWD_THREADS)
     }
 }
 
-static int g_dense_ks = 0, g_dense_kg = 0;  // pigs_set_dense_slots: 0 = chosen from the problem size
 
 // chunks of the streamed operand so that the grid has ~4 CTAs per SM even for small stationary counts
 static int64_t dn_chunks(int64_t stationary_blocks, int64_t streamed, int batch)
@@ -279,9 +404,11 @@ template <int D>
 static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means, const float* conics, const float* values,
                   const float* samples, float* u, float* ux, float* uxx, cudaStream_t st)
 {
-    // samples per thread: 4 for one channel, 2 for two, 1 beyond (register budget); one where N is small anyway
+    // samples per thread: 8 (packed kernel) for 2-D one-channel problems with enough samples, else 4 for one channel, 2 for
+    // two, 1 beyond (register budget); one where N is small anyway
     int ks = (N < (int64_t)DN_FWD_THREADS * 4 * num_sms()) ? 1 : (C == 1 ? 4 : (C == 2 ? 2 : 1));
-    if (g_dense_ks > 0) ks = g_dense_ks == 1 ? 1 : (C == 1 ? 4 : (C == 2 ? 2 : 1));
+    if (D == 2 && C == 1 && N >= (int64_t)DN_FWD_THREADS * DN2_KS * num_sms()) ks = DN2_KS;
+    if (g_dense_ks > 0) ks = g_dense_ks == 1 ? 1 : (g_dense_ks >= DN2_KS && D == 2 && C == 1 ? DN2_KS : (C == 1 ? 4 : (C == 2 ? 2 : 1)));
     const int64_t nx = (N + (int64_t)DN_FWD_THREADS * ks - 1) / ((int64_t)DN_FWD_THREADS * ks);
     const int64_t ny = dn_chunks(nx, n, DN_BATCH);
     const int64_t per = ((n + ny - 1) / ny + DN_BATCH - 1) / DN_BATCH * DN_BATCH;
@@ -293,7 +420,9 @@ static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
     }
 #define DN_F(CC, KK)                                                                                                    \
     dense_fwd_kernel<D, CC, KK><<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx)
-    if (C == 1 && ks == 4)
+    if (D == 2 && C == 1 && ks == DN2_KS)
+        dense_fwd2_kernel<<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx);
+    else if (C == 1 && ks == 4)
         DN_F(1, 4);
     else if (C == 1)
         DN_F(1, 1);

@@ -146,6 +146,87 @@ __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, cons
     }
 }
 
+#ifndef PIGS_FWD_PACKED_ACC
+#define PIGS_FWD_PACKED_ACC 0
+#endif
+// Fully packed variant (2-D, one channel, no third derivative): geometry AND accumulation on sample PAIRS, accumulators
+// kept as register pairs.  Every FFMA2 of the accumulation phase reads three distinct pairs (w, factor, accumulator) =
+// 3 issue cycles per 2 FMAs unless w sits in the operand-reuse cache (tools/mb_issue.cu) — tools/sass_issue_model.py
+// scores the loop ptxas produces; see DESIGN.md §4 for the comparison with the scalar accumulation.
+template <unsigned MASK, int MODE, int KS>
+__device__ __forceinline__ void fwd_gaussian_pairs(const GaussFwd<2, 1>& g, const f32x2 (&xp)[2][(KS + 1) / 2],
+                                                   f32x2 (&accp)[KS / 2][nacc(2, MASK)])
+{
+    constexpr int HP = KS / 2;
+    f32x2 X0[HP], X1[HP], A0[HP], A1[HP], E[HP], W[HP];
+#pragma unroll
+    for (int p = 0; p < HP; p++) X0[p] = add2(bc2(g.m[0]), neg2(xp[0][p]));
+#pragma unroll
+    for (int p = 0; p < HP; p++) X1[p] = add2(bc2(g.m[1]), neg2(xp[1][p]));
+    if constexpr (MODE == EV_SHIFT) {
+#pragma unroll
+        for (int p = 0; p < HP; p++) X0[p] = add2(X0[p], bc2(g.sh[0]));
+#pragma unroll
+        for (int p = 0; p < HP; p++) X1[p] = add2(X1[p], bc2(g.sh[1]));
+    }
+    if constexpr (MODE == EV_GENERAL) {
+#pragma unroll
+        for (int p = 0; p < HP; p++) {
+            float lo, hi;
+            upk2(X0[p], lo, hi);
+            X0[p] = pk2(torus_wrap(lo), torus_wrap(hi));
+            upk2(X1[p], lo, hi);
+            X1[p] = pk2(torus_wrap(lo), torus_wrap(hi));
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < HP; p++) A0[p] = mul2(bc2(g.k[0]), X0[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) A1[p] = mul2(bc2(g.k[1]), X0[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) A0[p] = fma2(bc2(g.k[1]), X1[p], A0[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) A1[p] = fma2(bc2(g.k[2]), X1[p], A1[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) E[p] = mul2(A0[p], X0[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) E[p] = fma2(A1[p], X1[p], E[p]);
+#pragma unroll
+    for (int p = 0; p < HP; p++) {
+        float elo, ehi;
+        upk2(E[p], elo, ehi);
+        float alo = ex2_approx(elo), ahi = ex2_approx(ehi);
+        if constexpr (MODE == EV_GENERAL) {
+            if (elo > 0.0f) alo = 0.0f;  // power > 0: skipped by the reference (forward.cu:171)
+            if (ehi > 0.0f) ahi = 0.0f;
+        }
+        W[p] = mul2(bc2(g.v[0]), pk2(alo, ahi));
+    }
+#pragma unroll
+    for (int p = 0; p < HP; p++) {
+        int k = 0;
+        if constexpr ((MASK & PIGS_FN_VALUE) != 0) {
+            accp[p][k] = add2(accp[p][k], W[p]);
+            k++;
+        }
+        if constexpr ((MASK & PIGS_FN_DERIV) != 0) {
+            accp[p][k] = fma2(W[p], A0[p], accp[p][k]);
+            accp[p][k + 1] = fma2(W[p], A1[p], accp[p][k + 1]);
+            k += 2;
+        }
+        if constexpr ((MASK & PIGS_FN_HESS) != 0) {
+            accp[p][k] = fma2(W[p], fma2(A0[p], A0[p], bc2(-g.mm[0])), accp[p][k]);
+            accp[p][k + 1] = fma2(W[p], fma2(A0[p], A1[p], bc2(-g.mm[1])), accp[p][k + 1]);
+            accp[p][k + 2] = fma2(W[p], fma2(A1[p], A1[p], bc2(-g.mm[2])), accp[p][k + 2]);
+            k += 3;
+        }
+        if constexpr ((MASK & PIGS_FN_LAPL) != 0) {
+            accp[p][k] = fma2(W[p], fma2(A0[p], A0[p], fma2(A1[p], A1[p], bc2(-(g.mm[0] + g.mm[2])))), accp[p][k]);
+            k++;
+        }
+    }
+}
+
 template <int D, int C, unsigned MASK, int MODE, int KS>
 __device__ __forceinline__ void fwd_one_gaussian(const GaussFwd<D, C>& g, const float (&x)[KS][D],
                                                  const f32x2 (&xp)[D][(KS + 1) / 2], float (&acc)[KS][C][nacc(D, MASK)])
@@ -210,6 +291,16 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 for (int p = 0; p < KS / 2; p++) xp[d][p] = pk2_once(x[2 * p][d], x[2 * p + 1][d], nz);
         }
 
+        constexpr bool PACC = PIGS_FWD_PACKED_ACC && PIGS_FWD_PACKED && D == 2 && C == 1 && (KS % 2) == 0 &&
+                              (MASK & PIGS_FN_THIRD) == 0;
+        f32x2 accp[PACC ? KS / 2 : 1][NA];
+        if constexpr (PACC) {
+#pragma unroll
+            for (int p = 0; p < KS / 2; p++)
+#pragma unroll
+                for (int k = 0; k < NA; k++) accp[p][k] = bc2(0.0f);
+        }
+
         // ---- streamed operand: Gaussian records through shared memory, double-buffered ----
         const float4* __restrict__ src = recs + (size_t)it.g_begin * NV;
         const uint32_t total_v4 = it.g_count * NV;
@@ -238,7 +329,10 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
 #pragma unroll 1
             for (int j = 0; j < cnt; j++) {
                 const GaussFwd<D, C> g = load_gauss_fwd<D, C>(batch + j * NV);
-                fwd_one_gaussian<D, C, MASK, MODE, KS>(g, x, xp, acc);
+                if constexpr (PACC)
+                    fwd_gaussian_pairs<MASK, MODE, KS>(g, xp, accp);
+                else
+                    fwd_one_gaussian<D, C, MASK, MODE, KS>(g, x, xp, acc);
             }
             if (b + 1 < nbatch) {
 #pragma unroll
@@ -247,6 +341,12 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
             __syncthreads();
         }
 
+        if constexpr (PACC) {
+#pragma unroll
+            for (int p = 0; p < KS / 2; p++)
+#pragma unroll
+                for (int k = 0; k < NA; k++) upk2(accp[p][k], acc[2 * p][0][k], acc[2 * p + 1][0][k]);
+        }
         // ---- epilogue: undo the KH^order scaling, one RED.ADD per output element per item ----
         constexpr float IK1 = 1.0f / KH, IK2 = IK1 * IK1, IK3 = IK2 * IK1;
 #pragma unroll
