@@ -177,7 +177,8 @@ def test_noncontiguous_and_dtype_errors(torch_mod):
     s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], big[:, :2])  # silently .contiguous()'d
     a = s.sample_gaussians()
     s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
-    assert torch.equal(a, s.sample_gaussians())
+    b = s.sample_gaussians()  # same inputs; the default mode's RED.ADD order varies run to run
+    assert float((a - b).abs().max()) <= 2e-6 * float(b.abs().max())
     with pytest.raises(RuntimeError):
         s.preprocess(d["means"].double(), d["values"], d["covariances"], d["conics"], d["samples"])
 
