@@ -418,8 +418,9 @@ def hbm_peak():
 def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
     """BASELINE config 5 (model_pn.py neighbour aggregation + PDE step, 1M Gaussians, 16 neighbours).  One step = the
     library calls of one Model.forward + loss backward around the (torch, out-of-scope) MLP:
-      preprocess(samples = means) -> sample_gaussians / _derivative / _laplacian without grad (model_pn.py:644-652)
-      -> preprocess_aggregate + ATTENTION_HEADS = 2 x aggregate_neighbors forward, then backward (model_pn.py:253-274).
+      preprocess(samples = means) -> [preprocess_aggregate: lists + exchange plan, they depend on the means only] ->
+      sample_gaussians / _derivative / _laplacian without grad (model_pn.py:644-652)
+      -> ATTENTION_HEADS = 2 x aggregate_neighbors forward, then backward (model_pn.py:253-274).
     Neighbour lists: a 16-regular CSR (the reference's own rule yields ~1.6 K neighbours at this P), passed
     as plain inputs like the reference API allows.  N > 1 (row-parallel): every rank samples at ITS window
     of the means (windows of equal pair counts) and owns that window's rows of features / queries / keys, of the output
@@ -468,14 +469,19 @@ def leg_c5(torch, dist, L, rank, world, steps=5, warmup=3):
     leaves = [feat, freq] + [t for ph in per_head for t in ph]
     gs = [torch.randn(n, 16, device="cuda", generator=torch.Generator(device="cuda").manual_seed(7 + h)) for h in range(HEADS)]
 
+    # Order inside the step: binning -> neighbour lists + exchange plan -> sampling -> aggregation.  The lists depend on
+    # the means (and the radii the binning yields) only, not on the sampled values, so installing them BEFORE the sampling
+    # launch puts the plan's one host read behind the short binning kernels instead of behind the ~10 ms evaluation
+    # kernel — the host then enqueues the whole aggregation while the GPU is still sampling.
     def sampling():
         with torch.no_grad():
             s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], mine)
+        s.preprocess_aggregate(row_range=(lo, hi), csr=csr)
+        with torch.no_grad():
             return s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_gaussians_laplacian()
 
     def aggregation():
-        s.preprocess_aggregate(row_range=(lo, hi), csr=csr)
-        outs = [s.aggregate_neighbors_rows(feat, T, Q, Kk, freq, DT) for T, Q, Kk, DT in per_head]
+        outs = s.aggregate_neighbors_rows_heads(feat, freq, [tuple(ph) for ph in per_head])  # both heads, one exchange each way
         for t in leaves:
             t.grad = None
         torch.autograd.backward(outs, gs)

@@ -301,6 +301,87 @@ class _AggregateRows(torch.autograd.Function):
         return g_feat[lo:hi], gt, gq, g_keys[lo:hi], gfr, gdt, None, None, None
 
 
+class _AggregateRowsHeads(torch.autograd.Function):
+    """All attention heads of one step in ONE node (model_pn.py:256-262 loops over ATTENTION_HEADS with the same
+    features and frequencies): one halo exchange forward (features + every head's keys), one backward (the summed
+    dL/dfeatures + every head's dL/dkeys) and one all-reduce of all shared-parameter gradients, instead of two exchanges
+    and one all-reduce PER HEAD — at 8 ranks the per-collective latency, not the bytes, is what the aggregation waits on."""
+
+    @staticmethod
+    def forward(ctx, features_rows, frequencies, plan, csr, debug, H, *heads):
+        indices, ranges, dists, densities, inv_total = csr
+        lo, hi, P = plan.lo, plan.hi, plan.P
+        T = heads[0::4]
+        Q = [q.contiguous() for q in heads[1::4]]
+        Kr = heads[2::4]
+        DT = heads[3::4]
+        local = plan.world == 1 and lo == 0 and hi == P
+        if local:
+            feat, keys = features_rows.contiguous(), [k.contiguous() for k in Kr]
+        else:
+            dev = features_rows.device
+            feat = torch.empty((P, features_rows.size(-1)), dtype=torch.float32, device=dev)
+            feat[lo:hi] = features_rows
+            keys = []
+            for k in Kr:
+                kf = torch.empty((P, k.size(-1)), dtype=torch.float32, device=dev)
+                kf[lo:hi] = k
+                keys.append(kf)
+            plan.gather([feat] + keys)
+        outs, saved = [], []
+        for h in range(H):
+            w, e, f, out = _C.aggregate_neighbors_rows(feat, T[h], Q[h], keys[h], frequencies, DT[h], indices, ranges, dists,
+                                                       densities, inv_total, (lo, hi), debug)
+            outs.append(out)
+            saved += [w, e, f]
+        ctx.plan, ctx.csr, ctx.debug, ctx.H = plan, csr, debug, H
+        ctx.save_for_backward(feat, frequencies, *T, *Q, *keys, *DT, *saved)
+        ctx.set_materialize_grads(False)
+        return tuple(outs)
+
+    @staticmethod
+    def backward(ctx, *g_outs):
+        plan, H = ctx.plan, ctx.H
+        indices, ranges, dists, densities, inv_total = ctx.csr
+        sv = ctx.saved_tensors
+        feat, frequencies = sv[0], sv[1]
+        T, Q, keys, DT = sv[2:2 + H], sv[2 + H:2 + 2 * H], sv[2 + 2 * H:2 + 3 * H], sv[2 + 3 * H:2 + 4 * H]
+        wef = sv[2 + 4 * H:]
+        lo, hi, P = plan.lo, plan.hi, plan.P
+        zero = (lambda t: t.zero_()) if plan.dense else (lambda t: t[plan.jlo:plan.jhi].zero_())
+        g_feat = torch.empty_like(feat)
+        zero(g_feat)  # every head ADDS its contribution into the same buffer
+        g_keys, small, gq_all = [], [], []
+        gfr_sum = None
+        for h in range(H):
+            gk = torch.empty_like(keys[h])
+            zero(gk)
+            g_keys.append(gk)
+            if g_outs[h] is None:
+                small += [torch.zeros_like(T[h]), torch.zeros_like(DT[h])]
+                gq_all.append(torch.zeros_like(Q[h]))
+                continue
+            w, e, f = wef[3 * h:3 * h + 3]
+            gt, gq, gfr, gdt = _C.aggregate_neighbors_rows_backward(
+                feat, T[h], Q[h], keys[h], frequencies, DT[h], indices, ranges, dists, densities, w, e, f, inv_total,
+                g_outs[h].contiguous(), g_feat, gk, (lo, hi), ctx.debug)
+            gfr_sum = gfr if gfr_sum is None else gfr_sum + gfr
+            small += [gt, gdt]
+            gq_all.append(gq)
+        if gfr_sum is None:
+            gfr_sum = torch.zeros_like(frequencies)
+        plan.scatter_add([g_feat] + g_keys)
+        if plan.world > 1:
+            flat, recipe = pack_grads([gfr_sum] + small)
+            allreduce_grads(flat, plan.group)
+            un = unpack_grads(flat, recipe, 1 + len(small))
+            gfr_sum, small = un[0], un[1:]
+        per_head = []
+        for h in range(H):
+            per_head += [small[2 * h], gq_all[h], g_keys[h][lo:hi], small[2 * h + 1]]
+        return (g_feat[lo:hi], gfr_sum, None, None, None, None) + tuple(per_head)
+
+
 class ShardedGaussianSampler(GaussianSampler):
     """GaussianSampler whose `samples` are this rank's shard.  Same API; preprocess() bins on the global tile
     grid, backward all-reduces the gradients w.r.t. means / values / conics (so every rank ends up with the
@@ -352,3 +433,12 @@ class ShardedGaussianSampler(GaussianSampler):
         csr = (self.indices, self.ranges, self.dists, self.densities, self.inv_total_densities)
         return _AggregateRows.apply(features_rows, transform, queries_rows, keys_rows, frequencies, distance_transform,
                                     self.row_plan, csr, self.debug)
+
+    def aggregate_neighbors_rows_heads(self, features_rows, frequencies, heads):
+        """All heads of a step at once.  heads = [(transform, queries_rows, keys_rows, distance_transform), ...] (the
+        per-head arguments of aggregate_neighbors_rows; features and frequencies are shared, model_pn.py:256-262).
+        Returns one [hi-lo, L] output per head.  Same results as calling aggregate_neighbors_rows per head, with one
+        exchange each way and one all-reduce for all of them."""
+        csr = (self.indices, self.ranges, self.dists, self.densities, self.inv_total_densities)
+        flat = [t for hd in heads for t in hd]
+        return list(_AggregateRowsHeads.apply(features_rows, frequencies, self.row_plan, csr, self.debug, len(heads), *flat))

@@ -259,6 +259,42 @@ def test_row_windowed_kernels_touch_only_their_rows(name, specialised):
         _lib.lib().pigs_set_aggregate_specialised(1)
 
 
+def test_multi_head_node_equals_per_head_calls():
+    """ShardedGaussianSampler.aggregate_neighbors_rows_heads (all attention heads in one autograd node: one exchange each
+    way) against one aggregate_neighbors call per head: same outputs, same gradients (features / frequencies summed over
+    the heads).  Single process: the plan has no peers."""
+    import torch
+    from pigs_b200.sharded import ShardedGaussianSampler
+    rec = AGG_RECIPES["agg_model"]()
+    d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+    s = ShardedGaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["samples"])
+    s.preprocess_aggregate()
+    g = torch.Generator(device="cuda").manual_seed(4)
+    H = 2
+    def leaves():
+        torch.manual_seed(7)
+        feat = d["features"].clone().requires_grad_(True)
+        freq = d["frequencies"].clone().requires_grad_(True)
+        heads = [[(d[k] * (1.0 + 0.25 * h)).clone().requires_grad_(True) for k in ("transform", "queries", "keys", "distance_transform")]
+                 for h in range(H)]
+        return feat, freq, heads
+    ups = [torch.randn(d["features"].shape, device="cuda", generator=g) for _ in range(H)]
+    fa, qa, ha = leaves()
+    outs_a = s.aggregate_neighbors_rows_heads(fa, qa, [tuple(h) for h in ha])
+    torch.autograd.backward(outs_a, ups)
+    fb, qb, hb = leaves()
+    outs_b = [s.aggregate_neighbors(fb, h[0], h[1], h[2], qb, h[3]) for h in hb]
+    torch.autograd.backward(outs_b, ups)
+    for a, b in zip(outs_a, outs_b):
+        assert torch.equal(a.detach(), b.detach())
+    pairs = [(fa, fb, "features"), (qa, qb, "frequencies")] + [(x, y, "head%d.%d" % (h, i)) for h in range(H)
+                                                               for i, (x, y) in enumerate(zip(ha[h], hb[h]))]
+    for x, y, nm in pairs:
+        assert x.grad is not None and y.grad is not None, nm
+        assert rel_err(x.grad.cpu().numpy(), y.grad.cpu().numpy()) <= TOL, nm
+
+
 def test_unaligned_feature_rows_take_the_generic_kernels():
     """A features tensor whose storage starts 4 bytes off a 16-byte boundary (a view into a larger buffer): the specialised
     kernels' 16-byte row loads / vector REDs do not apply, the call falls back to the generic kernels, same results."""

@@ -176,6 +176,16 @@ def _rows_worker(rank, world, port, out_dir):
             out = s.aggregate_neighbors_rows(*[t[k] for k in AGG_KEYS])
             out.backward(torch.from_numpy(agg_upstream(rec)[lo:hi]).cuda())
             torch.cuda.synchronize()
+            # the multi-head node with ONE head must reproduce the per-head call (same kernels, one exchange each way)
+            t2 = {k: t[k].detach().clone().requires_grad_(True) for k in AGG_KEYS}
+            (o2,) = s.aggregate_neighbors_rows_heads(t2["features"], t2["frequencies"],
+                                                     [(t2["transform"], t2["queries"], t2["keys"], t2["distance_transform"])])
+            o2.backward(torch.from_numpy(agg_upstream(rec)[lo:hi]).cuda())
+            torch.cuda.synchronize()
+            assert torch.equal(o2.detach(), out.detach())
+            for k in AGG_KEYS:
+                den = float(t[k].grad.abs().max()) + 1e-30
+                assert float((t2[k].grad - t[k].grad).abs().max()) <= 1e-5 * den, (tag, k)
             res.update({tag + "_out": out.detach().cpu().numpy(), tag + "_dense": int(s.row_plan.dense),
                         **{tag + "_grad_" + k: t[k].grad.cpu().numpy() for k in AGG_KEYS}})
         np.savez(os.path.join(out_dir, "rows_rank%d.npz" % rank), **res)
