@@ -161,6 +161,12 @@ int pigs_get_deterministic(void);
  * in order on the caller's stream.  Results are the same up to the order of the RED.ADDs. */
 void pigs_set_class_concurrency(int on);
 
+/* Optional per-stage device timing of the preprocess chain (development: tools/chain_timing.py).  While on, the
+ * library records a cudaEvent behind each stage of pigs_sample_bounds / pigs_preprocess_count / pigs_preprocess_bin;
+ * pigs_stage_timing_read synchronises on them and returns (stage name, ms since the previous mark) pairs. */
+void pigs_set_stage_timing(int on);
+int pigs_stage_timing_read(const char **names, float *ms, int cap);
+
 /* Optional device timing of the evaluation kernels (bench.py roofline).  While on, the forward /
  * backward evaluation launches of every pigs_sample_forward / pigs_sample_backward call are
  * bracketed by cudaEvents on the call's stream.  pigs_kernel_timing_read(which = 0 forward |

@@ -508,6 +508,7 @@ int pigs_sample_bounds(const float* samples, int64_t N, int D, float* d_minmax, 
     const int cap = num_sms() * 8;
     if (nb > cap) nb = cap;
     const bool direct = N <= 64 * 1024;  // one CTA writes the result itself: one launch instead of two
+    PIGS_STAGE(st, "origin");
     if (direct) {
         nb = 1;
     } else {
@@ -519,6 +520,7 @@ int pigs_sample_bounds(const float* samples, int64_t N, int D, float* d_minmax, 
     else
         bounds_kernel<1><<<(unsigned)nb, 256, 0, st>>>(samples, N, d_minmax, false, direct);
     PIGS_LAUNCH_CHECK();
+    PIGS_STAGE(st, "bounds");
     return 0;
 }
 
@@ -547,8 +549,11 @@ int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float* means
         count_kernel<1><<<nb, 256, 0, st>>>(P, N, means, covariances, d_minmax, g_recip_mode, subdiv, cull_sigmas, g.hdr, radii,
                                             g.touched, g.cull_r);
     PIGS_LAUNCH_CHECK();
+    PIGS_STAGE(st, "count (grid + radii + tiles touched)");
     // offsets + the total straight into header.num_rendered (the word the host reads back)
-    return exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st, (long long*)&g.hdr->num_rendered);
+    const int rc = exclusive_scan_u32(g.touched, g.touched, P, true, g.scan_ws, st, (long long*)&g.hdr->num_rendered);
+    PIGS_STAGE(st, "scan of tiles touched");
+    return rc;
 }
 
 size_t pigs_binning_bytes(int64_t num_rendered, int blocks) { return BinLayout(nullptr, num_rendered, blocks).bytes; }
@@ -581,6 +586,7 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
     const int bits = bit_length((uint32_t)(2 * blocks + 1));
     const int64_t nslots = 2 * (int64_t)blocks + 4;
 
+    PIGS_STAGE(st, "host readback + allocations (gap)");
     if (num_rendered > 0) {
         const unsigned nb = (unsigned)((P + 255) / 256);
         if (D == 2)
@@ -590,6 +596,7 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
             emit_kernel<1><<<nb, 256, 0, st>>>(P, means, radii, g.cull_r, g.touched, g.hdr, keys_u, vals_u, s.bbox, (int)nslots,
                                                b.hdr, s.hdr);
         PIGS_LAUNCH_CHECK();
+        PIGS_STAGE(st, "emit (Gaussian keys)");
         bool done = false;
         SortExtras ex;
         ex.ranges = (uint2*)ranges;
@@ -625,6 +632,7 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
         else
             sample_key_kernel<1, false><<<nb, 256, 0, st>>>(N, samples, g.hdr, keys_u, vals_u, s.bbox, (int)nslots, gh, ntiles, dmask);
         PIGS_LAUNCH_CHECK();
+        PIGS_STAGE(st, "sample keys + boxes + histogram");
         bool done = false;
         SortExtras ex;
         ex.hist_done = true;

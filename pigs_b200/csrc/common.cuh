@@ -65,6 +65,15 @@ struct Carver {
 
 int num_sms();
 
+// Optional per-stage device timing of the preprocess chain (tools/chain_timing.py): while on, PIGS_STAGE(st, "name")
+// records a cudaEvent on the stream behind the launches issued so far; pigs_stage_timing_read returns the gaps.
+extern bool g_stage_timing;
+void stage_mark(cudaStream_t st, const char* name);
+#define PIGS_STAGE(st, name)                          \
+    do {                                              \
+        if (pigs::g_stage_timing) pigs::stage_mark(st, name); \
+    } while (0)
+
 // ---------------------------------------------------------------------------------------------
 // exclusive scan of u32: ONE launch for any n (single-pass, decoupled look-back; one CTA for small n).  out may alias
 // in.  out[n] = total if write_total; *total_out (device int64, optional) = total.  ws: scan_ws_bytes(n).

@@ -387,8 +387,10 @@ int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, c
     else
         flag_kernel<1><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic, b.cls, b.scode);
     PIGS_LAUNCH_CHECK();
+    PIGS_STAGE(st, "class flags");
     int rc = exclusive_scan_u64(b.cls, b.cls, R, true, b.scan_ws, st);
     if (rc) return rc;
+    PIGS_STAGE(st, "class scan (u64)");
     WorkListCfg cfg;
     const uint32_t chunks[WL_COUNT] = {EV_THREADS * 8u, EV_THREADS * 4u, EV_THREADS * (uint32_t)bwd_kg(2, 1, 7u)};
     for (int wl = 0; wl < WL_COUNT; wl++) {
@@ -400,6 +402,7 @@ int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, c
     }
     worklist_kernel<<<WL_COUNT, 256, 0, st>>>(blocks, ranges, sample_ranges, b.cls, cfg, b.segs, b.wt);
     PIGS_LAUNCH_CHECK();
+    PIGS_STAGE(st, "work lists");
     return 0;
 }
 

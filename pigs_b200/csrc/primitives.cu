@@ -17,6 +17,26 @@ int set_error(int code, const char* what, const char* file, int line)
     return code;
 }
 
+bool g_stage_timing = false;
+namespace {
+struct StageMark {
+    cudaEvent_t ev;
+    const char* name;
+};
+StageMark g_marks[256];
+int g_nmarks = 0;
+}  // namespace
+
+void stage_mark(cudaStream_t st, const char* name)
+{
+    if (g_nmarks >= 256) return;
+    StageMark& m = g_marks[g_nmarks];
+    if (!m.ev) cudaEventCreate(&m.ev);
+    m.name = name;
+    cudaEventRecord(m.ev, st);
+    g_nmarks++;
+}
+
 int num_sms()
 {
     static int n = 0;
@@ -441,9 +461,11 @@ int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_o
         if (!(p == 0 && ex && ex->hist_done)) {  // the key-producing kernel may have left the first histogram behind
             radix_hist<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, n, shift, mask, ghist, nb);
             PIGS_LAUNCH_CHECK();
+            PIGS_STAGE(st, "radix histogram");
         }
         int rc = exclusive_scan_u32(ghist, ghist, RADIX * nb, false, scan_ws, st);
         if (rc) return rc;
+        PIGS_STAGE(st, "radix scan");
         uint2* rg = nullptr;
         int max_slot = 0;
         if (passes == 1 && ex && ex->ranges && ex->max_slot < RADIX) {
@@ -453,6 +475,7 @@ int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_o
         }
         radix_scatter<<<(unsigned)nb, SORT_THREADS, 0, st>>>(src_k, src_v, n, shift, mask, ghist, nb, dst_k, dst_v, rg, max_slot);
         PIGS_LAUNCH_CHECK();
+        PIGS_STAGE(st, "radix scatter (+ ranges)");
         src_k = dst_k;
         src_v = dst_v;
     }
@@ -460,3 +483,31 @@ int stable_sort_pairs_u32(uint32_t* keys_in, uint32_t* vals_in, uint32_t* keys_o
 }
 
 }  // namespace pigs
+
+extern "C" {
+
+void pigs_set_stage_timing(int on)
+{
+    pigs::g_stage_timing = on != 0;
+    pigs::g_nmarks = 0;
+}
+
+// Synchronises on the recorded marks; writes up to `cap` (name, milliseconds since the previous mark) pairs and returns
+// how many; the first mark is the origin (0 ms).  Clears the list.
+int pigs_stage_timing_read(const char** names, float* ms, int cap)
+{
+    using namespace pigs;
+    int n = 0;
+    for (int i = 0; i < g_nmarks && n < cap; i++) {
+        float t = 0.f;
+        if (cudaEventSynchronize(g_marks[i].ev) != cudaSuccess) break;
+        if (i > 0) cudaEventElapsedTime(&t, g_marks[i - 1].ev, g_marks[i].ev);
+        names[n] = g_marks[i].name;
+        ms[n] = t;
+        n++;
+    }
+    g_nmarks = 0;
+    return n;
+}
+
+}  // extern "C"
