@@ -425,8 +425,13 @@ __global__ void __launch_bounds__(256) sample_key_kernel(int64_t N, const float*
                 vals[i] = (uint32_t)i;
             }
             // one histogram atomic per distinct tile per warp (a 4x4 grid has 16); every lane takes part in the match
-            const uint32_t dg = ok ? (tile & digit_mask) : 0xffffffffu;
-            const uint32_t peers = __match_any_sync(0xffffffffu, dg);
+            const uint32_t dg = ok ? (tile & digit_mask) : 0u;
+            uint32_t peers = __ballot_sync(0xffffffffu, ok);
+            for (uint32_t bm = digit_mask, b = 0; bm; bm >>= 1, b++) {  // ballots over the digit's bits (primitives.cu match_digit)
+                const bool bit = (dg >> b) & 1u;
+                const uint32_t m = __ballot_sync(0xffffffffu, bit);
+                peers &= bit ? m : ~m;
+            }
             if (ok && (threadIdx.x & 31) == (__ffs(peers) - 1)) atomicAdd(&s_hist[dg], (uint32_t)__popc(peers));
             if (ok) {
                 float* box = (SMEM ? s_box : bbox) + (size_t)tile * 2 * D;
