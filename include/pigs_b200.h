@@ -244,6 +244,25 @@ int pigs_aggregate_backward_rows(int64_t P, int D, int L, int K, int E, int64_t 
                                  float *dL_dqueries, float *dL_dkeys, float *dL_dfrequencies,
                                  float *dL_ddistance_transform, void *workspace, void *stream);
 
+/* float64 instantiation of the (generic) aggregation kernels = the reference built with `typedef double FLOAT`
+ * (cuda_sampler/config.h:20), which its one live test needs: torch.autograd.gradcheck of aggregate_neighbors on double
+ * tensors (test_neighbor_aggregation.py:94-101).  Same arguments as pigs_aggregate_forward / _backward with every float
+ * array as double (the CSR's dists / densities / inv_total_densities converted by the caller); all P rows. */
+int pigs_aggregate_forward_f64(int64_t P, int D, int L, int K, int E, const double *features, const double *transform,
+                               const double *queries, const double *keys, const double *frequencies,
+                               const double *distance_transform, const int64_t *indices, const int64_t *ranges,
+                               const double *dists, const double *densities, const double *inv_total_densities,
+                               double *weights, double *embeddings, double *factors, double *neighbor_features,
+                               void *stream);
+int pigs_aggregate_backward_f64(int64_t P, int D, int L, int K, int E, const double *features, const double *transform,
+                                const double *queries, const double *keys, const double *frequencies,
+                                const double *distance_transform, const int64_t *indices, const int64_t *ranges,
+                                const double *dists, const double *densities, const double *weights,
+                                const double *embeddings, const double *factors, const double *inv_total_densities,
+                                const double *dL_dneighbor_features, double *dL_dfeatures, double *dL_dtransform,
+                                double *dL_dqueries, double *dL_dkeys, double *dL_dfrequencies,
+                                double *dL_ddistance_transform, void *stream);
+
 /* ---- covariance / conic construction ---------------------------------------
  * Replaces the torch chain of gaussians.py:163-193 `build_covariances(s, t)` (tanh, sqrt(prod), diag_embed, indexed
  * assignment, batched torch.inverse, flatten to [xx, xy, yy]) that feeds GaussianSampler.preprocess in every driver.

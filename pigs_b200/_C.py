@@ -304,11 +304,60 @@ def preprocess_aggregate(means, conics, radii, debug, rows=None):
     return indices, ranges, dists, densities, inv_total
 
 
+def _f64c(t, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (pigs_b200 has no CPU path)")
+    return t.to(torch.float64).contiguous()
+
+
+def _aggregate_neighbors_f64(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
+                             densities, inv_total_densities, debug):
+    """float64 path = the reference built with `typedef double FLOAT` (config.h:20), for gradcheck
+    (test_neighbor_aggregation.py:94-101): generic kernels instantiated for double, CSR values widened here."""
+    L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
+    a = [_f64c(t, n) for t, n in ((features, "features"), (transform, "transform"), (queries, "queries"), (keys, "keys"),
+                                  (frequencies, "frequencies"), (distance_transform, "distance_transform"))]
+    dists, densities, inv_total = _f64c(dists, "dists"), _f64c(densities, "densities"), _f64c(inv_total_densities, "inv_total")
+    P, D, L = a[0].size(0), dists.size(-1), a[0].size(-1)
+    K, E = a[2].size(-1), a[5].size(-1) // 2
+    w, e, f = torch.zeros_like(densities), torch.zeros_like(densities), torch.zeros_like(densities)
+    out = torch.zeros((P, L), dtype=torch.float64, device=a[0].device)
+    if P > 0:
+        check(L_.pigs_aggregate_forward_f64(P, D, L, K, E, *[_ptr(t) for t in a], _ptr(indices.contiguous()),
+                                            _ptr(ranges.contiguous()), _ptr(dists), _ptr(densities), _ptr(inv_total), _ptr(w),
+                                            _ptr(e), _ptr(f), _ptr(out), _stream()), "pigs_aggregate_forward_f64")
+    return w, e, f, out
+
+
+def _aggregate_neighbors_backward_f64(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
+                                      dists, densities, weights, embeddings, factors, inv_total_densities, g, debug):
+    L_ = _lib.lib()
+    L_.pigs_set_debug(1 if debug else 0)
+    a = [_f64c(t, n) for t, n in ((features, "features"), (transform, "transform"), (queries, "queries"), (keys, "keys"),
+                                  (frequencies, "frequencies"), (distance_transform, "distance_transform"))]
+    dists, densities, inv_total = _f64c(dists, "dists"), _f64c(densities, "densities"), _f64c(inv_total_densities, "inv_total")
+    saved = [_f64c(t, "saved") for t in (weights, embeddings, factors)]
+    g = _f64c(g, "dL_dneighbor_features")
+    P, D, L = a[0].size(0), dists.size(-1), a[0].size(-1)
+    K, E = a[2].size(-1), a[5].size(-1) // 2
+    outs = [torch.zeros_like(t) for t in a]
+    if P > 0:
+        check(L_.pigs_aggregate_backward_f64(P, D, L, K, E, *[_ptr(t) for t in a], _ptr(indices.contiguous()),
+                                             _ptr(ranges.contiguous()), _ptr(dists), _ptr(densities), *[_ptr(t) for t in saved],
+                                             _ptr(inv_total), _ptr(g), *[_ptr(t) for t in outs], _stream()),
+              "pigs_aggregate_backward_f64")
+    return tuple(outs)
+
+
 @_on_device
 def aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists,
                         densities, inv_total_densities, debug):
     """AggregateNeighborsCUDA (aggregate_neighbors.cu:369-415).  Returns
     (weights, embeddings, factors [M], neighbor_features [P,L])."""
+    if features.dtype == torch.float64:
+        return _aggregate_neighbors_f64(features, transform, queries, keys, frequencies, distance_transform, indices, ranges,
+                                        dists, densities, inv_total_densities, debug)
     L_ = _lib.lib()
     L_.pigs_set_debug(1 if debug else 0)
     features = _f32c(features, "features")
@@ -343,6 +392,10 @@ def aggregate_neighbors_backward(features, transform, queries, keys, frequencies
                                  dists, densities, weights, embeddings, factors, inv_total_densities,
                                  dL_dneighbor_features, debug):
     """AggregateNeighborsBackwardCUDA (aggregate_neighbors.cu:417-475)."""
+    if features.dtype == torch.float64:
+        return _aggregate_neighbors_backward_f64(features, transform, queries, keys, frequencies, distance_transform, indices,
+                                                 ranges, dists, densities, weights, embeddings, factors, inv_total_densities,
+                                                 dL_dneighbor_features, debug)
     L_ = _lib.lib()
     L_.pigs_set_debug(1 if debug else 0)
     features = _f32c(features, "features")
@@ -798,6 +851,14 @@ def _wrap_compiled(n):
                 cull = (float(cull[0]), int(cull[1]))
             return f(means, values, covariances, conics, samples, bool(debug), bounds, cull)
         return pre
+    if n in ("aggregate_neighbors", "aggregate_neighbors_backward"):
+        slow = globals()[n + "_ctypes"]
+
+        def agg(features, *rest):
+            if features.dtype == torch.float64:  # the double instantiation is bound through ctypes only
+                return slow(features, *rest)
+            return f(features, *rest)
+        return agg
     if n == "preprocess_aggregate":
         def pa(means, conics, radii, debug, rows=None):
             if rows is not None:

@@ -79,6 +79,8 @@ SIGNATURES = {
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
     "pigs_aggregate_forward_rows": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64] + [c_void_p] * 16),
     "pigs_aggregate_backward_rows": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64, c_int64, c_int64] + [c_void_p] * 23),
+    "pigs_aggregate_forward_f64": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),
+    "pigs_aggregate_backward_f64": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 22),
     "pigs_set_aggregate_specialised": (None, [c_int]),
     "pigs_set_neighbor_search": (None, [c_int, ctypes.c_float]),
     "pigs_aggregate_backward_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),

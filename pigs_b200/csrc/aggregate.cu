@@ -948,29 +948,42 @@ __device__ __forceinline__ void sincos_fpx(float f, float X, float& s, float& c)
     sincospif(__fadd_rn(r, e), &s, &c);
 }
 
+// scalar-type helpers of the generic aggregation kernels: T = float (the product) or double (the reference's
+// `typedef double FLOAT` build, cuda_sampler/config.h:20 — what its one live test, torch.autograd.gradcheck of
+// aggregate_neighbors, test_neighbor_aggregation.py:94-101, needs)
+__device__ __forceinline__ float tfma(float a, float b, float c) { return fmaf(a, b, c); }
+__device__ __forceinline__ double tfma(double a, double b, double c) { return fma(a, b, c); }
+__device__ __forceinline__ void sincos_fpx_t(float f, float X, float& s, float& c) { sincos_fpx(f, X, s, c); }
+__device__ __forceinline__ void sincos_fpx_t(double f, double X, double& s, double& c)
+{
+    sincos(f * 3.14159265358979323846 * X, &s, &c);  // the reference's own expression (aggregate_neighbors.cu:181-182)
+}
+
 struct AggDims {
     int D, L, K, E, nF, stride;  // stride = (E-1)/D, nF = stride/2
 };
 
+template <typename T>
 __global__ void __launch_bounds__(AG_THREADS)
-    agg_forward_kernel(int64_t row_lo, int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
-                       const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
-                       const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
-                       const float* __restrict__ dists, const float* __restrict__ densities,
-                       const float* __restrict__ inv_total, float* __restrict__ weights, float* __restrict__ embeddings,
-                       float* __restrict__ factors, float* __restrict__ out)
+    agg_forward_kernel(int64_t row_lo, int64_t P, AggDims dm, const T* __restrict__ features, const T* __restrict__ transform,
+                       const T* __restrict__ queries, const T* __restrict__ keys, const T* __restrict__ freqs,
+                       const T* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
+                       const T* __restrict__ dists, const T* __restrict__ densities,
+                       const T* __restrict__ inv_total, T* __restrict__ weights, T* __restrict__ embeddings,
+                       T* __restrict__ factors, T* __restrict__ out)
 {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) unsigned char agg_raw[];
+    T* sm = reinterpret_cast<T*>(agg_raw);
     const int D = dm.D, L = dm.L, K = dm.K, E = dm.E, nF = dm.nF, stride = dm.stride;
-    float* s_dt = sm;                 // [2E]
-    float* s_fr = s_dt + 2 * E;       // [nF]
-    float* wbase = s_fr + nF;
+    T* s_dt = sm;                 // [2E]
+    T* s_fr = s_dt + 2 * E;       // [nF]
+    T* wbase = s_fr + nF;
     const int per_warp = K + L + 3 * 32;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float* s_q = wbase + (size_t)w * per_warp;  // [K]
-    float* s_z = s_q + K;                       // [L]
-    float* s_dwe = s_z + L;                     // [32]
-    float* s_dwf = s_dwe + 32;                  // [32]
+    T* s_q = wbase + (size_t)w * per_warp;  // [K]
+    T* s_z = s_q + K;                       // [L]
+    T* s_dwe = s_z + L;                     // [32]
+    T* s_dwf = s_dwe + 32;                  // [32]
     int* s_j = (int*)(s_dwf + 32);              // [32]
     for (int i = threadIdx.x; i < 2 * E; i += AG_THREADS) s_dt[i] = dt[i];
     for (int i = threadIdx.x; i < nF; i += AG_THREADS) s_fr[i] = freqs[i];
@@ -979,30 +992,30 @@ __global__ void __launch_bounds__(AG_THREADS)
     for (int64_t row = row_lo + (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {  // rows [row_lo, P)
         const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
         for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
-        const float inv = inv_total[row];
-        float z[AG_MAX_L / 32];
+        const T inv = inv_total[row];
+        T z[AG_MAX_L / 32];
 #pragma unroll
-        for (int a = 0; a < AG_MAX_L / 32; a++) z[a] = 0.0f;
+        for (int a = 0; a < AG_MAX_L / 32; a++) z[a] = T(0.0);
         __syncwarp();
         for (int64_t chunk = start; chunk < end; chunk += 32) {
             const int64_t s = chunk + lane;
             const int64_t j = s < end ? indices[s] : -1;
-            float dwe = 0.0f, dwf = 0.0f;
+            T dwe = T(0.0), dwf = T(0.0);
             if (j >= 0) {
-                const float* key = keys + j * K;
-                float wgt = 0.0f;
-                for (int k = 0; k < K; k++) wgt = fmaf(s_q[k], key[k], wgt);
-                float emb = 0.0f, fac = 0.0f;
+                const T* key = keys + j * K;
+                T wgt = T(0.0);
+                for (int k = 0; k < K; k++) wgt = tfma(s_q[k], key[k], wgt);
+                T emb = T(0.0), fac = T(0.0);
                 for (int d = 0; d < D; d++) {
-                    const float X = dists[s * D + d];
+                    const T X = dists[s * D + d];
                     for (int e = 0; e < nF; e++) {
-                        float sn, cs;
-                        sincos_fpx(s_fr[e], X, sn, cs);
+                        T sn, cs;
+                        sincos_fpx_t(s_fr[e], X, sn, cs);
                         const int i0 = d * stride + 2 * e;
-                        emb = fmaf(s_dt[i0], sn, emb);
-                        emb = fmaf(s_dt[i0 + 1], cs, emb);
-                        fac = fmaf(s_dt[E + i0], sn, fac);
-                        fac = fmaf(s_dt[E + i0 + 1], cs, fac);
+                        emb = tfma(s_dt[i0], sn, emb);
+                        emb = tfma(s_dt[i0 + 1], cs, emb);
+                        fac = tfma(s_dt[E + i0], sn, fac);
+                        fac = tfma(s_dt[E + i0 + 1], cs, fac);
                     }
                 }
                 emb += s_dt[E - 1];
@@ -1010,14 +1023,14 @@ __global__ void __launch_bounds__(AG_THREADS)
                 weights[s] = wgt;
                 embeddings[s] = emb;
                 factors[s] = fac;
-                const float dw = inv * densities[s] * wgt;
+                const T dw = inv * densities[s] * wgt;
                 dwf = dw * fac;
                 dwe = dw * emb;
             } else if (s < end) {
                 // skipped neighbour: every slot of the row is written, so the caller's outputs need no zero fill
-                weights[s] = 0.0f;
-                embeddings[s] = 0.0f;
-                factors[s] = 0.0f;
+                weights[s] = T(0.0);
+                embeddings[s] = T(0.0);
+                factors[s] = T(0.0);
             }
             s_dwe[lane] = dwe;
             s_dwf[lane] = dwf;
@@ -1027,11 +1040,11 @@ __global__ void __launch_bounds__(AG_THREADS)
             for (int t = 0; t < cnt; t++) {
                 const int jj = s_j[t];
                 if (jj < 0) continue;
-                const float a0 = s_dwe[t], a1 = s_dwf[t];
-                const float* f = features + (size_t)jj * L;
+                const T a0 = s_dwe[t], a1 = s_dwf[t];
+                const T* f = features + (size_t)jj * L;
 #pragma unroll
                 for (int a = 0; a < AG_MAX_L / 32; a++)
-                    if (a * 32 + lane < L) z[a] += fmaf(a1, f[a * 32 + lane], a0);
+                    if (a * 32 + lane < L) z[a] += tfma(a1, f[a * 32 + lane], a0);
             }
             __syncwarp();
         }
@@ -1041,8 +1054,8 @@ __global__ void __launch_bounds__(AG_THREADS)
         __syncwarp();
         // out_i = z . T  (the reference applies T inside the neighbour loop, :201-206)
         for (int b = lane; b < L; b += 32) {
-            float acc = 0.0f;
-            for (int a = 0; a < L; a++) acc = fmaf(s_z[a], transform[a * L + b], acc);
+            T acc = T(0.0);
+            for (int a = 0; a < L; a++) acc = tfma(s_z[a], transform[a * L + b], acc);
             out[row * L + b] = acc;
         }
         __syncwarp();
@@ -1056,43 +1069,45 @@ __global__ void __launch_bounds__(AG_THREADS)
 //   dL/ddt, dL/dfreq: the per-slot sums over channels collapse to A and B (reference :266-281)
 // Shared-parameter gradients are accumulated per lane in shared-memory columns (no conflicts), reduced
 // once per CTA, then one atomic per address per CTA.
+template <typename T>
 __global__ void __launch_bounds__(AG_THREADS)
-    agg_backward_kernel(int64_t row_lo, int64_t P, AggDims dm, const float* __restrict__ features, const float* __restrict__ transform,
-                        const float* __restrict__ queries, const float* __restrict__ keys, const float* __restrict__ freqs,
-                        const float* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
-                        const float* __restrict__ dists, const float* __restrict__ densities,
-                        const float* __restrict__ weights, const float* __restrict__ embeddings,
-                        const float* __restrict__ factors, const float* __restrict__ inv_total,
-                        const float* __restrict__ gout, float* __restrict__ g_features, float* __restrict__ g_transform,
-                        float* __restrict__ g_queries, float* __restrict__ g_keys, float* __restrict__ g_freqs,
-                        float* __restrict__ g_dt)
+    agg_backward_kernel(int64_t row_lo, int64_t P, AggDims dm, const T* __restrict__ features, const T* __restrict__ transform,
+                        const T* __restrict__ queries, const T* __restrict__ keys, const T* __restrict__ freqs,
+                        const T* __restrict__ dt, const int64_t* __restrict__ indices, const int64_t* __restrict__ ranges,
+                        const T* __restrict__ dists, const T* __restrict__ densities,
+                        const T* __restrict__ weights, const T* __restrict__ embeddings,
+                        const T* __restrict__ factors, const T* __restrict__ inv_total,
+                        const T* __restrict__ gout, T* __restrict__ g_features, T* __restrict__ g_transform,
+                        T* __restrict__ g_queries, T* __restrict__ g_keys, T* __restrict__ g_freqs,
+                        T* __restrict__ g_dt)
 {
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) unsigned char agg_raw[];
+    T* sm = reinterpret_cast<T*>(agg_raw);
     const int D = dm.D, L = dm.L, K = dm.K, E = dm.E, nF = dm.nF, stride = dm.stride;
     const int ncol = 2 * E + nF;
-    float* s_dt = sm;                     // [2E]
-    float* s_fr = s_dt + 2 * E;           // [nF]
-    float* s_gt = s_fr + nF;              // [L*L]  CTA accumulator of dL/dT
-    float* wbase = s_gt + L * L;
+    T* s_dt = sm;                     // [2E]
+    T* s_fr = s_dt + 2 * E;           // [nF]
+    T* s_gt = s_fr + nF;              // [L*L]  CTA accumulator of dL/dT
+    T* wbase = s_gt + L * L;
     const int per_warp = K + 3 * L + 6 * 32 + ncol * 32;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    float* s_q = wbase + (size_t)w * per_warp;  // [K]
-    float* s_st = s_q + K;                      // [L]
-    float* s_g = s_st + L;                      // [L]
-    float* s_wz = s_g + L;                      // [L]
-    float* s_te = s_wz + L;                     // [32] x5 + j
-    float* s_c1 = s_te + 32;
-    float* s_w = s_c1 + 32;
-    float* s_dce = s_w + 32;
-    float* s_dcf = s_dce + 32;
-    int* s_j = (int*)(s_dcf + 32);
-    float* s_col = (float*)(s_j + 32);          // [ncol][32] per-lane partial sums of dL/ddt, dL/dfreq
+    T* s_q = wbase + (size_t)w * per_warp;  // [K]
+    T* s_st = s_q + K;                      // [L]
+    T* s_g = s_st + L;                      // [L]
+    T* s_wz = s_g + L;                      // [L]
+    T* s_te = s_wz + L;                     // [32] x5 + j
+    T* s_c1 = s_te + 32;
+    T* s_w = s_c1 + 32;
+    T* s_dce = s_w + 32;
+    T* s_dcf = s_dce + 32;
+    int* s_j = (int*)(s_dcf + 32);              // [32] ints inside a slot of 32 T
+    T* s_col = s_dcf + 64;                      // [ncol][32] per-lane partial sums of dL/ddt, dL/dfreq
     for (int i = threadIdx.x; i < 2 * E; i += AG_THREADS) s_dt[i] = dt[i];
     for (int i = threadIdx.x; i < nF; i += AG_THREADS) s_fr[i] = freqs[i];
-    for (int i = threadIdx.x; i < L * L; i += AG_THREADS) s_gt[i] = 0.0f;
-    for (int i = lane; i < ncol * 32; i += 32) s_col[i] = 0.0f;
+    for (int i = threadIdx.x; i < L * L; i += AG_THREADS) s_gt[i] = T(0.0);
+    for (int i = lane; i < ncol * 32; i += 32) s_col[i] = T(0.0);
     __syncthreads();
-    const float PI = 3.14159265358979323846f;
+    const T PI = T(3.14159265358979323846);
 
     for (int64_t row = row_lo + (int64_t)blockIdx.x * AG_WARPS + w; row < P; row += (int64_t)gridDim.x * AG_WARPS) {  // rows [row_lo, P)
         const int64_t start = row == 0 ? 0 : ranges[row - 1], end = ranges[row];
@@ -1100,53 +1115,53 @@ __global__ void __launch_bounds__(AG_THREADS)
         for (int k = lane; k < K; k += 32) s_q[k] = queries[row * K + k];
         for (int b = lane; b < L; b += 32) s_g[b] = gout[row * L + b];
         __syncwarp();
-        float Apart = 0.0f;
+        T Apart = T(0.0);
         for (int a = lane; a < L; a += 32) {
-            float acc = 0.0f;
-            for (int b = 0; b < L; b++) acc = fmaf(transform[a * L + b], s_g[b], acc);
+            T acc = T(0.0);
+            for (int b = 0; b < L; b++) acc = tfma(transform[a * L + b], s_g[b], acc);
             s_st[a] = acc;
             Apart += acc;
         }
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) Apart += __shfl_xor_sync(0xffffffffu, Apart, o);
-        const float A = Apart;
-        const float inv = inv_total[row];
-        float wz[AG_MAX_L / 32], gq[AG_MAX_K / 32];
+        const T A = Apart;
+        const T inv = inv_total[row];
+        T wz[AG_MAX_L / 32], gq[AG_MAX_K / 32];
 #pragma unroll
-        for (int a = 0; a < AG_MAX_L / 32; a++) wz[a] = 0.0f;
+        for (int a = 0; a < AG_MAX_L / 32; a++) wz[a] = T(0.0);
 #pragma unroll
-        for (int k = 0; k < AG_MAX_K / 32; k++) gq[k] = 0.0f;
+        for (int k = 0; k < AG_MAX_K / 32; k++) gq[k] = T(0.0);
         __syncwarp();
         for (int64_t chunk = start; chunk < end; chunk += 32) {
             const int64_t s = chunk + lane;
             const int64_t j = s < end ? indices[s] : -1;
-            float te = 0.f, c1 = 0.f, wgt = 0.f, dce = 0.f, dcf = 0.f;
+            T te = T(0), c1 = T(0), wgt = T(0), dce = T(0), dcf = T(0);
             if (j >= 0) {
-                const float* f = features + j * L;
-                float B = 0.0f;
-                for (int a = 0; a < L; a++) B = fmaf(s_st[a], f[a], B);
+                const T* f = features + j * L;
+                T B = T(0.0);
+                for (int a = 0; a < L; a++) B = tfma(s_st[a], f[a], B);
                 wgt = weights[s];
-                const float emb = embeddings[s], fac = factors[s];
-                const float dc = densities[s] * inv;
-                const float dcw = dc * wgt;
+                const T emb = embeddings[s], fac = factors[s];
+                const T dc = densities[s] * inv;
+                const T dcw = dc * wgt;
                 dce = dc * emb;
                 dcf = dc * fac;
-                te = fmaf(dce, A, dcf * B);
+                te = tfma(dce, A, dcf * B);
                 c1 = dcw * fac;
-                const float dA = dcw * A, dB = dcw * B;
+                const T dA = dcw * A, dB = dcw * B;
                 for (int d = 0; d < D; d++) {
-                    const float X = dists[s * D + d];
+                    const T X = dists[s * D + d];
                     for (int e = 0; e < nF; e++) {
-                        float sn, cs;
-                        sincos_fpx(s_fr[e], X, sn, cs);
+                        T sn, cs;
+                        sincos_fpx_t(s_fr[e], X, sn, cs);
                         const int i0 = d * stride + 2 * e;
                         s_col[(i0)*32 + lane] += dA * sn;
                         s_col[(E + i0) * 32 + lane] += dB * sn;
                         s_col[(i0 + 1) * 32 + lane] += dA * cs;
                         s_col[(E + i0 + 1) * 32 + lane] += dB * cs;
-                        const float ts = fmaf(s_dt[E + i0], dB, s_dt[i0] * dA);
-                        const float tc = fmaf(s_dt[E + i0 + 1], dB, s_dt[i0 + 1] * dA);
-                        s_col[(2 * E + e) * 32 + lane] += PI * X * fmaf(cs, ts, -sn * tc);
+                        const T ts = tfma(s_dt[E + i0], dB, s_dt[i0] * dA);
+                        const T tc = tfma(s_dt[E + i0 + 1], dB, s_dt[i0 + 1] * dA);
+                        s_col[(2 * E + e) * 32 + lane] += PI * X * tfma(cs, ts, -sn * tc);
                     }
                 }
                 s_col[(E - 1) * 32 + lane] += dA;
@@ -1163,22 +1178,22 @@ __global__ void __launch_bounds__(AG_THREADS)
             for (int t = 0; t < cnt; t++) {
                 const int jj = s_j[t];
                 if (jj < 0) continue;
-                const float t_te = s_te[t], t_c1 = s_c1[t], t_w = s_w[t], t_dce = s_dce[t], t_dcf = s_dcf[t];
-                const float* f = features + (size_t)jj * L;
+                const T t_te = s_te[t], t_c1 = s_c1[t], t_w = s_w[t], t_dce = s_dce[t], t_dcf = s_dcf[t];
+                const T* f = features + (size_t)jj * L;
 #pragma unroll
                 for (int a = 0; a < AG_MAX_L / 32; a++) {
                     const int ai = a * 32 + lane;
                     if (ai < L) {
                         atomicAdd(g_features + (size_t)jj * L + ai, t_c1 * s_st[ai]);
-                        wz[a] = fmaf(t_w, fmaf(t_dcf, f[ai], t_dce), wz[a]);
+                        wz[a] = tfma(t_w, tfma(t_dcf, f[ai], t_dce), wz[a]);
                     }
                 }
-                const float* key = keys + (size_t)jj * K;
+                const T* key = keys + (size_t)jj * K;
 #pragma unroll
                 for (int k = 0; k < AG_MAX_K / 32; k++) {
                     const int ki = k * 32 + lane;
                     if (ki < K) {
-                        gq[k] = fmaf(key[ki], t_te, gq[k]);
+                        gq[k] = tfma(key[ki], t_te, gq[k]);
                         atomicAdd(g_keys + (size_t)jj * K + ki, s_q[ki] * t_te);
                     }
                 }
@@ -1193,21 +1208,21 @@ __global__ void __launch_bounds__(AG_THREADS)
             if (a * 32 + lane < L) s_wz[a * 32 + lane] = wz[a];
         __syncwarp();
         for (int b = lane; b < L; b += 32) {
-            const float gb = s_g[b];
+            const T gb = s_g[b];
             for (int a = 0; a < L; a++) atomicAdd(&s_gt[a * L + b], s_wz[a] * gb);
         }
         __syncwarp();
     }
     __syncthreads();
     for (int i = threadIdx.x; i < L * L; i += AG_THREADS)
-        if (s_gt[i] != 0.0f) atomicAdd(g_transform + i, s_gt[i]);
+        if (s_gt[i] != T(0.0)) atomicAdd(g_transform + i, s_gt[i]);
     for (int i = threadIdx.x; i < ncol; i += AG_THREADS) {
-        float acc = 0.0f;
+        T acc = T(0.0);
         for (int ww = 0; ww < AG_WARPS; ww++) {
-            const float* col = wbase + (size_t)ww * per_warp + (K + 3 * L + 6 * 32) + i * 32;
+            const T* col = wbase + (size_t)ww * per_warp + (K + 3 * L + 6 * 32) + i * 32;
             for (int l = 0; l < 32; l++) acc += col[l];
         }
-        if (acc != 0.0f) atomicAdd(i < 2 * E ? g_dt + i : g_freqs + (i - 2 * E), acc);
+        if (acc != T(0.0)) atomicAdd(i < 2 * E ? g_dt + i : g_freqs + (i - 2 * E), acc);
     }
 }
 
@@ -1244,10 +1259,10 @@ int bit_len(uint32_t n)
     return b;
 }
 
-size_t agg_fwd_smem(int L, int K, int E, int nF) { return sizeof(float) * (2 * E + nF + (size_t)AG_WARPS * (K + L + 3 * 32)); }
-size_t agg_bwd_smem(int L, int K, int E, int nF)
+size_t agg_fwd_smem(int L, int K, int E, int nF, size_t elem = sizeof(float)) { return elem * (2 * E + nF + (size_t)AG_WARPS * (K + L + 3 * 32)); }
+size_t agg_bwd_smem(int L, int K, int E, int nF, size_t elem = sizeof(float))
 {
-    return sizeof(float) * (2 * E + nF + (size_t)L * L + (size_t)AG_WARPS * (K + 3 * L + 6 * 32 + (2 * E + nF) * 32));
+    return elem * (2 * E + nF + (size_t)L * L + (size_t)AG_WARPS * (K + 3 * L + 6 * 32 + (2 * E + nF) * 32));
 }
 
 int agg_dims(AggDims& dm, int D, int L, int K, int E)
@@ -1445,11 +1460,11 @@ int pigs_aggregate_forward_rows(int64_t P, int D, int L, int K, int E, int64_t r
     }
     const size_t smem = agg_fwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
-    PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t grid = (row_hi - row_lo + AG_WARPS - 1) / AG_WARPS;
     const int64_t cap = (int64_t)num_sms() * 16;
     if (grid > cap) grid = cap;
-    agg_forward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+    agg_forward_kernel<float><<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
         row_lo, row_hi, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
         inv_total_densities, weights, embeddings, factors, neighbor_features);
     PIGS_LAUNCH_CHECK();
@@ -1502,12 +1517,66 @@ int pigs_aggregate_backward_rows(int64_t P, int D, int L, int K, int E, int64_t 
     }
     const size_t smem = agg_bwd_smem(L, K, E, dm.nF);
     PIGS_ARG(smem <= 200 * 1024);
-    PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int64_t grid = (row_hi - row_lo + AG_WARPS - 1) / AG_WARPS;
     const int64_t cap = (int64_t)num_sms() * 2;
     if (grid > cap) grid = cap;
-    agg_backward_kernel<<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+    agg_backward_kernel<float><<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
         row_lo, row_hi, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities, weights,
+        embeddings, factors, inv_total_densities, dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
+        dL_dfrequencies, dL_ddistance_transform);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+// ---- float64 instantiation of the generic aggregation kernels (the reference's `typedef double FLOAT` build) -----------
+int pigs_aggregate_forward_f64(int64_t P, int D, int L, int K, int E, const double* features, const double* transform,
+                               const double* queries, const double* keys, const double* frequencies,
+                               const double* distance_transform, const int64_t* indices, const int64_t* ranges,
+                               const double* dists, const double* densities, const double* inv_total_densities,
+                               double* weights, double* embeddings, double* factors, double* neighbor_features, void* stream)
+{
+    AggDims dm;
+    int rc = agg_dims(dm, D, L, K, E);
+    if (rc) return rc;
+    PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
+             neighbor_features && weights && embeddings && factors);
+    PIGS_ARG(dm.nF == 0 || frequencies);
+    const size_t smem = agg_fwd_smem(L, K, E, dm.nF, sizeof(double));
+    PIGS_ARG(smem <= 200 * 1024);
+    PIGS_CHECK(cudaFuncSetAttribute(agg_forward_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    const int64_t cap = (int64_t)num_sms() * 8;
+    if (grid > cap) grid = cap;
+    agg_forward_kernel<double><<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+        0, P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities,
+        inv_total_densities, weights, embeddings, factors, neighbor_features);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
+
+int pigs_aggregate_backward_f64(int64_t P, int D, int L, int K, int E, const double* features, const double* transform,
+                                const double* queries, const double* keys, const double* frequencies,
+                                const double* distance_transform, const int64_t* indices, const int64_t* ranges,
+                                const double* dists, const double* densities, const double* weights, const double* embeddings,
+                                const double* factors, const double* inv_total_densities, const double* dL_dneighbor_features,
+                                double* dL_dfeatures, double* dL_dtransform, double* dL_dqueries, double* dL_dkeys,
+                                double* dL_dfrequencies, double* dL_ddistance_transform, void* stream)
+{
+    AggDims dm;
+    int rc = agg_dims(dm, D, L, K, E);
+    if (rc) return rc;
+    PIGS_ARG(P > 0 && features && transform && queries && keys && distance_transform && ranges && inv_total_densities &&
+             dL_dneighbor_features && dL_dfeatures && dL_dtransform && dL_dqueries && dL_dkeys && dL_ddistance_transform);
+    PIGS_ARG(dm.nF == 0 || (frequencies && dL_dfrequencies));
+    const size_t smem = agg_bwd_smem(L, K, E, dm.nF, sizeof(double));
+    PIGS_ARG(smem <= 200 * 1024);
+    PIGS_CHECK(cudaFuncSetAttribute(agg_backward_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t grid = (P + AG_WARPS - 1) / AG_WARPS;
+    const int64_t cap = (int64_t)num_sms() * 2;
+    if (grid > cap) grid = cap;
+    agg_backward_kernel<double><<<(unsigned)grid, AG_THREADS, smem, (cudaStream_t)stream>>>(
+        0, P, dm, features, transform, queries, keys, frequencies, distance_transform, indices, ranges, dists, densities, weights,
         embeddings, factors, inv_total_densities, dL_dneighbor_features, dL_dfeatures, dL_dtransform, dL_dqueries, dL_dkeys,
         dL_dfrequencies, dL_ddistance_transform);
     PIGS_LAUNCH_CHECK();

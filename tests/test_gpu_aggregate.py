@@ -295,6 +295,30 @@ def test_multi_head_node_equals_per_head_calls():
         assert rel_err(x.grad.cpu().numpy(), y.grad.cpu().numpy()) <= TOL, nm
 
 
+def test_float64_gradcheck_like_the_reference_test():
+    """The reference's one live test: torch.autograd.gradcheck of aggregate_neighbors on float64 tensors
+    (test_neighbor_aggregation.py:15-27, 69-101: 5x5 grid, LATENT 2, KEY 4, EMBEDDING 21), which there needs the
+    `typedef double FLOAT` build (cuda_sampler/config.h:20).  Here the generic kernels are instantiated for double."""
+    import torch
+    from pigs_b200 import GaussianSampler
+    rec = AGG_RECIPES["agg_grid5"]()
+    s, d = _prep(rec)
+    g = torch.Generator().manual_seed(0)
+    P = rec["means"].shape[0]
+    mk = lambda *sh: torch.rand(sh, generator=g, dtype=torch.float64).cuda().requires_grad_(True)
+    features, transform, queries, keys = mk(P, 2), mk(2, 2), mk(P, 4), mk(P, 4)
+    frequencies = (torch.randn(5, generator=g, dtype=torch.float64) * 10).cuda().requires_grad_(True)
+    distance_transform = mk(2, 42)
+    out = s.aggregate_neighbors(features, transform, queries, keys, frequencies, distance_transform)
+    assert out.dtype == torch.float64 and out.shape == (P, 2)
+    # the float32 product path on the same values agrees with the double one to fp32 accuracy
+    out32 = s.aggregate_neighbors(*[t.detach().float() for t in (features, transform, queries, keys, frequencies, distance_transform)])
+    assert rel_err(out32.cpu().numpy(), out.detach().cpu().numpy()) <= TOL
+    fn = lambda *a: s.aggregate_neighbors(*a)
+    assert torch.autograd.gradcheck(fn, (features, transform, queries, keys, frequencies, distance_transform),
+                                    nondet_tol=1e-9)  # double atomics: the summation order is not fixed (nor is the reference's)
+
+
 def test_unaligned_feature_rows_take_the_generic_kernels():
     """A features tensor whose storage starts 4 bytes off a 16-byte boundary (a view into a larger buffer): the specialised
     kernels' 16-byte row loads / vector REDs do not apply, the call falls back to the generic kernels, same results."""
