@@ -146,6 +146,9 @@ __device__ __forceinline__ void fwd_gaussian_block(const GaussFwd<D, C>& g, cons
     }
 }
 
+#ifndef PIGS_FWD_BLOCKED
+#define PIGS_FWD_BLOCKED 1
+#endif
 #ifndef PIGS_FWD_PACKED_ACC
 #define PIGS_FWD_PACKED_ACC 0
 #endif
@@ -266,13 +269,21 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
         if (!s_valid) break;
         const WorkItem it = s_item;
 
-        // ---- stationary operand: KS samples per thread, strided by the CTA width (coalesced) ----
+        // ---- stationary operand: KS samples per thread.  BLOCKED assignment (thread t owns samples t*KS .. t*KS+KS-1 of
+        // the chunk): in a part-filled chunk (the last one of every tile; a 125 K-sample shard fills its chunks to 95 %) the
+        // unused slots fall into WHOLE warps, whose batch loops run with a zero count and leave their issue slots to the SM's
+        // other warps, instead of every thread computing 6-7 live and 1-2 dummy samples.  Measured (tools/fwd_shard_probe.py,
+        // profiles/r03r_fwd_shard_probe.json): 125 K samples 11.27 -> 10.88 ms, 500 K 40.85 -> 40.69, 4 M unchanged (319.3) ----
         float x[KS][D];
         uint32_t sid[KS];
         float acc[KS][C][NA];
 #pragma unroll
         for (int s = 0; s < KS; s++) {
+#if PIGS_FWD_BLOCKED
+            const uint32_t idx = tid * KS + s;
+#else
             const uint32_t idx = tid + s * EV_THREADS;
+#endif
             sid[s] = idx < it.s_count ? slist[it.s_begin + idx] : 0xffffffffu;
 #pragma unroll
             for (int d = 0; d < D; d++) x[s][d] = sid[s] != 0xffffffffu ? samples[(size_t)sid[s] * D + d] : 0.0f;
@@ -301,6 +312,10 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                 for (int k = 0; k < NA; k++) accp[p][k] = bc2(0.0f);
         }
 
+#if PIGS_FWD_BLOCKED
+        // whole warps without samples (part-filled chunk, blocked assignment) run the batch loop with a zero count
+        const int live_mask = (uint32_t)((tid & ~31) * KS) < it.s_count ? -1 : 0;
+#endif
         // ---- streamed operand: Gaussian records through shared memory, double-buffered ----
         const float4* __restrict__ src = recs + (size_t)it.g_begin * NV;
         const uint32_t total_v4 = it.g_count * NV;
@@ -324,7 +339,11 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
                     pre[k] = o < total_v4 ? src[o] : make_float4(0.f, 0.f, 0.f, 0.f);
                 }
             }
+#if PIGS_FWD_BLOCKED
+            const int cnt = min((int)FWD_GB, (int)it.g_count - b * FWD_GB) & live_mask;
+#else
             const int cnt = min((int)FWD_GB, (int)it.g_count - b * FWD_GB);
+#endif
             const float4* __restrict__ batch = sm[buf];
 #pragma unroll 1
             for (int j = 0; j < cnt; j++) {
