@@ -379,16 +379,27 @@ __device__ __forceinline__ float nb_emit_core(int64_t slot, uint32_t j, const fl
         const float a = __fmul_rn(__fmul_rn(c0, X[0]), X[0]);
         const float q = __fmaf_rn(__fmul_rn(c2, X[D - 1]), X[D - 1], a);
         const float m = __fmul_rn(__fmul_rn(c1, X[0]), X[D - 1]);
-        power = __double2float_rn(-0.5 * (double)q - (double)m);
+        // The reference forms -0.5 * (double)q - (double)m and rounds it to float.  One float FMA forms the same exact
+        // value and rounds it once: the two can differ in the last bit of a tie, never in sign, so the `power > 0` skip
+        // (which decides an INDEX, bit-exact) is the same; only a result that underflows takes the double detour.
+        // (ncu, profiles/r03h_ncu_nb.json: the fill pass is issue bound; the F2F / DFMA / F2F chain and the full-range
+        // expf below were a quarter of its instructions.)
+        power = __fmaf_rn(-0.5f, q, -m);
+        if (fabsf(power) < 1e-30f) power = __double2float_rn(-0.5 * (double)q - (double)m);
     }
+    if (D == 2) {
+        reinterpret_cast<float2*>(dists)[slot] = make_float2(__fmul_rn(X[0], inv_r), __fmul_rn(X[D - 1], inv_r));
+    } else {
 #pragma unroll
-    for (int d = 0; d < D; d++) dists[slot * D + d] = __fmul_rn(X[d], inv_r);
+        for (int d = 0; d < D; d++) dists[slot * D + d] = __fmul_rn(X[d], inv_r);
+    }
     if (power > 0.0f) {  // skipped by the reference: index stays -1, density 0
         indices[slot] = -1;
         densities[slot] = 0.0f;
         return 0.0f;
     }
-    const float dens = expf(power);
+    // exp through MUFU.EX2 (2 ulp; the evaluation kernels' own exp): densities are compared to 1e-5, not bit for bit
+    const float dens = D == 2 ? ex2_approx(__fmul_rn(power, 1.4426950408889634f)) : expf(power);
     densities[slot] = dens;
     indices[slot] = (int64_t)j;
     return dens;
