@@ -190,6 +190,18 @@ int pigs_neighbors_fill(int64_t P, int D, const float *means, const float *conic
 size_t pigs_neighbors_scan_workspace_bytes(int64_t P);
 int pigs_neighbors_ranges(int64_t P, const int64_t *counts, int64_t *ranges, int64_t *total, void *workspace,
                           void *stream);
+/* Allocation-free variant of pigs_neighbors_ranges.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same inputs, outputs and results as pigs_neighbors_ranges, but the scan's scratch (ticket +
+ * one 64-bit descriptor per 4096-row tile) is a file-scope `static __device__` array inside the library (32 KB + 256 B
+ * per GPU that loads the library, held until the process exits) whose device address is resolved once per device with
+ * cudaGetSymbolAddress; the call itself performs no cudaMalloc / cudaFree / allocating library routine.
+ * Limit: P <= PIGS_RANGES_STATIC_MAX_P rows; a larger P returns -1 with a pigs_last_error() text naming the limit.
+ * Every call on a device shares the one array (the call clears the words it uses before its launch): calls that OVERLAP
+ * on the GPU — different streams, or graph branches without an ordering edge — race; serialise them.  The first call on a
+ * device resolves the symbol address; make it outside graph capture. */
+#define PIGS_RANGES_STATIC_MAX_P 16777216 /* 2^24 rows (16x the P = 1M of BASELINE config 5) */
+int pigs_neighbors_ranges_static(int64_t P, const int64_t *counts, int64_t *ranges, int64_t *total, void *stream);
 /* The same two stages for the rows (query Gaussians) [row_lo, row_hi) only — multi-GPU aggregation shards the CSR by
  * query Gaussian.  Every Gaussian stays a candidate neighbour; rows outside the window get count 0 and
  * the no-neighbour total 1/(0 + 1e-6), so the aggregation kernels run unchanged on the sharded CSR. */

@@ -74,6 +74,7 @@ SIGNATURES = {
     "pigs_neighbors_fill": (c_int, [c_int64, c_int] + [c_void_p] * 10),
     "pigs_neighbors_scan_workspace_bytes": (c_size_t, [c_int64]),
     "pigs_neighbors_ranges": (c_int, [c_int64] + [c_void_p] * 5),
+    "pigs_neighbors_ranges_static": (c_int, [c_int64] + [c_void_p] * 4),
     "pigs_neighbors_count_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 3),
     "pigs_neighbors_fill_rows": (c_int, [c_int64, c_int, c_void_p, c_void_p, c_void_p, c_int64, c_int64] + [c_void_p] * 7),
     "pigs_aggregate_forward": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 16),

@@ -562,3 +562,65 @@ int pigs_stage_timing_read(const char** names, float* ms, int cap)
 }
 
 }  // extern "C"
+
+// ---- allocation-free variant of pigs_neighbors_ranges ---------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  The look-back scan's scratch — [ticket u64]
+// [descriptor u64 x tiles] — lives in a file-scope device array instead of a caller workspace.  Sized like
+// scan_ws_bytes() for the stated maximum of PIGS_RANGES_STATIC_MAX_P rows (one descriptor per 4096-element tile + the
+// ticket): 32 KB + 256 B that every GPU which loads the library holds until the process exits.
+namespace pigs {
+
+constexpr int64_t RANGES_STATIC_MAX_P = PIGS_RANGES_STATIC_MAX_P;
+constexpr int64_t RANGES_STATIC_WORDS = RANGES_STATIC_MAX_P / LB_TILE + 2;
+static __device__ __align__(256) unsigned long long g_ranges_static_scratch[RANGES_STATIC_WORDS];
+
+// In host code `g_ranges_static_scratch` is a host-side stand-in, NOT a device address: the device address is resolved
+// once per device (with that device current) through cudaGetSymbolAddress and kept here.
+constexpr int RANGES_STATIC_MAX_DEVICES = 64;
+static unsigned long long* g_ranges_static_ptr[RANGES_STATIC_MAX_DEVICES] = {};
+
+static int ranges_static_scratch(unsigned long long** out)
+{
+    int dev = -1;
+    PIGS_CHECK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= RANGES_STATIC_MAX_DEVICES)
+        return set_error(-1, "pigs_neighbors_ranges_static: device ordinal beyond the 64 this entry point tracks", __FILE__, __LINE__);
+    unsigned long long* p = __atomic_load_n(&g_ranges_static_ptr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void* sym = nullptr;
+        PIGS_CHECK(cudaGetSymbolAddress(&sym, g_ranges_static_scratch));
+        if (!sym) return set_error(-1, "pigs_neighbors_ranges_static: cudaGetSymbolAddress returned a null address", __FILE__, __LINE__);
+        p = (unsigned long long*)sym;  // every thread resolves the same address for one device: a racing store is benign
+        __atomic_store_n(&g_ranges_static_ptr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return 0;
+}
+
+}  // namespace pigs
+
+extern "C" int pigs_neighbors_ranges_static(int64_t P, const int64_t* counts, int64_t* ranges, int64_t* total, void* stream)
+{
+    using namespace pigs;
+    PIGS_ARG(P > 0 && counts && ranges && total);
+    if (P > RANGES_STATIC_MAX_P) {
+        static thread_local char msg[160];
+        snprintf(msg, sizeof(msg), "pigs_neighbors_ranges_static: P = %lld exceeds the static scratch's maximum of %lld rows "
+                 "(use pigs_neighbors_ranges with a caller workspace)", (long long)P, (long long)RANGES_STATIC_MAX_P);
+        return set_error(-1, msg, __FILE__, __LINE__);
+    }
+    unsigned long long* ws = nullptr;
+    int rc = ranges_static_scratch(&ws);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t)stream;
+    int64_t nb, span;
+    scan_shape(P, nb, span);
+    if (nb + 1 > RANGES_STATIC_WORDS)
+        return set_error(-1, "pigs_neighbors_ranges_static: more scan spans than the static scratch holds", __FILE__, __LINE__);
+    // the array keeps the previous call's ticket and descriptors: clear what this launch reads before it runs
+    PIGS_CHECK(cudaMemsetAsync(ws, 0, (size_t)(nb + 1) * sizeof(unsigned long long), st));
+    scan_lookback_kernel<int64_t, true><<<(unsigned)nb, SCAN_THREADS, 0, st>>>(counts, ranges, P, 0, ws, (long long*)total, span);
+    PIGS_LAUNCH_CHECK();
+    return 0;
+}
