@@ -161,6 +161,16 @@ int pigs_get_deterministic(void);
  * in order on the caller's stream.  Results are the same up to the order of the RED.ADDs. */
 void pigs_set_class_concurrency(int on);
 
+/* Library-level option (default 20 000 000; environment PIGS_SMALL_PAIRS; read by pigs_preprocess_bin).  Problems whose
+ * estimated pair count — num_rendered x N / blocks — is at most `pairs` are launch-bound (the reference's own drivers:
+ * 1 K Gaussians x 10 K points), so the binning puts every (tile, Gaussian) instance into the GENERAL class (the exact
+ * per-pair torus wrap and `power > 0` skip of forward.cu:149-171: the reference's own arithmetic) and every forward /
+ * backward call of that binning launches ONE evaluation kernel instead of three on forked streams.  Results stay within
+ * the parity tolerance of the three-class path (tests compare the two).  0 disables it.  The library remembers on the
+ * host which binning buffers were built this way (by address and sizes); a buffer it does not know — e.g. a copy — gets
+ * the three launches, which are correct for both kinds. */
+void pigs_set_small_problem_pairs(int64_t pairs);
+
 /* Optional per-stage device timing of the preprocess chain (development: tools/chain_timing.py).  While on, the
  * library records a cudaEvent behind each stage of pigs_sample_bounds / pigs_preprocess_count / pigs_preprocess_bin;
  * pigs_stage_timing_read synchronises on them and returns (stage name, ms since the previous mark) pairs. */

@@ -65,6 +65,7 @@ SIGNATURES = {
     "pigs_set_deterministic": (None, [c_int]),
     "pigs_get_deterministic": (c_int, []),
     "pigs_set_class_concurrency": (None, [c_int]),
+    "pigs_set_small_problem_pairs": (None, [c_int64]),
     "pigs_set_stage_timing": (None, [c_int]),
     "pigs_stage_timing_read": (c_int, [c_void_p, c_void_p, c_int]),
     "pigs_set_kernel_timing": (None, [c_int]),

@@ -101,6 +101,7 @@ int resolve(EvalCall& c, int64_t P, int D, int64_t N, int C, int blocks, int64_t
     c.bbox = s.bbox;
     c.ranges = (const uint2*)ranges;
     c.sample_ranges = (const uint2*)sample_ranges;
+    c.single_class = small_binning_lookup(binning_buffer, R, N, blocks);
     return 0;
 }
 
@@ -116,6 +117,7 @@ void pigs_set_debug(int on) { g_debug_sync = on ? 1 : 0; }
 void pigs_set_deterministic(int on) { g_deterministic = on ? 1 : 0; }
 int pigs_get_deterministic(void) { return g_deterministic; }
 void pigs_set_class_concurrency(int on) { g_class_concurrency = on ? 1 : 0; }
+void pigs_set_small_problem_pairs(int64_t pairs) { g_small_pairs = pairs < 0 ? 0 : pairs; }
 int pigs_get_debug(void) { return g_debug_sync; }
 
 void pigs_set_kernel_timing(int on)

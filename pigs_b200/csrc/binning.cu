@@ -653,9 +653,11 @@ int pigs_preprocess_bin(int64_t P, int D, int64_t N, int blocks, int64_t num_ren
         }
     }
     // evaluation staging that depends on the binning only: instance classes, their scan, the three work lists
+    const bool single_class = num_rendered > 0 && small_problem(num_rendered, N, blocks);
+    small_binning_note(binning_buffer, num_rendered, N, blocks, single_class);
     if (num_rendered > 0) {
         int rc = stage_classes(D, blocks, num_rendered, N, means, conics, s.bbox, (const uint2*)ranges,
-                               (const uint2*)sample_ranges, b, st);
+                               (const uint2*)sample_ranges, b, st, single_class);
         if (rc) return rc;
     }
     return 0;

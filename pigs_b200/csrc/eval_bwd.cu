@@ -800,6 +800,11 @@ template <int D, int C, unsigned MASK>
 static int launch_bwd_t(const EvalCall& c, int ch0, const EvalWs& ws, BwdOut o, cudaStream_t st)
 {
     const TileSeg* segs = c.segs + (size_t)WL_BWD * EV_NSEG * c.blocks;
+    if (c.single_class) {  // small problem: every instance is GENERAL (pack.cu stage_classes) -> one launch, no fork / join
+        launch_bwd_m<D, C, MASK, EV_GENERAL>(c, segs, ch0, ws, o, st);
+        PIGS_LAUNCH_CHECK();
+        return 0;
+    }
     ClassFork fk;
     int rc = fk.fork(st);
     if (rc) return rc;

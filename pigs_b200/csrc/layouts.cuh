@@ -92,6 +92,7 @@ struct EvalCall {
     const uint32_t* scode;
     const TileSeg* segs;            // [WL_COUNT][EV_NSEG][blocks]
     const WorkTemplate* wt;         // [WL_COUNT]
+    bool single_class = false;      // the binning put every instance into the GENERAL class (small_binning_*): one kernel
 };
 
 // per-call workspace (torch-owned, sized by pigs_eval_workspace_bytes)
@@ -116,7 +117,20 @@ struct EvalWs {
 // once per preprocess (called from pigs_preprocess_bin): classify every (tile, Gaussian) instance, scan the class flags,
 // build the three work lists
 int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, const float* conics, const float* bbox,
-                  const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st);
+                  const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st, bool single_class = false);
+
+// Small problems (the reference's own drivers: 1 K Gaussians x 10 K points) are launch-bound: the three class kernels of a
+// call plus the fork / join of their streams cost more than the arithmetic.  Below g_small_pairs estimated pairs
+// (instances x samples per tile) stage_classes puts EVERY instance into the GENERAL class (exact per-pair wrap and skip:
+// the reference's own arithmetic, so results stay inside the parity tolerance of the three-class path) and writes the
+// scanned class prefix directly (no scan launch); forward / backward then launch the GENERAL kernel alone.  What a call
+// may assume about a binning buffer is recorded on the host when pigs_preprocess_bin fills it (small_binning_note) and
+// looked up by (pointer, R, N, blocks) at evaluation time (small_binning_lookup): an unknown buffer — a copy, another
+// process' — gets the three launches, which are correct for either kind of buffer.
+extern int64_t g_small_pairs;  // pigs_set_small_problem_pairs; 0 = never
+bool small_problem(int64_t R, int64_t N, int blocks);
+void small_binning_note(const void* binning_buffer, int64_t R, int64_t N, int blocks, bool single_class);
+bool small_binning_lookup(const void* binning_buffer, int64_t R, int64_t N, int blocks);
 // per call: packed Gaussian records in class order + the call's WorkHeader (from work list `wl`)
 int stage_gaussians(const EvalCall& c, int C, int ch0, bool fwd_layout, int wl, const EvalWs& ws, cudaStream_t st);
 // lap: gH is the upstream gradient of the Laplacian [N, C] (PIGS_FN_LAPL) instead of the Hessian's [N, D, D, C]

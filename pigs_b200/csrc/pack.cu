@@ -12,6 +12,8 @@
 
 #include <stdlib.h>
 
+#include <mutex>
+
 namespace pigs {
 
 // Classification of every (tile, Gaussian) list entry (classes: eval_common.cuh).
@@ -59,6 +61,17 @@ __global__ void __launch_bounds__(256) flag_kernel(int64_t R, const uint32_t* __
     const bool general = !ok;
     cls[e] = general ? CLS_GENERAL : (code != 0u ? CLS_SHIFT : 0ull);
     scode[e] = general ? 0u : code;
+}
+
+// Small problems / single-class mode: every instance GENERAL, so the EXCLUSIVE SCAN of the flags is known in closed form
+// (cls[e] = e * CLS_GENERAL, total at [R]) and is written directly: no flag pass, no scan launch.
+__global__ void __launch_bounds__(256) flag_all_general_kernel(int64_t R, unsigned long long* __restrict__ cls,
+                                                               uint32_t* __restrict__ scode)
+{
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e > R) return;
+    cls[e] = (unsigned long long)e * CLS_GENERAL;
+    if (e < R) scode[e] = 0u;
 }
 
 // cls = exclusive scan of the packed class flags (with the total at [R]).  Writes the records in partitioned order
@@ -329,6 +342,64 @@ struct ForkState {
 ForkState g_fork[64];  // per device
 }  // namespace
 
+int64_t g_small_pairs = -1;  // -1: not read yet (env PIGS_SMALL_PAIRS, default 20 M pairs)
+
+static int64_t small_pairs_threshold()
+{
+    if (g_small_pairs < 0) {
+        const char* e = getenv("PIGS_SMALL_PAIRS");
+        g_small_pairs = e ? atoll(e) : 20000000ll;
+        if (g_small_pairs < 0) g_small_pairs = 0;
+    }
+    return g_small_pairs;
+}
+
+bool small_problem(int64_t R, int64_t N, int blocks)
+{
+    const int64_t thr = small_pairs_threshold();
+    if (thr <= 0 || R <= 0 || blocks <= 0) return false;
+    // estimated pairs = instances x average samples per tile (exact when the tiles are equally populated)
+    const double est = (double)R * ((double)N / (double)blocks);
+    return est <= (double)thr;
+}
+
+namespace {
+struct SmallNote {
+    const void* ptr;
+    int64_t R, N;
+    int blocks;
+    bool single;
+};
+constexpr int SMALL_NOTES = 256;
+SmallNote g_notes[SMALL_NOTES];
+int g_note_next = 0;
+std::mutex g_note_mu;
+}  // namespace
+
+void small_binning_note(const void* ptr, int64_t R, int64_t N, int blocks, bool single)
+{
+    std::lock_guard<std::mutex> lk(g_note_mu);
+    for (int i = 0; i < SMALL_NOTES; i++) {
+        if (g_notes[i].ptr == ptr) {  // the buffer was refilled: its old note is void
+            g_notes[i] = SmallNote{ptr, R, N, blocks, single};
+            return;
+        }
+    }
+    if (!single) return;  // unknown buffers already mean "three classes"
+    g_notes[g_note_next] = SmallNote{ptr, R, N, blocks, single};
+    g_note_next = (g_note_next + 1) % SMALL_NOTES;
+}
+
+bool small_binning_lookup(const void* ptr, int64_t R, int64_t N, int blocks)
+{
+    std::lock_guard<std::mutex> lk(g_note_mu);
+    for (int i = 0; i < SMALL_NOTES; i++) {
+        const SmallNote& n = g_notes[i];
+        if (n.ptr == ptr) return n.single && n.R == R && n.N == N && n.blocks == blocks;
+    }
+    return false;
+}
+
 int ClassFork::fork(cudaStream_t st)
 {
     main = st;
@@ -376,21 +447,38 @@ int ClassFork::join()
 // ---------------------------------------------------------------------------------------------
 // host-side staging entry points
 // ---------------------------------------------------------------------------------------------
+static uint32_t small_min_stream(bool backward)
+{
+    static int v[2] = {0, 0};
+    if (v[backward] == 0) {
+        const char* e = getenv(backward ? "PIGS_SMALL_MIN_STREAM_BWD" : "PIGS_SMALL_MIN_STREAM_FWD");  // tuning hook
+        v[backward] = e ? atoi(e) : (backward ? 32 : 16);
+        if (v[backward] < 1) v[backward] = 32;
+    }
+    return (uint32_t)v[backward];
+}
+
 int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, const float* conics, const float* bbox,
-                  const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st)
+                  const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st, bool single_class)
 {
     const unsigned nb = (unsigned)((R + 255) / 256);
     // deterministic mode: every instance GENERAL (exact wrap + skip per pair), so a tile's list stays in ascending
     // Gaussian id and — with the forward's Gaussians unsplit — every output element is written by exactly one item
-    if (D == 2)
-        flag_kernel<2><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic, b.cls, b.scode);
-    else
-        flag_kernel<1><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic, b.cls, b.scode);
-    PIGS_LAUNCH_CHECK();
-    PIGS_STAGE(st, "class flags");
-    int rc = exclusive_scan_u64(b.cls, b.cls, R, true, b.scan_ws, st);
-    if (rc) return rc;
-    PIGS_STAGE(st, "class scan (u64)");
+    if (single_class && R < (int64_t)CLS_MASK) {
+        flag_all_general_kernel<<<(unsigned)((R + 256) / 256), 256, 0, st>>>(R, b.cls, b.scode);
+        PIGS_LAUNCH_CHECK();
+        PIGS_STAGE(st, "class flags (all general, scanned)");
+    } else {
+        if (D == 2)
+            flag_kernel<2><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic || single_class, b.cls, b.scode);
+        else
+            flag_kernel<1><<<nb, 256, 0, st>>>(R, b.list, b.tiles, means, conics, bbox, g_deterministic || single_class, b.cls, b.scode);
+        PIGS_LAUNCH_CHECK();
+        PIGS_STAGE(st, "class flags");
+        int rc = exclusive_scan_u64(b.cls, b.cls, R, true, b.scan_ws, st);
+        if (rc) return rc;
+        PIGS_STAGE(st, "class scan (u64)");
+    }
     WorkListCfg cfg;
     const uint32_t chunks[WL_COUNT] = {EV_THREADS * 8u, EV_THREADS * 4u, EV_THREADS * (uint32_t)bwd_kg(2, 1, 7u)};
     for (int wl = 0; wl < WL_COUNT; wl++) {
@@ -398,6 +486,9 @@ int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, c
         cfg.chunk[wl] = chunks[wl];
         cfg.split_hint[wl] = (g_deterministic && !bwd) ? 1u : split_hint(bwd ? R : N, chunks[wl], blocks, bwd);
         cfg.min_stream[wl] = bwd ? 128u : 256u;
+        // small problems are bound by the LONGEST work item, not by throughput (a few dozen items on 296 persistent CTAs):
+        // cut the streamed operand finer, so that every item is short and all of them run at once
+        if (single_class) cfg.min_stream[wl] = small_min_stream(bwd);
         cfg.stream_is_gauss[wl] = bwd ? 0 : 1;
     }
     worklist_kernel<<<WL_COUNT, 256, 0, st>>>(blocks, ranges, sample_ranges, b.cls, cfg, b.segs, b.wt);

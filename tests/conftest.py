@@ -25,3 +25,29 @@ def pytest_collection_modifyitems(config, items):
     for item in items:
         if "gpu" in item.keywords:
             item.add_marker(skip)
+
+
+# Small problems run ONE evaluation kernel (every instance in the GENERAL class, pigs_set_small_problem_pairs); the small
+# recipes of these modules would otherwise stop exercising the FAST / SHIFT kernels, so they run in both modes.
+_BOTH_CLASS_MODES = {"test_gpu_parity.py", "test_gpu_vs_reference.py", "test_culled.py"}
+SMALL_PAIRS_DEFAULT = 20_000_000
+
+
+def pytest_generate_tests(metafunc):
+    if os.path.basename(metafunc.module.__file__) in _BOTH_CLASS_MODES and "_class_mode" in metafunc.fixturenames:
+        metafunc.parametrize("_class_mode", ["single_class", "three_class"], indirect=True)
+
+
+@pytest.fixture(autouse=True)
+def _class_mode(request):
+    mode = getattr(request, "param", None)
+    if mode != "three_class":
+        yield mode
+        return
+    from pigs_b200 import _lib
+    L = _lib.lib()
+    L.pigs_set_small_problem_pairs(0)
+    try:
+        yield mode
+    finally:
+        L.pigs_set_small_problem_pairs(SMALL_PAIRS_DEFAULT)
