@@ -97,6 +97,16 @@ int pigs_preprocess_count_culled(int64_t P, int D, int64_t N, const float *means
                                  const float *d_minmax, float *radii, void *geom_ws, int subdiv,
                                  float cull_sigmas, void *stream);
 
+/* Bounds + stage A in one call (what the bindings call).  have_bounds = 0: the sample bounds are computed from
+ * `samples` and left in d_minmax (device float[2*D]); have_bounds = 1: d_minmax is an input (multi-GPU callers all-reduce
+ * it first) and `samples` may be NULL.  subdiv = 1 / cull_sigmas = 0 for the reference pair set.  Small problems
+ * (P <= 16 384 and N <= 16 384, the reference's own drivers; pigs_set_small_problem_pairs(0) switches it off) run ONE
+ * single-CTA launch instead of three dependent ones; larger ones run pigs_sample_bounds + pigs_preprocess_count_culled.
+ * Same results either way, bit for bit. */
+int pigs_preprocess_count_fused(int64_t P, int D, int64_t N, const float *means, const float *covariances,
+                                const float *samples, float *d_minmax, int have_bounds, float *radii, void *geom_ws,
+                                int subdiv, float cull_sigmas, void *stream);
+
 /* ---- preprocess stage B: key emission, stable sort by tile, ranges; sample binning ---------------
  * (sampler_impl.cu:54-189, 259-327).  Sizes are functions of the header values read back by the host.
  * Also builds, once per preprocess, the evaluation staging that depends on the binning only and is reused by every

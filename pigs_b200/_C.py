@@ -132,14 +132,12 @@ def preprocess_gaussians(means, values, covariances, conics, samples, debug, bou
     if cov.numel() != P * D * (D + 1) // 2:
         raise RuntimeError("covariances must hold P*D*(D+1)/2 elements")
     st = _stream()
-    mm = sample_bounds(samples, D) if bounds is None else _f32c(bounds, "bounds")
+    mm = torch.empty(2 * D, dtype=torch.float32, device=dev) if bounds is None else _f32c(bounds, "bounds")
     geom = _bytes(L.pigs_geom_workspace_bytes(P), dev)
-    if cull is None:
-        check(L.pigs_preprocess_count(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom), st),
-              "pigs_preprocess_count")
-    else:
-        check(L.pigs_preprocess_count_culled(P, D, N, _ptr(means), _ptr(cov), _ptr(mm), _ptr(radii), _ptr(geom),
-                                             int(cull[1]), float(cull[0]), st), "pigs_preprocess_count_culled")
+    # bounds + tile grid + radii / tiles touched + scan: one single-CTA launch for small problems, the grid-wide chain else
+    subdiv, sigmas = (1, 0.0) if cull is None else (int(cull[1]), float(cull[0]))
+    check(L.pigs_preprocess_count_fused(P, D, N, _ptr(means), _ptr(cov), _ptr(samples), _ptr(mm), 0 if bounds is None else 1,
+                                        _ptr(radii), _ptr(geom), subdiv, sigmas, st), "pigs_preprocess_count_fused")
     h = read_header(geom)
     blocks, R = int(h.blocks), int(h.num_rendered)
     binning = _bytes(L.pigs_binning_bytes(R, blocks), dev)

@@ -49,6 +49,8 @@ SIGNATURES = {
     "pigs_preprocess_count": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
     "pigs_preprocess_count_culled": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                              c_int, ctypes.c_float, c_void_p]),
+    "pigs_preprocess_count_fused": (c_int, [c_int64, c_int, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p,
+                                            c_void_p, c_int, ctypes.c_float, c_void_p]),
     "pigs_binning_bytes": (c_size_t, [c_int64, c_int]),
     "pigs_sample_binning_bytes": (c_size_t, [c_int64, c_int, c_int]),
     "pigs_sort_workspace_bytes": (c_size_t, [c_int64, c_int64]),

@@ -189,7 +189,7 @@ int pigs_sample_forward(unsigned fn_mask, int64_t P, int D, int64_t N, int C, in
         unsigned todo[2] = {native_low_mask(lap_native ? ((fn_mask & 3u) | PIGS_FN_LAPL) : fn_mask), fn_mask & PIGS_FN_THIRD};
         for (unsigned m : todo) {
             if (!m) continue;
-            const int wl = fwd_ks(D, cw, m) == 8 ? WL_FWD8 : WL_FWD4;
+            const int wl = fwd_ks(D, cw, m) >= 8 ? WL_FWD8 : WL_FWD4;
             rc = stage_gaussians(c, cw, ch0, true, wl, ws, st);  // packed records + this launch's work header
             if (rc) return rc;
             FwdOut o;

@@ -53,7 +53,13 @@ __host__ __device__ constexpr int frec_v4(int D, int C) { return (frec_floats(D,
 __host__ __device__ constexpr int srec_floats(int D, int C, unsigned mask) { return D + C * nacc(D, mask); }
 __host__ __device__ constexpr int srec_v4(int D, int C, unsigned mask) { return (srec_floats(D, C, mask) + 3) / 4; }
 // samples per thread (forward) / Gaussians per thread (backward)
-__host__ __device__ constexpr int fwd_ks(int D, int C, unsigned mask) { return (D + C * nacc(D, mask)) <= 8 ? 8 : 4; }
+#ifndef PIGS_FWD_KS16
+#define PIGS_FWD_KS16 0  // experiment: 16 samples per thread (one CTA per SM, 255 registers) for the fused 2-D kernel
+#endif
+__host__ __device__ constexpr int fwd_ks(int D, int C, unsigned mask)
+{
+    return (PIGS_FWD_KS16 && D == 2 && C == 1 && mask == 7u) ? 16 : ((D + C * nacc(D, mask)) <= 8 ? 8 : 4);
+}
 __host__ __device__ constexpr int bwd_kg(int D, int C, unsigned mask) { return 4; }
 
 // ---- work lists --------------------------------------------------------------------------------

@@ -244,7 +244,7 @@ __device__ __forceinline__ void fwd_one_gaussian(const GaussFwd<D, C>& g, const 
 }
 
 template <int D, int C, unsigned MASK, int MODE>
-__global__ void __launch_bounds__(EV_THREADS, 2)
+__global__ void __launch_bounds__(EV_THREADS, (fwd_ks(D, C, MASK) == 16 ? 1 : 2))
     eval_fwd_kernel(int blocks, const TileSeg* __restrict__ segs, WorkHeader* __restrict__ wh,
                     const float4* __restrict__ recs, const uint32_t* __restrict__ slist,
                     const float* __restrict__ samples, int Ctot, int ch0, float* __restrict__ out_u,
@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(EV_THREADS, 2)
 template <int D, int C, unsigned MASK, int MODE>
 static void launch_fwd_m(const EvalCall& c, const TileSeg* segs, int ch0, const EvalWs& ws, FwdOut o, cudaStream_t st)
 {
-    eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * 2, EV_THREADS, 0, st>>>(c.blocks, segs, ws.wh, ws.recs, c.slist, c.samples,
+    eval_fwd_kernel<D, C, MASK, MODE><<<num_sms() * (fwd_ks(D, C, MASK) == 16 ? 1 : 2), EV_THREADS, 0, st>>>(c.blocks, segs, ws.wh, ws.recs, c.slist, c.samples,
                                                                            c.C, ch0, o.u, o.du, o.ddu, o.dddu, o.lap);
 }
 

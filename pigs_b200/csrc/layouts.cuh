@@ -127,7 +127,8 @@ int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, c
 // may assume about a binning buffer is recorded on the host when pigs_preprocess_bin fills it (small_binning_note) and
 // looked up by (pointer, R, N, blocks) at evaluation time (small_binning_lookup): an unknown buffer — a copy, another
 // process' — gets the three launches, which are correct for either kind of buffer.
-extern int64_t g_small_pairs;  // pigs_set_small_problem_pairs; 0 = never
+extern int64_t g_small_pairs;  // pigs_set_small_problem_pairs; 0 = never; -1 = not read from the environment yet
+int64_t small_pairs_threshold();
 bool small_problem(int64_t R, int64_t N, int blocks);
 void small_binning_note(const void* binning_buffer, int64_t R, int64_t N, int blocks, bool single_class);
 bool small_binning_lookup(const void* binning_buffer, int64_t R, int64_t N, int blocks);

@@ -9,6 +9,7 @@
 // All HBM-bound, a few bytes per list entry; no host synchronisation.
 #include "eval_common.cuh"
 #include "layouts.cuh"
+#include "worklist.cuh"
 
 #include <stdlib.h>
 
@@ -208,102 +209,13 @@ __global__ void __launch_bounds__(256) pack_samples_kernel(int64_t N, const uint
     for (int k = 0; k < SV; k++) srecs[(size_t)i * SV + k] = make_float4(f[4 * k], f[4 * k + 1], f[4 * k + 2], f[4 * k + 3]);
 }
 
-// One CTA per work list (blockIdx.x = WL_FWD8 | WL_FWD4 | WL_BWD).  For every tile: the FAST / SHIFT / GENERAL segments
-// and how many work items each yields.
-//   forward : stationary = samples in chunks of `chunk`, streamed = Gaussians split `split_hint` ways
-//   backward: stationary = Gaussians in chunks of `chunk`, streamed = samples split `split_hint` ways
-struct WorkListCfg {
-    uint32_t chunk[WL_COUNT], split_hint[WL_COUNT], min_stream[WL_COUNT];
-    int stream_is_gauss[WL_COUNT];
-};
-
 __global__ void __launch_bounds__(256) worklist_kernel(int blocks, const uint2* __restrict__ ranges,
                                                        const uint2* __restrict__ sample_ranges,
                                                        const unsigned long long* __restrict__ cls, WorkListCfg cfg,
                                                        TileSeg* __restrict__ segs_all /* [WL_COUNT][EV_NSEG][blocks] */,
                                                        WorkTemplate* __restrict__ wt_all)
 {
-    const int wl = blockIdx.x;
-    const uint32_t chunk = cfg.chunk[wl], split_hint = cfg.split_hint[wl], min_stream = cfg.min_stream[wl];
-    const int stream_is_gauss = cfg.stream_is_gauss[wl];
-    TileSeg* segs = segs_all + (size_t)wl * EV_NSEG * blocks;
-    __shared__ uint32_t s_scan[256];
-    __shared__ uint32_t s_carry[EV_NSEG];
-    __shared__ unsigned long long s_pairs;
-    if (threadIdx.x == 0) {
-        for (int k = 0; k < EV_NSEG; k++) s_carry[k] = 0;
-        s_pairs = 0ull;
-    }
-    __syncthreads();
-    unsigned long long my_pairs = 0;
-    for (int base = 0; base < blocks; base += 256) {
-        const int t = base + threadIdx.x;
-        TileSeg sg[EV_NSEG];
-        uint32_t items[EV_NSEG];
-#pragma unroll
-        for (int k = 0; k < EV_NSEG; k++) items[k] = 0;
-        if (t < blocks) {
-            const uint2 gr = ranges[t], sr = sample_ranges[t];
-            const uint32_t G = gr.y - gr.x, S = sr.y - sr.x;
-            uint32_t ng = 0, ns = 0;
-            if (G > 0) {
-                const unsigned long long c0 = cls[gr.x], c1 = cls[gr.y];
-                ng = (uint32_t)((c1 & CLS_MASK) - (c0 & CLS_MASK));
-                ns = (uint32_t)((c1 >> 31) - (c0 >> 31));
-            }
-            const uint32_t nf = G - ng - ns;
-            my_pairs += (unsigned long long)G * S;
-            const uint32_t begin[EV_NSEG] = {gr.x, gr.x + nf, gr.x + nf + ns};
-            const uint32_t count[EV_NSEG] = {nf, ns, ng};
-#pragma unroll
-            for (int k = 0; k < EV_NSEG; k++) {
-                sg[k].g_begin = begin[k];
-                sg[k].g_count = count[k];
-                sg[k].s_begin = sr.x;
-                sg[k].s_count = S;
-                const uint32_t stat_n = stream_is_gauss ? sg[k].s_count : sg[k].g_count;
-                const uint32_t strm_n = stream_is_gauss ? sg[k].g_count : sg[k].s_count;
-                uint32_t split = 1;
-                if (stat_n > 0 && strm_n > 0) {
-                    split = min(split_hint, (strm_n + min_stream - 1) / min_stream);
-                    if (split < 1) split = 1;
-                    items[k] = ((stat_n + chunk - 1) / chunk) * split;
-                }
-                sg[k].split = split;
-            }
-        }
-#pragma unroll
-        for (int k = 0; k < EV_NSEG; k++) {
-            // block exclusive scan of items[k]
-            s_scan[threadIdx.x] = items[k];
-            __syncthreads();
-            for (int o = 1; o < 256; o <<= 1) {
-                uint32_t v = threadIdx.x >= o ? s_scan[threadIdx.x - o] : 0;
-                __syncthreads();
-                s_scan[threadIdx.x] += v;
-                __syncthreads();
-            }
-            const uint32_t incl = s_scan[threadIdx.x];
-            const uint32_t carry = s_carry[k];
-            if (t < blocks) {
-                sg[k].item_begin = carry + incl - items[k];
-                segs[(size_t)k * blocks + t] = sg[k];
-            }
-            __syncthreads();
-            if (threadIdx.x == 255) s_carry[k] = carry + incl;
-            __syncthreads();
-        }
-    }
-    atomicAdd(&s_pairs, my_pairs);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        WorkTemplate w;
-        for (int k = 0; k < EV_NSEG; k++) w.items[k] = s_carry[k];
-        w.items[3] = 0;
-        w.pairs = s_pairs;
-        w.pad[0] = w.pad[1] = 0;
-        wt_all[wl] = w;
-    }
+    worklist_body(blockIdx.x, blocks, ranges, sample_ranges, cls, cfg, segs_all, wt_all);
 }
 
 // Work items per SM the lists aim for.  The tail of a persistent launch is about one item long, and the backward's
@@ -344,7 +256,7 @@ ForkState g_fork[64];  // per device
 
 int64_t g_small_pairs = -1;  // -1: not read yet (env PIGS_SMALL_PAIRS, default 20 M pairs)
 
-static int64_t small_pairs_threshold()
+int64_t small_pairs_threshold()
 {
     if (g_small_pairs < 0) {
         const char* e = getenv("PIGS_SMALL_PAIRS");
@@ -458,6 +370,23 @@ static uint32_t small_min_stream(bool backward)
     return (uint32_t)v[backward];
 }
 
+WorkListCfg make_worklist_cfg(int64_t R, int64_t N, int blocks, bool single_class)
+{
+    WorkListCfg cfg;
+    const uint32_t chunks[WL_COUNT] = {EV_THREADS * (PIGS_FWD_KS16 ? 16u : 8u), EV_THREADS * 4u, EV_THREADS * (uint32_t)bwd_kg(2, 1, 7u)};
+    for (int wl = 0; wl < WL_COUNT; wl++) {
+        const bool bwd = wl == WL_BWD;
+        cfg.chunk[wl] = chunks[wl];
+        cfg.split_hint[wl] = (g_deterministic && !bwd) ? 1u : split_hint(bwd ? R : N, chunks[wl], blocks, bwd);
+        cfg.min_stream[wl] = bwd ? 128u : 256u;
+        // small problems are bound by the LONGEST work item, not by throughput (a few dozen items on 296 persistent CTAs):
+        // cut the streamed operand finer, so that every item is short and all of them run at once
+        if (single_class) cfg.min_stream[wl] = small_min_stream(bwd);
+        cfg.stream_is_gauss[wl] = bwd ? 0 : 1;
+    }
+    return cfg;
+}
+
 int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, const float* conics, const float* bbox,
                   const uint2* ranges, const uint2* sample_ranges, const BinLayout& b, cudaStream_t st, bool single_class)
 {
@@ -479,18 +408,7 @@ int stage_classes(int D, int blocks, int64_t R, int64_t N, const float* means, c
         if (rc) return rc;
         PIGS_STAGE(st, "class scan (u64)");
     }
-    WorkListCfg cfg;
-    const uint32_t chunks[WL_COUNT] = {EV_THREADS * 8u, EV_THREADS * 4u, EV_THREADS * (uint32_t)bwd_kg(2, 1, 7u)};
-    for (int wl = 0; wl < WL_COUNT; wl++) {
-        const bool bwd = wl == WL_BWD;
-        cfg.chunk[wl] = chunks[wl];
-        cfg.split_hint[wl] = (g_deterministic && !bwd) ? 1u : split_hint(bwd ? R : N, chunks[wl], blocks, bwd);
-        cfg.min_stream[wl] = bwd ? 128u : 256u;
-        // small problems are bound by the LONGEST work item, not by throughput (a few dozen items on 296 persistent CTAs):
-        // cut the streamed operand finer, so that every item is short and all of them run at once
-        if (single_class) cfg.min_stream[wl] = small_min_stream(bwd);
-        cfg.stream_is_gauss[wl] = bwd ? 0 : 1;
-    }
+    const WorkListCfg cfg = make_worklist_cfg(R, N, blocks, single_class);
     worklist_kernel<<<WL_COUNT, 256, 0, st>>>(blocks, ranges, sample_ranges, b.cls, cfg, b.segs, b.wt);
     PIGS_LAUNCH_CHECK();
     PIGS_STAGE(st, "work lists");

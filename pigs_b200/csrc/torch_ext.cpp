@@ -117,20 +117,13 @@ std::tuple<int64_t, Tensor, Tensor, Tensor, Tensor, Tensor> preprocess_gaussians
     f32c(values, "values");
     TORCH_CHECK(cov.numel() == d.P * d.D * (d.D + 1) / 2, "covariances must hold P*D*(D+1)/2 elements");
     void* st = cur_stream();
-    Tensor mm;
-    if (bounds.has_value()) {
-        mm = f32c(*bounds, "bounds");
-    } else {
-        mm = torch::empty({2 * d.D}, means.options());
-        check(pigs_sample_bounds(fp(samples), samples.numel() / d.D, d.D, fpw(mm), st), "pigs_sample_bounds");
-    }
+    Tensor mm = bounds.has_value() ? f32c(*bounds, "bounds") : torch::empty({2 * d.D}, means.options());
     Tensor geom = scratch(SLOT_GEOM, (int64_t)pigs_geom_workspace_bytes(d.P), means);
-    if (!cull.has_value())
-        check(pigs_preprocess_count(d.P, d.D, d.N, fp(means), fp(cov), fp(mm), fpw(radii), geom.data_ptr(), st), "pigs_preprocess_count");
-    else
-        check(pigs_preprocess_count_culled(d.P, d.D, d.N, fp(means), fp(cov), fp(mm), fpw(radii), geom.data_ptr(),
-                                           (int)std::get<1>(*cull), (float)std::get<0>(*cull), st),
-              "pigs_preprocess_count_culled");
+    // bounds + tile grid + radii / tiles touched + scan: one single-CTA launch for small problems, the grid-wide chain else
+    check(pigs_preprocess_count_fused(d.P, d.D, d.N, fp(means), fp(cov), fp(samples), fpw(mm), bounds.has_value() ? 1 : 0,
+                                      fpw(radii), geom.data_ptr(), cull.has_value() ? (int)std::get<1>(*cull) : 1,
+                                      cull.has_value() ? (float)std::get<0>(*cull) : 0.0f, st),
+          "pigs_preprocess_count_fused");
     Tensor host = pinned(sizeof(pigs_header));
     read_back(host.data_ptr(), geom.data_ptr(), sizeof(pigs_header));
     const pigs_header* h = (const pigs_header*)host.data_ptr();

@@ -12,7 +12,8 @@ from tests.fixtures import synthetic  # noqa: E402
 from tests.helpers import upstream  # noqa: E402
 
 L = _lib.lib()
-SIZES = [(1000, 10000, 1), (100, 65536, 2), (900, 10000, 2), (3000, 20000, 2), (5000, 50000, 2), (10000, 100000, 2)]
+SIZES = [(1000, 10000, 1), (100, 4096, 2), (100, 16384, 2), (100, 40000, 2), (400, 4096, 2), (900, 10000, 2), (2000, 12000, 2), (3000, 20000, 2),
+         (4000, 40000, 2), (5000, 50000, 2)]
 
 
 def step(d, ups):
