@@ -243,6 +243,11 @@ void pigs_set_aggregate_specialised(int on);
  * shared memory (default and maximum 4096; 0 sends every row through the per-row kernels), cell_div = grid cells per
  * largest effective radius (default 2).  Results do not depend on either; tests compare the paths. */
 void pigs_set_neighbor_search(int cell_cap, float cell_div);
+/* Library-level option (default 4096; environment PIGS_NB_SMALL_P): searches over at most max_P Gaussians — the reference's
+ * own models hold 400 .. a few thousand (main_pn.py) — test every pair with one warp per row walking the candidates in
+ * ascending id (the reference's loop order): one launch per stage instead of the grid path's dozen.  Same tests, same
+ * per-slot arithmetic, same lists.  0 sends every search through the grid path. */
+void pigs_set_neighbor_small(int64_t max_P);
 size_t pigs_aggregate_backward_workspace_bytes(int64_t P, int L, int K, int E);
 int pigs_aggregate_backward(int64_t P, int D, int L, int K, int E, int64_t M, const float *features,
                             const float *transform, const float *queries, const float *keys,

@@ -87,6 +87,7 @@ SIGNATURES = {
     "pigs_aggregate_backward_f64": (c_int, [c_int64, c_int, c_int, c_int, c_int] + [c_void_p] * 22),
     "pigs_set_aggregate_specialised": (None, [c_int]),
     "pigs_set_neighbor_search": (None, [c_int, ctypes.c_float]),
+    "pigs_set_neighbor_small": (None, [c_int64]),
     "pigs_aggregate_backward_workspace_bytes": (c_size_t, [c_int64, c_int, c_int, c_int]),
     "pigs_aggregate_backward": (c_int, [c_int64, c_int, c_int, c_int, c_int, c_int64] + [c_void_p] * 23),
     "pigs_build_covariances_forward": (c_int, [c_int64, c_int] + [c_void_p] * 5),

@@ -23,6 +23,10 @@
 #include "common.cuh"
 #include "eval_common.cuh"
 
+#include <stdlib.h>
+
+#include <mutex>
+
 namespace pigs {
 
 constexpr int NB_THREADS = 128;            // 4 warps, one row each
@@ -917,6 +921,113 @@ __global__ void __launch_bounds__(NBC_THREADS) nb_cell_fill_kernel(const NbGrid*
     }
 }
 
+// ---- small P: brute force, one launch per stage -------------------------------------------------------
+// The reference's own models hold 400 .. a few thousand Gaussians (main_pn.py: nx = ny = 20).  There the dozen dependent
+// launches of the grid path (grid build, key sort, cell tables, two cell passes, per-row passes) cost more than testing
+// every pair: one warp per row walks ALL candidates in ascending id, 32 per step — the reference's own loop order
+// (findCollisions scans i = 0..P-1), so the accepted ones leave in ascending id without any sort.  Same tests and the
+// same per-slot arithmetic as the grid path (nb_collides, nb_emit_core): indices / ranges bit for bit.
+constexpr int NBS_THREADS = 256;
+constexpr int NBS_WARPS = NBS_THREADS / 32;
+constexpr int64_t NBS_P_MAX = 4096;
+
+__device__ __forceinline__ float nbs_reff(float radius) { return __double2float_rn((double)radius * 0.2); }  // nb_prepare_kernel
+
+template <int D, bool FILL>
+__global__ void __launch_bounds__(NBS_THREADS) nb_small_kernel(int64_t P, const float* __restrict__ means,
+                                                               const float* __restrict__ conics,
+                                                               const float* __restrict__ radii,
+                                                               const int64_t* __restrict__ ranges,
+                                                               int64_t* __restrict__ counts, int64_t* __restrict__ indices,
+                                                               float* __restrict__ dists, float* __restrict__ densities,
+                                                               float* __restrict__ inv_total, NbWindow win)
+{
+    const int lane = threadIdx.x & 31;
+    const int64_t id = (int64_t)blockIdx.x * NBS_WARPS + (threadIdx.x >> 5);
+    if (id >= P) return;
+    const float ri = nbs_reff(radii[id]);
+    const bool row = !((double)ri < 1e-6) && win.has((uint32_t)id);  // degenerate rows / another shard's rows: empty list
+    if (!row) {
+        if (lane == 0) {
+            if (FILL)
+                inv_total[id] = __double2float_rn(1.0 / (0.0 + 1e-6));
+            else
+                counts[id] = 0;
+        }
+        return;
+    }
+    float mi[2] = {0.f, 0.f};
+#pragma unroll
+    for (int d = 0; d < D; d++) mi[d] = means[id * D + d];
+    const int64_t start = FILL ? (id == 0 ? 0 : ranges[id - 1]) : 0;
+    const float inv_r = FILL ? nb_inv_radius(radii[id]) : 0.f;
+    float total = 0.f;
+    uint32_t cnt = 0;
+    for (int64_t base = 0; base < P; base += 32) {
+        const int64_t j = base + lane;
+        bool ok = false;
+        float mj[2] = {0.f, 0.f};
+        if (j < P) {
+            const float rj = nbs_reff(radii[j]);
+#pragma unroll
+            for (int d = 0; d < D; d++) mj[d] = means[j * D + d];
+            ok = !((double)rj < 1e-6) && nb_collides<D>(mi, ri, mj, rj);
+        }
+        const uint32_t m = __ballot_sync(0xffffffffu, ok);
+        if (FILL && ok)
+            total += nb_emit_core<D>(start + cnt + __popc(m & ((1u << lane) - 1u)), (uint32_t)j, mj, mi, inv_r, conics, indices,
+                                     dists, densities);
+        cnt += __popc(m);
+    }
+    if (FILL) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
+        if (lane == 0) inv_total[id] = __double2float_rn(1.0 / ((double)total + 1e-6));
+    } else if (lane == 0) {
+        counts[id] = (int64_t)cnt;
+    }
+}
+
+// Which path a search took is remembered on the host per workspace (the count and the fill stage must agree even if the
+// knob changes between them)
+static int64_t g_nb_small_p = -1;  // -1: not read yet (env PIGS_NB_SMALL_P, default NBS_P_MAX); 0 = never
+static int64_t nb_small_p()
+{
+    if (g_nb_small_p < 0) {
+        const char* e = getenv("PIGS_NB_SMALL_P");
+        g_nb_small_p = e ? atoll(e) : NBS_P_MAX;
+        if (g_nb_small_p < 0) g_nb_small_p = 0;
+    }
+    return g_nb_small_p;
+}
+namespace {
+struct NbNote {
+    const void* ws;
+    bool small;
+};
+NbNote g_nb_notes[64];
+int g_nb_note_next = 0;
+std::mutex g_nb_note_mu;
+void nb_note(const void* ws, bool small)
+{
+    std::lock_guard<std::mutex> lk(g_nb_note_mu);
+    for (auto& n : g_nb_notes)
+        if (n.ws == ws) {
+            n.small = small;
+            return;
+        }
+    g_nb_notes[g_nb_note_next] = NbNote{ws, small};
+    g_nb_note_next = (g_nb_note_next + 1) % 64;
+}
+bool nb_noted_small(const void* ws)
+{
+    std::lock_guard<std::mutex> lk(g_nb_note_mu);
+    for (auto& n : g_nb_notes)
+        if (n.ws == ws) return n.small;
+    return false;
+}
+}  // namespace
+
 // run-time knobs of the neighbour search (pigs_set_neighbor_search; development and tests): cell_cap = 0 routes every
 // row through the per-row kernels, cell_div = grid cells per largest radius.  Environment defaults:
 // PIGS_NB_CELL_CAP, PIGS_NB_CELL_DIV.
@@ -1313,6 +1424,19 @@ int pigs_neighbors_count_rows(int64_t P, int D, const float* means, const float*
     const int windowed = row_lo > 0 || row_hi < P;
     cudaStream_t st = (cudaStream_t)stream;
     NbLayout w(workspace, P, D);
+    const bool small = P <= nb_small_p();
+    nb_note(workspace, small);
+    if (small) {  // brute force: one launch, no grid
+        const unsigned nbs = (unsigned)((P + NBS_WARPS - 1) / NBS_WARPS);
+        if (D == 2)
+            nb_small_kernel<2, false><<<nbs, NBS_THREADS, 0, st>>>(P, means, nullptr, radii, nullptr, counts, nullptr, nullptr,
+                                                                   nullptr, nullptr, win);
+        else
+            nb_small_kernel<1, false><<<nbs, NBS_THREADS, 0, st>>>(P, means, nullptr, radii, nullptr, counts, nullptr, nullptr,
+                                                                   nullptr, nullptr, win);
+        PIGS_LAUNCH_CHECK();
+        return 0;
+    }
     const unsigned nb = (unsigned)((P + 255) / 256);
     PIGS_CHECK(cudaMemsetAsync(counts, 0, (size_t)P * sizeof(int64_t), st));
     nb_init_kernel<<<1, 32, 0, st>>>(w.grid);
@@ -1381,6 +1505,17 @@ int pigs_neighbors_fill_rows(int64_t P, int D, const float* means, const float* 
     const int windowed = row_lo > 0 || row_hi < P;
     cudaStream_t st = (cudaStream_t)stream;
     NbLayout w(workspace, P, D);
+    if (nb_noted_small(workspace)) {  // the count stage of this workspace ran the brute-force kernel
+        const unsigned nbs = (unsigned)((P + NBS_WARPS - 1) / NBS_WARPS);
+        if (D == 2)
+            nb_small_kernel<2, true><<<nbs, NBS_THREADS, 0, st>>>(P, means, conics, radii, ranges, nullptr, indices, dists,
+                                                                  densities, inv_total_densities, win);
+        else
+            nb_small_kernel<1, true><<<nbs, NBS_THREADS, 0, st>>>(P, means, conics, radii, ranges, nullptr, indices, dists,
+                                                                  densities, inv_total_densities, win);
+        PIGS_LAUNCH_CHECK();
+        return 0;
+    }
     const unsigned nbw = (unsigned)((P + NB_WARPS - 1) / NB_WARPS);
     const int cap = nb_cell_cap();
     const unsigned ncta = (unsigned)std::min<int64_t>(w.ncells_max, (int64_t)num_sms() * 64);
@@ -1431,6 +1566,8 @@ int pigs_neighbors_ranges(int64_t P, const int64_t* counts, int64_t* ranges, int
 }
 
 void pigs_set_aggregate_specialised(int on) { g_agg_fast = on != 0; }
+
+void pigs_set_neighbor_small(int64_t max_P) { g_nb_small_p = max_P < 0 ? 0 : max_P; }
 
 void pigs_set_neighbor_search(int cell_cap, float cell_div)
 {

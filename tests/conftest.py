@@ -27,10 +27,13 @@ def pytest_collection_modifyitems(config, items):
             item.add_marker(skip)
 
 
-# Small problems run ONE evaluation kernel (every instance in the GENERAL class, pigs_set_small_problem_pairs); the small
-# recipes of these modules would otherwise stop exercising the FAST / SHIFT kernels, so they run in both modes.
-_BOTH_CLASS_MODES = {"test_gpu_parity.py", "test_gpu_vs_reference.py", "test_culled.py"}
+# Small problems run ONE evaluation kernel (every instance in the GENERAL class, pigs_set_small_problem_pairs), single-CTA
+# binning kernels and a brute-force neighbour search (pigs_set_neighbor_small); the small recipes of these modules would
+# otherwise stop exercising the FAST / SHIFT kernels, the grid-wide binning chain and the grid search, so they run in both
+# modes ("three_class" = every small-problem path off).
+_BOTH_CLASS_MODES = {"test_gpu_parity.py", "test_gpu_vs_reference.py", "test_culled.py", "test_gpu_aggregate.py"}
 SMALL_PAIRS_DEFAULT = 20_000_000
+NB_SMALL_P_DEFAULT = 4096
 
 
 def pytest_generate_tests(metafunc):
@@ -47,7 +50,9 @@ def _class_mode(request):
     from pigs_b200 import _lib
     L = _lib.lib()
     L.pigs_set_small_problem_pairs(0)
+    L.pigs_set_neighbor_small(0)
     try:
         yield mode
     finally:
         L.pigs_set_small_problem_pairs(SMALL_PAIRS_DEFAULT)
+        L.pigs_set_neighbor_small(NB_SMALL_P_DEFAULT)
