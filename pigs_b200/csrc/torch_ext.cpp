@@ -142,6 +142,33 @@ std::tuple<int64_t, Tensor, Tensor, Tensor, Tensor, Tensor> preprocess_gaussians
 }
 
 // ---- fused forward / backward (SampleGaussians*CUDA, sample_points.cu:100-372, any subset in one call) ------------
+// Zero-initialised tensors of the given shapes (an empty shape = not wanted).  Small problems are launch-bound, and every
+// torch::zeros is a fill kernel: up to 1 MB in total the tensors are views of ONE zeroed buffer (segments 256-byte
+// aligned), beyond that separate allocations — a caller that keeps only one of several large outputs must not pin the
+// others' memory.
+void zeros_many(const std::vector<std::vector<int64_t>>& shapes, const Tensor& like, std::vector<OptTensor>& out)
+{
+    constexpr int64_t ALIGN = 64, FLAT_MAX = 1 << 18;  // floats
+    int64_t total = 0, wanted = 0;
+    std::vector<int64_t> off(shapes.size(), 0), cnt(shapes.size(), 0);
+    for (size_t k = 0; k < shapes.size(); k++) {
+        if (shapes[k].empty()) continue;
+        int64_t n = 1;
+        for (int64_t v : shapes[k]) n *= v;
+        off[k] = total;
+        cnt[k] = n;
+        total += (n + ALIGN - 1) / ALIGN * ALIGN;
+        wanted++;
+    }
+    const bool flat = wanted > 1 && total <= FLAT_MAX;
+    Tensor base;
+    if (flat) base = torch::zeros({total}, like.options());
+    for (size_t k = 0; k < shapes.size(); k++) {
+        if (shapes[k].empty()) continue;
+        out[k] = flat ? base.narrow(0, off[k], cnt[k]).view(shapes[k]) : torch::zeros(shapes[k], like.options());
+    }
+}
+
 std::vector<OptTensor> sample_forward(int64_t fn_mask, const Tensor& means_, const Tensor& values_, const Tensor& conics_,
                                       const Tensor& samples_, int64_t num_rendered, const Tensor& binning_buffer,
                                       const Tensor& sample_binning_buffer, const Tensor& ranges, const Tensor& sample_ranges,
@@ -154,14 +181,15 @@ std::vector<OptTensor> sample_forward(int64_t fn_mask, const Tensor& means_, con
     const Dims d = dims(means, values, samples);
     TORCH_CHECK(!((fn_mask & PIGS_FN_LAPL) && (fn_mask & PIGS_FN_HESS)), "FN_LAPL and FN_HESS are mutually exclusive (they share an output slot)");
     std::vector<OptTensor> outs(4);
+    std::vector<std::vector<int64_t>> shapes(4);
     for (int k = 0; k < 4; k++) {
         if (!(fn_mask & (1 << k))) continue;
-        std::vector<int64_t> shp{d.N};
-        for (int i = 0; i < k; i++) shp.push_back(d.D);
-        shp.push_back(d.C);
-        outs[k] = torch::zeros(shp, means.options());
+        shapes[k] = {d.N};
+        for (int i = 0; i < k; i++) shapes[k].push_back(d.D);
+        shapes[k].push_back(d.C);
     }
-    if (fn_mask & PIGS_FN_LAPL) outs[2] = torch::zeros({d.N, (int64_t)d.C}, means.options());
+    if (fn_mask & PIGS_FN_LAPL) shapes[2] = {d.N, (int64_t)d.C};
+    zeros_many(shapes, means, outs);
     if (d.P != 0 && d.N != 0) {
         const int blocks = blocks_of(ranges);
         const size_t wsb = pigs_eval_workspace_bytes(num_rendered, d.N, blocks, d.D, d.C, (unsigned)fn_mask);
@@ -308,8 +336,10 @@ std::tuple<Tensor, Tensor, Tensor, Tensor, Tensor, Tensor> aggregate_neighbors_b
     Tensor indices = indices_.contiguous(), ranges = ranges_.contiguous();
     const int64_t P = features.size(0);
     const int D = (int)dists.size(-1), L = (int)features.size(-1), K = (int)queries.size(-1), E = (int)(dt.size(-1) / 2);
-    Tensor gf = torch::zeros_like(features), gt = torch::zeros_like(transform), gq = torch::zeros_like(queries),
-           gk = torch::zeros_like(keys), gfr = torch::zeros_like(freqs), gdt = torch::zeros_like(dt);
+    std::vector<OptTensor> z(6);
+    zeros_many({features.sizes().vec(), transform.sizes().vec(), queries.sizes().vec(), keys.sizes().vec(), freqs.sizes().vec(),
+                dt.sizes().vec()}, features, z);
+    Tensor gf = *z[0], gt = *z[1], gq = *z[2], gk = *z[3], gfr = *z[4], gdt = *z[5];
     if (P > 0)
         check(pigs_aggregate_backward(P, D, L, K, E, densities.numel(), fp(features), fp(transform), fp(queries), fp(keys), fp(freqs),
                                       fp(dt), indices.data_ptr<int64_t>(), ranges.data_ptr<int64_t>(), fp(dists), fp(densities),
