@@ -25,6 +25,7 @@ Extra legs, run AFTER the timed C3 region and reported under "legs" in the same 
              Hessian without grad (model_pn.py:644-652) -> neighbour aggregation on a 16-regular CSR, 2 heads forward +
              backward (model_pn.py:253-274)); row-parallel over the ranks when N > 1.  Runs at every N.
   c1/c2/c4 : the other BASELINE configs, device-resident and end-to-end, N = 1 only
+  pn_step  : a model_pn.py-style step at the reference's own scale (400 / 2500 Gaussians), ours and the reference extension
   ref_cuda : the UNMODIFIED reference CUDA extension (oracle/_ref/_C.so, built by oracle/build_ref.sh) on the same GPU
              and inputs next to ours, 20K Gaussians x 200K points (BASELINE.md's "GPU baseline to beat"), N = 1 only
 """
@@ -103,7 +104,7 @@ def parse_args():
     ap.add_argument("--workload", default=os.environ.get("PIGS_BENCH_WORKLOAD", "C3"), choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-legs", action="store_true", help="skip the c5 / c1 / c2 / c4 / ref_cuda legs")
+    ap.add_argument("--no-legs", action="store_true", help="skip the c5 / c1 / c2 / c4 / ref_cuda / pn_step legs")
     return ap.parse_args()
 
 
@@ -643,6 +644,76 @@ def leg_ref_cuda(torch, L, P=20_000, N=200_000):
             "timing": "CUDA events on the current stream around every step (median over the steps), inputs resident on the device"}
 
 
+def leg_pn_step(torch, L, sizes=(400, 2500)):
+    """One model_pn.py-style step at the reference's OWN scale (main_pn.py: nx = ny = 20 -> 400 Gaussians), through the public
+    API: preprocess(samples = means) -> u, grad u, Hessian -> preprocess_aggregate (the real neighbour search) -> 2 heads of
+    aggregate_neighbors, then the backward of a scalar loss through all of it (model_pn.py:644-652,253-274).  Next to it the
+    same calls on the UNMODIFIED reference extension (oracle/_ref/_C.so) where it is on the box.  Launch-bound on both sides."""
+    from diff_gaussian_sampling import GaussianSampler
+    from tests import refcuda
+    from tests.fixtures import agg_model
+    from tests.helpers import AGG_KEYS
+    HEADS = 2
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        n0 = L.pigs_launch_count()
+        ev[0].record()
+        for i in range(steps):
+            fn()
+            ev[i + 1].record()
+        torch.cuda.synchronize()
+        per = sorted(ev[i].elapsed_time(ev[i + 1]) for i in range(steps))
+        return per[len(per) // 2], (L.pigs_launch_count() - n0) / steps
+
+    rows = []
+    for P in sizes:
+        rec = agg_model(P, seed=21)
+        d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
+        for k in ("means", "values", "conics"):
+            d[k].requires_grad_(True)
+        heads = [[d[k].clone().requires_grad_(True) for k in AGG_KEYS] for _ in range(HEADS)]
+        s = GaussianSampler(False)
+
+        def ours():
+            s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["means"])
+            u, ux, uxx = s.sample_gaussians(), s.sample_gaussians_derivative(), s.sample_gaussians_laplacian()
+            s.preprocess_aggregate()
+            loss = u.sum() + ux.sum() + uxx.sum()
+            for h in heads:
+                loss = loss + s.aggregate_neighbors(*h).sum()
+            loss.backward()
+
+        ms, launches = timed(ours, 30, 10)
+        row = {"gaussians": P, "neighbour_slots": int(s.indices.numel()), "ours_ms_per_step": ms, "ours_launches_per_step": launches}
+        if refcuda.available():
+            r = refcuda.RefSampler(False)
+            dd = {k: v.detach() for k, v in d.items()}
+            hh = [[t.detach() for t in h] for h in heads]
+
+            def ref():
+                r.preprocess(dd["means"], dd["values"], dd["covariances"], dd["conics"], dd["means"])
+                outs = [r.forward(k) for k in range(3)]
+                csr = r.preprocess_aggregate()
+                for h in hh:
+                    w, e, f, out = r.C.aggregate_neighbors(*h, *csr, False)
+                    r.C.aggregate_neighbors_backward(*h, csr[0], csr[1], csr[2], csr[3], w, e, f, csr[4], torch.ones_like(out), False)
+                for k in range(3):
+                    r.backward(k, torch.ones_like(outs[k]))
+
+            rms, _ = timed(ref, 5, 2)
+            row["ref_ms_per_step"] = rms
+            row["speedup"] = rms / ms
+        rows.append(row)
+    return {"workload": "model_pn.py-style step at the reference's own scale: preprocess(samples = means) + u / grad u / Hessian + "
+                        "neighbour search + 2 heads of aggregate_neighbors, forward and backward, public API",
+            "reference": "oracle/_ref/_C.so, the same calls (its three forward and three backward passes, aggregate_neighbors.cu)",
+            "timing": "CUDA events around every step, median; both sides launch- / host-bound at these sizes", "rows": rows}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -702,6 +773,7 @@ def run_ours(args):
             legs["c4"] = guarded("c4", lambda: leg_sampling("C4", torch, dist, L, 3, 3))
             legs["c1"] = guarded("c1", lambda: leg_sampling("C1", torch, dist, L, 50, 10))
             legs["ref_cuda"] = guarded("ref_cuda", lambda: leg_ref_cuda(torch, L))
+            legs["pn_step"] = guarded("pn_step", lambda: leg_pn_step(torch, L))
 
     if rank != 0:
         if world > 1:
@@ -753,7 +825,7 @@ def run_ours(args):
         out["cpu_baseline"] = cpu_baseline(args.workload)
     if legs:
         out["legs"] = legs
-        for k in ("c5", "ref_cuda", "c1", "c2", "c4"):  # also at top level, where the verdict asked for them
+        for k in ("c5", "ref_cuda", "pn_step", "c1", "c2", "c4"):  # also at top level, where the verdict asked for them
             if k in legs:
                 out[k] = legs[k]
         del out["legs"]
