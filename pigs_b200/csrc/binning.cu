@@ -811,8 +811,10 @@ __global__ void __launch_bounds__(SMALL_THREADS) small_bin_kernel(int64_t P, int
 #pragma unroll
             for (int d = 0; d < D; d++) {
                 const float v = x[d] + 0.0f;  // -0 -> +0 (sample_key_kernel)
-                atomic_min_float(box + d, v);
-                atomic_max_float(box + D + d, v);
+                // the boxes only ever grow: a stale read can at worst let a redundant atomic through; without the check
+                // every sample of a tile serialises on the same two shared-memory words
+                if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
+                if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
             }
         }
         __syncthreads();
