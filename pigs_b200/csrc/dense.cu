@@ -13,6 +13,8 @@
 // FP32-issue bound like the tiled kernels (per pair, D = 2, C = 1, all three outputs: 22 FP32 ops + 1 ex2 forward).
 #include "common.cuh"
 
+#include <stdlib.h>
+
 namespace pigs {
 
 constexpr int DN_FWD_THREADS = 256, DN_BWD_THREADS = 128, DN_BATCH = 256;
@@ -389,16 +391,55 @@ __global__ void __launch_bounds__(DN_BWD_THREADS)
 }
 
 
-// chunks of the streamed operand so that the grid has ~4 CTAs per SM even for small stationary counts
-static int64_t dn_chunks(int64_t stationary_blocks, int64_t streamed, int batch)
+// Chunks of the streamed operand (grid.y).  Two aims: enough CTAs to fill the machine even for small stationary counts
+// (~4 per SM), and WHOLE WAVES: every CTA of these kernels does the same work, so nx * ny CTAs on `slots` resident ones
+// take ceil(nx * ny / slots) rounds — 489 x 2 CTAs on 296 slots are 3.3 waves paid as 4 (measured: 76 ms at 100K x 1M
+// where the tiled kernel's pair rate predicts 63).  Among the chunk counts from "fills the machine" up to a few more, take
+// the one that wastes the least of its last wave (ties: fewer chunks = fewer output atomics).
+static int64_t dn_chunks(int64_t stationary_blocks, int64_t streamed, int batch, int64_t slots)
 {
-    const int64_t want = 4 * (int64_t)num_sms();
-    int64_t ny = (want + stationary_blocks - 1) / stationary_blocks;
-    const int64_t most = (streamed + 4 * batch - 1) / (4 * batch);  // at least four batches per chunk
-    if (ny > most) ny = most;
-    if (ny > 65535) ny = 65535;
-    return ny < 1 ? 1 : ny;
+    // at least ~4 CTAs per SM, and about eight waves where the streamed operand is long enough: the CTAs do not run in
+    // lockstep, and the finer the last wave's CTAs the shorter the tail (100K x 1M forward: 2 / 3 / 6 / 12 chunks ->
+    // 76.0 / 72.3 / 72.1 / 71.9 ms; forward + backward 325.6 / 290.8 / 284.4 / 281.0 ms)
+    int64_t want = 4 * (int64_t)num_sms();
+    if (8 * slots > want) want = 8 * slots;
+    int64_t ny0 = (want + stationary_blocks - 1) / stationary_blocks;
+    int64_t most = (streamed + 4 * batch - 1) / (4 * batch);  // at least four batches per chunk
+    if (most > 65535) most = 65535;
+    if (most < 1) most = 1;
+    if (ny0 > most) ny0 = most;
+    if (ny0 < 1) ny0 = 1;
+    if (const char* e = getenv("PIGS_DENSE_NY")) {  // tuning hook
+        const int64_t v = atoll(e);
+        if (v >= 1) return v < most ? v : most;
+    }
+    if (slots <= 0) return ny0;
+    int64_t best = ny0;
+    double best_eff = -1.0;
+    for (int64_t ny = ny0; ny <= most && ny <= ny0 + 4; ny++) {
+        const double w = (double)(stationary_blocks * ny) / (double)slots;
+        const double eff = w / (double)((int64_t)(w + 0.999999));
+        if (eff > best_eff + 0.01) {  // a later candidate must be clearly better
+            best_eff = eff;
+            best = ny;
+        }
+    }
+    return best;
 }
+
+// resident CTAs of a kernel on this device (occupancy x SMs)
+template <typename K>
+static int64_t dn_slots(K kernel, int threads)
+{
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, threads, 0) != cudaSuccess || nb <= 0) return 0;
+    return (int64_t)nb * num_sms();
+}
+
+using DnFwdKernel = void (*)(unsigned, int64_t, int64_t, int64_t, const float*, const float*, const float*, const float*, float*,
+                             float*, float*);
+using DnBwdKernel = void (*)(unsigned, int64_t, int64_t, int64_t, const float*, const float*, const float*, const float*,
+                             const float*, const float*, const float*, float*, float*, float*);
 
 template <int D>
 static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means, const float* conics, const float* values,
@@ -409,8 +450,25 @@ static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
     int ks = (N < (int64_t)DN_FWD_THREADS * 4 * num_sms()) ? 1 : (C == 1 ? 4 : (C == 2 ? 2 : 1));
     if (D == 2 && C == 1 && N >= (int64_t)DN_FWD_THREADS * DN2_KS * num_sms()) ks = DN2_KS;
     if (g_dense_ks > 0) ks = g_dense_ks == 1 ? 1 : (g_dense_ks >= DN2_KS && D == 2 && C == 1 ? DN2_KS : (C == 1 ? 4 : (C == 2 ? 2 : 1)));
+    DnFwdKernel kern = nullptr;
+    if (D == 2 && C == 1 && ks == DN2_KS)
+        kern = dense_fwd2_kernel;
+    else if (C == 1 && ks == 4)
+        kern = dense_fwd_kernel<D, 1, 4>;
+    else if (C == 1)
+        kern = dense_fwd_kernel<D, 1, 1>;
+    else if (C == 2 && ks == 2)
+        kern = dense_fwd_kernel<D, 2, 2>;
+    else if (C == 2)
+        kern = dense_fwd_kernel<D, 2, 1>;
+    else if (C == 3)
+        kern = dense_fwd_kernel<D, 3, 1>;
+    else if (C == 4)
+        kern = dense_fwd_kernel<D, 4, 1>;
+    else
+        return -1;
     const int64_t nx = (N + (int64_t)DN_FWD_THREADS * ks - 1) / ((int64_t)DN_FWD_THREADS * ks);
-    const int64_t ny = dn_chunks(nx, n, DN_BATCH);
+    const int64_t ny = dn_chunks(nx, n, DN_BATCH, dn_slots(kern, DN_FWD_THREADS));
     const int64_t per = ((n + ny - 1) / ny + DN_BATCH - 1) / DN_BATCH * DN_BATCH;
     const dim3 grid((unsigned)nx, (unsigned)((n + per - 1) / per));
     if (grid.y > 1) {  // chunked: the kernel adds into zeroed outputs
@@ -418,25 +476,7 @@ static int dn_fwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
         if ((mask & PIGS_FN_DERIV) && cudaMemsetAsync(ux, 0, sizeof(float) * N * D * C, st) != cudaSuccess) return -2;
         if ((mask & PIGS_FN_HESS) && cudaMemsetAsync(uxx, 0, sizeof(float) * N * D * D * C, st) != cudaSuccess) return -2;
     }
-#define DN_F(CC, KK)                                                                                                    \
-    dense_fwd_kernel<D, CC, KK><<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx)
-    if (D == 2 && C == 1 && ks == DN2_KS)
-        dense_fwd2_kernel<<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx);
-    else if (C == 1 && ks == 4)
-        DN_F(1, 4);
-    else if (C == 1)
-        DN_F(1, 1);
-    else if (C == 2 && ks == 2)
-        DN_F(2, 2);
-    else if (C == 2)
-        DN_F(2, 1);
-    else if (C == 3)
-        DN_F(3, 1);
-    else if (C == 4)
-        DN_F(4, 1);
-    else
-        return -1;
-#undef DN_F
+    kern<<<grid, DN_FWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, u, ux, uxx);
     return 0;
 }
 
@@ -447,8 +487,21 @@ static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
 {
     int kg = (C == 1 && n >= (int64_t)DN_BWD_THREADS * 2 * num_sms()) ? 2 : 1;  // Gaussians per thread
     if (g_dense_kg > 0) kg = (g_dense_kg > 1 && C == 1) ? 2 : 1;
+    DnBwdKernel kern = nullptr;
+    if (C == 1 && kg == 2)
+        kern = dense_bwd_kernel<D, 1, 2>;
+    else if (C == 1)
+        kern = dense_bwd_kernel<D, 1, 1>;
+    else if (C == 2)
+        kern = dense_bwd_kernel<D, 2, 1>;
+    else if (C == 3)
+        kern = dense_bwd_kernel<D, 3, 1>;
+    else if (C == 4)
+        kern = dense_bwd_kernel<D, 4, 1>;
+    else
+        return -1;
     const int64_t nx = (n + (int64_t)DN_BWD_THREADS * kg - 1) / ((int64_t)DN_BWD_THREADS * kg);
-    const int64_t ny = dn_chunks(nx, N, 128);
+    const int64_t ny = dn_chunks(nx, N, 128, dn_slots(kern, DN_BWD_THREADS));
     const int64_t per = ((N + ny - 1) / ny + 127) / 128 * 128;
     const dim3 grid((unsigned)nx, (unsigned)((N + per - 1) / per));
     if (grid.y > 1) {
@@ -456,22 +509,7 @@ static int dn_bwd(int C, unsigned mask, int64_t n, int64_t N, const float* means
         if (cudaMemsetAsync(dc, 0, sizeof(float) * n * D * D, st) != cudaSuccess) return -2;
         if (cudaMemsetAsync(dv, 0, sizeof(float) * n * C, st) != cudaSuccess) return -2;
     }
-#define DN_B(CC, KK)                                                                                                    \
-    dense_bwd_kernel<D, CC, KK><<<grid, DN_BWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, gu, gux,  \
-                                                                 guxx, dm, dc, dv)
-    if (C == 1 && kg == 2)
-        DN_B(1, 2);
-    else if (C == 1)
-        DN_B(1, 1);
-    else if (C == 2)
-        DN_B(2, 1);
-    else if (C == 3)
-        DN_B(3, 1);
-    else if (C == 4)
-        DN_B(4, 1);
-    else
-        return -1;
-#undef DN_B
+    kern<<<grid, DN_BWD_THREADS, 0, st>>>(mask, n, N, per, means, conics, values, samples, gu, gux, guxx, dm, dc, dv);
     return 0;
 }
 
