@@ -57,7 +57,7 @@ def timed(fn, steps, warmup):
     return per[len(per) // 2], (L.pigs_launch_count() - n0) / steps
 
 
-for P in (400, 900, 2500, 4096, 10000):
+for P in [int(x) for x in os.environ.get("PN_SIZES", "400,900,2500,4096,10000").split(",")]:
     rec = agg_model(P, seed=21)
     d = {k: torch.from_numpy(v).cuda() for k, v in rec.items()}
     for k in ("means", "values", "conics"):
