@@ -801,20 +801,35 @@ __global__ void __launch_bounds__(SMALL_THREADS) small_bin_kernel(int64_t P, int
             mn[d] = hdr->min_b[d];
             gr[d] = hdr->ref_grid[d];
         }
-        for (int64_t i = tid; i < N; i += SMALL_THREADS) {
-            float x[D];
+        // four samples per thread and step: their loads are issued together (one CTA has little else to hide an L2 round
+        // trip per sample behind)
+        constexpr int UNR = 4;
+        for (int64_t i0 = tid; i0 < N; i0 += (int64_t)SMALL_THREADS * UNR) {
+            float xs[UNR][D];
 #pragma unroll
-            for (int d = 0; d < D; d++) x[d] = samples[i * D + d];
-            const uint32_t tile = sample_tile_of<D>(x, hdr, mn, gr, g0, kdiv, h, rblocks);
-            sk8[i] = (uint8_t)tile;
-            float* box = s_box + (size_t)tile * 2 * D;
+            for (int u = 0; u < UNR; u++) {
+                const int64_t i = i0 + (int64_t)u * SMALL_THREADS;
 #pragma unroll
-            for (int d = 0; d < D; d++) {
-                const float v = x[d] + 0.0f;  // -0 -> +0 (sample_key_kernel)
-                // the boxes only ever grow: a stale read can at worst let a redundant atomic through; without the check
-                // every sample of a tile serialises on the same two shared-memory words
-                if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
-                if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
+                for (int d = 0; d < D; d++) xs[u][d] = i < N ? samples[i * D + d] : 0.0f;
+            }
+#pragma unroll
+            for (int u = 0; u < UNR; u++) {
+                const int64_t i = i0 + (int64_t)u * SMALL_THREADS;
+                if (i >= N) break;
+                float x[D];
+#pragma unroll
+                for (int d = 0; d < D; d++) x[d] = xs[u][d];
+                const uint32_t tile = sample_tile_of<D>(x, hdr, mn, gr, g0, kdiv, h, rblocks);
+                sk8[i] = (uint8_t)tile;
+                float* box = s_box + (size_t)tile * 2 * D;
+#pragma unroll
+                for (int d = 0; d < D; d++) {
+                    const float v = x[d] + 0.0f;  // -0 -> +0 (sample_key_kernel)
+                    // the boxes only ever grow: a stale read can at worst let a redundant atomic through; without the
+                    // check every sample of a tile serialises on the same two shared-memory words
+                    if (v < *(volatile float*)(box + d)) atomic_min_float(box + d, v);
+                    if (v > *(volatile float*)(box + D + d)) atomic_max_float(box + D + d, v);
+                }
             }
         }
         __syncthreads();
