@@ -178,7 +178,8 @@ void pigs_set_class_concurrency(int on);
  * backward call of that binning launches ONE evaluation kernel instead of three on forked streams.  Results stay within
  * the parity tolerance of the three-class path (tests compare the two).  0 disables it.  The library remembers on the
  * host which binning buffers were built this way (by address and sizes); a buffer it does not know — e.g. a copy — gets
- * the three launches, which are correct for both kinds. */
+ * the three launches, which are correct for both kinds.  (Corollary: a binning buffer is written by pigs_preprocess_bin
+ * only — copying another binning's bytes INTO a buffer the library has noted is not supported.) */
 void pigs_set_small_problem_pairs(int64_t pairs);
 
 /* Optional per-stage device timing of the preprocess chain (development: tools/chain_timing.py).  While on, the
