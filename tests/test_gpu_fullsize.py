@@ -139,3 +139,55 @@ def test_neighbor_search_full_size_rows_against_oracle():
         assert bool((asc | ~same_row).all())
         n_self += int((ind[: min(step, M - a)] == ro[: min(step, M - a)]).sum())
     assert n_self == P   # every (valid) Gaussian neighbours itself exactly once
+
+
+@pytest.mark.timeout(900)
+def test_aggregation_full_size_c5_against_oracle():
+    """C5 part i at BASELINE size: aggregate_neighbors forward + backward over a 16-regular CSR at
+    P = 1M Gaussians, L = K = 16, E = 25 (model_pn.py:44-49) — the kernels of the bench's c5 leg — against the oracle
+    on ALL rows (its loops are O(slots); OpenMP): output and the six gradients to 1e-5 norm-wise, plus a size-independent
+    property: the operator is affine in the features."""
+    import torch
+    from scipy.spatial import cKDTree
+
+    from pigs_b200 import GaussianSampler, _C
+    from tests.fixtures import agg_params
+    from tests.helpers import AGG_KEYS
+    P, k = 1_000_000, 16
+    rec = synthetic(P, 16, seed=0)
+    d = {kk: torch.from_numpy(v).cuda() for kk, v in rec.items()}
+    s = GaussianSampler(False)
+    s.preprocess(d["means"], d["values"], d["covariances"], d["conics"], d["means"])
+    _, idx = cKDTree(rec["means"]).query(rec["means"], k=k, workers=-1)
+    indices = torch.from_numpy(np.sort(idx.astype(np.int64), axis=1).reshape(-1)).cuda()
+    ranges = (torch.arange(1, P + 1, device="cuda") * k).contiguous()
+    i_of = torch.arange(P, device="cuda").repeat_interleave(k)
+    X = d["means"][indices] - d["means"][i_of]
+    X = torch.where(X.abs() > 1, X - 2 * torch.sign(X), X)
+    dists = (X / (0.333 * s.radii[i_of] + 1e-6).unsqueeze(1)).contiguous()
+    cj = d["conics"][indices]
+    dens = torch.exp(-0.5 * (cj[:, 0] * X[:, 0] ** 2 + cj[:, 2] * X[:, 1] ** 2) - cj[:, 1] * X[:, 0] * X[:, 1]).contiguous()
+    inv_total = (1.0 / (dens.view(P, k).sum(1) + 1e-6)).contiguous()
+    del X, cj, i_of
+    ap = agg_params(P, 16, 16, 25, 2, seed=100)
+    a = [torch.from_numpy(ap[kk]).cuda().contiguous() for kk in AGG_KEYS]
+    csr = (indices, ranges, dists, dens, inv_total)
+    w, e, f, out = _C.aggregate_neighbors(*a, *csr, False)
+    g = torch.randn(P, 16, device="cuda", generator=torch.Generator(device="cuda").manual_seed(9))
+    grads = _C.aggregate_neighbors_backward(*a, indices, ranges, dists, dens, w, e, f, inv_total, g, False)
+    # ---- the oracle on every row ----
+    host = [ap[kk] for kk in AGG_KEYS]
+    c_idx, c_rng, c_d, c_dn, c_inv = (t.cpu().numpy() for t in csr)
+    ow, oe, of_, oout = po.aggregate_forward(*host, c_idx, c_rng, c_d, c_dn, c_inv)
+    assert rel_err(out.cpu().numpy(), oout) <= TOL
+    assert rel_err(w.cpu().numpy(), ow) <= TOL and rel_err(e.cpu().numpy(), oe) <= TOL and rel_err(f.cpu().numpy(), of_) <= TOL
+    ograds = po.aggregate_backward(*host, c_idx, c_rng, c_d, c_dn, ow, oe, of_, c_inv, g.cpu().numpy())
+    for key, got, want in zip(AGG_KEYS, grads, ograds):
+        assert rel_err(got.cpu().numpy().reshape(want.shape), want) <= TOL, key
+    # ---- the operator is AFFINE in the features (embedded = dw e + dw f feature, aggregate_neighbors.cu:190-200): an
+    # affine combination (coefficients summing to 1) of feature sets maps to the same combination of outputs (no oracle) ----
+    f2 = torch.randn_like(a[0])
+    out2 = _C.aggregate_neighbors(f2, *a[1:], *csr, False)[3]
+    mix = _C.aggregate_neighbors(1.75 * a[0] - 0.75 * f2, *a[1:], *csr, False)[3]
+    lin = 1.75 * out - 0.75 * out2
+    assert float((mix - lin).abs().max()) <= 1e-5 * float(lin.abs().max())
