@@ -146,3 +146,46 @@ def test_dense_cuda_empty_operands():
     assert u.shape == (0, 1)
     u.sum().backward()
     assert m.grad is not None and not m.grad.any()
+
+
+@pytest.mark.gpu
+def test_dense_cuda_large_rows_and_adjoint():
+    """20K Gaussians x 400K points (8e9 pairs): the sizes where the 8-sample packed forward and the 2-Gaussian backward run
+    on grids cut into several whole waves of chunks (csrc/dense.cu dn_chunks).  Rows: u / grad u / Hessian of a sample
+    subset against the PyTorch formulation on the host (every row depends on its own sample only).  Whole problem, no
+    oracle: the operator is linear in the values, so <u(v), G> = <v, dL/dv(G)> ties the forward to the backward, and the
+    gradient w.r.t. the values of a sum over a sample subset equals the port's."""
+    import torch
+
+    from oracle import dense_torch as dt
+    from pigs_b200 import gaussians as pg
+    n, N, D = 20_000, 400_000, 2
+    g = torch.Generator().manual_seed(17)
+    means = torch.rand(n, D, generator=g) * 2 - 1
+    s = torch.exp(torch.randn(n, D, generator=g) * 0.3 - 5.0)
+    off = torch.tanh(torch.randn(n, generator=g) * 0.3) * torch.sqrt(s[:, 0] * s[:, 1])
+    con = torch.linalg.inv(torch.stack([s[:, 0], off, off, s[:, 1]], -1).reshape(n, 2, 2))
+    values = torch.rand(n, 1, generator=g) * 2 - 1
+    samples = torch.rand(N, D, generator=g) * 2 - 1
+    mc, kc, vc, sc = means.cuda(), con.cuda(), values.cuda().requires_grad_(True), samples.cuda()
+    u, ux, uxx = pg.dense_sample(7, mc, kc, vc, sc)
+    rows = torch.arange(0, N, 1571)
+    sub = samples[rows]
+    for got, want in ((u, dt.sample_gaussians(means, con, values, sub)), (ux, dt.gaussian_derivative(means, con, values, sub)),
+                      (uxx, dt.gaussian_derivative2(means, con, values, sub))):
+        assert rel_err(got.detach()[rows.cuda()].cpu().numpy(), want.numpy()) <= TOL
+    G = torch.randn(N, 1, device="cuda", generator=torch.Generator(device="cuda").manual_seed(3))
+    (dv,) = torch.autograd.grad((u * G).sum(), vc, retain_graph=True)
+    lhs = (u.detach().double() * G.double()).sum().item()
+    rhs = (vc.detach().double() * dv.double()).sum().item()
+    assert abs(lhs - rhs) <= 1e-5 * max(abs(lhs), abs(rhs), 1.0)
+    # gradients of a loss that touches the subset's rows only: equal to the port's over the subset
+    Gs = torch.zeros(N, D, 1, device="cuda")
+    Gs[rows.cuda()] = torch.randn(rows.numel(), D, 1, device="cuda", generator=torch.Generator(device="cuda").manual_seed(4))
+    mg, kg = mc.clone().requires_grad_(True), kc.clone().requires_grad_(True)
+    ux2 = pg.gaussian_derivative(mg, kg, vc.detach(), sc)
+    (ux2 * Gs).sum().backward()
+    mh, kh = means.clone().requires_grad_(True), con.clone().requires_grad_(True)
+    (dt.gaussian_derivative(mh, kh, values, sub) * Gs[rows.cuda()].cpu()).sum().backward()
+    assert rel_err(mg.grad.cpu().numpy(), mh.grad.numpy()) <= 2 * TOL
+    assert rel_err(kg.grad.cpu().numpy(), kh.grad.numpy()) <= 2 * TOL
